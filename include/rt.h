@@ -1,0 +1,198 @@
+/* rt.h — C ABI of the B200-native path tracer (librt_b200.so).
+ *
+ * This is the drop-in boundary for the render path of WhenMelancholy/ray-tracing-in-cuda
+ * (reference paths below are relative to the reference repository root):
+ *
+ *   rt_scene_upload_json  replaces  parse_scene()            gpu-version/parser.hpp:504-573
+ *                         and       move_to_device<<<1,1>>>  gpu-version/main.cu:374-446,473
+ *   rt_scene_upload       same, for callers that already hold the scene as flat tables
+ *                         (the `struct scene` seam, gpu-version/parser.hpp:16-32)
+ *   rt_render             replaces  init_random_library<<<>>> + render<<<>>>   gpu-version/main.cu:120-125,72-105,496,505
+ *   rt_download           replaces  the managed-memory read-back + write_color/write_image tonemap
+ *                                   gpu-version/main.cu:359-372, gpu-version/color.cuh:15-35,70-95
+ *   rt_write_ppm/_png     replace   output_image()/write_image()   gpu-version/main.cu:359-372, color.cuh:15-35
+ *
+ * Conventions: every function returns 0 on success and a non-zero RT_ERR_* code otherwise; the
+ * message is available from rt_last_error().  Nothing in the library calls exit() or throws across
+ * the boundary (the reference's check_cuda() does exit(99): gpu-version/rtweekend.cuh:43-53 — the
+ * CLI, not the library, keeps that exit code).  Plain pointers and sizes only; the library copies
+ * what it needs, the caller keeps ownership of every host buffer.  One rt_ctx may be driven from one
+ * host thread at a time; different contexts are independent.
+ *
+ * Image convention (same as the reference): float RGB SUMS over samples, 12 bytes per pixel,
+ * row 0 = BOTTOM row (gpu-version/main.cu:104; the writers flip rows).
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+/* error codes */
+enum { RT_OK = 0, RT_ERR_INVALID = 1, RT_ERR_CUDA = 2, RT_ERR_IO = 3, RT_ERR_PARSE = 4, RT_ERR_NO_SCENE = 5, RT_ERR_NO_DEVICE = 6 };
+
+/* scene vocabulary: gpu-version/rtweekend.cuh:70-91 (enum class class_type) + the extensions BASELINE.json names */
+enum { RT_OBJ_SPHERE = 0, RT_OBJ_XY_RECT = 1, RT_OBJ_XZ_RECT = 2, RT_OBJ_YZ_RECT = 3, RT_OBJ_CYLINDER = 4,
+       RT_OBJ_BOX = 5, RT_OBJ_TRIANGLE = 6 };
+enum { RT_MAT_LAMBERTIAN = 0, RT_MAT_METAL = 1, RT_MAT_DIELECTRIC = 2, RT_MAT_DIFFUSE_LIGHT = 3 };
+enum { RT_TEX_SOLID = 0, RT_TEX_CHECKER = 1, RT_TEX_IMAGE = 2 };
+/* miss colour: constant `background` (gpu-version/main.cu:61-63) or the RTIOW sky gradient (cmake-cpu-version/main.cpp:36-38) */
+enum { RT_BG_CONSTANT = 0, RT_BG_SKY_GRADIENT = 1 };
+/* which of the reference's two (disagreeing) sampling conventions to reproduce — SURVEY.md §7.2-1:
+ *  REFERENCE_GPU: uniforms in (0,1]; random_in_unit_sphere over the positive octant only (gpu-version/vec3.cuh:133-141);
+ *                 lambertian = n + random_in_unit_sphere (material.cuh:42); no lens jitter (camera.cuh:33-34)
+ *  REFERENCE_CPU: uniforms in [0,1); ball sampled over [-1,1)^3 (cmake-cpu-version/vec3.h:121-129);
+ *                 lambertian = n + random_unit_vector (material.h:27); thin-lens defocus (camera.h:32-39) */
+enum { RT_SAMPLING_REFERENCE_GPU = 0, RT_SAMPLING_REFERENCE_CPU = 1 };
+
+typedef struct rt_object_desc {
+    int32_t type;       /* RT_OBJ_* */
+    int32_t material;   /* index into materials */
+    int32_t xform;      /* index into xforms (object-to-world) or -1; honoured for CYLINDER and BOX */
+    int32_t reserved;
+    /* SPHERE:   cx cy cz radius              (object.cuh:40-94; radius may be negative)
+     * ??_RECT:  a0 a1 b0 b1 k                (object.cuh:96-197; xy: x0 x1 y0 y1 | xz: x0 x1 z0 z1 | yz: y0 y1 z0 z1)
+     * CYLINDER: radius zmin zmax             (object.cuh:216-297; axis = object-space z, no caps)
+     * BOX:      minx miny minz maxx maxy maxz (extension; object-space if xform >= 0)
+     * TRIANGLE: v0 v1 v2 (9 floats, world space; extension) */
+    float p[12];
+} rt_object_desc;
+
+/* 3x4 row-major object-to-world matrix and its inverse (gpu-version/vec3.cuh:303-379 keeps both) */
+typedef struct rt_xform_desc { float m[12]; float m_inv[12]; } rt_xform_desc;
+
+typedef struct rt_material_desc {
+    int32_t type;       /* RT_MAT_* */
+    int32_t texture;    /* LAMBERTIAN albedo / DIFFUSE_LIGHT emit: index into textures (material.cuh:31-35,163-167) */
+    float albedo[3];    /* METAL (material.cuh:57-61) */
+    float fuzz;         /* METAL; clamped to <= 1 on upload (material.cuh:61) */
+    float ior;          /* DIELECTRIC index_of_refraction (material.cuh:89-92) */
+    int32_t reserved;
+} rt_material_desc;
+
+typedef struct rt_texture_desc {
+    int32_t type;       /* RT_TEX_* */
+    int32_t even, odd;  /* CHECKER: texture indices (texture.cuh:33-57) */
+    int32_t image;      /* IMAGE: index into images */
+    float color[3];     /* SOLID (texture.cuh:14-31); values > 1 allowed (emitters) */
+    float reserved;
+} rt_texture_desc;
+
+typedef struct rt_image_desc { int32_t width, height; const uint8_t *rgb8; /* width*height*3, row 0 = top */ } rt_image_desc;
+
+typedef struct rt_camera_desc {      /* gpu-version/camera.cuh:9-29, parser.hpp:113-126 */
+    float lookfrom[3], lookat[3], vup[3];
+    float vfov_deg;
+    float aspect;       /* reference: width/height (parser.hpp:122); cmake-cpu-version pins 16/9 (main.cpp:64,94) */
+    float aperture;
+    float focus_dist;   /* reference: |lookfrom - lookat| (parser.hpp:124) */
+} rt_camera_desc;
+
+typedef struct rt_scene_desc {
+    int32_t width, height, max_depth, samples_per_pixel;   /* parser.hpp:512-517 */
+    float background[3];
+    int32_t background_mode;   /* RT_BG_* */
+    int32_t sampling;          /* RT_SAMPLING_* */
+    rt_camera_desc camera;
+    int32_t n_objects, n_xforms, n_materials, n_textures, n_images;
+    int32_t reserved;
+    const rt_object_desc *objects;
+    const rt_xform_desc *xforms;
+    const rt_material_desc *materials;
+    const rt_texture_desc *textures;
+    const rt_image_desc *images;
+} rt_scene_desc;
+
+/* rt_render flags */
+enum { RT_RENDER_KEEP_ACCUM = 1,     /* add to the accumulation buffer instead of clearing it first */
+       RT_RENDER_COUNT_EVENTS = 2,   /* fill the event counters of rt_stats (slower; counts are deterministic) */
+       RT_RENDER_NO_SORT = 4,        /* do not bin rays by material before shading (ablation switch) */
+       RT_RENDER_NEE = 8 };          /* next-event estimation through the shadow stage (changes the estimator; default off) */
+
+typedef struct rt_render_params {
+    uint32_t seed;          /* Philox key word 0 */
+    int32_t spp_begin;      /* absolute index of the first sample rendered by this call */
+    int32_t spp_count;      /* number of samples; <= 0 means the scene's samples_per_pixel */
+    int32_t flags;          /* RT_RENDER_* */
+    int64_t max_paths_per_pass;   /* wavefront size cap; <= 0 picks a default from free device memory */
+} rt_render_params;
+
+typedef struct rt_stats {
+    int64_t samples;            /* camera paths started */
+    int64_t rays;               /* path segments traced (extend-queue entries) */
+    int64_t shadow_rays;
+    int64_t launches;           /* kernels launched by the library since rt_create/rt_stats_reset */
+    int64_t passes;
+    float ms_total;             /* device time of the last rt_render, CUDA events on the ctx stream */
+    float ms_generate, ms_extend, ms_shade, ms_shadow, ms_accumulate, ms_build;   /* per-stage device time (only with COUNT_EVENTS) */
+    /* event counters for the algorithmic-flop model of SURVEY.md §8(d) (only with COUNT_EVENTS) */
+    int64_t n_box_tests, n_sphere_reject, n_sphere_accept, n_rect_tests, n_cyl_reject, n_cyl_accept,
+            n_tri_tests, n_boxprim_tests, n_shade, n_generate, n_node_visits;
+} rt_stats;
+
+typedef struct rt_scene_info {
+    int32_t width, height, max_depth, samples_per_pixel;
+    int32_t n_objects, n_materials, n_textures, n_bvh_nodes;
+    char output_file[512];      /* JSON "output_file", default "main.png" (parser.hpp:567-568) */
+} rt_scene_info;
+
+typedef struct rt_ctx rt_ctx;   /* opaque: owns the device buffers, the BVH, the queues and (unless given one) a stream */
+
+/* device: CUDA ordinal.  stream: a cudaStream_t to enqueue on (e.g. the caller's torch stream), or NULL for a private one. */
+int rt_create(rt_ctx **out, int device, void *stream);
+void rt_destroy(rt_ctx *ctx);
+/* message for the last failing call on ctx (ctx == NULL: last failing rt_create on this thread) */
+const char *rt_last_error(const rt_ctx *ctx);
+int rt_abi_version(void);
+
+/* Copies the tables to the device, flattens them to SoA and builds the LBVH there. */
+int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *scene);
+/* Same JSON schema as gpu-version/parser.hpp (+ optional extension keys). */
+int rt_scene_upload_json(rt_ctx *ctx, const char *path);
+/* As above from an in-memory JSON text; base_dir resolves relative texture/mesh paths (may be NULL). */
+int rt_scene_upload_json_text(rt_ctx *ctx, const char *json_text, const char *base_dir);
+int rt_scene_info_get(rt_ctx *ctx, rt_scene_info *out);
+/* Overrides applied to the uploaded scene before rendering (<= 0 leaves a field unchanged). */
+int rt_scene_override(rt_ctx *ctx, int width, int height, int samples_per_pixel, int max_depth);
+
+/* Asynchronous: enqueues the wavefront passes for samples [spp_begin, spp_begin+spp_count) on the ctx stream. */
+int rt_render(rt_ctx *ctx, const rt_render_params *params);
+/* Deterministic first-hit pass (1 sample, pixel-centre rays, no lens offset, no scattering): 24 floats per pixel,
+ * layout documented in DESIGN.md §6 — the "deterministic path" of the parity contract.  Synchronises. */
+int rt_render_aov(rt_ctx *ctx, float *aov_out, size_t n_floats);
+
+/* Device address of the accumulation buffer (width*height*3 float sums) so that a multi-GPU caller can
+ * reduce it in place (NCCL over NVLink) before rt_download on the root rank. */
+int rt_accum_device_ptr(rt_ctx *ctx, void **dev_ptr, size_t *n_floats);
+/* Fixed-order sum of n_partials accumulation buffers (device pointers, e.g. gathered from the ranks) into this
+ * ctx's accumulation buffer: acc = ((p0 + p1) + p2) + ...  — bit-reproducible for any GPU count. */
+int rt_accum_sum_ordered(rt_ctx *ctx, const void *const *partials, int n_partials);
+
+/* Synchronises.  rgb_sum (may be NULL): width*height*3 float sums, row 0 = bottom.  rgb8 (may be NULL):
+ * width*height*3 bytes, tonemapped on the device by total_spp, rows flipped (row 0 = top), gamma != 0 applies the
+ * PPM writer's sqrt (color.cuh:58-62), gamma == 0 is the PNG writer (color.cuh:15-35).  stats may be NULL. */
+int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigned char *rgb8, int total_spp, int gamma, rt_stats *stats);
+int rt_synchronize(rt_ctx *ctx);
+int rt_stats_reset(rt_ctx *ctx);
+
+/* LBVH introspection for the bit-exact build tests.  n_prims leaves, n_prims-1 internal nodes (0 if n_prims < 2).
+ * Any output pointer may be NULL.  child encoding: >= 0 internal node index, < 0 leaf ~index into the sorted order. */
+int rt_bvh_download(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left,
+                    int32_t *right, int32_t *parent, float *node_aabb /* 6 per internal node */,
+                    float *leaf_aabb /* 6 per sorted leaf */, float *scene_aabb /* 6 */);
+
+/* Host image writers (row 0 of rgb8 = top).  PPM is the reference's P3 text format (color.cuh:70-95). */
+int rt_write_ppm(const char *path, const unsigned char *rgb8, int width, int height);
+int rt_write_png(const char *path, const unsigned char *rgb8, int width, int height);
+/* PNG reader for image textures (8-bit RGB/RGBA/grey, non-interlaced); caller frees *rgb8 with rt_free. */
+int rt_read_png(const char *path, unsigned char **rgb8, int *width, int *height);
+void rt_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

@@ -1,0 +1,227 @@
+/* orc_render.c — textures, materials, path loop, AOV pass, tonemap of the CPU oracle.
+ * TEST INFRASTRUCTURE ONLY (see rt_oracle.h). */
+#include "orc_internal.h"
+#include <float.h>
+#include <pthread.h>
+
+/* ---------------- textures (texture.cuh:24-52; image: taichi-version/material.py:137-144 semantics, nearest) ---------------- */
+v3 orc_texture_value(const rt_scene_desc *sc, int tex, float u, float v, v3 p) {
+    for (int guard = 0; guard < 8; ++guard) {
+        const rt_texture_desc *t = &sc->textures[tex];
+        if (t->type == RT_TEX_SOLID) return V(t->color[0], t->color[1], t->color[2]);
+        if (t->type == RT_TEX_CHECKER) {
+            float sines = orc_sinf(10.0f * p.x) * orc_sinf(10.0f * p.y) * orc_sinf(10.0f * p.z);
+            tex = sines < 0.0f ? t->odd : t->even;
+            continue;
+        }
+        if (t->type == RT_TEX_IMAGE) {
+            const rt_image_desc *im = &sc->images[t->image];
+            /* clamp u,v to [0,1], flip v (row 0 = top), nearest texel */
+            float uu = u < 0.0f ? 0.0f : (u > 1.0f ? 1.0f : u);
+            float vv = 1.0f - (v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v));
+            int i = (int)(uu * (float)im->width), j = (int)(vv * (float)im->height);
+            if (i >= im->width) i = im->width - 1;
+            if (j >= im->height) j = im->height - 1;
+            const uint8_t *px = im->rgb8 + 3 * ((size_t)j * im->width + i);
+            return V((float)px[0] / 255.0f, (float)px[1] / 255.0f, (float)px[2] / 255.0f);
+        }
+        break;
+    }
+    return V(0, 0, 0);
+}
+
+v3 orc_emitted(const rt_scene_desc *sc, int mat, float u, float v, v3 p) {   /* material.cuh:23-25,175-178 */
+    const rt_material_desc *m = &sc->materials[mat];
+    if (m->type == RT_MAT_DIFFUSE_LIGHT) return orc_texture_value(sc, m->texture, u, v, p);
+    return V(0, 0, 0);
+}
+
+/* random_in_unit_sphere: vec3.cuh:133-141 (positive octant, GPU semantics) | vec3.h:121-129 (full cube, CPU semantics) */
+static v3 random_in_unit_sphere(orc_rng *rng) {
+    for (;;) {
+        float a = orc_rng_next(rng), b = orc_rng_next(rng), c = orc_rng_next(rng);
+        v3 p = rng->sampling == RT_SAMPLING_REFERENCE_GPU ? V(a, b, c)
+                                                          : V(fmaf(2.0f, a, -1.0f), fmaf(2.0f, b, -1.0f), fmaf(2.0f, c, -1.0f));
+        if (dot3(p, p) >= 1.0f) continue;
+        return p;
+    }
+}
+
+static v3 reflect(v3 v, v3 n) {   /* vec3.cuh:121-123 */
+    float k = 2.0f * dot3(v, n);
+    return V(fmaf(-k, n.x, v.x), fmaf(-k, n.y, v.y), fmaf(-k, n.z, v.z));
+}
+
+int orc_scatter(const rt_scene_desc *sc, int mat, v3 rd, const orc_hit *rec, orc_rng *rng, v3 *att, v3 *so, v3 *sd) {
+    const rt_material_desc *m = &sc->materials[mat];
+    *so = rec->p;
+    switch (m->type) {
+    case RT_MAT_LAMBERTIAN: {   /* material.cuh:37-52 (GPU) | material.h:25-35 (CPU) */
+        v3 r = random_in_unit_sphere(rng);
+        if (rng->sampling == RT_SAMPLING_REFERENCE_CPU) r = vunit(r);     /* random_unit_vector, vec3.h:131-134 */
+        v3 dir = vadd(rec->n, r);
+        if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = rec->n;   /* near_zero, vec3.cuh:66-68 */
+        *sd = dir;
+        *att = orc_texture_value(sc, m->texture, rec->u, rec->v, rec->p);
+        return 1;
+    }
+    case RT_MAT_METAL: {        /* material.cuh:63-70 */
+        v3 refl = reflect(vunit(rd), rec->n);
+        float fuzz = m->fuzz < 1.0f ? m->fuzz : 1.0f;
+        v3 r = random_in_unit_sphere(rng);
+        *sd = vfma(fuzz, r, refl);
+        *att = V(m->albedo[0], m->albedo[1], m->albedo[2]);
+        return dot3(*sd, rec->n) > 0.0f;
+    }
+    case RT_MAT_DIELECTRIC: {   /* material.cuh:130-147,152-158; refract: vec3.cuh:125-131 */
+        *att = V(1.0f, 1.0f, 1.0f);
+        float ratio = rec->front ? (1.0f / m->ior) : m->ior;
+        v3 ud = vunit(rd);
+        float cos_theta = fminf(-dot3(ud, rec->n), 1.0f);
+        float sin_theta = sqrtf(fmaf(-cos_theta, cos_theta, 1.0f));
+        int cannot_refract = ratio * sin_theta > 1.0f;
+        int do_reflect = cannot_refract;
+        if (!do_reflect) {
+            float r0 = (1.0f - ratio) / (1.0f + ratio);
+            r0 = r0 * r0;
+            float x = 1.0f - cos_theta, x2 = x * x;
+            float refl = fmaf(1.0f - r0, x2 * x2 * x, r0);    /* pow(1-cos,5) as exact products */
+            do_reflect = refl > orc_rng_next(rng);
+        }
+        if (do_reflect) *sd = reflect(ud, rec->n);
+        else {
+            v3 perp = vscale(ratio, vfma(cos_theta, rec->n, ud));
+            float k = -sqrtf(fabsf(1.0f - dot3(perp, perp)));
+            *sd = vfma(k, rec->n, perp);
+        }
+        return 1;
+    }
+    default:                    /* diffuse_light, material.cuh:169-173 */
+        *att = V(0, 0, 0); *sd = V(0, 0, 0);
+        return 0;
+    }
+}
+
+v3 orc_background(const rt_scene_desc *sc, v3 d) {
+    if (sc->background_mode == RT_BG_SKY_GRADIENT) {   /* main.cpp:36-38 */
+        v3 ud = vunit(d);
+        float t = 0.5f * (ud.y + 1.0f), w = 1.0f - t;
+        return V(fmaf(t, 0.5f, w), fmaf(t, 0.7f, w), fmaf(t, 1.0f, w));
+    }
+    return V(sc->background[0], sc->background[1], sc->background[2]);   /* main.cu:61-63 */
+}
+
+/* ray_color, main.cu:17-70 / main.cpp:13-43.  Emission is non-zero only on diffuse_light, which never
+ * scatters, so the radiance of a path is throughput * (E | background | 0) at its last vertex. */
+static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t pixel, uint32_t sample, int64_t *nrays) {
+    v3 thr = V(1, 1, 1), L = V(0, 0, 0);
+    for (int bounce = 0; bounce < sc->max_depth; ++bounce) {
+        orc_hit rec;
+        ++*nrays;
+        if (!orc_hit_world(sc, o, d, 0.001f, FLT_MAX, &rec)) { L = vadd(L, vmul(thr, orc_background(sc, d))); break; }
+        v3 E = orc_emitted(sc, rec.mat, rec.u, rec.v, rec.p);
+        orc_rng rng; orc_rng_init(&rng, seed, pixel, sample, (uint32_t)bounce + 1u, sc->sampling);
+        v3 att, so, sd;
+        int ok = orc_scatter(sc, rec.mat, d, &rec, &rng, &att, &so, &sd);
+        L = vadd(L, vmul(thr, E));
+        if (!ok) break;
+        thr = vmul(thr, att);
+        o = so; d = sd;
+    }
+    return L;
+}
+
+typedef struct {
+    const rt_scene_desc *sc; orc_camera cam; uint32_t seed; int s0, sn; float *out;
+    int row_next; pthread_mutex_t mu; int64_t rays;
+} job_t;
+
+static void *worker(void *arg) {
+    job_t *j = (job_t *)arg;
+    const rt_scene_desc *sc = j->sc;
+    const int W = sc->width, H = sc->height;
+    int64_t rays = 0;
+    for (;;) {
+        pthread_mutex_lock(&j->mu);
+        int y = j->row_next++;
+        pthread_mutex_unlock(&j->mu);
+        if (y >= H) break;
+        for (int x = 0; x < W; ++x) {
+            uint32_t pixel = (uint32_t)(y * W + x);
+            v3 sum = V(0, 0, 0);
+            for (int s = j->s0; s < j->s0 + j->sn; ++s) {          /* main.cu:95-103 */
+                orc_rng rng; orc_rng_init(&rng, j->seed, pixel, (uint32_t)s, 0u, sc->sampling);
+                float u = ((float)x + orc_rng_next(&rng)) / (float)(W - 1);
+                float v = ((float)y + orc_rng_next(&rng)) / (float)(H - 1);
+                v3 o, d;
+                int defocus = sc->sampling == RT_SAMPLING_REFERENCE_CPU && sc->camera.aperture > 0.0f;
+                orc_get_ray(&j->cam, u, v, defocus, &rng, &o, &d);
+                v3 c = ray_color(sc, o, d, j->seed, pixel, (uint32_t)s, &rays);
+                sum = vadd(sum, c);                                   /* fixed order: ascending sample index */
+            }
+            float *q = j->out + 3 * (size_t)pixel;
+            q[0] = sum.x; q[1] = sum.y; q[2] = sum.z;
+        }
+    }
+    pthread_mutex_lock(&j->mu); j->rays += rays; pthread_mutex_unlock(&j->mu);
+    return NULL;
+}
+
+int orc_render(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
+               int64_t *n_rays) {
+    if (!sc || !rgb_sum || sc->width < 1 || sc->height < 1) return RT_ERR_INVALID;
+    job_t j; memset(&j, 0, sizeof j);
+    j.sc = sc; j.seed = seed; j.s0 = spp_begin; j.sn = spp_count > 0 ? spp_count : sc->samples_per_pixel; j.out = rgb_sum;
+    orc_camera_setup(&sc->camera, &j.cam);
+    pthread_mutex_init(&j.mu, NULL);
+    if (n_threads < 1) n_threads = 1;
+    if (n_threads > 256) n_threads = 256;
+    pthread_t th[256];
+    for (int i = 0; i < n_threads; ++i) pthread_create(&th[i], NULL, worker, &j);
+    for (int i = 0; i < n_threads; ++i) pthread_join(th[i], NULL);
+    pthread_mutex_destroy(&j.mu);
+    if (n_rays) *n_rays = j.rays;
+    return 0;
+}
+
+/* first-hit record per pixel: the "deterministic path" (pixel-centre ray, no lens offset, no scattering) */
+int orc_aov(const rt_scene_desc *sc, float *aov) {
+    orc_camera cam; orc_camera_setup(&sc->camera, &cam);
+    const int W = sc->width, H = sc->height;
+    static const float fixed_u[8] = {0.5f, 0.5f, 0.5f, 0.25f, 0.25f, 0.25f, 0.1f, 0.1f};
+    for (int y = 0; y < H; ++y) for (int x = 0; x < W; ++x) {
+        float *q = aov + 24 * ((size_t)y * W + x);
+        memset(q, 0, 24 * sizeof(float));
+        float u = ((float)x + 0.5f) / (float)(W - 1), v = ((float)y + 0.5f) / (float)(H - 1);
+        v3 o, d; orc_get_ray(&cam, u, v, 0, NULL, &o, &d);
+        orc_hit rec;
+        if (orc_hit_world(sc, o, d, 0.001f, FLT_MAX, &rec)) {
+            q[0] = 1.0f; q[1] = rec.t; q[2] = rec.p.x; q[3] = rec.p.y; q[4] = rec.p.z;
+            q[5] = rec.n.x; q[6] = rec.n.y; q[7] = rec.n.z; q[8] = (float)rec.front; q[9] = rec.u; q[10] = rec.v;
+            q[11] = (float)rec.prim; q[12] = (float)rec.mat;
+            orc_rng rng; memset(&rng, 0, sizeof rng); rng.replay = fixed_u; rng.replay_n = 8; rng.sampling = sc->sampling;
+            v3 att, so, sd;
+            int ok = orc_scatter(sc, rec.mat, d, &rec, &rng, &att, &so, &sd);
+            q[13] = att.x; q[14] = att.y; q[15] = att.z;
+            v3 E = orc_emitted(sc, rec.mat, rec.u, rec.v, rec.p);
+            q[16] = E.x; q[17] = E.y; q[18] = E.z; q[22] = (float)ok;
+        } else {
+            v3 b = orc_background(sc, d);
+            q[19] = b.x; q[20] = b.y; q[21] = b.z;
+        }
+    }
+    return 0;
+}
+
+/* write_image (PNG, no gamma) color.cuh:15-35 ; write_color (PPM, sqrt gamma) color.cuh:70-95 */
+void orc_tonemap(const float *rgb_sum, int W, int H, int spp, int gamma, unsigned char *rgb8) {
+    float scale = 1.0f / (float)spp;   /* PPM path multiplies by 1/spp (color.cuh:82-85); PNG path divides (color.cuh:24) */
+    for (int j = H - 1, row = 0; j >= 0; --j, ++row)
+        for (int i = 0; i < W; ++i)
+            for (int c = 0; c < 3; ++c) {
+                float x = rgb_sum[3 * ((size_t)j * W + i) + c];
+                x = gamma ? sqrtf(x * scale) : x / (float)spp;
+                x = x < 0.0f ? 0.0f : (x > 0.999f ? 0.999f : x);   /* clamp(x,0,0.999); NaN falls through as in the reference */
+                rgb8[3 * ((size_t)row * W + i) + c] = (unsigned char)(int)(256.0f * x);
+            }
+}

@@ -1,0 +1,176 @@
+"""Host-side mirror of the reference's render-path interface, on top of the C ABI (include/rt.h).
+
+Reference seams (gpu-version/): `parse_scene(filename)` parser.hpp:504, the `render<<<>>>` launch
+main.cu:505, `output_image` / `write_image` main.cu:359-372 + color.cuh:15-35, and the whole of
+`jsonmain` main.cu:448-522 (= `render_scene_file`).  All pixels come from librt_b200.so; there is no
+CPU fallback here — a missing library or device raises RtError.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import capi
+
+
+class RtError(RuntimeError):
+    pass
+
+
+class Renderer:
+    """One rt_ctx = one GPU.  `stream` may be a raw cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
+
+    def __init__(self, device=0, stream=None, lib_path=None):
+        self.lib = capi.load_library(lib_path)
+        self.ctx = C.c_void_p()
+        rc = self.lib.rt_create(C.byref(self.ctx), int(device), C.c_void_p(stream) if stream else None)
+        if rc != 0:
+            msg = self.lib.rt_last_error(None)
+            raise RtError(f"rt_create failed ({rc}): {msg.decode() if msg else ''}")
+        self.device = device
+
+    def _check(self, rc, what):
+        if rc != 0:
+            msg = self.lib.rt_last_error(self.ctx)
+            raise RtError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.rt_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- scene in (parse_scene + move_to_device) ----
+    def upload_json(self, path):
+        self._check(self.lib.rt_scene_upload_json(self.ctx, os.fsencode(path)), "rt_scene_upload_json")
+        return self.info()
+
+    def upload_json_text(self, text, base_dir=None):
+        self._check(self.lib.rt_scene_upload_json_text(self.ctx, text.encode(), os.fsencode(base_dir) if base_dir else None),
+                    "rt_scene_upload_json_text")
+        return self.info()
+
+    def upload(self, scene_desc):
+        """scene_desc: capi.SceneDesc (or an object with a `.desc` attribute holding one)."""
+        d = getattr(scene_desc, "desc", scene_desc)
+        self._check(self.lib.rt_scene_upload(self.ctx, C.byref(d)), "rt_scene_upload")
+        return self.info()
+
+    def override(self, width=0, height=0, spp=0, max_depth=0):
+        self._check(self.lib.rt_scene_override(self.ctx, width or 0, height or 0, spp or 0, max_depth or 0), "rt_scene_override")
+        return self.info()
+
+    def info(self):
+        i = capi.SceneInfo()
+        self._check(self.lib.rt_scene_info_get(self.ctx, C.byref(i)), "rt_scene_info_get")
+        return i
+
+    # ---- render ----
+    def render(self, seed=0x2023, spp_begin=0, spp_count=0, flags=0, max_paths_per_pass=0):
+        p = capi.RenderParams(seed, spp_begin, spp_count, flags, max_paths_per_pass)
+        self._check(self.lib.rt_render(self.ctx, C.byref(p)), "rt_render")
+
+    def render_aov(self):
+        i = self.info()
+        out = np.zeros((i.height, i.width, 24), np.float32)
+        self._check(self.lib.rt_render_aov(self.ctx, out.ctypes.data_as(C.POINTER(C.c_float)), out.size), "rt_render_aov")
+        return out
+
+    def synchronize(self):
+        self._check(self.lib.rt_synchronize(self.ctx), "rt_synchronize")
+
+    def accum_device_ptr(self):
+        p = C.c_void_p(); n = C.c_size_t()
+        self._check(self.lib.rt_accum_device_ptr(self.ctx, C.byref(p), C.byref(n)), "rt_accum_device_ptr")
+        return p.value, n.value
+
+    def accum_sum_ordered(self, device_ptrs):
+        arr = (C.c_void_p * len(device_ptrs))(*device_ptrs)
+        self._check(self.lib.rt_accum_sum_ordered(self.ctx, arr, len(device_ptrs)), "rt_accum_sum_ordered")
+
+    # ---- image out ----
+    def download(self, total_spp=0, gamma=0, want_sum=True, want_rgb8=True):
+        """Returns (rgb_sum[H,W,3] float32 with row 0 = bottom, rgb8[H,W,3] uint8 with row 0 = top, stats dict)."""
+        i = self.info()
+        rgb_sum = np.zeros((i.height, i.width, 3), np.float32) if want_sum else None
+        rgb8 = np.zeros((i.height, i.width, 3), np.uint8) if want_rgb8 else None
+        st = capi.Stats()
+        self._check(self.lib.rt_download(
+            self.ctx, rgb_sum.ctypes.data_as(C.POINTER(C.c_float)) if want_sum else None, rgb_sum.size if want_sum else 0,
+            rgb8.ctypes.data_as(C.POINTER(C.c_ubyte)) if want_rgb8 else None, int(total_spp or i.samples_per_pixel),
+            int(gamma), C.byref(st)), "rt_download")
+        return rgb_sum, rgb8, st.as_dict()
+
+    def stats_reset(self):
+        self._check(self.lib.rt_stats_reset(self.ctx), "rt_stats_reset")
+
+    def bvh(self):
+        n = C.c_int32()
+        self._check(self.lib.rt_bvh_download(self.ctx, C.byref(n), None, None, None, None, None, None, None, None), "rt_bvh_download")
+        n = n.value
+        m = max(n - 1, 1)
+        r = dict(morton=np.zeros(max(n, 1), np.uint64), prim=np.zeros(max(n, 1), np.int32), left=np.zeros(m, np.int32),
+                 right=np.zeros(m, np.int32), parent=np.zeros(max(2 * n - 1, 1), np.int32),
+                 node_aabb=np.zeros((m, 6), np.float32), leaf_aabb=np.zeros((max(n, 1), 6), np.float32),
+                 scene_aabb=np.zeros(6, np.float32))
+        P = C.POINTER
+        nn = C.c_int32()
+        self._check(self.lib.rt_bvh_download(
+            self.ctx, C.byref(nn), r["morton"].ctypes.data_as(P(C.c_uint64)), r["prim"].ctypes.data_as(P(C.c_int32)),
+            r["left"].ctypes.data_as(P(C.c_int32)), r["right"].ctypes.data_as(P(C.c_int32)),
+            r["parent"].ctypes.data_as(P(C.c_int32)), r["node_aabb"].ctypes.data_as(P(C.c_float)),
+            r["leaf_aabb"].ctypes.data_as(P(C.c_float)), r["scene_aabb"].ctypes.data_as(P(C.c_float))), "rt_bvh_download")
+        r["n"] = n
+        return r
+
+
+def write_ppm(path, rgb8):
+    lib = capi.load_library()
+    a = np.ascontiguousarray(rgb8, np.uint8)
+    if lib.rt_write_ppm(os.fsencode(path), a.ctypes.data_as(C.POINTER(C.c_ubyte)), a.shape[1], a.shape[0]) != 0:
+        raise RtError(f"cannot write {path}")
+
+
+def write_png(path, rgb8):
+    lib = capi.load_library()
+    a = np.ascontiguousarray(rgb8, np.uint8)
+    if lib.rt_write_png(os.fsencode(path), a.ctypes.data_as(C.POINTER(C.c_ubyte)), a.shape[1], a.shape[0]) != 0:
+        raise RtError(f"cannot write {path}")
+
+
+def read_png(path):
+    lib = capi.load_library()
+    p = C.POINTER(C.c_ubyte)(); w = C.c_int(); h = C.c_int()
+    if lib.rt_read_png(os.fsencode(path), C.byref(p), C.byref(w), C.byref(h)) != 0:
+        raise RtError(f"cannot read {path}")
+    a = np.ctypeslib.as_array(p, shape=(h.value, w.value, 3)).copy()
+    lib.rt_free(p)
+    return a
+
+
+def parse_scene(filename, device=0, stream=None):
+    """parse_scene(filename) of gpu-version/parser.hpp:504 — returns a Renderer holding the uploaded scene."""
+    r = Renderer(device, stream)
+    r.upload_json(filename)
+    return r
+
+
+def render_scene_file(filename, device=0, seed=0x2023, write_outputs=True, out_dir=None):
+    """jsonmain() of gpu-version/main.cu:448-522: parse, render, write main.ppm (gamma) + output_file PNG (no gamma)."""
+    r = parse_scene(filename, device)
+    info = r.info()
+    r.render(seed=seed)
+    rgb_sum, png8, stats = r.download(gamma=0)
+    if write_outputs:
+        _, ppm8, _ = r.download(gamma=1, want_sum=False)
+        base = out_dir or os.getcwd()
+        write_ppm(os.path.join(base, "main.ppm"), ppm8)
+        out = info.output_file.decode() or "main.png"
+        write_png(out if os.path.isabs(out) else os.path.join(base, out), png8)
+    r.close()
+    return rgb_sum, png8, stats

@@ -1,0 +1,230 @@
+"""Test-side binding of the CPU oracle (oracle/liboracle.so) and an independent JSON -> flat-table loader.
+
+TEST INFRASTRUCTURE.  The product has its own C++ JSON reader (rt_scene_upload_json); this Python
+loader follows gpu-version/parser.hpp:504-573 independently so that tests can (a) feed the oracle and
+(b) cross-check the C++ reader by uploading the same tables through rt_scene_upload.
+"""
+import ctypes as C
+import json
+import math
+import os
+import subprocess
+
+import numpy as np
+
+from rt_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(ORACLE_DIR, "liboracle.so")
+        if not os.path.exists(path):
+            subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle.so"])
+        L = C.CDLL(path)
+        P = C.POINTER
+        fp = P(C.c_float)
+        L.orc_render.argtypes = [P(capi.SceneDesc), C.c_uint32, C.c_int, C.c_int, fp, C.c_int, P(C.c_int64)]
+        L.orc_aov.argtypes = [P(capi.SceneDesc), fp]
+        L.orc_tonemap.argtypes = [fp, C.c_int, C.c_int, C.c_int, C.c_int, P(C.c_ubyte)]
+        L.orc_tonemap.restype = None
+        L.orc_make_xform.argtypes = [fp, C.c_float, C.c_int, fp, C.c_int, P(capi.XformDesc)]
+        L.orc_make_xform.restype = None
+        L.orc_philox4x32_10.argtypes = [P(C.c_uint32), P(C.c_uint32), P(C.c_uint32)]
+        L.orc_philox4x32_10.restype = None
+        L.orc_uniforms.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, fp]
+        L.orc_uniforms.restype = None
+        for k in ("sphere", "rect", "cyl", "camera", "xform"):
+            f = getattr(L, "orc_kat_" + k); f.argtypes = [fp, fp, C.c_int]; f.restype = None
+        L.orc_kat_scatter.argtypes = [fp, fp, C.c_int, C.c_int]; L.orc_kat_scatter.restype = None
+        for k in ("orc_sinf", "orc_acosf"):
+            f = getattr(L, k); f.argtypes = [C.c_float]; f.restype = C.c_float
+        L.orc_atan2f.argtypes = [C.c_float, C.c_float]; L.orc_atan2f.restype = C.c_float
+        L.orc_lbvh_build.argtypes = [P(capi.SceneDesc), P(C.c_uint64), P(C.c_int32), P(C.c_int32), P(C.c_int32),
+                                     P(C.c_int32), fp, fp, fp]
+        L.orc_radix_sort_pairs.argtypes = [P(C.c_uint64), P(C.c_int32), C.c_int]
+        L.orc_radix_sort_pairs.restype = None
+        _lib = L
+    return _lib
+
+
+def fptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+class Scene:
+    """Owns the ctypes arrays behind a capi.SceneDesc."""
+
+    def __init__(self):
+        self.desc = capi.SceneDesc()
+        self.keep = []
+        self.output_file = "main.png"
+
+    @property
+    def ptr(self):
+        return C.byref(self.desc)
+
+
+_OBJ = {"sphere": capi.RT_OBJ_SPHERE, "xy_rect": capi.RT_OBJ_XY_RECT, "xz_rect": capi.RT_OBJ_XZ_RECT,
+        "yz_rect": capi.RT_OBJ_YZ_RECT, "cylinder": capi.RT_OBJ_CYLINDER, "box": capi.RT_OBJ_BOX,
+        "triangle": capi.RT_OBJ_TRIANGLE}
+_MAT = {"lambertian": capi.RT_MAT_LAMBERTIAN, "metal": capi.RT_MAT_METAL, "dielectric": capi.RT_MAT_DIELECTRIC,
+        "diffuse_light": capi.RT_MAT_DIFFUSE_LIGHT}
+
+
+def read_image_rgb8(path):
+    from PIL import Image
+    im = np.asarray(Image.open(path).convert("RGB"), dtype=np.uint8)
+    return np.ascontiguousarray(im)
+
+
+def load_scene(src, width=None, height=None, spp=None, max_depth=None, base_dir=None):
+    """src: path to a JSON scene or an already parsed dict (schema of gpu-version/parser.hpp + extensions)."""
+    if isinstance(src, (str, os.PathLike)):
+        base_dir = base_dir or os.path.dirname(os.path.abspath(src))
+        with open(src) as f:
+            d = json.load(f)
+    else:
+        d = src
+    L = lib()
+    sc = Scene()
+    D = sc.desc
+    D.width = int(width or d["width"]); D.height = int(height or d["height"])
+    D.max_depth = int(max_depth or d["max_depth"]); D.samples_per_pixel = int(spp or d["samples_per_pixel"])
+    for k in range(3):
+        D.background[k] = d["background"][k]
+    D.background_mode = capi.RT_BG_SKY_GRADIENT if d.get("background_mode") == "sky_gradient" else capi.RT_BG_CONSTANT
+    D.sampling = capi.RT_SAMPLING_REFERENCE_CPU if d.get("sampling") == "reference_cpu" else capi.RT_SAMPLING_REFERENCE_GPU
+    cam = d["camera"]
+    for k in range(3):
+        D.camera.lookfrom[k] = cam["lookfrom"][k]; D.camera.lookat[k] = cam["lookat"][k]; D.camera.vup[k] = cam["vup"][k]
+    D.camera.vfov_deg = cam["vfov"]
+    # parser.hpp:122 — aspect from the JSON's own width/height (not from overrides), as float division
+    D.camera.aspect = cam.get("aspect_ratio", float(np.float32(d["width"]) / np.float32(d["height"])))
+    D.camera.aperture = cam["aperture"]
+    lf = np.array(cam["lookfrom"], np.float32) - np.array(cam["lookat"], np.float32)
+    fd = np.sqrt(np.float32(lf[0] * lf[0] + lf[1] * lf[1]) + lf[2] * lf[2], dtype=np.float32)   # parser.hpp:124
+    D.camera.focus_dist = cam.get("focus_dist", float(fd))
+    sc.output_file = d.get("output_file", "main.png")
+
+    objs = d["object"]["data"]; mats = d["material"]["data"]; texs = d["texture"]["data"]
+    xforms = []
+    OA = (capi.ObjectDesc * max(1, len(objs)))()
+    for i, o in enumerate(objs):
+        q = OA[i]
+        q.type = _OBJ[o["type"]]; q.material = int(o.get("material", 0)); q.xform = -1
+        t = o["type"]
+        if t == "sphere":
+            vals = list(o["center"]) + [o["radius"]]
+        elif t == "xy_rect":
+            vals = [o["x0"], o["x1"], o["y0"], o["y1"], o["k"]]
+        elif t == "xz_rect":
+            vals = [o["x0"], o["x1"], o["z0"], o["z1"], o["k"]]
+        elif t == "yz_rect":
+            vals = [o["y0"], o["y1"], o["z0"], o["z1"], o["k"]]
+        elif t == "cylinder":
+            vals = [o["radius"], o["zmin"], o["zmax"]]
+        elif t == "box":
+            vals = list(o["min"]) + list(o["max"])
+        elif t == "triangle":
+            vals = list(o["v0"]) + list(o["v1"]) + list(o["v2"])
+        for k, v in enumerate(vals):
+            q.p[k] = v
+        if t in ("cylinder", "box") and (t == "cylinder" or "rotate" in o or "translate" in o):
+            xf = capi.XformDesc()
+            ax = np.array(o.get("rotate", {}).get("axis", [0, 0, 1]), np.float32)
+            tr = np.array(o.get("translate", [0, 0, 0]), np.float32)
+            L.orc_make_xform(fptr(ax), float(o.get("rotate", {}).get("angle", 0.0)), int("rotate" in o), fptr(tr),
+                             int("translate" in o), C.byref(xf))
+            q.xform = len(xforms); xforms.append(xf)
+    XA = (capi.XformDesc * max(1, len(xforms)))(*xforms)
+    MA = (capi.MaterialDesc * max(1, len(mats)))()
+    for i, m in enumerate(mats):
+        q = MA[i]
+        q.type = _MAT[m["type"]]
+        q.texture = int(m.get("texture", 0)) if m["type"] in ("lambertian", "diffuse_light") else 0
+        if m["type"] == "metal":
+            for k in range(3):
+                q.albedo[k] = m["albedo"][k]
+            q.fuzz = m["fuzz"]
+        if m["type"] == "dielectric":
+            q.ior = m["index_of_refraction"]
+    images = []
+    TA = (capi.TextureDesc * max(1, len(texs)))()
+    for i, t in enumerate(texs):
+        q = TA[i]
+        if t["type"] == "solid_color":
+            q.type = capi.RT_TEX_SOLID
+            for k in range(3):
+                q.color[k] = t["color"][k]
+        elif t["type"] == "checker":
+            q.type = capi.RT_TEX_CHECKER; q.even = int(t["even"]); q.odd = int(t["odd"])
+        elif t["type"] == "image":
+            q.type = capi.RT_TEX_IMAGE; q.image = len(images)
+            path = t["file"] if os.path.isabs(t["file"]) else os.path.join(base_dir or ".", t["file"])
+            images.append(read_image_rgb8(path))
+    IA = (capi.ImageDesc * max(1, len(images)))()
+    for i, im in enumerate(images):
+        IA[i].height, IA[i].width = im.shape[0], im.shape[1]
+        IA[i].rgb8 = im.ctypes.data_as(C.POINTER(C.c_uint8))
+    D.n_objects, D.n_xforms, D.n_materials, D.n_textures, D.n_images = len(objs), len(xforms), len(mats), len(texs), len(images)
+    D.objects = C.cast(OA, C.POINTER(capi.ObjectDesc)); D.xforms = C.cast(XA, C.POINTER(capi.XformDesc))
+    D.materials = C.cast(MA, C.POINTER(capi.MaterialDesc)); D.textures = C.cast(TA, C.POINTER(capi.TextureDesc))
+    D.images = C.cast(IA, C.POINTER(capi.ImageDesc))
+    sc.keep = [OA, XA, MA, TA, IA, images]
+    return sc
+
+
+def render(sc, seed=0x2023, spp_begin=0, spp_count=0, threads=None):
+    W, H = sc.desc.width, sc.desc.height
+    out = np.zeros((H, W, 3), np.float32)
+    nr = C.c_int64(0)
+    rc = lib().orc_render(sc.ptr, seed, spp_begin, spp_count, fptr(out), threads or os.cpu_count() or 1, C.byref(nr))
+    assert rc == 0
+    return out, nr.value
+
+
+def aov(sc):
+    out = np.zeros((sc.desc.height, sc.desc.width, 24), np.float32)
+    assert lib().orc_aov(sc.ptr, fptr(out)) == 0
+    return out
+
+
+def tonemap(rgb_sum, spp, gamma):
+    H, W, _ = rgb_sum.shape
+    out = np.zeros((H, W, 3), np.uint8)
+    lib().orc_tonemap(fptr(np.ascontiguousarray(rgb_sum, np.float32)), W, H, spp, gamma,
+                      out.ctypes.data_as(C.POINTER(C.c_ubyte)))
+    return out
+
+
+def lbvh(sc):
+    n = sc.desc.n_objects
+    m = max(n - 1, 1)
+    r = dict(morton=np.zeros(max(n, 1), np.uint64), prim=np.zeros(max(n, 1), np.int32), left=np.zeros(m, np.int32),
+             right=np.zeros(m, np.int32), parent=np.zeros(max(2 * n - 1, 1), np.int32), node_aabb=np.zeros((m, 6), np.float32),
+             leaf_aabb=np.zeros((max(n, 1), 6), np.float32), scene_aabb=np.zeros(6, np.float32))
+    P = C.POINTER
+    lib().orc_lbvh_build(sc.ptr, r["morton"].ctypes.data_as(P(C.c_uint64)), r["prim"].ctypes.data_as(P(C.c_int32)),
+                         r["left"].ctypes.data_as(P(C.c_int32)), r["right"].ctypes.data_as(P(C.c_int32)),
+                         r["parent"].ctypes.data_as(P(C.c_int32)), fptr(r["node_aabb"]), fptr(r["leaf_aabb"]),
+                         fptr(r["scene_aabb"]))
+    return r
+
+
+def kat(kind, inp, sampling=capi.RT_SAMPLING_REFERENCE_GPU):
+    widths = {"sphere": (12, 11), "rect": (14, 11), "cyl": (18, 11), "scatter": (32, 11), "camera": (14, 6), "xform": (10, 12)}
+    wi, wo = widths[kind]
+    inp = np.ascontiguousarray(inp, np.float32).reshape(-1, wi)
+    out = np.zeros((inp.shape[0], wo), np.float32)
+    f = getattr(lib(), "orc_kat_" + kind)
+    if kind == "scatter":
+        f(fptr(inp), fptr(out), inp.shape[0], sampling)
+    else:
+        f(fptr(inp), fptr(out), inp.shape[0])
+    return out

@@ -1,0 +1,191 @@
+"""CPU tests: the oracle (oracle/liboracle.so) against the golden vectors produced by the REAL reference
+(tests/golden/make_golden.py, from oracle/_ref).  These pin the oracle; the -m gpu tests then compare
+the CUDA path with the oracle."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import orc
+from rt_b200 import capi
+
+SCENES = ["sample_scene", "blue", "blue2", "dna_000", "rtiow_486"]
+
+
+@pytest.fixture(scope="module")
+def kat():
+    return np.load(orc.GOLDEN + "/kat.npz")
+
+
+def rel_err(a, b):
+    return np.abs(a - b) / np.maximum(1.0, np.abs(b))
+
+
+def test_philox_known_answers():
+    """Random123 kat_vectors for philox4x32-10."""
+    L = orc.lib()
+
+    def ph(c, k):
+        c = (C.c_uint32 * 4)(*c); k = (C.c_uint32 * 2)(*k); o = (C.c_uint32 * 4)()
+        L.orc_philox4x32_10(c, k, o)
+        return list(o)
+    assert ph([0] * 4, [0] * 2) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert ph([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert ph([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+
+
+def test_uniform_ranges():
+    """CPU semantics [0,1) (rtweekend.h:18-21), GPU semantics (0,1] (curand_uniform)."""
+    L = orc.lib()
+    out = np.zeros(4096, np.float32)
+    L.orc_uniforms(1, 2, 3, 4, capi.RT_SAMPLING_REFERENCE_CPU, out.size, orc.fptr(out))
+    cpu = out.copy()
+    L.orc_uniforms(1, 2, 3, 4, capi.RT_SAMPLING_REFERENCE_GPU, out.size, orc.fptr(out))
+    assert cpu.min() >= 0.0 and cpu.max() < 1.0 and out.min() > 0.0 and out.max() <= 1.0
+    assert np.allclose(out - cpu, 2.0 ** -24, atol=1e-9)
+    assert abs(cpu.mean() - 0.5) < 0.02
+
+
+def test_transcendentals_against_libm():
+    L = orc.lib()
+    rng = np.random.default_rng(0)
+    x = rng.uniform(-2e4, 2e4, 20000).astype(np.float32)
+    s = np.array([L.orc_sinf(float(v)) for v in x])
+    assert np.abs(s - np.sin(x.astype(np.float64))).max() < 3e-7
+    x = np.concatenate([rng.uniform(-1, 1, 20000), [-1, 1, 0, 0.5, -0.5]]).astype(np.float32)
+    s = np.array([L.orc_acosf(float(v)) for v in x])
+    assert np.abs(s - np.arccos(x.astype(np.float64))).max() < 6e-7
+    y = rng.normal(size=20000).astype(np.float32); x = rng.normal(size=20000).astype(np.float32)
+    s = np.array([L.orc_atan2f(float(a), float(b)) for a, b in zip(y, x)])
+    assert np.abs(s - np.arctan2(y.astype(np.float64), x.astype(np.float64))).max() < 6e-7
+
+
+@pytest.mark.parametrize("kind", ["sphere", "rect", "cyl"])
+def test_hit_kat(kat, kind):
+    """sphere::hit / *_rect::hit / cylinder::hit (object.cuh) on seeded rays: identical hit decisions; t, p, n, u, v
+    within float conditioning (grazing roots amplify the one-ulp differences between fused and unfused products)."""
+    out = orc.kat(kind, kat[kind + "_in"])
+    ref = kat[kind + "_out"].reshape(out.shape)
+    assert np.array_equal(out[:, 0], ref[:, 0]), "hit/miss decisions differ from the reference"
+    assert ref[:, 0].sum() > 20
+    e = rel_err(out, ref)[ref[:, 0] == 1]
+    assert np.array_equal(out[:, 8], ref[:, 8]), "front_face differs"
+    assert np.median(e.max(1)) < 2e-6 and np.percentile(e.max(1), 90) < 5e-5 and e.max() < 2e-3
+
+
+def _reverse_triples(u):
+    """g++ evaluates the three random_float() arguments of vec3(...) right to left (vec3.cuh:135-136 compiled on
+    the host), nvcc left to right: feed the oracle the same numbers in the order the host-compiled reference saw."""
+    v = u.copy()
+    for t in range(5):
+        v[:, 3 * t:3 * t + 3] = u[:, 3 * t:3 * t + 3][:, ::-1]
+    return v
+
+
+def test_scatter_kat(kat):
+    """lambertian / metal / dielectric / diffuse_light ::scatter (material.cuh:37-178) with replayed uniforms."""
+    inp = kat["scatter_in"].reshape(-1, 32).copy()
+    tri = inp[:, 0] < 2
+    inp[tri, 16:] = _reverse_triples(inp[tri, 16:])
+    out = orc.kat("scatter", inp, capi.RT_SAMPLING_REFERENCE_GPU)
+    ref = kat["scatter_out"].reshape(out.shape)
+    assert np.array_equal(out[:, 10], ref[:, 10]), "number of uniforms consumed differs"
+    d = np.abs(out[:, :10] - ref[:, :10])
+    metal = inp[:, 0] == 1
+    # metal's `dot(scattered, n) > 0` is decided on a value near zero for a few vectors: allow sign ties there
+    dots = np.abs(np.sum(ref[:, 7:10] * inp[:, 7:10], 1))
+    decided = ~(metal & (dots < 1e-5))
+    assert np.array_equal(out[decided, 0], ref[decided, 0])
+    assert d[:, 1:].max() < 3e-6
+
+
+def test_camera_kat(kat):
+    out = orc.kat("camera", kat["camera_in"])
+    ref = kat["camera_out"].reshape(out.shape)
+    assert rel_err(out, ref).max() < 5e-6
+
+
+def test_xform_kat(kat):
+    """rotate()/translate() composition and apply_point/vec/normal (vec3.cuh:331-416)."""
+    out = orc.kat("xform", kat["xform_in"])
+    ref = kat["xform_out"].reshape(out.shape)
+    assert rel_err(out, ref).max() < 2e-6
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_aov_against_reference(name):
+    """The deterministic path: pixel-centre primary rays, first hit, no scattering.  Colour channels (albedo,
+    emission, background) must match the reference within 1e-5; hit flags and object ids must be identical
+    (float-vs-double silhouettes excepted for the double-precision cmake-cpu scene)."""
+    ref = np.load(f"{orc.GOLDEN}/aov_{name}.npz")["aov"]
+    H, W, _ = ref.shape
+    a = orc.aov(orc.load_scene(f"{orc.GOLDEN}/{name}.json", width=W, height=H))
+    is_double_ref = name == "rtiow_486"
+    assert (a[..., 0] != ref[..., 0]).sum() <= (3 if is_double_ref else 0)
+    same = a[..., 0] == ref[..., 0]
+    prim_mism = ((a[..., 11] != ref[..., 11]) & same).sum()
+    assert prim_mism <= (5 if is_double_ref else 0)
+    same &= a[..., 11] == ref[..., 11]
+    col = np.abs(a[..., 13:22] - ref[..., 13:22])[same]
+    assert col.max() <= 1e-5, f"colour AOV differs by {col.max()}"
+    if not is_double_ref:
+        assert np.array_equal(a[..., 12][same], ref[..., 12][same]), "material ids differ"
+    hit = same & (ref[..., 0] == 1)
+    if hit.any():
+        e = rel_err(a, ref)[hit][:, 1:11].max(1)
+        assert np.median(e) < 5e-5 and np.percentile(e, 99) < 5e-3 and e.max() < 2e-2
+
+
+@pytest.mark.parametrize("name", ["sample_scene", "blue2", "dna_000", "rtiow_486"])
+def test_converged_against_reference(name):
+    """Converged render (same spp as the golden): RMSE(oracle, reference) must not exceed 1.5 x the RMSE between
+    the reference's own two independent estimates (pure Monte-Carlo noise), and means must agree to 1%."""
+    g = np.load(f"{orc.GOLDEN}/conv_{name}.npz")
+    a, b, spp = g["a"], g["b"], int(g["spp"])
+    if name == "rtiow_486":
+        spp_run = 256      # keep the CPU suite short: 256 spp has 2x the noise of the 1024-spp golden
+    else:
+        spp_run = spp
+    H, W, _ = a.shape
+    img, _ = orc.render(orc.load_scene(f"{orc.GOLDEN}/{name}.json", width=W, height=H, spp=spp_run), seed=11)
+    img /= spp_run
+
+    def rmse(x, y):
+        return float(np.sqrt(np.mean((x - y) ** 2)))
+    noise = rmse(a, b)
+    scale = np.sqrt((1 + spp / spp_run) / 2)          # expected RMSE ratio when the two estimates use different spp
+    assert rmse(img, a) < 1.5 * noise * scale and rmse(img, b) < 1.5 * noise * scale
+    assert np.allclose(img.mean((0, 1)), a.mean((0, 1)), rtol=0.01, atol=2e-3)
+
+
+def test_tonemap_matches_reference_formulas():
+    rng = np.random.default_rng(5)
+    s = (rng.random((7, 9, 3)) * 40).astype(np.float32)
+    spp = 32
+    png = orc.tonemap(s, spp, 0); ppm = orc.tonemap(s, spp, 1)
+    x = s[::-1] / np.float32(spp)
+    assert np.array_equal(png, (np.float32(256) * np.clip(x, 0, np.float32(0.999))).astype(np.uint8))
+    y = np.sqrt(s[::-1] * (np.float32(1) / np.float32(spp)))
+    assert np.array_equal(ppm, (np.float32(256) * np.clip(y, 0, np.float32(0.999))).astype(np.uint8))
+
+
+def test_lbvh_host_invariants():
+    """Host LBVH twin: sorted keys, every leaf reachable exactly once, boxes enclose children."""
+    sc = orc.load_scene(orc.GOLDEN + "/rtiow_486.json")
+    r = orc.lbvh(sc)
+    n = sc.desc.n_objects
+    assert np.all(np.diff(r["morton"].astype(np.float64)) >= 0) and sorted(r["prim"].tolist()) == list(range(n))
+    seen = np.zeros(n, int)
+    stack = [0]
+    while stack:
+        i = stack.pop()
+        for c in (int(r["left"][i]), int(r["right"][i])):
+            box = r["node_aabb"][c] if c >= 0 else r["leaf_aabb"][~c]
+            assert np.all(r["node_aabb"][i][:3] <= box[:3]) and np.all(r["node_aabb"][i][3:] >= box[3:])
+            if c >= 0:
+                stack.append(c)
+            else:
+                seen[~c] += 1
+    assert np.all(seen == 1)
+    assert r["parent"][0] == -1
