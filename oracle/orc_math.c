@@ -125,13 +125,13 @@ static void mat4_mul(const float a[16], const float b[16], float r[16]) {   /* v
                            a[i * 4 + 3] * b[3 * 4 + j];
 }
 
-void orc_make_xform(const float axis[3], float angle_deg, int has_rotate, const float tr[3], int has_translate,
+void orc_make_xform(const float axis[3], double angle_deg, int has_rotate, const float tr[3], int has_translate,
                     rt_xform_desc *out) {
     /* o2w starts as identity() = translate(0,0,0) (object.cuh:296, vec3.cuh:426) */
     float m[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}, mi[16];
     memcpy(mi, m, sizeof m);
     if (has_rotate) {   /* o2w = rotate(axis, rad) * o2w   (object.cuh:225-227) */
-        float theta = (float)((double)angle_deg / 180.0 * M_PI);           /* parser.hpp:427-429 */
+        float theta = (float)(angle_deg / 180.0 * M_PI);           /* parser.hpp:427-429 */
         float len = sqrtf(axis[0] * axis[0] + axis[1] * axis[1] + axis[2] * axis[2]);   /* vec3::normalize, vec3.cuh:70-73 */
         float ax = axis[0] / len, ay = axis[1] / len, az = axis[2] / len;
         float s = sinf(theta), c = cosf(theta);

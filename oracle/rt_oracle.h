@@ -39,7 +39,7 @@ int orc_aov(const rt_scene_desc *scene, float *aov);
 void orc_tonemap(const float *rgb_sum, int width, int height, int spp, int gamma, unsigned char *rgb8);
 
 /* object-to-world = translate(t) * rotate(axis, angle_deg) as parser.hpp:423-440 builds it for cylinders */
-void orc_make_xform(const float axis[3], float angle_deg, int has_rotate, const float tr[3], int has_translate,
+void orc_make_xform(const float axis[3], double angle_deg, int has_rotate, const float tr[3], int has_translate,
                     rt_xform_desc *out);
 
 /* Philox4x32-10 block function (key 2 words, counter 4 words) */

@@ -1,0 +1,562 @@
+// rt_ctx.cu — C ABI implementation (include/rt.h): context, scene upload (flatten + GPU LBVH build), the wavefront
+// pass loop, download/tonemap.  Replaces jsonmain() of gpu-version/main.cu:448-522 minus file I/O.
+#include "rt_ctx.h"
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+
+static thread_local std::string g_create_err;
+
+int rt_fail(rt_ctx *ctx, int code, const std::string &msg) {
+    if (ctx) ctx->err = msg; else g_create_err = msg;
+    return code;
+}
+
+#define CU(call)                                                                                            \
+    do {                                                                                                    \
+        cudaError_t e__ = (call);                                                                           \
+        if (e__ != cudaSuccess)                                                                             \
+            return rt_fail(ctx, RT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));          \
+    } while (0)
+
+void HostScene::fix_pointers() {
+    d.n_objects = (int)objects.size(); d.n_xforms = (int)xforms.size(); d.n_materials = (int)materials.size();
+    d.n_textures = (int)textures.size(); d.n_images = (int)images.size();
+    for (size_t i = 0; i < images.size(); ++i) images[i].rgb8 = image_data[i].data();
+    d.objects = objects.data(); d.xforms = xforms.data(); d.materials = materials.data(); d.textures = textures.data();
+    d.images = images.data();
+}
+
+extern "C" int rt_abi_version(void) { return RT_ABI_VERSION; }
+
+extern "C" const char *rt_last_error(const rt_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+extern "C" int rt_create(rt_ctx **out, int device, void *stream) {
+    rt_ctx *ctx = nullptr;   // errors before the ctx exists go to the thread-local slot
+    if (!out) return rt_fail(nullptr, RT_ERR_INVALID, "rt_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return rt_fail(nullptr, RT_ERR_NO_DEVICE, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                                                      " (this library has no CPU fallback)");
+    if (device < 0 || device >= count) return rt_fail(nullptr, RT_ERR_INVALID, "rt_create: bad device ordinal");
+    CU(cudaSetDevice(device));
+    rt_ctx *c = new rt_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) { delete c; return rt_fail(nullptr, RT_ERR_CUDA, cudaGetErrorString(e)); }
+    c->num_sms = prop.multiProcessorCount;
+    c->smem_optin = prop.sharedMemPerBlockOptin;
+    if (stream) { c->stream = (cudaStream_t)stream; c->own_stream = false; }
+    else {
+        e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) { delete c; return rt_fail(nullptr, RT_ERR_CUDA, cudaGetErrorString(e)); }
+        c->own_stream = true;
+    }
+    cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1);
+    c->cfg.stream = c->stream; c->cfg.num_sms = c->num_sms; c->cfg.launches = &c->launches;
+    *out = c;
+    return RT_OK;
+}
+
+static void free_images(rt_ctx *c) {
+    for (auto t : c->img_tex) cudaDestroyTextureObject(t);
+    for (auto a : c->img_arrays) cudaFreeArray(a);
+    c->img_tex.clear(); c->img_arrays.clear();
+}
+
+extern "C" void rt_destroy(rt_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_images(c);
+    c->d_objects.release(); c->d_xforms.release(); c->d_mats.release(); c->d_texs.release(); c->d_images.release();
+    c->d_obmin.release(); c->d_obmax.release(); c->d_node_aabb.release(); c->d_leaf_aabb.release(); c->d_bounds.release();
+    c->d_hist.release(); c->d_keys[0].release(); c->d_keys[1].release(); c->d_vals[0].release(); c->d_vals[1].release();
+    c->d_left.release(); c->d_right.release(); c->d_parent.release(); c->d_flags.release(); c->d_prim_obj.release();
+    c->d_prim_mat.release(); c->d_nodes.release(); c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
+    for (int k = 0; k < 2; ++k) { c->d_ray_o[k].release(); c->d_ray_d[k].release(); c->d_thr[k].release(); }
+    c->d_radiance.release(); c->d_hits.release(); c->d_bins.release(); c->d_qcount.release(); c->d_bincount.release();
+    c->d_workctr.release(); c->d_counters.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
+    c->d_partials.release(); c->d_rays.release();
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+// ---- host-side set-up that the reference also does on the host ----
+struct H3 { float x, y, z; };
+static inline H3 hsub(H3 a, H3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+static inline H3 hscale(float t, H3 a) { return {t * a.x, t * a.y, t * a.z}; }
+static inline float hdot(H3 a, H3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+static inline H3 hunit(H3 a) { float r = 1.0f / sqrtf(hdot(a, a)); return hscale(r, a); }
+static inline H3 hcross(H3 u, H3 v) { return {u.y * v.z - u.z * v.y, u.z * v.x - u.x * v.z, u.x * v.y - u.y * v.x}; }
+static inline float3 f3(H3 a) { return make_float3(a.x, a.y, a.z); }
+
+// camera::camera, gpu-version/camera.cuh:9-29 (float arithmetic, unfused: this file is built with -ffp-contract=off)
+static void camera_setup(const rt_camera_desc &c, DCamera &cam) {
+    float theta = (float)((double)c.vfov_deg * M_PI / (double)180.0f);       // rtweekend.cuh:17-19
+    float h = tanf(theta / 2.0f);
+    float viewport_height = 2.0f * h;
+    float viewport_width = c.aspect * viewport_height;
+    H3 from = {c.lookfrom[0], c.lookfrom[1], c.lookfrom[2]}, at = {c.lookat[0], c.lookat[1], c.lookat[2]};
+    H3 vup = {c.vup[0], c.vup[1], c.vup[2]};
+    H3 w = hunit(hsub(from, at)), u = hunit(hcross(vup, w)), v = hcross(w, u);
+    H3 horizontal = hscale(c.focus_dist * viewport_width, u), vertical = hscale(c.focus_dist * viewport_height, v);
+    H3 hh = hscale(1.0f / 2.0f, horizontal), vh = hscale(1.0f / 2.0f, vertical);
+    H3 llc = hsub(hsub(hsub(from, hh), vh), hscale(c.focus_dist, w));
+    cam.origin = f3(from); cam.llc = f3(llc); cam.horizontal = f3(horizontal); cam.vertical = f3(vertical);
+    cam.u = f3(u); cam.v = f3(v); cam.w = f3(w);
+    cam.lens_radius = c.aperture / 2.0f;
+}
+
+static bool texture_reads_uv(const HostScene &hs, int tex, int depth = 0) {
+    if (tex < 0 || tex >= (int)hs.textures.size() || depth > 8) return false;
+    const rt_texture_desc &t = hs.textures[tex];
+    if (t.type == RT_TEX_IMAGE) return true;
+    if (t.type == RT_TEX_CHECKER) return texture_reads_uv(hs, t.even, depth + 1) || texture_reads_uv(hs, t.odd, depth + 1);
+    return false;
+}
+
+static int validate_scene(rt_ctx *ctx, const HostScene &hs) {
+    const rt_scene_desc &d = hs.d;
+    if (d.width < 2 || d.height < 2) return rt_fail(ctx, RT_ERR_INVALID, "scene: width and height must be >= 2");
+    if (d.max_depth < 1 || d.samples_per_pixel < 1) return rt_fail(ctx, RT_ERR_INVALID, "scene: max_depth and samples_per_pixel must be >= 1");
+    if ((long long)d.n_objects >= (1ll << 28)) return rt_fail(ctx, RT_ERR_INVALID, "scene: too many objects");
+    for (int i = 0; i < d.n_objects; ++i) {
+        const rt_object_desc &o = hs.objects[i];
+        if (o.type < 0 || o.type > RT_OBJ_TRIANGLE) return rt_fail(ctx, RT_ERR_INVALID, "scene: unknown object type at index " + std::to_string(i));
+        if (o.material < 0 || o.material >= d.n_materials) return rt_fail(ctx, RT_ERR_INVALID, "scene: object " + std::to_string(i) + " references a missing material");
+        if (o.xform >= d.n_xforms) return rt_fail(ctx, RT_ERR_INVALID, "scene: object " + std::to_string(i) + " references a missing transform");
+        if (o.type == RT_OBJ_CYLINDER && o.xform < 0) return rt_fail(ctx, RT_ERR_INVALID, "scene: cylinder without a transform");
+    }
+    for (int i = 0; i < d.n_materials; ++i) {
+        const rt_material_desc &m = hs.materials[i];
+        if (m.type < 0 || m.type > RT_MAT_DIFFUSE_LIGHT) return rt_fail(ctx, RT_ERR_INVALID, "scene: unknown material type");
+        if ((m.type == RT_MAT_LAMBERTIAN || m.type == RT_MAT_DIFFUSE_LIGHT) && (m.texture < 0 || m.texture >= d.n_textures))
+            return rt_fail(ctx, RT_ERR_INVALID, "scene: material " + std::to_string(i) + " references a missing texture");
+    }
+    for (int i = 0; i < d.n_textures; ++i) {
+        const rt_texture_desc &t = hs.textures[i];
+        if (t.type < 0 || t.type > RT_TEX_IMAGE) return rt_fail(ctx, RT_ERR_INVALID, "scene: unknown texture type");
+        if (t.type == RT_TEX_CHECKER && (t.even < 0 || t.even >= d.n_textures || t.odd < 0 || t.odd >= d.n_textures))
+            return rt_fail(ctx, RT_ERR_INVALID, "scene: checker texture references a missing texture");
+        if (t.type == RT_TEX_IMAGE && (t.image < 0 || t.image >= d.n_images)) return rt_fail(ctx, RT_ERR_INVALID, "scene: image texture references a missing image");
+    }
+    return RT_OK;
+}
+
+// Copies the tables to the device and builds the LBVH there (replaces parse_scene's per-node cudaMalloc/cudaMemcpy,
+// parser.hpp:130-561, and the single-thread move_to_device kernel, main.cu:374-446).
+static int upload_to_device(rt_ctx *ctx) {
+    HostScene &hs = ctx->hs;
+    const rt_scene_desc &d = hs.d;
+    CU(cudaSetDevice(ctx->device));
+    const int n = d.n_objects;
+    cudaStream_t s = ctx->stream;
+
+    // objects, transforms, materials, textures
+    static_assert(sizeof(DObject) == sizeof(rt_object_desc), "DObject must mirror rt_object_desc");
+    CU(ctx->d_objects.alloc(n));
+    if (n) CU(cudaMemcpyAsync(ctx->d_objects.p, hs.objects.data(), sizeof(DObject) * n, cudaMemcpyHostToDevice, s));
+    std::vector<float4> xf(6 * (size_t)std::max(1, d.n_xforms));
+    for (int i = 0; i < d.n_xforms; ++i)
+        for (int r = 0; r < 3; ++r) {
+            const float *m = hs.xforms[i].m + 4 * r, *mi = hs.xforms[i].m_inv + 4 * r;
+            xf[6 * i + r] = make_float4(m[0], m[1], m[2], m[3]);
+            xf[6 * i + 3 + r] = make_float4(mi[0], mi[1], mi[2], mi[3]);
+        }
+    CU(ctx->d_xforms.alloc(xf.size()));
+    CU(cudaMemcpyAsync(ctx->d_xforms.p, xf.data(), sizeof(float4) * xf.size(), cudaMemcpyHostToDevice, s));
+    std::vector<DMaterial> mats(std::max(1, d.n_materials));
+    for (int i = 0; i < d.n_materials; ++i) {
+        const rt_material_desc &m = hs.materials[i];
+        DMaterial dm{};
+        dm.type = m.type; dm.texture = m.texture;
+        dm.fuzz = m.fuzz < 1.0f ? m.fuzz : 1.0f;                         // metal ctor, material.cuh:61
+        dm.ior = m.ior;
+        const bool uv = (m.type == RT_MAT_LAMBERTIAN || m.type == RT_MAT_DIFFUSE_LIGHT) && texture_reads_uv(hs, m.texture);
+        dm.albedo = make_float4(m.albedo[0], m.albedo[1], m.albedo[2], uv ? 1.0f : 0.0f);
+        mats[i] = dm;
+    }
+    CU(ctx->d_mats.alloc(mats.size()));
+    CU(cudaMemcpyAsync(ctx->d_mats.p, mats.data(), sizeof(DMaterial) * mats.size(), cudaMemcpyHostToDevice, s));
+    std::vector<DTexture> texs(std::max(1, d.n_textures));
+    for (int i = 0; i < d.n_textures; ++i) {
+        const rt_texture_desc &t = hs.textures[i];
+        DTexture dt{};
+        dt.type = t.type; dt.even = t.even; dt.odd = t.odd; dt.image = t.image;
+        dt.color = make_float4(t.color[0], t.color[1], t.color[2], 0.0f);
+        texs[i] = dt;
+    }
+    CU(ctx->d_texs.alloc(texs.size()));
+    CU(cudaMemcpyAsync(ctx->d_texs.p, texs.data(), sizeof(DTexture) * texs.size(), cudaMemcpyHostToDevice, s));
+
+    // image textures -> CUDA arrays sampled by the texture unit (point filter, unnormalised coordinates, uchar4 -> [0,1])
+    free_images(ctx);
+    std::vector<DImage> imgs(std::max(1, d.n_images));
+    for (int i = 0; i < d.n_images; ++i) {
+        const rt_image_desc &im = hs.images[i];
+        if (im.width < 1 || im.height < 1 || !im.rgb8) return rt_fail(ctx, RT_ERR_INVALID, "scene: empty image");
+        std::vector<uchar4> px((size_t)im.width * im.height);
+        for (size_t k = 0; k < px.size(); ++k) px[k] = make_uchar4(im.rgb8[3 * k], im.rgb8[3 * k + 1], im.rgb8[3 * k + 2], 255);
+        cudaChannelFormatDesc fmt = cudaCreateChannelDesc<uchar4>();
+        cudaArray_t arr;
+        CU(cudaMallocArray(&arr, &fmt, im.width, im.height));
+        ctx->img_arrays.push_back(arr);
+        CU(cudaMemcpy2DToArray(arr, 0, 0, px.data(), sizeof(uchar4) * im.width, sizeof(uchar4) * im.width, im.height, cudaMemcpyHostToDevice));
+        cudaResourceDesc rd{}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+        cudaTextureDesc td{};
+        td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeNormalizedFloat; td.normalizedCoords = 0;
+        cudaTextureObject_t tex;
+        CU(cudaCreateTextureObject(&tex, &rd, &td, nullptr));
+        ctx->img_tex.push_back(tex);
+        imgs[i].tex = tex; imgs[i].width = im.width; imgs[i].height = im.height;
+    }
+    CU(ctx->d_images.alloc(imgs.size()));
+    CU(cudaMemcpyAsync(ctx->d_images.p, imgs.data(), sizeof(DImage) * imgs.size(), cudaMemcpyHostToDevice, s));
+
+    // LBVH buffers
+    const size_t nn = (size_t)std::max(1, n);
+    CU(ctx->d_obmin.alloc(3 * nn)); CU(ctx->d_obmax.alloc(3 * nn)); CU(ctx->d_bounds.alloc(12));
+    CU(ctx->d_keys[0].alloc(nn)); CU(ctx->d_keys[1].alloc(nn)); CU(ctx->d_vals[0].alloc(nn)); CU(ctx->d_vals[1].alloc(nn));
+    CU(ctx->d_hist.alloc(lbvh_hist_words(n)));
+    CU(ctx->d_left.alloc(nn)); CU(ctx->d_right.alloc(nn)); CU(ctx->d_parent.alloc(2 * nn)); CU(ctx->d_flags.alloc(nn));
+    CU(ctx->d_node_aabb.alloc(6 * nn)); CU(ctx->d_leaf_aabb.alloc(6 * nn));
+    CU(ctx->d_nodes.alloc(nn)); CU(ctx->d_primA.alloc(nn)); CU(ctx->d_primB.alloc(nn)); CU(ctx->d_primC.alloc(nn));
+    CU(ctx->d_prim_obj.alloc(nn)); CU(ctx->d_prim_mat.alloc(nn));
+    LbvhBuffers &lb = ctx->lb;
+    lb.n = n; lb.objects = ctx->d_objects.p; lb.xforms = ctx->d_xforms.p; lb.obj_bmin = ctx->d_obmin.p; lb.obj_bmax = ctx->d_obmax.p;
+    lb.bounds = ctx->d_bounds.p; lb.keys[0] = ctx->d_keys[0].p; lb.keys[1] = ctx->d_keys[1].p; lb.vals[0] = ctx->d_vals[0].p;
+    lb.vals[1] = ctx->d_vals[1].p; lb.hist = ctx->d_hist.p; lb.left = ctx->d_left.p; lb.right = ctx->d_right.p;
+    lb.parent = ctx->d_parent.p; lb.flags = ctx->d_flags.p; lb.node_aabb = ctx->d_node_aabb.p; lb.leaf_aabb = ctx->d_leaf_aabb.p;
+    lb.nodes = ctx->d_nodes.p; lb.primA = ctx->d_primA.p; lb.primB = ctx->d_primB.p; lb.primC = ctx->d_primC.p;
+    lb.prim_obj = ctx->d_prim_obj.p; lb.prim_mat = ctx->d_prim_mat.p;
+    CU(cudaEventRecord(ctx->ev0, s));
+    lbvh_build(ctx->cfg, lb);
+    CU(cudaEventRecord(ctx->ev1, s));
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(s));       // the host vectors above go out of scope
+    float ms = 0; cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1); ctx->stats.ms_build = ms;
+
+    // device scene header
+    DScene &ds = ctx->ds;
+    ds.n_prims = n; ds.n_nodes = n >= 2 ? n - 1 : 1;
+    ds.width = d.width; ds.height = d.height; ds.max_depth = d.max_depth; ds.sampling = d.sampling; ds.bg_mode = d.background_mode;
+    ds.defocus = (d.sampling == RT_SAMPLING_REFERENCE_CPU && d.camera.aperture > 0.0f) ? 1 : 0;
+    ds.background = make_float3(d.background[0], d.background[1], d.background[2]);
+    camera_setup(d.camera, ds.cam);
+    ds.nodes = ctx->d_nodes.p; ds.primA = ctx->d_primA.p; ds.primB = ctx->d_primB.p; ds.primC = ctx->d_primC.p;
+    ds.prim_obj = ctx->d_prim_obj.p; ds.prim_mat = ctx->d_prim_mat.p; ds.xforms = ctx->d_xforms.p; ds.mats = ctx->d_mats.p;
+    ds.texs = ctx->d_texs.p; ds.images = ctx->d_images.p;
+
+    // extend-kernel configuration: stage the whole BVH in shared memory when it leaves room for >= 2 CTAs per SM
+    const size_t bvh_bytes = sizeof(BvhNode) * (size_t)ds.n_nodes;
+    ctx->cfg.bvh_smem_bytes = 0;
+    if (bvh_bytes <= ctx->smem_optin && bvh_bytes <= 100 * 1024) {
+        if (extend_configure_smem(bvh_bytes) == cudaSuccess) ctx->cfg.bvh_smem_bytes = bvh_bytes;
+        else cudaGetLastError();
+    }
+    int per_sm = extend_max_blocks_per_sm(ctx->cfg.bvh_smem_bytes);
+    if (per_sm < 1) { ctx->cfg.bvh_smem_bytes = 0; per_sm = extend_max_blocks_per_sm(0); }
+    ctx->cfg.extend_blocks_per_sm = per_sm < 1 ? 1 : per_sm;
+    ctx->have_scene = true;
+    ctx->accum_valid = false;
+    return RT_OK;
+}
+
+extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *sc) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!sc) return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload: scene is NULL");
+    HostScene hs;
+    hs.d = *sc;
+    if (sc->n_objects < 0 || sc->n_xforms < 0 || sc->n_materials < 0 || sc->n_textures < 0 || sc->n_images < 0)
+        return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload: negative table size");
+    hs.objects.assign(sc->objects, sc->objects + sc->n_objects);
+    hs.xforms.assign(sc->xforms, sc->xforms + sc->n_xforms);
+    hs.materials.assign(sc->materials, sc->materials + sc->n_materials);
+    hs.textures.assign(sc->textures, sc->textures + sc->n_textures);
+    hs.images.assign(sc->images, sc->images + sc->n_images);
+    for (int i = 0; i < sc->n_images; ++i) {
+        const rt_image_desc &im = sc->images[i];
+        if (!im.rgb8 || im.width < 1 || im.height < 1) return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload: empty image");
+        hs.image_data.emplace_back(im.rgb8, im.rgb8 + (size_t)im.width * im.height * 3);
+    }
+    hs.fix_pointers();
+    int rc = validate_scene(ctx, hs);
+    if (rc) return rc;
+    ctx->hs = std::move(hs);
+    ctx->hs.fix_pointers();
+    return upload_to_device(ctx);
+}
+
+extern "C" int rt_scene_upload_json_text(rt_ctx *ctx, const char *text, const char *base_dir) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!text) return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload_json_text: text is NULL");
+    HostScene hs; std::string err;
+    int rc = rt_json_to_scene(text, base_dir, hs, err);
+    if (rc) return rt_fail(ctx, rc, err);
+    hs.fix_pointers();
+    rc = validate_scene(ctx, hs);
+    if (rc) return rc;
+    ctx->hs = std::move(hs);
+    ctx->hs.fix_pointers();
+    return upload_to_device(ctx);
+}
+
+extern "C" int rt_scene_upload_json(rt_ctx *ctx, const char *path) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!path) return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload_json: path is NULL");
+    std::ifstream f(path, std::ios::binary);
+    if (!f) return rt_fail(ctx, RT_ERR_IO, std::string("cannot open scene file ") + path);
+    std::stringstream ss; ss << f.rdbuf();
+    std::string p(path), dir = ".";
+    size_t k = p.find_last_of('/');
+    if (k != std::string::npos) dir = p.substr(0, k);
+    return rt_scene_upload_json_text(ctx, ss.str().c_str(), dir.c_str());
+}
+
+extern "C" int rt_scene_info_get(rt_ctx *ctx, rt_scene_info *out) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!out) return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_info_get: out is NULL");
+    if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "no scene uploaded");
+    const rt_scene_desc &d = ctx->hs.d;
+    memset(out, 0, sizeof *out);
+    out->width = d.width; out->height = d.height; out->max_depth = d.max_depth; out->samples_per_pixel = d.samples_per_pixel;
+    out->n_objects = d.n_objects; out->n_materials = d.n_materials; out->n_textures = d.n_textures; out->n_bvh_nodes = ctx->ds.n_nodes;
+    snprintf(out->output_file, sizeof out->output_file, "%s", ctx->hs.output_file.c_str());
+    return RT_OK;
+}
+
+extern "C" int rt_scene_override(rt_ctx *ctx, int width, int height, int spp, int max_depth) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "no scene uploaded");
+    rt_scene_desc &d = ctx->hs.d;
+    if (width > 0) d.width = width;
+    if (height > 0) d.height = height;
+    if (spp > 0) d.samples_per_pixel = spp;
+    if (max_depth > 0) d.max_depth = max_depth;
+    if (d.width < 2 || d.height < 2) return rt_fail(ctx, RT_ERR_INVALID, "override: width and height must be >= 2");
+    // the camera keeps the aspect the scene was loaded with (the reference ties it to the JSON's width/height, parser.hpp:122)
+    ctx->ds.width = d.width; ctx->ds.height = d.height; ctx->ds.max_depth = d.max_depth;
+    ctx->accum_valid = false;
+    return RT_OK;
+}
+
+// ---- wavefront queues ----
+static int ensure_queues(rt_ctx *ctx, long long cap) {
+    if (cap <= ctx->queue_cap && ctx->d_qcount.p) return RT_OK;
+    for (int k = 0; k < 2; ++k) { CU(ctx->d_ray_o[k].alloc(cap)); CU(ctx->d_ray_d[k].alloc(cap)); CU(ctx->d_thr[k].alloc(cap)); }
+    CU(ctx->d_radiance.alloc(cap)); CU(ctx->d_hits.alloc(cap)); CU(ctx->d_bins.alloc((size_t)cap * RT_NUM_BINS));
+    CU(ctx->d_counters.alloc(CTR_COUNT));
+    if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(1)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, sizeof(unsigned long long), ctx->stream)); }
+    ctx->queue_cap = cap;
+    Queues &q = ctx->q;
+    for (int k = 0; k < 2; ++k) { q.ray_o[k] = ctx->d_ray_o[k].p; q.ray_d[k] = ctx->d_ray_d[k].p; q.thr[k] = ctx->d_thr[k].p; }
+    q.hits = ctx->d_hits.p; q.bins = ctx->d_bins.p; q.radiance = ctx->d_radiance.p; q.counters = ctx->d_counters.p; q.cap = cap;
+    return RT_OK;
+}
+
+static int ensure_depth_buffers(rt_ctx *ctx, int max_depth) {
+    CU(ctx->d_qcount.alloc(max_depth + 2)); CU(ctx->d_bincount.alloc((size_t)max_depth * RT_BIN_STRIDE)); CU(ctx->d_workctr.alloc((size_t)max_depth * 2));
+    ctx->q.qcount = ctx->d_qcount.p; ctx->q.bincount = ctx->d_bincount.p; ctx->q.workctr = ctx->d_workctr.p;
+    return RT_OK;
+}
+
+static int ensure_accum(rt_ctx *ctx) {
+    const size_t n = (size_t)ctx->ds.width * ctx->ds.height * 3;
+    if (ctx->d_accum.n < n) { CU(ctx->d_accum.alloc(n)); ctx->accum_valid = false; }
+    return RT_OK;
+}
+
+extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!prm) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: params is NULL");
+    if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "rt_render: no scene uploaded");
+    CU(cudaSetDevice(ctx->device));
+    const DScene &ds = ctx->ds;
+    const int np = ds.width * ds.height;
+    const int spp = prm->spp_count > 0 ? prm->spp_count : ctx->hs.d.samples_per_pixel;
+    if (prm->spp_begin < 0) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: spp_begin < 0");
+    const bool count = (prm->flags & RT_RENDER_COUNT_EVENTS) != 0;
+    const bool sort = (prm->flags & RT_RENDER_NO_SORT) == 0;
+    // wavefront size: whole sample planes, at most max_paths_per_pass paths and at most 2^30 queue entries
+    long long max_paths = prm->max_paths_per_pass;
+    if (max_paths <= 0) {
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        const long long per_path = 2 * 48 + 16 + 8 + 4 * RT_NUM_BINS;            // bytes per queue entry
+        long long by_mem = (long long)((double)(free_b + ctx->queue_cap * per_path) * 0.5 / per_path);
+        max_paths = std::min<long long>(by_mem, 64ll << 20);
+    }
+    max_paths = std::min<long long>(max_paths, 1ll << 30);
+    int s_pass = (int)std::max<long long>(1, std::min<long long>(spp, max_paths / np));
+    const long long cap = (long long)s_pass * np;
+    if (cap > (1ll << 31) - 64) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: image too large for one wavefront pass");
+    int rc = ensure_queues(ctx, cap); if (rc) return rc;
+    rc = ensure_depth_buffers(ctx, ds.max_depth); if (rc) return rc;
+    rc = ensure_accum(ctx); if (rc) return rc;
+    cudaStream_t s = ctx->stream;
+    bool clear = !((prm->flags & RT_RENDER_KEEP_ACCUM) && ctx->accum_valid);
+    if (count) CU(cudaMemsetAsync(ctx->d_counters.p, 0, sizeof(unsigned long long) * CTR_COUNT, s));
+    long long passes = 0;
+    float ms_stage[4] = {0, 0, 0, 0};
+    cudaEvent_t evs[2] = {nullptr, nullptr};
+    if (count) { cudaEventCreate(&evs[0]); cudaEventCreate(&evs[1]); }
+    auto timed = [&](int stage, auto &&fn) {
+        if (count) cudaEventRecord(evs[0], s);
+        fn();
+        if (count) { cudaEventRecord(evs[1], s); cudaEventSynchronize(evs[1]); float ms = 0; cudaEventElapsedTime(&ms, evs[0], evs[1]); ms_stage[stage] += ms; }
+    };
+    CU(cudaEventRecord(ctx->ev0, s));
+    for (int done = 0; done < spp; done += s_pass) {
+        const int sn = std::min(s_pass, spp - done);
+        const int n_paths = sn * np;
+        launch_pass_init(ctx->cfg, ctx->q, ds.max_depth, n_paths);
+        timed(0, [&] { launch_generate(ctx->cfg, ds, ctx->q, prm->seed, prm->spp_begin + done, n_paths); });
+        int buf = 0;
+        for (int b = 0; b < ds.max_depth; ++b) {
+            timed(1, [&] { launch_extend(ctx->cfg, ds, ctx->q, b, buf, count, sort); });
+            timed(2, [&] { launch_shade(ctx->cfg, ds, ctx->q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort); });
+            buf ^= 1;
+        }
+        timed(3, [&] { launch_accumulate(ctx->cfg, ctx->q, ctx->d_accum.p, np, sn, clear, ds.max_depth, ctx->d_rays.p); });
+        clear = false;
+        ++passes;
+    }
+    CU(cudaEventRecord(ctx->ev1, s));
+    CU(cudaGetLastError());
+    ctx->accum_valid = true;
+    rt_stats &st = ctx->stats;
+    st.samples += (long long)spp * np; st.passes += passes;
+    if (count) {
+        unsigned long long c[CTR_COUNT];
+        CU(cudaMemcpyAsync(c, ctx->d_counters.p, sizeof c, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        st.n_box_tests += c[CTR_BOX]; st.n_sphere_reject += c[CTR_SPH_REJECT]; st.n_sphere_accept += c[CTR_SPH_ACCEPT];
+        st.n_rect_tests += c[CTR_RECT]; st.n_cyl_reject += c[CTR_CYL_REJECT]; st.n_cyl_accept += c[CTR_CYL_ACCEPT];
+        st.n_tri_tests += c[CTR_TRI]; st.n_boxprim_tests += c[CTR_BOXPRIM]; st.n_shade += c[CTR_SHADE];
+        st.n_generate += (long long)spp * np; st.n_node_visits += c[CTR_NODE_VISITS];
+        st.ms_generate += ms_stage[0]; st.ms_extend += ms_stage[1]; st.ms_shade += ms_stage[2]; st.ms_accumulate += ms_stage[3];
+        cudaEventDestroy(evs[0]); cudaEventDestroy(evs[1]);
+        if (c[CTR_STACK_OVERFLOW]) return rt_fail(ctx, RT_ERR_INVALID, "traversal stack overflow (BVH deeper than RT_TRAV_STACK)");
+    }
+    return RT_OK;
+}
+
+extern "C" int rt_render_aov(rt_ctx *ctx, float *out, size_t n_floats) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "rt_render_aov: no scene uploaded");
+    CU(cudaSetDevice(ctx->device));
+    const size_t need = (size_t)ctx->ds.width * ctx->ds.height * 24;
+    if (!out || n_floats < need) return rt_fail(ctx, RT_ERR_INVALID, "rt_render_aov: output buffer too small");
+    CU(ctx->d_aov.alloc(need));
+    launch_aov(ctx->cfg, ctx->ds, ctx->d_aov.p);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out, ctx->d_aov.p, sizeof(float) * need, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+extern "C" int rt_accum_device_ptr(rt_ctx *ctx, void **dev_ptr, size_t *n_floats) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "no scene uploaded");
+    CU(cudaSetDevice(ctx->device));
+    int rc = ensure_accum(ctx); if (rc) return rc;
+    if (dev_ptr) *dev_ptr = ctx->d_accum.p;
+    if (n_floats) *n_floats = (size_t)ctx->ds.width * ctx->ds.height * 3;
+    return RT_OK;
+}
+
+extern "C" int rt_accum_sum_ordered(rt_ctx *ctx, const void *const *partials, int n_partials) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "no scene uploaded");
+    if (!partials || n_partials < 1) return rt_fail(ctx, RT_ERR_INVALID, "rt_accum_sum_ordered: no partial buffers");
+    CU(cudaSetDevice(ctx->device));
+    int rc = ensure_accum(ctx); if (rc) return rc;
+    CU(ctx->d_partials.alloc(n_partials));
+    CU(cudaMemcpyAsync(ctx->d_partials.p, partials, sizeof(void *) * n_partials, cudaMemcpyHostToDevice, ctx->stream));
+    launch_sum_ordered(ctx->cfg, ctx->d_accum.p, ctx->d_partials.p, n_partials, (long long)ctx->ds.width * ctx->ds.height * 3);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->accum_valid = true;
+    return RT_OK;
+}
+
+extern "C" int rt_synchronize(rt_ctx *ctx) {
+    if (!ctx) return RT_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+extern "C" int rt_stats_reset(rt_ctx *ctx) {
+    if (!ctx) return RT_ERR_INVALID;
+    float ms_build = ctx->stats.ms_build;
+    memset(&ctx->stats, 0, sizeof ctx->stats);
+    ctx->stats.ms_build = ms_build;
+    ctx->launches = 0;
+    if (ctx->d_rays.p) { CU(cudaSetDevice(ctx->device)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, sizeof(unsigned long long), ctx->stream)); }
+    return RT_OK;
+}
+
+extern "C" int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigned char *rgb8, int total_spp, int gamma, rt_stats *stats) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "rt_download: no scene uploaded");
+    CU(cudaSetDevice(ctx->device));
+    const size_t need = (size_t)ctx->ds.width * ctx->ds.height * 3;
+    if ((rgb_sum || rgb8) && !ctx->accum_valid) return rt_fail(ctx, RT_ERR_INVALID, "rt_download: nothing rendered yet");
+    if (rgb_sum && n_floats < need) return rt_fail(ctx, RT_ERR_INVALID, "rt_download: rgb_sum buffer too small");
+    cudaStream_t s = ctx->stream;
+    if (rgb8) {
+        if (total_spp < 1) total_spp = ctx->hs.d.samples_per_pixel;
+        CU(ctx->d_rgb8.alloc(need));
+        launch_tonemap(ctx->cfg, ctx->d_accum.p, ctx->d_rgb8.p, ctx->ds.width, ctx->ds.height, total_spp, gamma);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(rgb8, ctx->d_rgb8.p, need, cudaMemcpyDeviceToHost, s));
+    }
+    if (rgb_sum) CU(cudaMemcpyAsync(rgb_sum, ctx->d_accum.p, sizeof(float) * need, cudaMemcpyDeviceToHost, s));
+    if (stats && ctx->d_rays.p) { unsigned long long r = 0; CU(cudaMemcpyAsync(&r, ctx->d_rays.p, sizeof r, cudaMemcpyDeviceToHost, s)); CU(cudaStreamSynchronize(s)); ctx->stats.rays = (long long)r; }
+    CU(cudaStreamSynchronize(s));
+    if (stats) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) == cudaSuccess) ctx->stats.ms_total = ms; else cudaGetLastError();
+        ctx->stats.launches = ctx->launches;
+        *stats = ctx->stats;
+    }
+    return RT_OK;
+}
+
+extern "C" int rt_bvh_download(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left,
+                               int32_t *right, int32_t *parent, float *node_aabb, float *leaf_aabb, float *scene_aabb) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "rt_bvh_download: no scene uploaded");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const int n = ctx->lb.n;
+    if (n_prims) *n_prims = n;
+    if (n <= 0) return RT_OK;
+    if (morton_sorted) CU(cudaMemcpy(morton_sorted, ctx->d_keys[0].p, sizeof(uint64_t) * n, cudaMemcpyDeviceToHost));
+    if (prim_sorted) CU(cudaMemcpy(prim_sorted, ctx->d_vals[0].p, sizeof(int) * n, cudaMemcpyDeviceToHost));
+    if (leaf_aabb) CU(cudaMemcpy(leaf_aabb, ctx->d_leaf_aabb.p, sizeof(float) * 6 * n, cudaMemcpyDeviceToHost));
+    if (scene_aabb) {
+        unsigned b[12];
+        CU(cudaMemcpy(b, ctx->d_bounds.p, sizeof b, cudaMemcpyDeviceToHost));
+        for (int k = 0; k < 6; ++k) { unsigned u = b[k]; u ^= (u >> 31) ? 0x80000000u : 0xffffffffu; memcpy(&scene_aabb[k], &u, 4); }
+    }
+    if (n >= 2) {
+        if (left) CU(cudaMemcpy(left, ctx->d_left.p, sizeof(int) * (n - 1), cudaMemcpyDeviceToHost));
+        if (right) CU(cudaMemcpy(right, ctx->d_right.p, sizeof(int) * (n - 1), cudaMemcpyDeviceToHost));
+        if (parent) CU(cudaMemcpy(parent, ctx->d_parent.p, sizeof(int) * (2 * n - 1), cudaMemcpyDeviceToHost));
+        if (node_aabb) CU(cudaMemcpy(node_aabb, ctx->d_node_aabb.p, sizeof(float) * 6 * (n - 1), cudaMemcpyDeviceToHost));
+    } else if (parent) parent[0] = -1;
+    return RT_OK;
+}
+
+extern "C" void rt_free(void *p) { free(p); }

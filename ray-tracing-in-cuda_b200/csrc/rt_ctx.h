@@ -1,0 +1,67 @@
+// rt_ctx.h — the host-side context behind the opaque rt_ctx of include/rt.h.
+#pragma once
+#include <string>
+#include <vector>
+#include "rt_kernels.h"
+
+struct HostScene {                 // owning copy of an rt_scene_desc (what rt_scene_upload received / the JSON reader produced)
+    rt_scene_desc d{};
+    std::vector<rt_object_desc> objects;
+    std::vector<rt_xform_desc> xforms;
+    std::vector<rt_material_desc> materials;
+    std::vector<rt_texture_desc> textures;
+    std::vector<rt_image_desc> images;
+    std::vector<std::vector<uint8_t>> image_data;
+    std::string output_file = "main.png";
+    void fix_pointers();
+};
+
+template <class T> struct DevBuf {
+    T *p = nullptr; size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        release();
+        cudaError_t e = cudaMalloc((void **)&p, sizeof(T) * (count ? count : 1));
+        if (e == cudaSuccess) n = count ? count : 1; else p = nullptr;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+struct rt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int num_sms = 0;
+    size_t smem_optin = 0;
+    std::string err;
+    long long launches = 0;
+
+    bool have_scene = false;
+    HostScene hs;
+    DScene ds{};
+    LaunchCfg cfg{};
+
+    // scene tables
+    DevBuf<DObject> d_objects; DevBuf<float4> d_xforms; DevBuf<DMaterial> d_mats; DevBuf<DTexture> d_texs; DevBuf<DImage> d_images;
+    std::vector<cudaArray_t> img_arrays; std::vector<cudaTextureObject_t> img_tex;
+    // LBVH
+    LbvhBuffers lb{};
+    DevBuf<float> d_obmin, d_obmax, d_node_aabb, d_leaf_aabb; DevBuf<unsigned> d_bounds, d_hist;
+    DevBuf<unsigned long long> d_keys[2]; DevBuf<int> d_vals[2], d_left, d_right, d_parent, d_flags, d_prim_obj, d_prim_mat;
+    DevBuf<BvhNode> d_nodes; DevBuf<float4> d_primA, d_primB, d_primC;
+    // wavefront
+    Queues q{};
+    DevBuf<float4> d_ray_o[2], d_ray_d[2], d_thr[2], d_radiance; DevBuf<int2> d_hits; DevBuf<int> d_bins, d_qcount, d_bincount, d_workctr;
+    DevBuf<unsigned long long> d_counters, d_rays;
+    DevBuf<float> d_accum; DevBuf<unsigned char> d_rgb8; DevBuf<float> d_aov; DevBuf<const float *> d_partials;
+    long long queue_cap = 0;
+    // stats
+    rt_stats stats{};
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool accum_valid = false;
+};
+
+int rt_fail(rt_ctx *ctx, int code, const std::string &msg);
+int rt_json_to_scene(const char *text, const char *base_dir, HostScene &out, std::string &err);
+int rt_png_decode_file(const char *path, std::vector<uint8_t> &rgb, int &w, int &h, std::string &err);

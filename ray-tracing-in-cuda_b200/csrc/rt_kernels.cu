@@ -1,0 +1,400 @@
+// rt_kernels.cu — the wavefront path-tracing kernels for sm_100a:
+//   generate -> [ extend (LBVH traversal) -> shade (+ stream compaction) ] x max_depth -> accumulate ; tonemap
+// They replace the reference's megakernel (gpu-version/main.cu:72-105 `render` + 17-70 `ray_color`), which runs one
+// thread per pixel, serial over samples, with virtual dispatch through device-heap pointers.
+//
+// Design for B200 (148 SMs, 228 KB smem/SM, 126 MB L2):
+//   * persistent grids (SM count x resident CTAs) pulling work in warp-sized chunks from a device-side cursor,
+//     so queue lengths never travel to the host and nearly-empty late bounces cost one tiny launch each;
+//   * SoA float4 ray queues (coalesced 16-byte accesses), hit records of 8 bytes;
+//   * the whole BVH is staged in shared memory when it fits (RTIOW: 485 nodes = 31 KB), else read via L1/L2;
+//   * warp-ballot / popc / shfl compaction with one atomic per warp per destination queue;
+//   * rays binned by material class at the end of extend so that shade warps are (almost) divergence-free;
+//   * Philox4x32-10 keyed (pixel, sample, bounce): no RNG state in memory;
+//   * radiance is written once per path and summed per pixel in sample order by `accumulate` (no float atomics).
+#include "rt_kernels.h"
+#include "rt_traverse.cuh"
+
+__device__ __forceinline__ unsigned lanemask_lt() { unsigned m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+// One warp fetches `chunk` consecutive work items from a device cursor; returns the first index to all lanes.
+__device__ __forceinline__ int warp_fetch(int *cursor, int chunk) {
+    int base = 0;
+    if (lane_id() == 0) base = atomicAdd(cursor, chunk);
+    return __shfl_sync(0xffffffffu, base, 0);
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void flush_counter(unsigned long long *counters, int which, unsigned v) {
+    if (!COUNT) return;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane_id() == 0 && v) atomicAdd(&counters[which], (unsigned long long)v);
+}
+
+// ------------------------------------------------------------------------------------------------
+// pass_init: zero the per-bounce cursors/counters of a pass and publish the length of the bounce-0 queue
+// ------------------------------------------------------------------------------------------------
+__global__ void k_pass_init(Queues q, int max_depth, int n_paths) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i <= max_depth) q.qcount[i] = i == 0 ? n_paths : 0;
+    if (i < max_depth * RT_BIN_STRIDE) q.bincount[i] = 0;
+    if (i < max_depth * 2) q.workctr[i] = 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// generate: one camera path per (pixel, sample) — main.cu:95-99.  Path id = s_local * n_pixels + pixel, so that
+// `accumulate` reads the radiance of one sample index as one contiguous, coalesced plane.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsigned seed, int spp_begin, int n_paths) {
+    const int np = sc.width * sc.height;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_paths; i += gridDim.x * blockDim.x) {
+        const int s_local = i / np, pixel = i - s_local * np;
+        const int y = pixel / sc.width, x = pixel - y * sc.width;
+        Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), 0u, sc.sampling);
+        const float u = ((float)x + rng.next()) / (float)(sc.width - 1);
+        const float v = ((float)y + rng.next()) / (float)(sc.height - 1);
+        float3 o, d;
+        camera_ray(sc.cam, u, v, sc.defocus != 0, rng, o, d);
+        q.ray_o[0][i] = make_float4(o.x, o.y, o.z, __int_as_float(i));
+        q.ray_d[0][i] = make_float4(d.x, d.y, d.z, 0.0f);
+        q.thr[0][i] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// extend: closest hit for every ray of the bounce's queue; bins the queue entry by material class.
+// ------------------------------------------------------------------------------------------------
+template <bool SMEM, bool COUNT, bool SORT>
+__global__ void __launch_bounds__(RT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf) {
+    extern __shared__ float4 s_raw[];
+    const BvhNode *nodes = sc.nodes;
+    if (SMEM) {
+        const float4 *src = reinterpret_cast<const float4 *>(sc.nodes);
+        for (int i = threadIdx.x; i < sc.n_nodes * 4; i += blockDim.x) s_raw[i] = __ldg(&src[i]);
+        __syncthreads();
+        nodes = reinterpret_cast<const BvhNode *>(s_raw);
+    }
+    const int n = q.qcount[bounce];
+    int *cursor = &q.workctr[bounce * 2 + 0];
+    int *bincount = &q.bincount[bounce * RT_BIN_STRIDE];
+    const float4 *__restrict__ ray_o = q.ray_o[buf];
+    const float4 *__restrict__ ray_d = q.ray_d[buf];
+    TravCounters cnt = {};
+    const int CHUNK = 128;
+    for (;;) {
+        const int base = warp_fetch(cursor, CHUNK);
+        if (base >= n) break;
+#pragma unroll 1
+        for (int k = 0; k < CHUNK; k += 32) {
+            const int i = base + k + lane_id();
+            const bool valid = i < n;
+            int bin = -1;
+            if (valid) {
+                const float4 o4 = ray_o[i], d4 = ray_d[i];
+                float t; int code;
+                traverse<COUNT, false>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt);
+                q.hits[i] = make_int2(__float_as_int(t), code);
+                if (SORT) bin = code < 0 ? 0 : 1 + sc.mats[__ldg(&sc.prim_mat[code & RT_LEAF_SLOT_MASK])].type;
+            }
+            if (SORT) {
+                // warp-aggregated append of the queue index to the list of its material class
+#pragma unroll
+                for (int b = 0; b < RT_NUM_BINS; ++b) {
+                    const unsigned m = __ballot_sync(0xffffffffu, bin == b);
+                    if (m) {
+                        int pos = 0;
+                        const int leader = __ffs(m) - 1;
+                        if (lane_id() == leader) pos = atomicAdd(&bincount[b], __popc(m));
+                        pos = __shfl_sync(0xffffffffu, pos, leader);
+                        if (bin == b) q.bins[(long long)b * q.cap + pos + __popc(m & lanemask_lt())] = i;
+                    }
+                }
+            }
+            if (base + k + 32 >= n) break;
+        }
+    }
+    if (COUNT) {
+        flush_counter<COUNT>(q.counters, CTR_BOX, cnt.box); flush_counter<COUNT>(q.counters, CTR_SPH_REJECT, cnt.sph_rej);
+        flush_counter<COUNT>(q.counters, CTR_SPH_ACCEPT, cnt.sph_acc); flush_counter<COUNT>(q.counters, CTR_RECT, cnt.rect);
+        flush_counter<COUNT>(q.counters, CTR_CYL_REJECT, cnt.cyl_rej); flush_counter<COUNT>(q.counters, CTR_CYL_ACCEPT, cnt.cyl_acc);
+        flush_counter<COUNT>(q.counters, CTR_TRI, cnt.tri); flush_counter<COUNT>(q.counters, CTR_BOXPRIM, cnt.boxprim);
+        flush_counter<COUNT>(q.counters, CTR_NODE_VISITS, cnt.nodes); flush_counter<COUNT>(q.counters, CTR_STACK_OVERFLOW, cnt.overflow);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// shade: rebuild the hit record, evaluate emitted/scatter (main.cu:45-63), write the radiance of paths that end,
+// and compact the survivors into the next bounce's queue.  With SORT the work list is the concatenation of the
+// material-class bins (each padded to a warp), so a warp shades one material class.
+// ------------------------------------------------------------------------------------------------
+template <bool COUNT, bool SORT>
+__global__ void __launch_bounds__(RT_BLOCK) k_shade(DScene sc, Queues q, unsigned seed, int spp_begin, int bounce, int buf,
+                                                    int last_bounce) {
+    const int n = q.qcount[bounce];
+    const int np = sc.width * sc.height;
+    int cnt[RT_NUM_BINS], start[RT_NUM_BINS + 1];
+    start[0] = 0;
+#pragma unroll
+    for (int b = 0; b < RT_NUM_BINS; ++b) {
+        cnt[b] = SORT ? q.bincount[bounce * RT_BIN_STRIDE + b] : 0;
+        start[b + 1] = start[b] + ((cnt[b] + 31) & ~31);
+    }
+    const int total = SORT ? start[RT_NUM_BINS] : ((n + 31) & ~31);
+    int *cursor = &q.workctr[bounce * 2 + 1];
+    int *next_count = &q.qcount[bounce + 1];
+    const float4 *__restrict__ ray_o = q.ray_o[buf];
+    const float4 *__restrict__ ray_d = q.ray_d[buf];
+    const float4 *__restrict__ thr_in = q.thr[buf];
+    float4 *__restrict__ out_o = q.ray_o[buf ^ 1];
+    float4 *__restrict__ out_d = q.ray_d[buf ^ 1];
+    float4 *__restrict__ out_thr = q.thr[buf ^ 1];
+    unsigned n_shaded = 0;
+    for (;;) {
+        const int base = warp_fetch(cursor, 32);
+        if (base >= total) break;
+        int i = base + lane_id();
+        bool valid = i < n;
+        if (SORT) {
+            int b = 0;
+#pragma unroll
+            for (int k = 1; k < RT_NUM_BINS; ++k) if (base >= start[k]) b = k;
+            int off = 0, c = 0;
+#pragma unroll
+            for (int k = 0; k < RT_NUM_BINS; ++k) if (k == b) { off = start[k]; c = cnt[k]; }
+            const int kk = base - off + lane_id();
+            valid = kk < c;
+            i = valid ? q.bins[(long long)b * q.cap + kk] : 0;
+        }
+        bool alive = false;
+        float3 no = v3(0, 0, 0), nd = v3(0, 0, 0), nthr = v3(0, 0, 0);
+        int path_id = 0;
+        if (valid) {
+            const float4 o4 = ray_o[i], d4 = ray_d[i], t4 = thr_in[i];
+            const int2 h = q.hits[i];
+            const float3 o = f4xyz(o4), d = f4xyz(d4), thr = f4xyz(t4);
+            path_id = __float_as_int(o4.w);
+            float3 rad = v3(0, 0, 0);
+            if (h.y < 0) {
+                rad = thr * background(sc, d);
+            } else {
+                if (COUNT) n_shaded++;
+                const int type = (unsigned)h.y >> 28, slot = h.y & RT_LEAF_SLOT_MASK;
+                const DMaterial m = sc.mats[__ldg(&sc.prim_mat[slot])];
+                HitRec rec;
+                hit_record(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec);
+                if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
+                    rad = thr * texture_value(sc, m.texture, rec.u, rec.v, rec.p);
+                } else {
+                    const int s_local = path_id / np, pixel = path_id - s_local * np;
+                    Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), (unsigned)bounce + 1u, sc.sampling);
+                    float3 att, sd;
+                    if (scatter(sc, m, d, rec, rng, att, sd) && !last_bounce) {
+                        alive = true;
+                        no = rec.p; nd = sd; nthr = thr * att;
+                    }
+                }
+            }
+            if (!alive) q.radiance[path_id] = make_float4(rad.x, rad.y, rad.z, 0.0f);
+        }
+        // stream compaction: one atomic per warp, survivors written to consecutive slots
+        const unsigned m = __ballot_sync(0xffffffffu, alive);
+        if (m) {
+            int pos = 0;
+            const int leader = __ffs(m) - 1;
+            if (lane_id() == leader) pos = atomicAdd(next_count, __popc(m));
+            pos = __shfl_sync(0xffffffffu, pos, leader) + __popc(m & lanemask_lt());
+            if (alive) {
+                out_o[pos] = make_float4(no.x, no.y, no.z, __int_as_float(path_id));
+                out_d[pos] = make_float4(nd.x, nd.y, nd.z, 0.0f);
+                out_thr[pos] = make_float4(nthr.x, nthr.y, nthr.z, 0.0f);
+            }
+        }
+    }
+    flush_counter<COUNT>(q.counters, CTR_SHADE, n_shaded);
+}
+
+// ------------------------------------------------------------------------------------------------
+// accumulate: accum[pixel] += sum over this pass's samples, in ascending sample order (fixed order => the image is
+// bit-reproducible; replaces the register sum of main.cu:95-104).  One thread per pixel, S coalesced plane reads.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restrict__ radiance, float *__restrict__ accum, int np,
+                                                         int n_samples, int clear, const int *__restrict__ qcount, int max_depth,
+                                                         unsigned long long *total_rays) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {     // rays traced this pass = sum of the per-bounce queue lengths
+        unsigned long long r = 0;
+        for (int b = 0; b < max_depth; ++b) r += (unsigned long long)qcount[b];
+        *total_rays += r;
+    }
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < np; p += gridDim.x * blockDim.x) {
+        float r = 0.0f, g = 0.0f, b = 0.0f;
+        if (!clear) { r = accum[3 * p]; g = accum[3 * p + 1]; b = accum[3 * p + 2]; }
+        for (int s = 0; s < n_samples; ++s) {
+            const float4 c = radiance[(long long)s * np + p];
+            r += c.x; g += c.y; b += c.z;
+        }
+        accum[3 * p] = r; accum[3 * p + 1] = g; accum[3 * p + 2] = b;
+    }
+}
+
+// acc = ((p0 + p1) + p2) + ... : fixed-order combination of per-GPU partial sums
+__global__ void k_sum_ordered(float *__restrict__ accum, const float *const *__restrict__ partials, int n_partials, long long n) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float a = partials[0][i];
+        for (int k = 1; k < n_partials; ++k) a += partials[k][i];
+        accum[i] = a;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// tonemap: write_image (PNG: sum/spp, clamp, x256, no gamma — color.cuh:15-35) or write_color (PPM: sum*(1/spp),
+// sqrt, clamp, x256 — color.cuh:70-95); rows flipped so that row 0 of the output is the top row.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RT_BLOCK) k_tonemap(const float *__restrict__ accum, unsigned char *__restrict__ rgb8, int W,
+                                                      int H, int spp, int gamma) {
+    const int n = W * H * 3;
+    const float fspp = (float)spp, scale = 1.0f / fspp;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int c = i % 3, px = i / 3, row = px / W, col = px - row * W;
+        float x = accum[3 * ((H - 1 - row) * W + col) + c];
+        x = gamma ? sqrtf(x * scale) : x / fspp;
+        x = x < 0.0f ? 0.0f : (x > 0.999f ? 0.999f : x);
+        rgb8[i] = (unsigned char)(int)(256.0f * x);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// aov: the deterministic path — pixel-centre primary ray, first hit through the same traversal and hit-record code,
+// albedo / emission / background colour; 24 floats per pixel (layout: DESIGN.md §6).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RT_BLOCK) k_aov(DScene sc, float *__restrict__ out) {
+    const int np = sc.width * sc.height;
+    TravCounters cnt = {};
+    for (int pixel = blockIdx.x * blockDim.x + threadIdx.x; pixel < np; pixel += gridDim.x * blockDim.x) {
+        const int y = pixel / sc.width, x = pixel - y * sc.width;
+        const float u = ((float)x + 0.5f) / (float)(sc.width - 1), v = ((float)y + 0.5f) / (float)(sc.height - 1);
+        Rng rng; rng.init(0, 0, 0, 0, sc.sampling);
+        float3 o, d;
+        camera_ray(sc.cam, u, v, false, rng, o, d);
+        float t; int code;
+        traverse<false, false>(sc, sc.nodes, o, d, 0.001f, FLT_MAX, t, code, cnt);
+        float q[24];
+#pragma unroll
+        for (int k = 0; k < 24; ++k) q[k] = 0.0f;
+        if (code >= 0) {
+            const int type = (unsigned)code >> 28, slot = code & RT_LEAF_SLOT_MASK;
+            const int mi = sc.prim_mat[slot];
+            const DMaterial m = sc.mats[mi];
+            HitRec rec;
+            hit_record(sc, type, slot, o, d, t, true, rec);
+            q[0] = 1.0f; q[1] = rec.t; q[2] = rec.p.x; q[3] = rec.p.y; q[4] = rec.p.z;
+            q[5] = rec.n.x; q[6] = rec.n.y; q[7] = rec.n.z; q[8] = (float)rec.front; q[9] = rec.u; q[10] = rec.v;
+            q[11] = (float)sc.prim_obj[slot]; q[12] = (float)mi;
+            float3 att = v3(0, 0, 0), E = v3(0, 0, 0);
+            bool ok = false;
+            if (m.type == RT_MAT_DIFFUSE_LIGHT) E = texture_value(sc, m.texture, rec.u, rec.v, rec.p);
+            else {
+                // fixed uniforms 0.5,0.5,0.5,... as in the oracle/reference harness: only `att` and `ok` are recorded
+                FixedRng fr;
+                float3 sd;
+                ok = scatter(sc, m, d, rec, fr, att, sd);
+            }
+            q[13] = att.x; q[14] = att.y; q[15] = att.z; q[16] = E.x; q[17] = E.y; q[18] = E.z; q[22] = ok ? 1.0f : 0.0f;
+        } else {
+            const float3 b = background(sc, d);
+            q[19] = b.x; q[20] = b.y; q[21] = b.z;
+        }
+#pragma unroll
+        for (int k = 0; k < 24; ++k) out[(long long)pixel * 24 + k] = q[k];
+    }
+}
+
+// ================================================================================================
+// host launchers
+// ================================================================================================
+static inline int persistent_grid(const LaunchCfg &c, int per_sm) { return c.num_sms * per_sm; }
+static inline void bump(const LaunchCfg &c) { if (c.launches) ++*c.launches; }
+
+void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_paths) {
+    int n = max_depth * RT_BIN_STRIDE + 1;
+    k_pass_init<<<(n + 255) / 256, 256, 0, c.stream>>>(q, max_depth, n_paths);
+    bump(c);
+}
+
+void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths) {
+    long long blocks = ((long long)n_paths + RT_BLOCK - 1) / RT_BLOCK;
+    int grid = (int)(blocks < (long long)c.num_sms * 16 ? blocks : (long long)c.num_sms * 16);
+    k_generate<<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, n_paths);
+    bump(c);
+}
+
+template <bool SMEM>
+static void launch_extend_t(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort) {
+    const int grid = persistent_grid(c, c.extend_blocks_per_sm);
+    const size_t sm = SMEM ? c.bvh_smem_bytes : 0;
+    if (count) {
+        if (sort) k_extend<SMEM, true, true><<<grid, RT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf);
+        else k_extend<SMEM, true, false><<<grid, RT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf);
+    } else {
+        if (sort) k_extend<SMEM, false, true><<<grid, RT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf);
+        else k_extend<SMEM, false, false><<<grid, RT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf);
+    }
+}
+
+void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort) {
+    if (c.bvh_smem_bytes) launch_extend_t<true>(c, sc, q, bounce, buf, count, sort);
+    else launch_extend_t<false>(c, sc, q, bounce, buf, count, sort);
+    bump(c);
+}
+
+cudaError_t extend_configure_smem(size_t smem_bytes) {
+    cudaError_t e = cudaSuccess;
+#define SET(K) if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes)
+    SET((k_extend<true, false, true>)); SET((k_extend<true, false, false>)); SET((k_extend<true, true, true>)); SET((k_extend<true, true, false>));
+#undef SET
+    return e;
+}
+
+int extend_max_blocks_per_sm(size_t smem_bytes) {
+    int nb = 0;
+    if (smem_bytes) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<true, false, true>, RT_BLOCK, smem_bytes);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<false, false, true>, RT_BLOCK, 0);
+    return nb;
+}
+
+void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
+                  bool last_bounce, bool count, bool sort) {
+    const int grid = persistent_grid(c, 4);
+    if (count) {
+        if (sort) k_shade<true, true><<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce);
+        else k_shade<true, false><<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce);
+    } else {
+        if (sort) k_shade<false, true><<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce);
+        else k_shade<false, false><<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce);
+    }
+    bump(c);
+}
+
+void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int np, int n_samples, bool clear, int max_depth,
+                       unsigned long long *total_rays) {
+    int blocks = (np + RT_BLOCK - 1) / RT_BLOCK;
+    k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, accum, np, n_samples, clear ? 1 : 0, q.qcount, max_depth, total_rays);
+    bump(c);
+}
+
+void launch_sum_ordered(const LaunchCfg &c, float *accum, const float *const *partials_dev, int n_partials, long long n) {
+    k_sum_ordered<<<persistent_grid(c, 8), RT_BLOCK, 0, c.stream>>>(accum, partials_dev, n_partials, n);
+    bump(c);
+}
+
+void launch_tonemap(const LaunchCfg &c, const float *accum, unsigned char *rgb8, int W, int H, int spp, int gamma) {
+    k_tonemap<<<persistent_grid(c, 8), RT_BLOCK, 0, c.stream>>>(accum, rgb8, W, H, spp, gamma);
+    bump(c);
+}
+
+void launch_aov(const LaunchCfg &c, const DScene &sc, float *out) {
+    int np = sc.width * sc.height;
+    k_aov<<<(np + RT_BLOCK - 1) / RT_BLOCK, RT_BLOCK, 0, c.stream>>>(sc, out);
+    bump(c);
+}

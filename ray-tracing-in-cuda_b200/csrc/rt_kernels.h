@@ -1,0 +1,47 @@
+// rt_kernels.h — host-callable launchers of the device kernels (rt_kernels.cu, rt_lbvh.cu).
+#pragma once
+#include "rt_wavefront.cuh"
+
+struct LaunchCfg {
+    cudaStream_t stream;
+    int num_sms;
+    int extend_blocks_per_sm;     // resident CTAs per SM for the extend kernel (depends on the smem BVH copy)
+    size_t bvh_smem_bytes;        // 0: traverse from global memory
+    long long *launches;          // counter of kernels launched (rt_stats.launches)
+};
+
+void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_paths);
+void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths);
+void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort);
+void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
+                  bool last_bounce, bool count, bool sort);
+void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int np, int n_samples, bool clear, int max_depth,
+                       unsigned long long *total_rays);
+void launch_sum_ordered(const LaunchCfg &c, float *accum, const float *const *partials_dev, int n_partials, long long n);
+void launch_tonemap(const LaunchCfg &c, const float *accum, unsigned char *rgb8, int W, int H, int spp, int gamma);
+void launch_aov(const LaunchCfg &c, const DScene &sc, float *out);
+int extend_max_blocks_per_sm(size_t smem_bytes);
+cudaError_t extend_configure_smem(size_t smem_bytes);
+
+// ---- LBVH build (rt_lbvh.cu) ----
+struct DObject { int type, material, xform, pad; float p[12]; };   // = rt_object_desc
+
+struct LbvhBuffers {                // all device pointers, sized for n objects
+    int n;
+    const DObject *objects;
+    const float4 *xforms;           // 6 float4 per transform
+    float *obj_bmin, *obj_bmax;     // 3 floats per object (unpadded boxes)
+    unsigned *bounds;               // 12 ordered-uint words: scene min/max, centroid min/max
+    unsigned long long *keys[2];    // Morton keys, ping-pong
+    int *vals[2];                   // object indices, ping-pong
+    unsigned *hist;                 // radix histograms: 256 * n_tiles
+    int *left, *right, *parent;     // Karras topology (n-1, n-1, 2n-1)
+    int *flags;                     // refit arrival counters (n-1)
+    float *node_aabb, *leaf_aabb;   // 6 floats per internal node / per sorted leaf
+    // outputs consumed by traversal
+    BvhNode *nodes;
+    float4 *primA, *primB, *primC;
+    int *prim_obj, *prim_mat;
+};
+void lbvh_build(const LaunchCfg &c, LbvhBuffers &b);
+size_t lbvh_hist_words(int n);

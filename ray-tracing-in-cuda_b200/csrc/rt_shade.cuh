@@ -1,0 +1,134 @@
+// rt_shade.cuh — textures, materials, camera rays and miss colour as device functions.
+// Same operation order as oracle/orc_render.c; reference citations per function.
+#pragma once
+#include "rt_scene.cuh"
+
+// texture.cuh:24-27 (solid), 44-52 (checker); image: CUDA texture unit, point sampling, unnormalised coordinates
+__device__ __forceinline__ float3 texture_value(const DScene &sc, int tex, float u, float v, float3 p) {
+#pragma unroll 1
+    for (int guard = 0; guard < 8; ++guard) {
+        const DTexture t = sc.texs[tex];
+        if (t.type == RT_TEX_SOLID) return f4xyz(t.color);
+        if (t.type == RT_TEX_CHECKER) {
+            float sines = rt_sinf(10.0f * p.x) * rt_sinf(10.0f * p.y) * rt_sinf(10.0f * p.z);
+            tex = sines < 0.0f ? t.odd : t.even;
+            continue;
+        }
+        if (t.type == RT_TEX_IMAGE) {
+            const DImage im = sc.images[t.image];
+            float uu = u < 0.0f ? 0.0f : (u > 1.0f ? 1.0f : u);
+            float vv = 1.0f - (v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v));
+            int i = (int)(uu * (float)im.width), j = (int)(vv * (float)im.height);
+            if (i >= im.width) i = im.width - 1;
+            if (j >= im.height) j = im.height - 1;
+            // texel centre (i+0.5, j+0.5): the texture unit fetches texel (i, j); uchar4 -> float in [0,1] (= b/255)
+            float4 c = tex2D<float4>(im.tex, (float)i + 0.5f, (float)j + 0.5f);
+            return v3(c.x, c.y, c.z);
+        }
+        break;
+    }
+    return v3(0, 0, 0);
+}
+
+// replayed uniforms for the deterministic AOV pass (same sequence as the oracle and the reference harness)
+struct FixedRng {
+    int pos = 0;
+    __device__ __forceinline__ float next() {
+        const int k = pos++ & 7;
+        return k < 3 ? 0.5f : (k < 6 ? 0.25f : 0.1f);
+    }
+};
+
+// random_in_unit_sphere: vec3.cuh:133-141 (octant, (0,1] uniforms) | cmake-cpu-version/vec3.h:121-129 (full cube)
+template <class R>
+__device__ __forceinline__ float3 random_in_unit_sphere(R &rng, int sampling) {
+    for (;;) {
+        float a = rng.next(), b = rng.next(), c = rng.next();
+        float3 p = sampling == RT_SAMPLING_REFERENCE_GPU ? v3(a, b, c)
+                                                         : v3(__fmaf_rn(2.0f, a, -1.0f), __fmaf_rn(2.0f, b, -1.0f), __fmaf_rn(2.0f, c, -1.0f));
+        if (dot3(p, p) >= 1.0f) continue;
+        return p;
+    }
+}
+
+__device__ __forceinline__ float3 reflect3(float3 v, float3 n) {   // vec3.cuh:121-123
+    float k = 2.0f * dot3(v, n);
+    return v3(__fmaf_rn(-k, n.x, v.x), __fmaf_rn(-k, n.y, v.y), __fmaf_rn(-k, n.z, v.z));
+}
+
+// material::scatter for the four material classes (material.cuh:37-52, 63-70, 130-158, 169-173).
+// Returns false when the path ends here.  att: attenuation; sd: scattered direction (origin is rec.p).
+template <class R>
+__device__ __forceinline__ bool scatter(const DScene &sc, const DMaterial &m, float3 rd, const HitRec &rec, R &rng,
+                                        float3 &att, float3 &sd) {
+    switch (m.type) {
+    case RT_MAT_LAMBERTIAN: {
+        float3 r = random_in_unit_sphere(rng, sc.sampling);
+        if (sc.sampling == RT_SAMPLING_REFERENCE_CPU) r = vunit(r);     // random_unit_vector (material.h:27)
+        float3 dir = rec.n + r;
+        if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = rec.n;
+        sd = dir;
+        att = texture_value(sc, m.texture, rec.u, rec.v, rec.p);
+        return true;
+    }
+    case RT_MAT_METAL: {
+        float3 refl = reflect3(vunit(rd), rec.n);
+        float3 r = random_in_unit_sphere(rng, sc.sampling);
+        sd = vfma(m.fuzz, r, refl);
+        att = f4xyz(m.albedo);
+        return dot3(sd, rec.n) > 0.0f;
+    }
+    case RT_MAT_DIELECTRIC: {
+        att = v3(1.0f, 1.0f, 1.0f);
+        float ratio = rec.front ? (1.0f / m.ior) : m.ior;
+        float3 ud = vunit(rd);
+        float cos_theta = fminf(-dot3(ud, rec.n), 1.0f);
+        float sin_theta = sqrtf(__fmaf_rn(-cos_theta, cos_theta, 1.0f));
+        bool do_reflect = ratio * sin_theta > 1.0f;
+        if (!do_reflect) {
+            float r0 = (1.0f - ratio) / (1.0f + ratio);
+            r0 = r0 * r0;
+            float x = 1.0f - cos_theta, x2 = x * x;
+            float refl = __fmaf_rn(1.0f - r0, x2 * x2 * x, r0);
+            do_reflect = refl > rng.next();
+        }
+        if (do_reflect) sd = reflect3(ud, rec.n);
+        else {
+            float3 perp = ratio * vfma(cos_theta, rec.n, ud);
+            float k = -sqrtf(fabsf(1.0f - dot3(perp, perp)));
+            sd = vfma(k, rec.n, perp);
+        }
+        return true;
+    }
+    default:
+        att = v3(0, 0, 0); sd = v3(0, 0, 0);
+        return false;
+    }
+}
+
+// miss colour: constant background (main.cu:61-63) or the RTIOW sky gradient (cmake-cpu-version/main.cpp:36-38)
+__device__ __forceinline__ float3 background(const DScene &sc, float3 d) {
+    if (sc.bg_mode == RT_BG_SKY_GRADIENT) {
+        float3 ud = vunit(d);
+        float t = 0.5f * (ud.y + 1.0f), w = 1.0f - t;
+        return v3(__fmaf_rn(t, 0.5f, w), __fmaf_rn(t, 0.7f, w), __fmaf_rn(t, 1.0f, w));
+    }
+    return sc.background;
+}
+
+// camera::get_ray, camera.cuh:31-39 (no lens) / cmake-cpu-version/camera.h:32-39 (thin lens)
+__device__ __forceinline__ void camera_ray(const DCamera &cam, float s, float t, bool defocus, Rng &rng, float3 &o, float3 &d) {
+    float rx = 0.0f, ry = 0.0f;
+    if (defocus) {
+        for (;;) {
+            float px = __fmaf_rn(2.0f, rng.next(), -1.0f), py = __fmaf_rn(2.0f, rng.next(), -1.0f);
+            if (__fmaf_rn(py, py, px * px) >= 1.0f) continue;
+            rx = cam.lens_radius * px; ry = cam.lens_radius * py;
+            break;
+        }
+    }
+    float3 off = v3(__fmaf_rn(cam.v.x, ry, cam.u.x * rx), __fmaf_rn(cam.v.y, ry, cam.u.y * rx), __fmaf_rn(cam.v.z, ry, cam.u.z * rx));
+    o = cam.origin + off;
+    float3 a = vfma(t, cam.vertical, vfma(s, cam.horizontal, cam.llc));
+    d = (a - cam.origin) - off;
+}

@@ -1,0 +1,27 @@
+// rt_wavefront.cuh — queue layout shared by the wavefront kernels and the host-side pass loop.
+#pragma once
+#include "rt_shade.cuh"
+
+#define RT_NUM_BINS 5          // miss, lambertian, metal, dielectric, diffuse_light
+#define RT_BIN_STRIDE 8
+#define RT_TRAV_STACK 64
+#define RT_BLOCK 256
+
+// event counters (rt_stats, SURVEY.md §8(d) flop model)
+enum { CTR_BOX = 0, CTR_SPH_REJECT, CTR_SPH_ACCEPT, CTR_RECT, CTR_CYL_REJECT, CTR_CYL_ACCEPT, CTR_TRI, CTR_BOXPRIM,
+       CTR_SHADE, CTR_GENERATE, CTR_NODE_VISITS, CTR_STACK_OVERFLOW, CTR_COUNT = 16 };
+
+// SoA ray queues: every per-ray field is one float4 array, read and written with coalesced 16-byte accesses.
+struct Queues {
+    float4 *ray_o[2];      // origin.xyz, path id (int bits)            — ping-pong between bounces
+    float4 *ray_d[2];      // direction.xyz (unnormalised, as the reference keeps it), unused
+    float4 *thr[2];        // throughput rgb, unused
+    int2 *hits;            // (t bits, leaf code or -1) per queue entry, written by extend, read by shade
+    int *bins;             // RT_NUM_BINS index lists of capacity `cap` each: queue entries grouped by material class
+    float4 *radiance;      // per path id: the radiance this sample contributes (written exactly once)
+    int *qcount;           // [max_depth + 1] queue length per bounce
+    int *bincount;         // [max_depth][RT_BIN_STRIDE]
+    int *workctr;          // [max_depth][2] dynamic work-fetch cursors (extend, shade)
+    unsigned long long *counters;   // [CTR_COUNT]
+    long long cap;
+};

@@ -33,7 +33,7 @@ def lib():
         L.orc_aov.argtypes = [P(capi.SceneDesc), fp]
         L.orc_tonemap.argtypes = [fp, C.c_int, C.c_int, C.c_int, C.c_int, P(C.c_ubyte)]
         L.orc_tonemap.restype = None
-        L.orc_make_xform.argtypes = [fp, C.c_float, C.c_int, fp, C.c_int, P(capi.XformDesc)]
+        L.orc_make_xform.argtypes = [fp, C.c_double, C.c_int, fp, C.c_int, P(capi.XformDesc)]
         L.orc_make_xform.restype = None
         L.orc_philox4x32_10.argtypes = [P(C.c_uint32), P(C.c_uint32), P(C.c_uint32)]
         L.orc_philox4x32_10.restype = None

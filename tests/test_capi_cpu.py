@@ -1,0 +1,93 @@
+"""CPU tests of the drop-in boundary: librt_b200.so loads without a GPU, exports every symbol include/rt.h declares,
+fails loudly (no CPU fallback) when there is no device, and its host-side image writers/reader are correct."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import __graft_entry__ as ge
+from rt_b200 import Renderer, RtError, animation, capi, renderer
+
+ROOT = ge.ROOT
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(capi.LIB_PATH):
+        ge.build()
+    return capi.load_library()
+
+
+def test_header_and_library_export_the_same_symbols(lib):
+    hdr = open(os.path.join(ROOT, "include", "rt.h")).read()
+    declared = set(re.findall(r"^(?:int|void|const char \*)\s*(rt_[a-z0-9_]+)\(", hdr, re.M))
+    assert declared == set(capi.RT_SYMBOLS), declared ^ set(capi.RT_SYMBOLS)
+    for name in declared:
+        assert getattr(lib, name) is not None
+    assert lib.rt_abi_version() == 1
+
+
+def test_struct_layouts_match_header():
+    assert C.sizeof(capi.ObjectDesc) == 64 and C.sizeof(capi.XformDesc) == 96
+    assert C.sizeof(capi.MaterialDesc) == 32 and C.sizeof(capi.TextureDesc) == 32
+    assert C.sizeof(capi.CameraDesc) == 52 and C.sizeof(capi.RenderParams) == 24
+
+
+def test_no_device_is_an_error_not_a_fallback(lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(RtError, match="no CUDA device"):
+        Renderer(0)
+
+
+def test_product_never_references_the_oracle():
+    """The product tree must not include, link or load anything under oracle/."""
+    pkg = os.path.join(ROOT, "ray-tracing-in-cuda_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".cu", ".cuh", ".cpp", ".h", ".py")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "liboracle" not in text and not re.search(r'#include\s+"[^"]*(oracle|orc_)', text), f
+                assert not re.search(r"^\s*(import|from)\s+orc\b", text, re.M), f
+    out = os.popen(f"ldd {capi.LIB_PATH}").read()
+    assert "oracle" not in out
+
+
+def test_png_and_ppm_writers(lib, tmp_path):
+    from PIL import Image
+    rng = np.random.default_rng(0)
+    img = rng.integers(0, 256, (37, 53, 3), dtype=np.uint8)
+    renderer.write_png(str(tmp_path / "x.png"), img)
+    renderer.write_ppm(str(tmp_path / "x.ppm"), img)
+    assert np.array_equal(np.asarray(Image.open(tmp_path / "x.png")), img)
+    assert np.array_equal(np.asarray(Image.open(tmp_path / "x.ppm")), img)
+    assert np.array_equal(renderer.read_png(str(tmp_path / "x.png")), img)
+    # PPM is the reference's P3 text layout (color.cuh:70-95): header then one "r g b" line per pixel, top row first
+    lines = open(tmp_path / "x.ppm").read().split("\n")
+    assert lines[:3] == ["P3", "53 37", "255"] and lines[3] == " ".join(map(str, img[0, 0]))
+    # reader handles PIL-written RGBA / grey / palette / filtered PNGs
+    for mode in ("RGBA", "L", "P"):
+        Image.fromarray(img).convert(mode).save(tmp_path / f"m_{mode}.png", optimize=True)
+        want = np.asarray(Image.open(tmp_path / f"m_{mode}.png").convert("RGB"))
+        assert np.array_equal(renderer.read_png(str(tmp_path / f"m_{mode}.png")), want)
+    with pytest.raises(RtError):
+        renderer.read_png(str(tmp_path / "missing.png"))
+
+
+def test_animation_rules_follow_the_reference_scripts():
+    import json
+    basic = json.load(open(os.path.join(ROOT, "tests", "golden", "basic_scene.json")))
+    f0 = animation.dna_frame(basic, 0)
+    assert f0 == json.load(open(os.path.join(ROOT, "tests", "golden", "dna_000.json")))   # golden was made from dna.py's rules
+    assert len(f0["object"]["data"]) == 90 and len(f0["material"]["data"]) == 90 and len(f0["texture"]["data"]) == 90
+    f7 = animation.dna_frame(basic, 7)
+    assert f7["object"]["data"][2]["rotate"]["angle"] == 90 + 7 and f7["output_file"].endswith("output_007.png")
+    blue2 = json.load(open(os.path.join(ROOT, "tests", "golden", "blue2.json")))
+    g = animation.blue2_frame(blue2, 3)      # blue2.py: +2 degrees per frame, applied before the frame is written
+    cyl = [o for o in g["object"]["data"] if o["type"] == "cylinder"]
+    base = [o for o in blue2["object"]["data"] if o["type"] == "cylinder"]
+    assert [c["rotate"]["angle"] for c in cyl] == [b["rotate"]["angle"] + 8 for b in base]
+    assert animation.frames_for_rank(20, 3, 8) == [3, 11, 19]

@@ -1,0 +1,250 @@
+"""GPU parity tests (-m gpu): the CUDA wavefront renderer, called through the C ABI (librt_b200.so), against the
+CPU oracle on the same seeded inputs, and against the golden vectors made from the real reference.
+
+Bars: integer work (LBVH keys / order / topology, ray counts) bit-exact; float radiance within 1e-5 per sample
+(the north star's deterministic-path tolerance; in practice the images are bit-identical because both sides follow
+the same fma contract); converged renders within Monte-Carlo noise of the reference's own images."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import orc
+from rt_b200 import Renderer, RtError, capi, renderer
+
+pytestmark = pytest.mark.gpu
+SCENES = ["sample_scene", "blue", "blue2", "dna_000", "rtiow_486"]
+G = orc.GOLDEN
+
+
+@pytest.fixture(scope="module")
+def rt():
+    r = Renderer(0)
+    yield r
+    r.close()
+
+
+def scene_path(name):
+    return f"{G}/{name}.json"
+
+
+@pytest.mark.parametrize("name", SCENES + ["basic_scene"])
+def test_lbvh_bit_exact(rt, name):
+    """GPU LBVH build vs the host twin: Morton keys, sorted order, Karras child/parent links bit-exact; boxes equal."""
+    rt.upload_json(scene_path(name))
+    got = rt.bvh()
+    want = orc.lbvh(orc.load_scene(scene_path(name)))
+    n = got["n"]
+    if n == 0:
+        return
+    assert np.array_equal(got["morton"], want["morton"])
+    assert np.array_equal(got["prim"], want["prim"])
+    assert np.array_equal(got["scene_aabb"], want["scene_aabb"])
+    assert np.array_equal(got["leaf_aabb"], want["leaf_aabb"])
+    if n >= 2:
+        for k in ("left", "right", "parent"):
+            assert np.array_equal(got[k], want[k]), k
+        assert np.array_equal(got["node_aabb"], want["node_aabb"])
+
+
+def random_scene(rng, n, with_ext=True):
+    """Seeded scene mixing every primitive type (incl. duplicates => equal Morton codes and exact-tie hits)."""
+    objs, mats, texs = [], [], []
+    texs.append({"type": "solid_color", "color": [0.8, 0.3, 0.3]})
+    texs.append({"type": "solid_color", "color": [4, 4, 4]})
+    texs.append({"type": "solid_color", "color": [0.2, 0.3, 0.1]})
+    texs.append({"type": "checker", "even": 0, "odd": 2})
+    mats += [{"type": "lambertian", "texture": 0}, {"type": "lambertian", "texture": 3},
+             {"type": "metal", "albedo": [0.7, 0.6, 0.5], "fuzz": 0.2}, {"type": "dielectric", "index_of_refraction": 1.5},
+             {"type": "diffuse_light", "texture": 1}]
+    kinds = ["sphere", "xy_rect", "xz_rect", "yz_rect", "cylinder"] + (["box", "triangle"] if with_ext else [])
+    for i in range(n):
+        k = kinds[int(rng.integers(len(kinds)))]
+        c = rng.uniform(-4, 4, 3).round(3).tolist()
+        m = int(rng.integers(len(mats)))
+        if k == "sphere":
+            o = {"type": k, "center": c, "radius": float(np.round(rng.uniform(0.2, 0.9), 3)) * (-1 if rng.random() < 0.1 else 1)}
+        elif k.endswith("rect"):
+            a, b = k[0], k[1]
+            o = {"type": k, a + "0": c[0] - 1, a + "1": c[0] + 1, b + "0": c[1] - 0.7, b + "1": c[1] + 0.7, "k": c[2]}
+        elif k == "cylinder":
+            o = {"type": k, "radius": 0.4, "zmin": -0.8, "zmax": 0.8, "translate": c,
+                 "rotate": {"axis": rng.normal(size=3).round(3).tolist(), "angle": float(rng.uniform(0, 360))}}
+        elif k == "box":
+            o = {"type": k, "min": [-0.5, -0.4, -0.3], "max": [0.5, 0.4, 0.3], "translate": c}
+            if rng.random() < 0.7:
+                o["rotate"] = {"axis": [0, 1, 0], "angle": float(rng.uniform(0, 90))}
+        else:
+            v = (np.array(c) + rng.normal(size=(3, 3))).round(3)
+            o = {"type": k, "v0": v[0].tolist(), "v1": v[1].tolist(), "v2": v[2].tolist()}
+        o["material"] = m
+        objs.append(o)
+        if rng.random() < 0.08:           # exact duplicate with another material: equal t => "last index wins"
+            d = dict(o); d["material"] = int(rng.integers(len(mats))); objs.append(d)
+    return {"background": [0.5, 0.7, 0.99], "max_depth": 12, "samples_per_pixel": 4, "width": 80, "height": 45,
+            "camera": {"lookfrom": [0, 2, 14], "lookat": [0, 0, 0], "vup": [0, 1, 0], "vfov": 40, "aperture": 0.1},
+            "object": {"data": objs}, "material": {"data": mats}, "texture": {"data": texs}}
+
+
+@pytest.mark.parametrize("n,seed", [(1, 1), (2, 2), (3, 3), (40, 4), (700, 5), (5000, 6)])
+def test_lbvh_bit_exact_random(rt, n, seed):
+    sc = random_scene(np.random.default_rng(seed), n)
+    rt.upload_json_text(json.dumps(sc))
+    got = rt.bvh()
+    want = orc.lbvh(orc.load_scene(sc))
+    assert got["n"] == len(sc["object"]["data"])
+    for k in ("morton", "prim", "leaf_aabb", "scene_aabb"):
+        assert np.array_equal(got[k], want[k]), k
+    if got["n"] >= 2:
+        for k in ("left", "right", "parent", "node_aabb"):
+            assert np.array_equal(got[k], want[k]), k
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_aov_matches_oracle_and_reference(rt, name):
+    """Deterministic path (pixel-centre primary rays, first hit): CUDA == oracle on every field, and the colour channels
+    are within 1e-5 of the REAL reference's output (golden)."""
+    ref = np.load(f"{G}/aov_{name}.npz")["aov"]
+    H, W, _ = ref.shape
+    rt.upload_json(scene_path(name))
+    rt.override(width=W, height=H)
+    got = rt.render_aov()
+    want = orc.aov(orc.load_scene(scene_path(name), width=W, height=H))
+    assert np.array_equal(got[..., 0], want[..., 0]) and np.array_equal(got[..., 11], want[..., 11]), "BVH traversal != linear walk"
+    assert np.abs(got - want).max() <= 1e-5 * max(1.0, np.abs(want).max())
+    same = (got[..., 0] == ref[..., 0]) & (got[..., 11] == ref[..., 11])
+    assert (~same).sum() <= (5 if name == "rtiow_486" else 0)
+    assert np.abs(got[..., 13:22] - ref[..., 13:22])[same].max() <= 1e-5
+
+
+@pytest.mark.parametrize("name,spp", [("sample_scene", 8), ("blue", 4), ("blue2", 8), ("dna_000", 4), ("rtiow_486", 8), ("basic_scene", 3)])
+def test_render_matches_oracle_sample_for_sample(rt, name, spp):
+    """Full path tracing, same Philox streams: per-pixel radiance sums within 1e-5 per sample of the brute-force oracle,
+    and exactly the same number of path segments."""
+    W, H = 96, 54
+    rt.upload_json(scene_path(name))
+    rt.override(width=W, height=H, spp=spp)
+    rt.stats_reset()
+    rt.render(seed=0x2023)
+    got, _, st = rt.download()
+    want, nrays = orc.render(orc.load_scene(scene_path(name), width=W, height=H, spp=spp), seed=0x2023)
+    assert st["rays"] == nrays
+    err = np.abs(got - want)
+    bad = (err > 1e-5 * spp).any(-1).sum()
+    assert bad == 0, f"{bad} pixels differ, max {err.max()}"
+
+
+def test_render_options_do_not_change_the_image(rt):
+    """Material sorting, pass size, split sample ranges and event counting change scheduling only: images are bit-identical."""
+    W, H, spp = 64, 36, 6
+    rt.upload_json(scene_path("blue2"))
+    rt.override(width=W, height=H, spp=spp)
+    rt.render(seed=5)
+    base, _, _ = rt.download()
+    rt.render(seed=5, flags=capi.RT_RENDER_NO_SORT)
+    assert np.array_equal(rt.download()[0], base)
+    rt.render(seed=5, max_paths_per_pass=W * H * 2)
+    assert np.array_equal(rt.download()[0], base)
+    rt.render(seed=5, flags=capi.RT_RENDER_COUNT_EVENTS)
+    img, _, st = rt.download()
+    assert np.array_equal(img, base) and st["n_box_tests"] > 0 and st["n_shade"] > 0
+    rt.render(seed=5, spp_begin=0, spp_count=4)
+    rt.render(seed=5, spp_begin=4, spp_count=2, flags=capi.RT_RENDER_KEEP_ACCUM)
+    assert np.array_equal(rt.download()[0], base)
+    rt.render(seed=6)
+    assert not np.array_equal(rt.download()[0], base)
+
+
+@pytest.mark.parametrize("seed", [11, 12])
+def test_random_scenes_all_primitives(rt, seed):
+    """Every primitive type incl. box/triangle extensions, duplicates (exact ties) and negative radii vs the oracle."""
+    sc = random_scene(np.random.default_rng(seed), 60)
+    rt.upload_json_text(json.dumps(sc))
+    got_aov = rt.render_aov()
+    osc = orc.load_scene(sc)
+    want_aov = orc.aov(osc)
+    assert np.array_equal(got_aov[..., 11], want_aov[..., 11]), "closest-hit object differs (tie rule?)"
+    assert np.abs(got_aov - want_aov).max() <= 1e-5 * max(1.0, np.abs(want_aov).max())
+    rt.stats_reset()
+    rt.render(seed=3)
+    got, _, st = rt.download()
+    want, nrays = orc.render(osc, seed=3)
+    assert st["rays"] == nrays
+    assert np.abs(got - want).max() <= 1e-5 * sc["samples_per_pixel"]
+
+
+def test_json_reader_equals_table_upload(rt):
+    """rt_scene_upload_json (C++ reader) and rt_scene_upload (tables from the independent Python loader) agree bit for bit."""
+    for name in ("sample_scene", "blue2"):
+        rt.upload_json(scene_path(name)); rt.override(width=64, height=36, spp=2); rt.render(seed=9)
+        a = rt.download()[0]
+        rt.upload(orc.load_scene(scene_path(name), width=64, height=36, spp=2)); rt.render(seed=9)
+        b = rt.download()[0]
+        assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("name", ["sample_scene", "blue2", "dna_000", "rtiow_486"])
+def test_converged_against_reference(rt, name):
+    """Converged render at the golden's spp vs the REAL reference's two independent converged images:
+    RMSE <= 1.5 x the reference's own run-to-run RMSE; PSNR reported."""
+    g = np.load(f"{G}/conv_{name}.npz")
+    a, b, spp = g["a"], g["b"], int(g["spp"])
+    H, W, _ = a.shape
+    rt.upload_json(scene_path(name)); rt.override(width=W, height=H, spp=spp)
+    rt.render(seed=77)
+    img = rt.download()[0] / spp
+
+    def rmse(x, y):
+        return float(np.sqrt(np.mean((x - y) ** 2)))
+    noise = rmse(a, b)
+    assert rmse(img, a) < 1.5 * noise and rmse(img, b) < 1.5 * noise
+    ref_mean = 0.5 * (a + b)
+    psnr = 10 * np.log10(1.0 / max(np.mean((np.clip(img, 0, 1) - np.clip(ref_mean, 0, 1)) ** 2), 1e-12))
+    print(f"{name}: rmse={rmse(img, ref_mean):.5f} noise={noise:.5f} psnr={psnr:.1f} dB")
+    assert psnr > 30.0
+
+
+def test_full_size_properties(rt):
+    """BASELINE-size properties that need no oracle: the literal basic_scene.json (0 objects) at 1920x1080 must give
+    exactly spp * background in every pixel; sample-range linearity holds at full size on blue2."""
+    rt.upload_json(scene_path("basic_scene")); rt.override(width=1920, height=1080, spp=16)
+    rt.stats_reset(); rt.render(seed=1)
+    img, _, st = rt.download()
+    bg = np.array([0.0005, 0.0007, 0.00099], np.float32)
+    want = np.zeros(3, np.float32)
+    for _ in range(16):
+        want = want + bg
+    assert np.array_equal(img, np.broadcast_to(want, img.shape)) and st["rays"] == 1920 * 1080 * 16
+    rt.upload_json(scene_path("blue2")); rt.override(spp=4)
+    rt.render(seed=2)
+    full = rt.download()[0]
+    rt.render(seed=2, spp_begin=0, spp_count=2); rt.render(seed=2, spp_begin=2, spp_count=2, flags=capi.RT_RENDER_KEEP_ACCUM)
+    assert np.array_equal(rt.download()[0], full)
+    assert np.isfinite(full).all() and full.min() >= 0
+
+
+def test_tonemap_and_image_writers(rt, tmp_path):
+    rt.upload_json(scene_path("sample_scene")); rt.override(width=64, height=36, spp=4); rt.render(seed=1)
+    s, png8, _ = rt.download(gamma=0)
+    _, ppm8, _ = rt.download(gamma=1)
+    assert np.array_equal(png8, orc.tonemap(s, 4, 0)) and np.array_equal(ppm8, orc.tonemap(s, 4, 1))
+    renderer.write_png(str(tmp_path / "a.png"), png8); renderer.write_ppm(str(tmp_path / "a.ppm"), ppm8)
+    assert np.array_equal(renderer.read_png(str(tmp_path / "a.png")), png8)
+    from PIL import Image
+    assert np.array_equal(np.asarray(Image.open(tmp_path / "a.png")), png8)
+    assert np.array_equal(np.asarray(Image.open(tmp_path / "a.ppm")), ppm8)
+
+
+def test_errors_are_reported_not_fatal(rt):
+    with pytest.raises(RtError, match="cannot open"):
+        rt.upload_json("/nonexistent/scene.json")
+    with pytest.raises(RtError, match="JSON"):
+        rt.upload_json_text("{ not json")
+    with pytest.raises(RtError, match="missing material"):
+        rt.upload_json_text(json.dumps({"background": [0, 0, 0], "max_depth": 5, "samples_per_pixel": 1, "width": 8, "height": 8,
+                                        "camera": {"lookfrom": [0, 0, 1], "lookat": [0, 0, 0], "vup": [0, 1, 0], "vfov": 20, "aperture": 0},
+                                        "object": {"data": [{"type": "sphere", "center": [0, 0, 0], "radius": 1, "material": 3}]},
+                                        "material": {"data": []}, "texture": {"data": []}}))
+    rt.upload_json(scene_path("sample_scene"))      # the context is still usable
+    assert rt.info().n_objects == 6
