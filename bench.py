@@ -1,0 +1,307 @@
+#!/usr/bin/env python3
+"""bench.py — headline measurement of the render path on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+  (N > 1: launched by torchrun, one rank per GPU; strong scaling: the spp of one image are split across ranks and
+   the float accumulation buffers are summed to rank 0 with one NCCL reduce over NVLink.)
+
+One "step" = one complete render of the workload image (all samples per pixel) with the scene already resident in
+HBM; `e2e` = the same step through the reference-facing call sequence with HOST buffers (JSON text -> upload + LBVH
+build -> render -> reduce -> download of float sums and RGB8).  Prints ONE JSON line (contract in the task statement).
+"""
+import argparse
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as ge  # noqa: E402
+
+WORKLOADS = {
+    # name: (scene file, width, height, spp) — BASELINE.json north_star target + configs
+    "rtiow_1080p_1024spp": ("rtiow_486.json", 1920, 1080, 1024),
+    "rtiow_c1_1200x800_10spp": ("rtiow_486.json", 1200, 800, 10),
+    "basic_scene_1080p_1024spp": ("basic_scene.json", 1920, 1080, 1024),
+    "dna000_1080p_1024spp": ("dna_000.json", 1920, 1080, 1024),
+    "blue2_1080p_256spp": ("blue2.json", 1920, 1080, 256),
+    "sample_scene_1600x900_512spp": ("sample_scene.json", 1600, 900, 512),
+}
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "cmake_cpu_mt")
+REF_GPU_HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_harness")
+
+
+def flop_model(st):
+    """Algorithmic FLOPs of SURVEY.md §8(d); extend = box + primitive tests, shade = shade + generate."""
+    ext = (24 * st["n_box_tests"] + 23 * st["n_sphere_reject"] + 47 * st["n_sphere_accept"] + 6 * st["n_rect_tests"] +
+           62 * st["n_cyl_reject"] + 130 * st["n_cyl_accept"] + 48 * st["n_tri_tests"] + 24 * st["n_boxprim_tests"])
+    shade = 60 * st["n_shade"] + 30 * st["n_generate"]
+    return ext, shade
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 3 + k and r[3 + k].lower().startswith("active") for r in self.rows)]
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "power_w_max": max(pw) if pw else None, "samples": len(self.rows)}
+
+
+def scene_text(name, width, height, spp):
+    d = json.load(open(os.path.join(GOLDEN, name)))
+    if "aspect_ratio" not in d["camera"]:
+        d["camera"]["aspect_ratio"] = d["width"] / d["height"]     # keep the scene's own aspect when the size is overridden
+    d["width"], d["height"], d["samples_per_pixel"] = width, height, spp
+    return json.dumps(d)
+
+
+def run_reference_binary(width, height, spp, procs):
+    """Runs `procs` concurrent copies of the UNMODIFIED reference cmake-cpu-version binary (it is single-threaded:
+    cmake-cpu-version/main.cpp has no omp pragma).  Returns wall seconds for all of them."""
+    dirs = [tempfile.mkdtemp(prefix="refcpu_") for _ in range(procs)]
+    t0 = time.time()
+    ps = [subprocess.Popen([REF_BIN, "-w", str(width), "-h", str(height), "-spp", str(spp), "-d", "50"], cwd=d,
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL) for d in dirs]
+    rcs = [p.wait() for p in ps]
+    dt = time.time() - t0
+    for d in dirs:
+        shutil.rmtree(d, ignore_errors=True)
+    if any(rcs):
+        raise RuntimeError(f"reference binary failed: {rcs}")
+    return dt
+
+
+def reference_sample(workload, procs):
+    """A bounded sample of the workload for the CPU arm: same scene and camera, reduced size (the reference keeps the
+    16:9 camera regardless of -w/-h, main.cpp:64,94) and 1 spp.  Returns (samples, seconds, description)."""
+    scene, W, H, spp = WORKLOADS[workload]
+    if scene == "rtiow_486.json":
+        w, h, s = 960, 540, 1
+        dt = run_reference_binary(w, h, s, procs)
+        return procs * w * h * s, dt, f"{procs} x cmake_cpu_mt -w {w} -h {h} -spp {s} -d 50 (unmodified reference binary, 1 thread each)"
+    # JSON scenes: the reference gpu-version headers compiled for the host (oracle/_ref/ref_gpu_harness), `procs` threads
+    w, h, s = 480, 270, 16
+    d = json.loads(scene_text(scene, w, h, s))
+    d.pop("aspect_ratio", None); d["camera"].pop("aspect_ratio", None)
+    with tempfile.TemporaryDirectory() as td:
+        fs = os.path.join(td, "s.json"); json.dump(d, open(fs, "w"))
+        t0 = time.time()
+        subprocess.run([REF_GPU_HARNESS, "render", fs, "1", os.path.join(td, "o.bin"), str(procs)], check=True, capture_output=True)
+        dt = time.time() - t0
+    return w * h * s, dt, f"ref_gpu_harness render {w}x{h}x{s}spp, {procs} threads (reference gpu-version headers on the host)"
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    procs = os.cpu_count() or 1
+    scene, W, H, spp = WORKLOADS[args.workload]
+    if not os.path.exists(REF_BIN):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (run __graft_entry__.build() where /root/reference is mounted)"}))
+        return
+    for _ in range(args.warmup):
+        reference_sample(args.workload, procs)
+    tot_s, tot_t, desc = 0, 0.0, ""
+    for _ in range(args.steps):
+        n, dt, desc = reference_sample(args.workload, procs)
+        tot_s += n; tot_t += dt
+    v = tot_s / tot_t
+    print(json.dumps({
+        "impl": "reference", "metric": "samples_per_second", "value": v, "unit": "samples/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64" if scene == "rtiow_486.json" else "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "scene": scene, "width": W, "height": H, "spp": spp, "note": "CPU arm renders a bounded sample of this workload per step"},
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": procs, "kind": "reference", "sample": desc},
+        "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="rtiow_1080p_1024spp", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sort", action="store_true")
+    ap.add_argument("--max-paths", type=int, default=0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return main_reference(args)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    rt = ge.load_package()
+    from rt_b200 import capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    scene, W, H, spp = WORKLOADS[args.workload]
+    text = scene_text(scene, W, H, spp)
+    stream = torch.cuda.Stream()
+    s0, s1 = rank * spp // world, (rank + 1) * spp // world        # this rank's slice of the sample indices
+    flags = capi.RT_RENDER_TIME_STAGES | (capi.RT_RENDER_NO_SORT if args.no_sort else 0)
+
+    with torch.cuda.stream(stream):
+        r = rt.Renderer(local, stream=stream.cuda_stream)
+        r.upload_json_text(text, GOLDEN)
+        ptr, nfl = r.accum_device_ptr()
+
+        class _CAI:      # zero-copy torch view of the library's accumulation buffer for the NCCL reduce
+            __cuda_array_interface__ = {"shape": (nfl,), "typestr": "<f4", "data": (ptr, False), "version": 3}
+        accum = torch.as_tensor(_CAI(), device=f"cuda:{local}")
+
+        def step_resident():
+            r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=flags, max_paths_per_pass=args.max_paths)
+            if world > 1:
+                dist.reduce(accum, dst=0)
+
+        def barrier():
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+
+        fp32_peak = r.probe_fp32_peak() if rank == 0 else 0.0
+        # event counts for the flop model (deterministic: counter-based RNG); outside the timed region
+        counts = None
+        if rank == 0:
+            r.stats_reset()
+            r.render(seed=0x2023, spp_begin=0, spp_count=max(1, spp // 16), flags=capi.RT_RENDER_COUNT_EVENTS)
+            _, _, counts = r.download(want_sum=False, want_rgb8=False)
+            scale = spp / max(1, spp // 16) / world      # counts scale linearly with the number of samples
+        for _ in range(args.warmup):
+            step_resident()
+        barrier()
+        r.stats_reset()
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            step_resident()
+        e1.record(stream)
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+        ms = torch.tensor([e0.elapsed_time(e1)], device=f"cuda:{local}")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms_step = float(ms.item()) / args.steps
+        _, _, st = r.download(want_sum=False, want_rgb8=False)       # resolves the per-stage events of the timed region
+
+        # ---- e2e: host JSON text -> upload (+BVH build) -> render -> reduce -> download to host, every step ----
+        def step_e2e():
+            r.upload_json_text(text, GOLDEN)
+            r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=0, max_paths_per_pass=args.max_paths)
+            if world > 1:
+                dist.reduce(accum, dst=0)
+            if rank == 0:
+                return r.download(gamma=0)
+            r.synchronize()
+            return None
+        step_e2e()
+        barrier()
+        t0 = time.perf_counter()
+        e0.record(stream)
+        for _ in range(max(1, args.steps // 2)):
+            out = step_e2e()
+        e1.record(stream)
+        barrier()
+        wall = time.perf_counter() - t0
+        ms2 = torch.tensor([max(e0.elapsed_time(e1), wall * 1e3)], device=f"cuda:{local}")
+        if world > 1:
+            dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
+        ms_e2e = float(ms2.item()) / max(1, args.steps // 2)
+
+    if rank == 0:
+        total_samples = W * H * spp
+        value = total_samples / (ms_step * 1e-3)
+        rays = st["rays"] / args.steps * world            # rank 0 traced 1/world of them
+        ext_flops, shade_flops = flop_model(counts)
+        ext_flops *= scale; shade_flops *= scale
+        ms_extend = st["ms_extend"] / args.steps
+        ms_other = (st["ms_generate"] + st["ms_shade"] + st["ms_accumulate"]) / args.steps
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        ach = ext_flops / (ms_extend * 1e-3) / 1e12 if ms_extend > 0 else 0.0
+        queue_bytes = (168.0 * st["rays"] / args.steps) + 80.0 * total_samples / world
+        hbm_ach = queue_bytes / (ms_other * 1e-3) / 1e9 if ms_other > 0 else 0.0
+        sc_desc = json.loads(text)
+        h2d = 64 * len(sc_desc["object"]["data"]) + 32 * (len(sc_desc["material"]["data"]) + len(sc_desc["texture"]["data"])) + len(text)
+        line = {
+            "metric": "samples_per_second", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "scene": scene, "width": W, "height": H, "spp": spp, "max_depth": sc_desc["max_depth"],
+                       "objects": len(sc_desc["object"]["data"]), "partition": f"spp split over {world} GPU(s), one NCCL reduce of the float accumulation buffer",
+                       "l2": "wavefront queues (GBs) exceed the 126 MB L2 every pass; no explicit flush needed"},
+            "mrays_per_s": rays / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays / total_samples,
+            "stage_ms_per_step": {"generate": st["ms_generate"] / args.steps, "extend": ms_extend, "shade": st["ms_shade"] / args.steps,
+                                  "accumulate": st["ms_accumulate"] / args.steps},
+            "roofline": {"bound": "fp32", "kernel": "k_extend", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": ach / fp32_peak if fp32_peak else None, "traffic": None,
+                         "note": "algorithmic FLOPs (SURVEY §8(d) model, device event counters) / CUDA-event time of the extend launches "
+                                 "in the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)"},
+            "roofline_hbm": {"bound": "hbm", "kernel": "generate+shade+accumulate", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": hbm_ach / hbm_peak, "note": "168 B/segment + 80 B/sample (SURVEY §8(d)) / CUDA-event time of those stages; peak from MEASURED_PEAKS.json" if peaks else "fallback peak"},
+            "e2e": {"value": total_samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": W * H * 3 * 4 + W * H * 3, "ms_per_step": ms_e2e},
+            "gpu_launches": int(st["launches"] / args.steps), "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline and os.path.exists(REF_BIN):
+            n, dt, desc = reference_sample(args.workload, 1)
+            line["cpu_baseline"] = {"value": n / dt, "unit": "samples/s", "cores": 1, "kind": "reference", "sample": desc.replace("1 x ", "")}
+        elif world == 1 and not args.no_cpu_baseline:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import orc
+            sc = orc.load_scene(json.loads(text), width=240, height=135, spp=4)
+            t0 = time.time(); orc.render(sc, threads=1); dt = time.time() - t0
+            line["cpu_baseline"] = {"value": 240 * 135 * 4 / dt, "unit": "samples/s", "cores": 1, "kind": "port", "sample": "oracle 240x135x4spp, 1 thread"}
+        print(json.dumps(line))
+    r.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -111,7 +111,8 @@ typedef struct rt_scene_desc {
 enum { RT_RENDER_KEEP_ACCUM = 1,     /* add to the accumulation buffer instead of clearing it first */
        RT_RENDER_COUNT_EVENTS = 2,   /* fill the event counters of rt_stats (slower; counts are deterministic) */
        RT_RENDER_NO_SORT = 4,        /* do not bin rays by material before shading (ablation switch) */
-       RT_RENDER_NEE = 8 };          /* next-event estimation through the shadow stage (changes the estimator; default off) */
+       RT_RENDER_NEE = 8,            /* next-event estimation through the shadow stage (changes the estimator; default off) */
+       RT_RENDER_TIME_STAGES = 16 }; /* record CUDA events around every stage launch (no synchronisation); per-stage ms in rt_stats */
 
 typedef struct rt_render_params {
     uint32_t seed;          /* Philox key word 0 */
@@ -128,7 +129,7 @@ typedef struct rt_stats {
     int64_t launches;           /* kernels launched by the library since rt_create/rt_stats_reset */
     int64_t passes;
     float ms_total;             /* device time of the last rt_render, CUDA events on the ctx stream */
-    float ms_generate, ms_extend, ms_shade, ms_shadow, ms_accumulate, ms_build;   /* per-stage device time (only with COUNT_EVENTS) */
+    float ms_generate, ms_extend, ms_shade, ms_shadow, ms_accumulate, ms_build;   /* per-stage device time (COUNT_EVENTS or TIME_STAGES) */
     /* event counters for the algorithmic-flop model of SURVEY.md §8(d) (only with COUNT_EVENTS) */
     int64_t n_box_tests, n_sphere_reject, n_sphere_accept, n_rect_tests, n_cyl_reject, n_cyl_accept,
             n_tri_tests, n_boxprim_tests, n_shade, n_generate, n_node_visits;
@@ -191,6 +192,10 @@ int rt_write_png(const char *path, const unsigned char *rgb8, int width, int hei
 /* PNG reader for image textures (8-bit RGB/RGBA/grey, non-interlaced); caller frees *rgb8 with rt_free. */
 int rt_read_png(const char *path, unsigned char **rgb8, int *width, int *height);
 void rt_free(void *p);
+
+/* Measurement helper: FP32 FMA-chain microbenchmark on the ctx device (TFLOP/s, best of 4 after warm-up) — the measured
+ * denominator of the extend/shade roofline. */
+int rt_probe_fp32_peak(rt_ctx *ctx, double *tflops);
 
 #ifdef __cplusplus
 }

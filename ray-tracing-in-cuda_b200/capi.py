@@ -13,7 +13,7 @@ RT_MAT_LAMBERTIAN, RT_MAT_METAL, RT_MAT_DIELECTRIC, RT_MAT_DIFFUSE_LIGHT = range
 RT_TEX_SOLID, RT_TEX_CHECKER, RT_TEX_IMAGE = range(3)
 RT_BG_CONSTANT, RT_BG_SKY_GRADIENT = range(2)
 RT_SAMPLING_REFERENCE_GPU, RT_SAMPLING_REFERENCE_CPU = range(2)
-RT_RENDER_KEEP_ACCUM, RT_RENDER_COUNT_EVENTS, RT_RENDER_NO_SORT, RT_RENDER_NEE = 1, 2, 4, 8
+RT_RENDER_KEEP_ACCUM, RT_RENDER_COUNT_EVENTS, RT_RENDER_NO_SORT, RT_RENDER_NEE, RT_RENDER_TIME_STAGES = 1, 2, 4, 8, 16
 
 
 class ObjectDesc(C.Structure):
@@ -83,7 +83,7 @@ class SceneInfo(C.Structure):
 RT_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_scene_upload", "rt_scene_upload_json",
               "rt_scene_upload_json_text", "rt_scene_info_get", "rt_scene_override", "rt_render", "rt_render_aov",
               "rt_accum_device_ptr", "rt_accum_sum_ordered", "rt_download", "rt_synchronize", "rt_stats_reset",
-              "rt_bvh_download", "rt_write_ppm", "rt_write_png", "rt_read_png", "rt_free"]
+              "rt_bvh_download", "rt_write_ppm", "rt_write_png", "rt_read_png", "rt_free", "rt_probe_fp32_peak"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librt_b200.so")
@@ -124,6 +124,7 @@ def load_library(path=None):
     lib.rt_write_png.argtypes = [C.c_char_p, P(C.c_ubyte), C.c_int, C.c_int]
     lib.rt_read_png.argtypes = [C.c_char_p, P(P(C.c_ubyte)), P(C.c_int), P(C.c_int)]
     lib.rt_free.argtypes = [vp]; lib.rt_free.restype = None
+    lib.rt_probe_fp32_peak.argtypes = [vp, P(C.c_double)]
     for name in RT_SYMBOLS:
         if getattr(lib, name).restype is C.c_int:
             pass

@@ -83,6 +83,7 @@ extern "C" void rt_destroy(rt_ctx *c) {
     c->d_radiance.release(); c->d_hits.release(); c->d_bins.release(); c->d_qcount.release(); c->d_bincount.release();
     c->d_workctr.release(); c->d_counters.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
     c->d_partials.release(); c->d_rays.release();
+    for (auto e : c->ev_pool) cudaEventDestroy(e);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -409,9 +410,18 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     float ms_stage[4] = {0, 0, 0, 0};
     cudaEvent_t evs[2] = {nullptr, nullptr};
     if (count) { cudaEventCreate(&evs[0]); cudaEventCreate(&evs[1]); }
+    const bool time_stages = !count && (prm->flags & RT_RENDER_TIME_STAGES) != 0;
+    if (time_stages) {          // event pairs are recorded without synchronising and resolved in rt_download
+        const size_t n_passes = (size_t)((spp + s_pass - 1) / s_pass);
+        const size_t need = ctx->pending.size() + n_passes * (2 + 2 * (size_t)ds.max_depth);
+        while (ctx->ev_pool.size() < 2 * need) { cudaEvent_t e; if (cudaEventCreate(&e) != cudaSuccess) return rt_fail(ctx, RT_ERR_CUDA, "cudaEventCreate"); ctx->ev_pool.push_back(e); }
+    }
     auto timed = [&](int stage, auto &&fn) {
         if (count) cudaEventRecord(evs[0], s);
+        size_t slot = 0;
+        if (time_stages) { slot = ctx->pending.size(); ctx->pending.push_back(stage); cudaEventRecord(ctx->ev_pool[2 * slot], s); }
         fn();
+        if (time_stages) cudaEventRecord(ctx->ev_pool[2 * slot + 1], s);
         if (count) { cudaEventRecord(evs[1], s); cudaEventSynchronize(evs[1]); float ms = 0; cudaEventElapsedTime(&ms, evs[0], evs[1]); ms_stage[stage] += ms; }
     };
     CU(cudaEventRecord(ctx->ev0, s));
@@ -502,6 +512,7 @@ extern "C" int rt_stats_reset(rt_ctx *ctx) {
     memset(&ctx->stats, 0, sizeof ctx->stats);
     ctx->stats.ms_build = ms_build;
     ctx->launches = 0;
+    ctx->pending.clear();
     if (ctx->d_rays.p) { CU(cudaSetDevice(ctx->device)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, sizeof(unsigned long long), ctx->stream)); }
     return RT_OK;
 }
@@ -524,6 +535,14 @@ extern "C" int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigne
     if (rgb_sum) CU(cudaMemcpyAsync(rgb_sum, ctx->d_accum.p, sizeof(float) * need, cudaMemcpyDeviceToHost, s));
     if (stats && ctx->d_rays.p) { unsigned long long r = 0; CU(cudaMemcpyAsync(&r, ctx->d_rays.p, sizeof r, cudaMemcpyDeviceToHost, s)); CU(cudaStreamSynchronize(s)); ctx->stats.rays = (long long)r; }
     CU(cudaStreamSynchronize(s));
+    if (!ctx->pending.empty()) {
+        float *acc[4] = {&ctx->stats.ms_generate, &ctx->stats.ms_extend, &ctx->stats.ms_shade, &ctx->stats.ms_accumulate};
+        for (size_t k = 0; k < ctx->pending.size(); ++k) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, ctx->ev_pool[2 * k], ctx->ev_pool[2 * k + 1]) == cudaSuccess) *acc[ctx->pending[k]] += ms; else cudaGetLastError();
+        }
+        ctx->pending.clear();
+    }
     if (stats) {
         float ms = 0;
         if (cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) == cudaSuccess) ctx->stats.ms_total = ms; else cudaGetLastError();

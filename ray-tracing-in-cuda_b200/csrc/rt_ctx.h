@@ -59,6 +59,8 @@ struct rt_ctx {
     // stats
     rt_stats stats{};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::vector<cudaEvent_t> ev_pool;   // RT_RENDER_TIME_STAGES: (start, stop) pairs, resolved in rt_download
+    std::vector<int> pending;           // stage id per recorded pair
     bool accum_valid = false;
 };
 

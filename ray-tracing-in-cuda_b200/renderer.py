@@ -106,6 +106,11 @@ class Renderer:
             int(gamma), C.byref(st)), "rt_download")
         return rgb_sum, rgb8, st.as_dict()
 
+    def probe_fp32_peak(self):
+        v = C.c_double()
+        self._check(self.lib.rt_probe_fp32_peak(self.ctx, C.byref(v)), "rt_probe_fp32_peak")
+        return v.value
+
     def stats_reset(self):
         self._check(self.lib.rt_stats_reset(self.ctx), "rt_stats_reset")
 
