@@ -86,7 +86,7 @@ RT_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_
               "rt_bvh_download", "rt_write_ppm", "rt_write_png", "rt_read_png", "rt_free", "rt_probe_fp32_peak"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")   # env override: tuning builds only
 _lib = None
 
 

@@ -354,7 +354,7 @@ extern "C" int rt_scene_override(rt_ctx *ctx, int width, int height, int spp, in
 static int ensure_queues(rt_ctx *ctx, long long cap) {
     if (cap <= ctx->queue_cap && ctx->d_qcount.p) return RT_OK;
     for (int k = 0; k < 2; ++k) { CU(ctx->d_ray_o[k].alloc(cap)); CU(ctx->d_ray_d[k].alloc(cap)); CU(ctx->d_thr[k].alloc(cap)); }
-    CU(ctx->d_radiance.alloc(cap)); CU(ctx->d_hits.alloc(cap)); CU(ctx->d_bins.alloc((size_t)cap * RT_NUM_BINS));
+    CU(ctx->d_radiance.alloc(cap)); CU(ctx->d_hits.alloc(cap + 2));   // +2: the TMA copy of an odd-sized tail rounds up to 16 B CU(ctx->d_bins.alloc((size_t)cap * RT_NUM_BINS));
     CU(ctx->d_counters.alloc(CTR_COUNT));
     if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(1)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, sizeof(unsigned long long), ctx->stream)); }
     ctx->queue_cap = cap;

@@ -14,6 +14,7 @@
 //   * radiance is written once per path and summed per pixel in sample order by `accumulate` (no float atomics).
 #include "rt_kernels.h"
 #include "rt_traverse.cuh"
+#include <cstdlib>
 
 __device__ __forceinline__ unsigned lanemask_lt() { unsigned m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
@@ -64,11 +65,31 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
 }
 
 // ------------------------------------------------------------------------------------------------
-// extend: closest hit for every ray of the bounce's queue; bins the queue entry by material class.
+// extend: closest hit for every ray of the bounce's queue (replaces hittable_list::hit, object.cuh:23-37).
+//
+// Persistent warps with PER-LANE dynamic ray fetch: a lane whose ray has terminated does not wait for the slowest
+// ray of its warp; as soon as RT_EXT_REFILL lanes are idle they are handed new rays from the warp's private batch
+// of queue indices (one global atomic per RT_EXT_BATCH rays).  Keeps SIMT lanes busy on incoherent bounces.
+// Box tests are one FFMA per slab plane (t = plane * (1/d) - o/d) with a conservative error margin; they only prune.
+// Leaf tests are the exact reference arithmetic (rt_scene.cuh), so the result equals the brute-force walk.
 // ------------------------------------------------------------------------------------------------
-template <bool SMEM, bool COUNT, bool SORT>
-__global__ void __launch_bounds__(RT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf) {
+#define RT_EXT_BLOCK 512
+#define RT_EXT_BATCH 256
+#define RT_EXT_REFILL 32
+#define RT_BOX_REL 9.5367431640625e-07f      // 2^-20: rcp.approx error + fma rounding, relative to t
+#define RT_BOX_ABS 2.384185791015625e-07f    // 2^-22 * max|o/d|: rounding of the hoisted o/d term
+
+template <bool SMEM, bool COUNT>
+__global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf, int refill, int max_batch) {
     extern __shared__ float4 s_raw[];
+    const int n = q.qcount[bounce];
+    if (n == 0) return;
+    // batch of queue indices a warp takes per global atomic: large for long queues, small enough on short ones that
+    // every resident warp gets work; CTAs that cannot get any work leave before staging the BVH
+    const int total_warps = gridDim.x * (RT_EXT_BLOCK / 32);
+    int batch = (n + total_warps - 1) / total_warps;
+    batch = batch < 32 ? 32 : (batch > max_batch ? max_batch : ((batch + 31) & ~31));
+    if ((long long)blockIdx.x * (RT_EXT_BLOCK / 32) * batch >= n) return;
     const BvhNode *nodes = sc.nodes;
     if (SMEM) {
         const float4 *src = reinterpret_cast<const float4 *>(sc.nodes);
@@ -76,44 +97,118 @@ __global__ void __launch_bounds__(RT_BLOCK) k_extend(DScene sc, Queues q, int bo
         __syncthreads();
         nodes = reinterpret_cast<const BvhNode *>(s_raw);
     }
-    const int n = q.qcount[bounce];
     int *cursor = &q.workctr[bounce * 2 + 0];
-    int *bincount = &q.bincount[bounce * RT_BIN_STRIDE];
     const float4 *__restrict__ ray_o = q.ray_o[buf];
     const float4 *__restrict__ ray_d = q.ray_d[buf];
+    const bool no_prims = sc.n_prims == 0;
     TravCounters cnt = {};
-    const int CHUNK = 128;
+    int batch_next = 0, batch_end = 0;     // warp-uniform: this warp's private range of queue indices
+    bool exhausted = false;                // warp-uniform: the global cursor ran past the queue
+    // per-lane traversal state
+    bool active = false;
+    int ray_i = 0, cur = 0, sp = 0, best_code = -1;
+    float3 o = v3(0, 0, 0), d = v3(0, 0, 0), ood = v3(0, 0, 0), oo = v3(0, 0, 0);
+    float a = 1.0f, inv_a = 1.0f, E = 0.0f, best_t = FLT_MAX;
+    int2 stack[RT_TRAV_STACK];
+    const float tmin = 0.001f;
     for (;;) {
-        const int base = warp_fetch(cursor, CHUNK);
-        if (base >= n) break;
-#pragma unroll 1
-        for (int k = 0; k < CHUNK; k += 32) {
-            const int i = base + k + lane_id();
-            const bool valid = i < n;
-            int bin = -1;
-            if (valid) {
-                const float4 o4 = ray_o[i], d4 = ray_d[i];
-                float t; int code;
-                traverse<COUNT, false>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt);
-                q.hits[i] = make_int2(__float_as_int(t), code);
-                if (SORT) bin = code < 0 ? 0 : 1 + sc.mats[__ldg(&sc.prim_mat[code & RT_LEAF_SLOT_MASK])].type;
+        // ---- hand new rays to idle lanes ----
+        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        if (idle && !exhausted) {
+            if (batch_next == batch_end) {
+                const int base = warp_fetch(cursor, batch);
+                if (base >= n) { exhausted = true; batch_next = batch_end = 0; }
+                else { batch_next = base; batch_end = min(base + batch, n); }
             }
-            if (SORT) {
-                // warp-aggregated append of the queue index to the list of its material class
-#pragma unroll
-                for (int b = 0; b < RT_NUM_BINS; ++b) {
-                    const unsigned m = __ballot_sync(0xffffffffu, bin == b);
-                    if (m) {
-                        int pos = 0;
-                        const int leader = __ffs(m) - 1;
-                        if (lane_id() == leader) pos = atomicAdd(&bincount[b], __popc(m));
-                        pos = __shfl_sync(0xffffffffu, pos, leader);
-                        if (bin == b) q.bins[(long long)b * q.cap + pos + __popc(m & lanemask_lt())] = i;
+            const int take = min(__popc(idle), batch_end - batch_next);
+            if (!active) {
+                const int rank = __popc(idle & lanemask_lt());
+                if (rank < take) {
+                    ray_i = batch_next + rank;
+                    const float4 o4 = ray_o[ray_i], d4 = ray_d[ray_i];
+                    o = f4xyz(o4); d = f4xyz(d4);
+                    best_t = FLT_MAX; best_code = -1; sp = 0; cur = 0;
+                    a = dot3(d, d); inv_a = 1.0f / a;
+                    ood = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+                    oo = v3(-(o.x * ood.x), -(o.y * ood.y), -(o.z * ood.z));
+                    float ex = fabsf(oo.x), ey = fabsf(oo.y), ez = fabsf(oo.z);
+                    ex = ex < INFINITY ? ex : 0.0f; ey = ey < INFINITY ? ey : 0.0f; ez = ez < INFINITY ? ez : 0.0f;
+                    E = RT_BOX_ABS * fmaxf(ex, fmaxf(ey, ez));
+                    active = true;
+                    if (no_prims) { q.hits[ray_i] = make_int2(__float_as_int(FLT_MAX), -1); active = false; }
+                }
+            }
+            batch_next += take;
+        }
+        if (!__any_sync(0xffffffffu, active)) {
+            if (exhausted) break;
+            continue;
+        }
+        // ---- traverse until enough lanes are idle again ----
+        const int thresh = exhausted ? 32 : refill;
+        do {
+            if (active) {
+                // next subtree that can still contain a closer (or equally close) hit; none left: the ray is done
+                auto pop_next = [&]() {
+                    for (;;) {
+                        if (sp == 0) {
+                            q.hits[ray_i] = make_int2(__float_as_int(best_t), best_code);
+                            active = false;
+                            break;
+                        }
+                        --sp;
+                        const int2 e = stack[sp];
+                        if (__int_as_float(e.y) <= best_t) { cur = e.x; break; }
+                    }
+                };
+                // leaf step first, inner step second: a lane that holds a leaf tests it, pops, and still takes part in
+                // this iteration's inner-node step (the two halves are executed by the warp anyway)
+                if (cur < 0) {
+                    const int code = ~cur;
+                    float t;
+                    const bool h = leaf_t(sc, code, o, d, a, inv_a, tmin, best_t, t);
+                    count_leaf<COUNT>(cnt, code, h);
+                    if (h) {
+                        bool take = t < best_t || best_code < 0;
+                        if (!take)   // t == best_t: the later object in the scene file wins (object.cuh:29-33)
+                            take = __ldg(&sc.prim_obj[code & RT_LEAF_SLOT_MASK]) > __ldg(&sc.prim_obj[best_code & RT_LEAF_SLOT_MASK]);
+                        if (take) { best_t = t; best_code = code; }
+                    }
+                    pop_next();
+                }
+                if (active && cur >= 0) {
+                    const float4 na = nodes[cur].a, nb = nodes[cur].b, nc = nodes[cur].c;
+                    const int4 nd = nodes[cur].d;
+                    if (COUNT) { cnt.box += 2; cnt.nodes++; }
+                    // left box: min (na.x na.y na.z) max (na.w nb.x nb.y); right box: min (nb.z nb.w nc.x) max (nc.y nc.z nc.w)
+                    float x0 = __fmaf_rn(na.x, ood.x, oo.x), x1 = __fmaf_rn(na.w, ood.x, oo.x);
+                    float y0 = __fmaf_rn(na.y, ood.y, oo.y), y1 = __fmaf_rn(nb.x, ood.y, oo.y);
+                    float z0 = __fmaf_rn(na.z, ood.z, oo.z), z1 = __fmaf_rn(nb.y, ood.z, oo.z);
+                    const float tnl = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+                    const float tfl = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
+                    x0 = __fmaf_rn(nb.z, ood.x, oo.x); x1 = __fmaf_rn(nc.y, ood.x, oo.x);
+                    y0 = __fmaf_rn(nb.w, ood.y, oo.y); y1 = __fmaf_rn(nc.z, ood.y, oo.y);
+                    z0 = __fmaf_rn(nc.x, ood.z, oo.z); z1 = __fmaf_rn(nc.w, ood.z, oo.z);
+                    const float tnr = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+                    const float tfr = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
+                    const bool hl = tnl <= __fmaf_rn(fabsf(tfl), RT_BOX_REL, tfl + E);
+                    const bool hr = tnr <= __fmaf_rn(fabsf(tfr), RT_BOX_REL, tfr + E);
+                    if (hl && hr) {
+                        const bool lfirst = tnl <= tnr;
+                        const float tfar = lfirst ? tnr : tnl;
+                        if (sp < RT_TRAV_STACK) {
+                            stack[sp] = make_int2(lfirst ? nd.y : nd.x, __float_as_int(__fmaf_rn(-fabsf(tfar), RT_BOX_REL, tfar) - E));
+                            ++sp;
+                        } else if (COUNT) cnt.overflow++;
+                        cur = lfirst ? nd.x : nd.y;
+                    } else if (hl || hr) {
+                        cur = hl ? nd.x : nd.y;
+                    } else {
+                        pop_next();
                     }
                 }
             }
-            if (base + k + 32 >= n) break;
-        }
+        } while (__popc(__ballot_sync(0xffffffffu, !active)) < thresh);
     }
     if (COUNT) {
         flush_counter<COUNT>(q.counters, CTR_BOX, cnt.box); flush_counter<COUNT>(q.counters, CTR_SPH_REJECT, cnt.sph_rej);
@@ -126,53 +221,140 @@ __global__ void __launch_bounds__(RT_BLOCK) k_extend(DScene sc, Queues q, int bo
 
 // ------------------------------------------------------------------------------------------------
 // shade: rebuild the hit record, evaluate emitted/scatter (main.cu:45-63), write the radiance of paths that end,
-// and compact the survivors into the next bounce's queue.  With SORT the work list is the concatenation of the
-// material-class bins (each padded to a warp), so a warp shades one material class.
+// and compact the survivors into the next bounce's queue.
+//
+// One CTA owns one chunk of RT_SH_CHUNK consecutive queue entries at a time (static round-robin, no work atomics):
+//   1. the chunk's ray / throughput / hit records arrive in shared memory by four TMA bulk copies
+//      (cp.async.bulk + mbarrier), double-buffered so the next chunk streams in while this one is shaded;
+//   2. the entries are sorted by material class inside shared memory (ballot + popc multisplit), so a warp shades
+//      one material class (miss / lambertian / metal / dielectric / light) except at the <= 4 class boundaries;
+//   3. survivors are compacted into a shared-memory staging area (ballot + popc, one shared atomic per warp), the CTA
+//      reserves its output range with ONE global atomic per chunk and three TMA bulk stores write full lines.
 // ------------------------------------------------------------------------------------------------
-template <bool COUNT, bool SORT>
-__global__ void __launch_bounds__(RT_BLOCK) k_shade(DScene sc, Queues q, unsigned seed, int spp_begin, int bounce, int buf,
-                                                    int last_bounce) {
+#ifndef RT_SH_CHUNK
+#define RT_SH_CHUNK 128
+#endif
+#define RT_SH_CTAS_PER_SM (1024 / RT_SH_CHUNK)
+#define RT_SH_WARPS (RT_SH_CHUNK / 32)
+
+struct __align__(128) ShadeSmem {
+    float4 in_o[2][RT_SH_CHUNK], in_d[2][RT_SH_CHUNK], in_thr[2][RT_SH_CHUNK];
+    int2 in_hit[2][RT_SH_CHUNK];
+    float4 out_o[RT_SH_CHUNK], out_d[RT_SH_CHUNK], out_thr[RT_SH_CHUNK];
+    unsigned long long full[2];       // mbarriers: "stage s has landed"
+    int cls_count[8];
+    int n_out, out_base;
+    unsigned short perm[RT_SH_CHUNK];
+};
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA 1-D bulk copy global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void tma_load_1d(void *dst_smem, const void *src_gmem, unsigned bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// TMA 1-D bulk copy shared -> global (bulk async-group completion)
+__device__ __forceinline__ void tma_store_1d(void *dst_gmem, const void *src_smem, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void shade_issue_loads(ShadeSmem &sm, const Queues &q, int buf, int chunk, int n, int stage) {
+    const int first = chunk * RT_SH_CHUNK;
+    const int cnt = min(RT_SH_CHUNK, n - first);
+    const unsigned b16 = (unsigned)cnt * 16u, b8 = ((unsigned)cnt * 8u + 15u) & ~15u;
+    mbar_expect_tx(&sm.full[stage], 3u * b16 + b8);
+    tma_load_1d(sm.in_o[stage], q.ray_o[buf] + first, b16, &sm.full[stage]);
+    tma_load_1d(sm.in_d[stage], q.ray_d[buf] + first, b16, &sm.full[stage]);
+    tma_load_1d(sm.in_thr[stage], q.thr[buf] + first, b16, &sm.full[stage]);
+    tma_load_1d(sm.in_hit[stage], q.hits + first, b8, &sm.full[stage]);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene sc, Queues q, unsigned seed, int spp_begin, int bounce, int buf,
+                                                         int last_bounce, int sort) {
+    extern __shared__ __align__(128) unsigned char s_shade_raw[];
+    ShadeSmem &sm = *reinterpret_cast<ShadeSmem *>(s_shade_raw);
     const int n = q.qcount[bounce];
+    const int n_chunks = (n + RT_SH_CHUNK - 1) / RT_SH_CHUNK;
+    if ((int)blockIdx.x >= n_chunks) return;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int np = sc.width * sc.height;
-    int cnt[RT_NUM_BINS], start[RT_NUM_BINS + 1];
-    start[0] = 0;
-#pragma unroll
-    for (int b = 0; b < RT_NUM_BINS; ++b) {
-        cnt[b] = SORT ? q.bincount[bounce * RT_BIN_STRIDE + b] : 0;
-        start[b + 1] = start[b] + ((cnt[b] + 31) & ~31);
-    }
-    const int total = SORT ? start[RT_NUM_BINS] : ((n + 31) & ~31);
-    int *cursor = &q.workctr[bounce * 2 + 1];
     int *next_count = &q.qcount[bounce + 1];
-    const float4 *__restrict__ ray_o = q.ray_o[buf];
-    const float4 *__restrict__ ray_d = q.ray_d[buf];
-    const float4 *__restrict__ thr_in = q.thr[buf];
-    float4 *__restrict__ out_o = q.ray_o[buf ^ 1];
-    float4 *__restrict__ out_d = q.ray_d[buf ^ 1];
-    float4 *__restrict__ out_thr = q.thr[buf ^ 1];
+    if (tid == 0) {
+        mbar_init(&sm.full[0], 1); mbar_init(&sm.full[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        sm.n_out = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) sm.cls_count[b] = 0;
+    }
+    __syncthreads();
+    if (tid == 0) shade_issue_loads(sm, q, buf, blockIdx.x, n, 0);
     unsigned n_shaded = 0;
-    for (;;) {
-        const int base = warp_fetch(cursor, 32);
-        if (base >= total) break;
-        int i = base + lane_id();
-        bool valid = i < n;
-        if (SORT) {
-            int b = 0;
+    int it = 0;
+    for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x, ++it) {
+        const int st = it & 1;
+        const int cnt = min(RT_SH_CHUNK, n - chunk * RT_SH_CHUNK);
+        if (tid == 0 && chunk + (int)gridDim.x < n_chunks) shade_issue_loads(sm, q, buf, chunk + gridDim.x, n, st ^ 1);
+        mbar_wait(&sm.full[st], (unsigned)(it >> 1) & 1u);
+        // ---- 1. sort the chunk by material class (shared memory only) ----
+        int j = tid;                                   // the entry this thread shades
+        if (sort) {
+            int cls = -1;
+            if (tid < cnt) {
+                const int code = sm.in_hit[st][tid].y;
+                cls = code < 0 ? 0 : 1 + sc.mats[__ldg(&sc.prim_mat[code & RT_LEAF_SLOT_MASK])].type;
+            }
+            int pos_in_cls = 0;
 #pragma unroll
-            for (int k = 1; k < RT_NUM_BINS; ++k) if (base >= start[k]) b = k;
-            int off = 0, c = 0;
+            for (int b = 0; b < RT_NUM_BINS; ++b) {
+                const unsigned m = __ballot_sync(0xffffffffu, cls == b);
+                if (m) {
+                    int base = 0;
+                    const int leader = __ffs(m) - 1;
+                    if (lane == leader) base = atomicAdd(&sm.cls_count[b], __popc(m));
+                    base = __shfl_sync(0xffffffffu, base, leader);
+                    if (cls == b) pos_in_cls = base + __popc(m & lanemask_lt());
+                }
+            }
+            __syncthreads();
+            if (cls >= 0) {
+                int off = 0;
 #pragma unroll
-            for (int k = 0; k < RT_NUM_BINS; ++k) if (k == b) { off = start[k]; c = cnt[k]; }
-            const int kk = base - off + lane_id();
-            valid = kk < c;
-            i = valid ? q.bins[(long long)b * q.cap + kk] : 0;
+                for (int b = 0; b < RT_NUM_BINS; ++b) if (b < cls) off += sm.cls_count[b];
+                sm.perm[off + pos_in_cls] = (unsigned short)tid;
+            }
+            __syncthreads();
+            if (tid < cnt) j = sm.perm[tid];
+            if (tid < 8) sm.cls_count[tid] = 0;        // next use is after the two barriers of step 3
         }
+        // ---- 2. shade ----
         bool alive = false;
         float3 no = v3(0, 0, 0), nd = v3(0, 0, 0), nthr = v3(0, 0, 0);
         int path_id = 0;
-        if (valid) {
-            const float4 o4 = ray_o[i], d4 = ray_d[i], t4 = thr_in[i];
-            const int2 h = q.hits[i];
+        if (tid < cnt) {
+            const float4 o4 = sm.in_o[st][j], d4 = sm.in_d[st][j], t4 = sm.in_thr[st][j];
+            const int2 h = sm.in_hit[st][j];
             const float3 o = f4xyz(o4), d = f4xyz(d4), thr = f4xyz(t4);
             path_id = __float_as_int(o4.w);
             float3 rad = v3(0, 0, 0);
@@ -198,20 +380,36 @@ __global__ void __launch_bounds__(RT_BLOCK) k_shade(DScene sc, Queues q, unsigne
             }
             if (!alive) q.radiance[path_id] = make_float4(rad.x, rad.y, rad.z, 0.0f);
         }
-        // stream compaction: one atomic per warp, survivors written to consecutive slots
+        // ---- 3. compact the survivors into the staging area; one global atomic + three TMA stores per chunk ----
+        if (tid == 0) tma_store_wait_read();          // the previous chunk's stores have finished reading the staging area
+        __syncthreads();
         const unsigned m = __ballot_sync(0xffffffffu, alive);
         if (m) {
             int pos = 0;
             const int leader = __ffs(m) - 1;
-            if (lane_id() == leader) pos = atomicAdd(next_count, __popc(m));
+            if (lane == leader) pos = atomicAdd(&sm.n_out, __popc(m));
             pos = __shfl_sync(0xffffffffu, pos, leader) + __popc(m & lanemask_lt());
             if (alive) {
-                out_o[pos] = make_float4(no.x, no.y, no.z, __int_as_float(path_id));
-                out_d[pos] = make_float4(nd.x, nd.y, nd.z, 0.0f);
-                out_thr[pos] = make_float4(nthr.x, nthr.y, nthr.z, 0.0f);
+                sm.out_o[pos] = make_float4(no.x, no.y, no.z, __int_as_float(path_id));
+                sm.out_d[pos] = make_float4(nd.x, nd.y, nd.z, 0.0f);
+                sm.out_thr[pos] = make_float4(nthr.x, nthr.y, nthr.z, 0.0f);
             }
         }
+        fence_proxy_async();                          // make the generic-proxy writes visible to the TMA engine
+        __syncthreads();
+        if (tid == 0) {
+            const int n_out = sm.n_out;
+            if (n_out) {
+                const int base = atomicAdd(next_count, n_out);
+                tma_store_1d(q.ray_o[buf ^ 1] + base, sm.out_o, (unsigned)n_out * 16u);
+                tma_store_1d(q.ray_d[buf ^ 1] + base, sm.out_d, (unsigned)n_out * 16u);
+                tma_store_1d(q.thr[buf ^ 1] + base, sm.out_thr, (unsigned)n_out * 16u);
+                tma_store_commit();
+            }
+            sm.n_out = 0;                             // next use is after the first barrier of the next step 3
+        }
     }
+    if (tid == 0) tma_store_wait_all();
     flush_counter<COUNT>(q.counters, CTR_SHADE, n_shaded);
 }
 
@@ -330,49 +528,48 @@ void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsi
 }
 
 template <bool SMEM>
-static void launch_extend_t(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort) {
+static void launch_extend_t(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count) {
     const int grid = persistent_grid(c, c.extend_blocks_per_sm);
     const size_t sm = SMEM ? c.bvh_smem_bytes : 0;
-    if (count) {
-        if (sort) k_extend<SMEM, true, true><<<grid, RT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf);
-        else k_extend<SMEM, true, false><<<grid, RT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf);
-    } else {
-        if (sort) k_extend<SMEM, false, true><<<grid, RT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf);
-        else k_extend<SMEM, false, false><<<grid, RT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf);
-    }
+    static const int refill = getenv("RT_EXT_REFILL") ? atoi(getenv("RT_EXT_REFILL")) : RT_EXT_REFILL;
+    static const int batch = getenv("RT_EXT_BATCH") ? atoi(getenv("RT_EXT_BATCH")) : RT_EXT_BATCH;
+    if (count) k_extend<SMEM, true><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, refill, batch);
+    else k_extend<SMEM, false><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, refill, batch);
 }
 
 void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort) {
-    if (c.bvh_smem_bytes) launch_extend_t<true>(c, sc, q, bounce, buf, count, sort);
-    else launch_extend_t<false>(c, sc, q, bounce, buf, count, sort);
+    (void)sort;
+    if (c.bvh_smem_bytes) launch_extend_t<true>(c, sc, q, bounce, buf, count);
+    else launch_extend_t<false>(c, sc, q, bounce, buf, count);
     bump(c);
 }
 
 cudaError_t extend_configure_smem(size_t smem_bytes) {
     cudaError_t e = cudaSuccess;
 #define SET(K) if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes)
-    SET((k_extend<true, false, true>)); SET((k_extend<true, false, false>)); SET((k_extend<true, true, true>)); SET((k_extend<true, true, false>));
+    SET((k_extend<true, false>)); SET((k_extend<true, true>));
 #undef SET
     return e;
 }
 
 int extend_max_blocks_per_sm(size_t smem_bytes) {
     int nb = 0;
-    if (smem_bytes) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<true, false, true>, RT_BLOCK, smem_bytes);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<false, false, true>, RT_BLOCK, 0);
+    if (smem_bytes) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<true, false>, RT_EXT_BLOCK, smem_bytes);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<false, false>, RT_EXT_BLOCK, 0);
     return nb;
 }
 
 void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
                   bool last_bounce, bool count, bool sort) {
-    const int grid = persistent_grid(c, 4);
-    if (count) {
-        if (sort) k_shade<true, true><<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce);
-        else k_shade<true, false><<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce);
-    } else {
-        if (sort) k_shade<false, true><<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce);
-        else k_shade<false, false><<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce);
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(k_shade<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        configured = true;
     }
+    const int grid = persistent_grid(c, RT_SH_CTAS_PER_SM);
+    if (count) k_shade<true><<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort);
+    else k_shade<false><<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort);
     bump(c);
 }
 

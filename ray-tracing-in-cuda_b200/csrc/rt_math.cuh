@@ -120,4 +120,8 @@ struct Rng {
         ++idx;
         return (float)((x >> 8) + inc) * 5.9604644775390625e-08f;
     }
+    // block-wise access for samplers that consume whole blocks with compile-time word indices (same stream as next())
+    __device__ __forceinline__ bool at_block_start() const { return idx == 4; }
+    __device__ __forceinline__ uint4 next_block() { uint4 r = philox4x32_10(make_uint4(sample, bounce, block, 0x5254u), key); ++block; return r; }
+    __device__ __forceinline__ float to_uniform(uint32_t x) const { return (float)((x >> 8) + inc) * 5.9604644775390625e-08f; }
 };

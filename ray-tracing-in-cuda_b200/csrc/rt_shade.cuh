@@ -40,14 +40,38 @@ struct FixedRng {
 };
 
 // random_in_unit_sphere: vec3.cuh:133-141 (octant, (0,1] uniforms) | cmake-cpu-version/vec3.h:121-129 (full cube)
+__device__ __forceinline__ bool ball_trial(float a, float b, float c, int sampling, float3 &p) {
+    p = sampling == RT_SAMPLING_REFERENCE_GPU ? v3(a, b, c)
+                                              : v3(__fmaf_rn(2.0f, a, -1.0f), __fmaf_rn(2.0f, b, -1.0f), __fmaf_rn(2.0f, c, -1.0f));
+    return !(dot3(p, p) >= 1.0f);
+}
 template <class R>
 __device__ __forceinline__ float3 random_in_unit_sphere(R &rng, int sampling) {
     for (;;) {
         float a = rng.next(), b = rng.next(), c = rng.next();
-        float3 p = sampling == RT_SAMPLING_REFERENCE_GPU ? v3(a, b, c)
-                                                         : v3(__fmaf_rn(2.0f, a, -1.0f), __fmaf_rn(2.0f, b, -1.0f), __fmaf_rn(2.0f, c, -1.0f));
-        if (dot3(p, p) >= 1.0f) continue;
-        return p;
+        float3 p;
+        if (ball_trial(a, b, c, sampling, p)) return p;
+    }
+}
+// Same draws in the same order for a generator standing at a block boundary (every scatter() call: the stream is keyed
+// per bounce), consumed as whole Philox blocks with compile-time word indices: trials 4k..4k+3 use blocks 3k..3k+2.
+template <>
+__device__ __forceinline__ float3 random_in_unit_sphere<Rng>(Rng &rng, int sampling) {
+    float3 p;
+    if (!rng.at_block_start()) {
+        for (;;) {
+            float a = rng.next(), b = rng.next(), c = rng.next();
+            if (ball_trial(a, b, c, sampling, p)) return p;
+        }
+    }
+    for (;;) {
+        const uint4 A = rng.next_block();
+        if (ball_trial(rng.to_uniform(A.x), rng.to_uniform(A.y), rng.to_uniform(A.z), sampling, p)) return p;
+        const uint4 B = rng.next_block();
+        if (ball_trial(rng.to_uniform(A.w), rng.to_uniform(B.x), rng.to_uniform(B.y), sampling, p)) return p;
+        const uint4 C = rng.next_block();
+        if (ball_trial(rng.to_uniform(B.z), rng.to_uniform(B.w), rng.to_uniform(C.x), sampling, p)) return p;
+        if (ball_trial(rng.to_uniform(C.y), rng.to_uniform(C.z), rng.to_uniform(C.w), sampling, p)) return p;
     }
 }
 
