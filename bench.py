@@ -168,7 +168,7 @@ def main():
     import torch
     import torch.distributed as dist
     rt = ge.load_package()
-    from rt_b200 import capi
+    from rt_b200 import capi, multi_gpu
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -179,22 +179,17 @@ def main():
     scene, W, H, spp = WORKLOADS[args.workload]
     text = scene_text(scene, W, H, spp)
     stream = torch.cuda.Stream()
-    s0, s1 = rank * spp // world, (rank + 1) * spp // world        # this rank's slice of the sample indices
+    s0, s1 = multi_gpu.spp_slice(spp, rank, world)                 # this rank's slice of the sample indices
     flags = capi.RT_RENDER_TIME_STAGES | (capi.RT_RENDER_NO_SORT if args.no_sort else 0)
 
     with torch.cuda.stream(stream):
         r = rt.Renderer(local, stream=stream.cuda_stream)
         r.upload_json_text(text, GOLDEN)
-        ptr, nfl = r.accum_device_ptr()
-
-        class _CAI:      # zero-copy torch view of the library's accumulation buffer for the NCCL reduce
-            __cuda_array_interface__ = {"shape": (nfl,), "typestr": "<f4", "data": (ptr, False), "version": 3}
-        accum = torch.as_tensor(_CAI(), device=f"cuda:{local}")
+        accum = multi_gpu.accum_view(r, local)      # zero-copy torch view of the library's accumulation buffer
 
         def step_resident():
             r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=flags, max_paths_per_pass=args.max_paths)
-            if world > 1:
-                dist.reduce(accum, dst=0)
+            multi_gpu.reduce_image(accum, dst=0)
 
         def barrier():
             if world > 1:
@@ -234,8 +229,7 @@ def main():
         def step_e2e():
             r.upload_json_text(text, GOLDEN)
             r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=0, max_paths_per_pass=args.max_paths)
-            if world > 1:
-                dist.reduce(accum, dst=0)
+            multi_gpu.reduce_image(accum, dst=0)
             if rank == 0:
                 return r.download(gamma=0)
             r.synchronize()
@@ -265,7 +259,10 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         ach = ext_flops / (ms_extend * 1e-3) / 1e12 if ms_extend > 0 else 0.0
-        queue_bytes = (168.0 * st["rays"] / args.steps) + 80.0 * total_samples / world
+        # algorithmic bytes of the queue stages on this rank: generate W48/sample; shade R56/ray + W48 per
+        # survivor (rays - samples) + W16 per finished path; accumulate R16/sample (+12 B/pixel RMW per pass, ignored)
+        rays_rank, samples_rank = st["rays"] / args.steps, total_samples / world
+        queue_bytes = 48.0 * samples_rank + 56.0 * rays_rank + 48.0 * (rays_rank - samples_rank) + 16.0 * samples_rank + 16.0 * samples_rank
         hbm_ach = queue_bytes / (ms_other * 1e-3) / 1e9 if ms_other > 0 else 0.0
         sc_desc = json.loads(text)
         h2d = 64 * len(sc_desc["object"]["data"]) + 32 * (len(sc_desc["material"]["data"]) + len(sc_desc["texture"]["data"])) + len(text)
@@ -283,7 +280,7 @@ def main():
                          "note": "algorithmic FLOPs (SURVEY §8(d) model, device event counters) / CUDA-event time of the extend launches "
                                  "in the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)"},
             "roofline_hbm": {"bound": "hbm", "kernel": "generate+shade+accumulate", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": hbm_ach / hbm_peak, "note": "168 B/segment + 80 B/sample (SURVEY §8(d)) / CUDA-event time of those stages; peak from MEASURED_PEAKS.json" if peaks else "fallback peak"},
+                             "frac": hbm_ach / hbm_peak, "note": ("104 B/ray + 32 B/sample (DESIGN.md §6) / CUDA-event time of those stages; peak from MEASURED_PEAKS.json (of measured)" if peaks else "of fallback")},
             "e2e": {"value": total_samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": W * H * 3 * 4 + W * H * 3, "ms_per_step": ms_e2e},
             "gpu_launches": int(st["launches"] / args.steps), "clocks": clocks,

@@ -3,5 +3,5 @@
 The directory name contains hyphens (it follows the reference repository's name), so import it through
 `__graft_entry__.load_package()`, which registers it as the module `rt_b200`.
 """
-from . import capi  # noqa: F401
+from . import capi, multi_gpu  # noqa: F401
 from .renderer import Renderer, RtError, parse_scene, render_scene_file  # noqa: F401

@@ -91,3 +91,18 @@ def test_animation_rules_follow_the_reference_scripts():
     base = [o for o in blue2["object"]["data"] if o["type"] == "cylinder"]
     assert [c["rotate"]["angle"] for c in cyl] == [b["rotate"]["angle"] + 8 for b in base]
     assert animation.frames_for_rank(20, 3, 8) == [3, 11, 19]
+
+
+def test_cli_keeps_the_reference_exit_code_without_a_device(lib, tmp_path):
+    """parallel_compute -f scene.json: exit 99 on failure like check_cuda() (rtweekend.cuh:43-53); never a CPU render."""
+    import subprocess
+    import torch
+    cli = os.path.join(ROOT, "ray-tracing-in-cuda_b200", "parallel_compute")
+    assert os.path.exists(cli)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = subprocess.run([cli, "-f", os.path.join(ROOT, "tests", "golden", "sample_scene.json")], cwd=tmp_path, capture_output=True, text=True)
+    assert p.returncode == 99 and "no CUDA device" in p.stderr
+    assert not (tmp_path / "main.ppm").exists()
+    p = subprocess.run([cli, "--bogus"], cwd=tmp_path, capture_output=True, text=True)
+    assert p.returncode == 99

@@ -248,3 +248,25 @@ def test_errors_are_reported_not_fatal(rt):
                                         "material": {"data": []}, "texture": {"data": []}}))
     rt.upload_json(scene_path("sample_scene"))      # the context is still usable
     assert rt.info().n_objects == 6
+
+
+def test_cli_matches_the_library_and_the_reference_contract(rt, tmp_path):
+    """parallel_compute -f scene.json (main.cu:448-522): writes main.ppm + output_file, exit 0; pixels equal rt_download's."""
+    import subprocess
+    from PIL import Image
+    d = json.load(open(scene_path("sample_scene")))
+    d.update(width=64, height=36, samples_per_pixel=3, output_file=str(tmp_path / "out.png"))
+    f = tmp_path / "s.json"
+    f.write_text(json.dumps(d))
+    cli = os.path.join(os.path.dirname(capi.LIB_PATH), "parallel_compute")
+    p = subprocess.run([cli, "-f", str(f)], cwd=tmp_path, capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    rt.upload_json(str(f))
+    rt.render(seed=0x2023)
+    _, png8, _ = rt.download(gamma=0)
+    _, ppm8, _ = rt.download(gamma=1, want_sum=False)
+    assert np.array_equal(np.asarray(Image.open(tmp_path / "out.png")), png8)
+    assert np.array_equal(np.asarray(Image.open(tmp_path / "main.ppm")), ppm8)
+    bad = tmp_path / "bad.json"
+    bad.write_text("{ not json")
+    assert subprocess.run([cli, "-f", str(bad)], cwd=tmp_path, capture_output=True).returncode == 99
