@@ -31,6 +31,9 @@ WORKLOADS = {
     "dna000_1080p_1024spp": ("dna_000.json", 1920, 1080, 1024),
     "blue2_1080p_256spp": ("blue2.json", 1920, 1080, 256),
     "sample_scene_1600x900_512spp": ("sample_scene.json", 1600, 900, 512),
+    # config 4: procedural ~1M-triangle mesh (scenes.mesh_scene, seeded) under the GPU LBVH; "@" = tables, not a JSON file
+    "mesh1m_4k_1024spp": ("@mesh:708", 3840, 2160, 1024),
+    "mesh1m_1080p_64spp": ("@mesh:708", 1920, 1080, 64),
 }
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "cmake_cpu_mt")
@@ -89,6 +92,22 @@ def scene_text(name, width, height, spp):
     return json.dumps(d)
 
 
+def make_upload(rt, workload):
+    """Returns (upload(renderer), description dict): JSON text through rt_scene_upload_json_text, or flat tables through
+    rt_scene_upload for the procedural mesh workloads."""
+    scene, W, H, spp = WORKLOADS[workload]
+    if scene.startswith("@mesh"):
+        from rt_b200 import scenes
+        n = int(scene.split(":")[1])
+        ts = scenes.mesh_scene(n, n, W, H, spp)
+        desc = {"max_depth": ts.desc.max_depth, "objects": int(ts.desc.n_objects), "h2d": int(ts.objects.nbytes) + 32 * 8, "tables": ts}
+        return (lambda r: r.upload(ts)), desc
+    text = scene_text(scene, W, H, spp)
+    d = json.loads(text)
+    h2d = 64 * len(d["object"]["data"]) + 32 * (len(d["material"]["data"]) + len(d["texture"]["data"])) + len(text)
+    return (lambda r: r.upload_json_text(text, GOLDEN)), {"max_depth": d["max_depth"], "objects": len(d["object"]["data"]), "h2d": h2d, "text": text}
+
+
 def run_reference_binary(width, height, spp, procs):
     """Runs `procs` concurrent copies of the UNMODIFIED reference cmake-cpu-version binary (it is single-threaded:
     cmake-cpu-version/main.cpp has no omp pragma).  Returns wall seconds for all of them."""
@@ -105,14 +124,35 @@ def run_reference_binary(width, height, spp, procs):
     return dt
 
 
+def oracle_sample(workload, threads, w, h, s):
+    """The CPU restatement (oracle/, brute-force closest hit like the reference's hittable_list) on a bounded sample."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import orc
+    scene, W, H, spp = WORKLOADS[workload]
+    if scene.startswith("@mesh"):
+        rt = ge.load_package()
+        from rt_b200 import scenes
+        n = int(scene.split(":")[1])
+        sc = scenes.mesh_scene(n, n, w, h, s)
+        sc.desc.camera.aspect = W / H
+    else:
+        sc = orc.load_scene(json.loads(scene_text(scene, W, H, spp)), width=w, height=h, spp=s)
+    t0 = time.time(); orc.render(sc, threads=threads); dt = time.time() - t0
+    return w * h * s, dt, f"oracle port {w}x{h}x{s}spp, {threads} thread(s), brute-force closest hit", "port"
+
+
 def reference_sample(workload, procs):
     """A bounded sample of the workload for the CPU arm: same scene and camera, reduced size (the reference keeps the
-    16:9 camera regardless of -w/-h, main.cpp:64,94) and 1 spp.  Returns (samples, seconds, description)."""
+    16:9 camera regardless of -w/-h, main.cpp:64,94).  Returns (samples, seconds, description, kind)."""
     scene, W, H, spp = WORKLOADS[workload]
-    if scene == "rtiow_486.json":
+    if scene.startswith("@mesh"):      # the reference has no C++ mesh path at all: the oracle port is the CPU statement
+        return oracle_sample(workload, procs, 32, 18, 1)
+    if scene == "rtiow_486.json" and os.path.exists(REF_BIN):
         w, h, s = 960, 540, 1
         dt = run_reference_binary(w, h, s, procs)
-        return procs * w * h * s, dt, f"{procs} x cmake_cpu_mt -w {w} -h {h} -spp {s} -d 50 (unmodified reference binary, 1 thread each)"
+        return procs * w * h * s, dt, f"{procs} x cmake_cpu_mt -w {w} -h {h} -spp {s} -d 50 (unmodified reference binary, 1 thread each)", "reference"
+    if not os.path.exists(REF_GPU_HARNESS):
+        return oracle_sample(workload, procs, 480, 270, 4)
     # JSON scenes: the reference gpu-version headers compiled for the host (oracle/_ref/ref_gpu_harness), `procs` threads
     w, h, s = 480, 270, 16
     d = json.loads(scene_text(scene, w, h, s))
@@ -122,7 +162,7 @@ def reference_sample(workload, procs):
         t0 = time.time()
         subprocess.run([REF_GPU_HARNESS, "render", fs, "1", os.path.join(td, "o.bin"), str(procs)], check=True, capture_output=True)
         dt = time.time() - t0
-    return w * h * s, dt, f"ref_gpu_harness render {w}x{h}x{s}spp, {procs} threads (reference gpu-version headers on the host)"
+    return w * h * s, dt, f"ref_gpu_harness render {w}x{h}x{s}spp, {procs} threads (reference gpu-version headers on the host)", "reference"
 
 
 def main_reference(args):
@@ -131,14 +171,11 @@ def main_reference(args):
         return
     procs = os.cpu_count() or 1
     scene, W, H, spp = WORKLOADS[args.workload]
-    if not os.path.exists(REF_BIN):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (run __graft_entry__.build() where /root/reference is mounted)"}))
-        return
     for _ in range(args.warmup):
         reference_sample(args.workload, procs)
-    tot_s, tot_t, desc = 0, 0.0, ""
+    tot_s, tot_t, desc, kind = 0, 0.0, "", "port"
     for _ in range(args.steps):
-        n, dt, desc = reference_sample(args.workload, procs)
+        n, dt, desc, kind = reference_sample(args.workload, procs)
         tot_s += n; tot_t += dt
     v = tot_s / tot_t
     print(json.dumps({
@@ -146,7 +183,7 @@ def main_reference(args):
         "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64" if scene == "rtiow_486.json" else "f32", "data": "synthetic",
         "config": {"workload": args.workload, "scene": scene, "width": W, "height": H, "spp": spp, "note": "CPU arm renders a bounded sample of this workload per step"},
-        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": procs, "kind": "reference", "sample": desc},
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": procs, "kind": kind, "sample": desc},
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
 
 
@@ -177,14 +214,14 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     scene, W, H, spp = WORKLOADS[args.workload]
-    text = scene_text(scene, W, H, spp)
+    upload, sdesc = make_upload(rt, args.workload)
     stream = torch.cuda.Stream()
     s0, s1 = multi_gpu.spp_slice(spp, rank, world)                 # this rank's slice of the sample indices
     flags = capi.RT_RENDER_TIME_STAGES | (capi.RT_RENDER_NO_SORT if args.no_sort else 0)
 
     with torch.cuda.stream(stream):
         r = rt.Renderer(local, stream=stream.cuda_stream)
-        r.upload_json_text(text, GOLDEN)
+        upload(r)
         accum = multi_gpu.accum_view(r, local)      # zero-copy torch view of the library's accumulation buffer
 
         def step_resident():
@@ -227,7 +264,7 @@ def main():
 
         # ---- e2e: host JSON text -> upload (+BVH build) -> render -> reduce -> download to host, every step ----
         def step_e2e():
-            r.upload_json_text(text, GOLDEN)
+            upload(r)
             r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=0, max_paths_per_pass=args.max_paths)
             multi_gpu.reduce_image(accum, dst=0)
             if rank == 0:
@@ -264,13 +301,12 @@ def main():
         rays_rank, samples_rank = st["rays"] / args.steps, total_samples / world
         queue_bytes = 48.0 * samples_rank + 56.0 * rays_rank + 48.0 * (rays_rank - samples_rank) + 16.0 * samples_rank + 16.0 * samples_rank
         hbm_ach = queue_bytes / (ms_other * 1e-3) / 1e9 if ms_other > 0 else 0.0
-        sc_desc = json.loads(text)
-        h2d = 64 * len(sc_desc["object"]["data"]) + 32 * (len(sc_desc["material"]["data"]) + len(sc_desc["texture"]["data"])) + len(text)
+        h2d = sdesc["h2d"]
         line = {
             "metric": "samples_per_second", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "scene": scene, "width": W, "height": H, "spp": spp, "max_depth": sc_desc["max_depth"],
-                       "objects": len(sc_desc["object"]["data"]), "partition": f"spp split over {world} GPU(s), one NCCL reduce of the float accumulation buffer",
+            "config": {"workload": args.workload, "scene": scene, "width": W, "height": H, "spp": spp, "max_depth": sdesc["max_depth"],
+                       "objects": sdesc["objects"], "partition": f"spp split over {world} GPU(s), one NCCL reduce of the float accumulation buffer",
                        "l2": "wavefront queues (GBs) exceed the 126 MB L2 every pass; no explicit flush needed"},
             "mrays_per_s": rays / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays / total_samples,
             "stage_ms_per_step": {"generate": st["ms_generate"] / args.steps, "extend": ms_extend, "shade": st["ms_shade"] / args.steps,
@@ -285,15 +321,9 @@ def main():
                     "d2h_bytes_per_step": W * H * 3 * 4 + W * H * 3, "ms_per_step": ms_e2e},
             "gpu_launches": int(st["launches"] / args.steps), "clocks": clocks,
         }
-        if world == 1 and not args.no_cpu_baseline and os.path.exists(REF_BIN):
-            n, dt, desc = reference_sample(args.workload, 1)
-            line["cpu_baseline"] = {"value": n / dt, "unit": "samples/s", "cores": 1, "kind": "reference", "sample": desc.replace("1 x ", "")}
-        elif world == 1 and not args.no_cpu_baseline:
-            sys.path.insert(0, os.path.join(ROOT, "tests"))
-            import orc
-            sc = orc.load_scene(json.loads(text), width=240, height=135, spp=4)
-            t0 = time.time(); orc.render(sc, threads=1); dt = time.time() - t0
-            line["cpu_baseline"] = {"value": 240 * 135 * 4 / dt, "unit": "samples/s", "cores": 1, "kind": "port", "sample": "oracle 240x135x4spp, 1 thread"}
+        if world == 1 and not args.no_cpu_baseline:
+            n, dt, desc, kind = reference_sample(args.workload, 1)
+            line["cpu_baseline"] = {"value": n / dt, "unit": "samples/s", "cores": 1, "kind": kind, "sample": desc.replace("1 x ", "")}
         print(json.dumps(line))
     r.close()
     if world > 1:

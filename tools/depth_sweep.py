@@ -11,7 +11,9 @@ workload = sys.argv[1] if len(sys.argv) > 1 else "rtiow_1080p_1024spp"
 scene, W, H, spp = bench.WORKLOADS[workload]
 spp = int(sys.argv[2]) if len(sys.argv) > 2 else 16
 r = rt.Renderer(0)
-r.upload_json_text(bench.scene_text(scene, W, H, spp), bench.GOLDEN)
+bench.WORKLOADS[workload] = (scene, W, H, spp)
+upload, _ = bench.make_upload(rt, workload)
+upload(r)
 prev = None
 for depth in (1, 2, 3, 4, 6, 8, 12, 16, 24, 50):
     r.override(max_depth=depth)

@@ -16,7 +16,9 @@ scene, W, H, spp = bench.WORKLOADS[workload]
 if len(sys.argv) > 3:
     spp = int(sys.argv[3])
 r = rt.Renderer(0)
-r.upload_json_text(bench.scene_text(scene, W, H, spp), bench.GOLDEN)
+bench.WORKLOADS[workload] = (scene, W, H, spp)
+upload, _ = bench.make_upload(rt, workload)
+upload(r)
 for _ in range(renders):
     r.render(seed=0x2023)
 _, _, st = r.download(want_sum=False, want_rgb8=False)

@@ -19,7 +19,9 @@ spp = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 extra = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 r = rt.Renderer(0)
-r.upload_json_text(bench.scene_text(scene, W, H, spp), bench.GOLDEN)
+bench.WORKLOADS[workload] = (scene, W, H, spp)
+upload, _ = bench.make_upload(rt, workload)
+upload(r)
 r.render(seed=0x2023, flags=capi.RT_RENDER_COUNT_EVENTS | extra, spp_count=max(1, spp // 8))
 _, _, c = r.download(want_sum=False, want_rgb8=False)
 rays = c["rays"]
