@@ -436,7 +436,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
             timed(2, [&] { launch_shade(ctx->cfg, ds, ctx->q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort); });
             buf ^= 1;
         }
-        timed(3, [&] { launch_accumulate(ctx->cfg, ctx->q, ctx->d_accum.p, np, sn, clear, ds.max_depth, ctx->d_rays.p); });
+        timed(3, [&] { launch_accumulate(ctx->cfg, ctx->q, ctx->d_accum.p, ds.width, ds.height, sn, clear, ds.max_depth, ctx->d_rays.p); });
         clear = false;
         ++passes;
     }

@@ -51,7 +51,7 @@ __global__ void k_pass_init(Queues q, int max_depth, int n_paths) {
 __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsigned seed, int spp_begin, int n_paths) {
     const int np = sc.width * sc.height;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_paths; i += gridDim.x * blockDim.x) {
-        const int s_local = i / np, pixel = i - s_local * np;
+        const int s_local = i / np, pixel = plane_to_pixel(sc.width, sc.height, i - s_local * np);
         const int y = pixel / sc.width, x = pixel - y * sc.width;
         Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), 0u, sc.sampling);
         const float u = ((float)x + rng.next()) / (float)(sc.width - 1);
@@ -369,7 +369,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
                     rad = thr * texture_value(sc, m.texture, rec.u, rec.v, rec.p);
                 } else {
-                    const int s_local = path_id / np, pixel = path_id - s_local * np;
+                    const int s_local = path_id / np, pixel = plane_to_pixel(sc.width, sc.height, path_id - s_local * np);
                     Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), (unsigned)bounce + 1u, sc.sampling);
                     float3 att, sd;
                     if (scatter(sc, m, d, rec, rng, att, sd) && !last_bounce) {
@@ -417,19 +417,21 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
 // accumulate: accum[pixel] += sum over this pass's samples, in ascending sample order (fixed order => the image is
 // bit-reproducible; replaces the register sum of main.cu:95-104).  One thread per pixel, S coalesced plane reads.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restrict__ radiance, float *__restrict__ accum, int np,
+__global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restrict__ radiance, float *__restrict__ accum, int W, int H,
                                                          int n_samples, int clear, const int *__restrict__ qcount, int max_depth,
                                                          unsigned long long *total_rays) {
+    const int np = W * H;
     if (blockIdx.x == 0 && threadIdx.x == 0) {     // rays traced this pass = sum of the per-bounce queue lengths
         unsigned long long r = 0;
         for (int b = 0; b < max_depth; ++b) r += (unsigned long long)qcount[b];
         *total_rays += r;
     }
-    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < np; p += gridDim.x * blockDim.x) {
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < np; k += gridDim.x * blockDim.x) {
+        const int p = plane_to_pixel(W, H, k);
         float r = 0.0f, g = 0.0f, b = 0.0f;
         if (!clear) { r = accum[3 * p]; g = accum[3 * p + 1]; b = accum[3 * p + 2]; }
         for (int s = 0; s < n_samples; ++s) {
-            const float4 c = radiance[(long long)s * np + p];
+            const float4 c = radiance[(long long)s * np + k];
             r += c.x; g += c.y; b += c.z;
         }
         accum[3 * p] = r; accum[3 * p + 1] = g; accum[3 * p + 2] = b;
@@ -573,10 +575,10 @@ void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigne
     bump(c);
 }
 
-void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int np, int n_samples, bool clear, int max_depth,
+void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W, int H, int n_samples, bool clear, int max_depth,
                        unsigned long long *total_rays) {
-    int blocks = (np + RT_BLOCK - 1) / RT_BLOCK;
-    k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, accum, np, n_samples, clear ? 1 : 0, q.qcount, max_depth, total_rays);
+    int blocks = (W * H + RT_BLOCK - 1) / RT_BLOCK;
+    k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, accum, W, H, n_samples, clear ? 1 : 0, q.qcount, max_depth, total_rays);
     bump(c);
 }
 

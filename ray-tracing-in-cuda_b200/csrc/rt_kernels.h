@@ -15,7 +15,7 @@ void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsi
 void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort);
 void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
                   bool last_bounce, bool count, bool sort);
-void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int np, int n_samples, bool clear, int max_depth,
+void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W, int H, int n_samples, bool clear, int max_depth,
                        unsigned long long *total_rays);
 void launch_sum_ordered(const LaunchCfg &c, float *accum, const float *const *partials_dev, int n_partials, long long n);
 void launch_tonemap(const LaunchCfg &c, const float *accum, unsigned char *rgb8, int W, int H, int spp, int gamma);

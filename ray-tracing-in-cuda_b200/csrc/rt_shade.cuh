@@ -130,6 +130,26 @@ __device__ __forceinline__ bool scatter(const DScene &sc, const DMaterial &m, fl
     }
 }
 
+// Position k of a sample plane -> pixel index.  Camera paths are laid out in 8x4 pixel tiles (one warp = one tile), so the
+// 32 primary rays of a warp form a compact bundle instead of a 32x1 strip; pixels outside the tiled W8 x H4 region
+// (right and top margins when the image size is not a multiple of the tile) follow in row order.  Pure bookkeeping:
+// the Philox key is the true pixel index, so images do not depend on this layout.
+__device__ __forceinline__ int plane_to_pixel(int W, int H, int k) {
+    const int W8 = W & ~7, H4 = H & ~3, nt = W8 * H4;
+    int x, y;
+    if (k < nt) {
+        const int tile = k >> 5, j = k & 31, tiles_x = W8 >> 3;
+        const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
+        x = tx * 8 + (j & 7); y = ty * 4 + (j >> 3);
+    } else {
+        int r = k - nt;
+        const int wr = W - W8;
+        if (r < wr * H4) { y = r / wr; x = W8 + (r - y * wr); }
+        else { r -= wr * H4; y = H4 + r / W; x = r - (r / W) * W; }
+    }
+    return y * W + x;
+}
+
 // miss colour: constant background (main.cu:61-63) or the RTIOW sky gradient (cmake-cpu-version/main.cpp:36-38)
 __device__ __forceinline__ float3 background(const DScene &sc, float3 d) {
     if (sc.bg_mode == RT_BG_SKY_GRADIENT) {
