@@ -78,7 +78,7 @@ extern "C" void rt_destroy(rt_ctx *c) {
     c->d_obmin.release(); c->d_obmax.release(); c->d_node_aabb.release(); c->d_leaf_aabb.release(); c->d_bounds.release();
     c->d_hist.release(); c->d_keys[0].release(); c->d_keys[1].release(); c->d_vals[0].release(); c->d_vals[1].release();
     c->d_left.release(); c->d_right.release(); c->d_parent.release(); c->d_flags.release(); c->d_prim_obj.release();
-    c->d_prim_mat.release(); c->d_nodes.release(); c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
+    c->d_prim_mat.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
     for (int k = 0; k < 2; ++k) { c->d_ray_o[k].release(); c->d_ray_d[k].release(); c->d_thr[k].release(); }
     c->d_radiance.release(); c->d_hits.release(); c->d_bins.release(); c->d_qcount.release(); c->d_bincount.release();
     c->d_workctr.release(); c->d_counters.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
@@ -230,14 +230,14 @@ static int upload_to_device(rt_ctx *ctx) {
     CU(ctx->d_hist.alloc(lbvh_hist_words(n)));
     CU(ctx->d_left.alloc(nn)); CU(ctx->d_right.alloc(nn)); CU(ctx->d_parent.alloc(2 * nn)); CU(ctx->d_flags.alloc(nn));
     CU(ctx->d_node_aabb.alloc(6 * nn)); CU(ctx->d_leaf_aabb.alloc(6 * nn));
-    CU(ctx->d_nodes.alloc(nn)); CU(ctx->d_primA.alloc(nn)); CU(ctx->d_primB.alloc(nn)); CU(ctx->d_primC.alloc(nn));
+    CU(ctx->d_nodes.alloc(nn)); CU(ctx->d_nodes_s.alloc(nn)); CU(ctx->d_primA.alloc(nn)); CU(ctx->d_primB.alloc(nn)); CU(ctx->d_primC.alloc(nn));
     CU(ctx->d_prim_obj.alloc(nn)); CU(ctx->d_prim_mat.alloc(nn));
     LbvhBuffers &lb = ctx->lb;
     lb.n = n; lb.objects = ctx->d_objects.p; lb.xforms = ctx->d_xforms.p; lb.obj_bmin = ctx->d_obmin.p; lb.obj_bmax = ctx->d_obmax.p;
     lb.bounds = ctx->d_bounds.p; lb.keys[0] = ctx->d_keys[0].p; lb.keys[1] = ctx->d_keys[1].p; lb.vals[0] = ctx->d_vals[0].p;
     lb.vals[1] = ctx->d_vals[1].p; lb.hist = ctx->d_hist.p; lb.left = ctx->d_left.p; lb.right = ctx->d_right.p;
     lb.parent = ctx->d_parent.p; lb.flags = ctx->d_flags.p; lb.node_aabb = ctx->d_node_aabb.p; lb.leaf_aabb = ctx->d_leaf_aabb.p;
-    lb.nodes = ctx->d_nodes.p; lb.primA = ctx->d_primA.p; lb.primB = ctx->d_primB.p; lb.primC = ctx->d_primC.p;
+    lb.nodes = ctx->d_nodes.p; lb.nodes_s = ctx->d_nodes_s.p; lb.primA = ctx->d_primA.p; lb.primB = ctx->d_primB.p; lb.primC = ctx->d_primC.p;
     lb.prim_obj = ctx->d_prim_obj.p; lb.prim_mat = ctx->d_prim_mat.p;
     CU(cudaEventRecord(ctx->ev0, s));
     lbvh_build(ctx->cfg, lb);
@@ -253,12 +253,12 @@ static int upload_to_device(rt_ctx *ctx) {
     ds.defocus = (d.sampling == RT_SAMPLING_REFERENCE_CPU && d.camera.aperture > 0.0f) ? 1 : 0;
     ds.background = make_float3(d.background[0], d.background[1], d.background[2]);
     camera_setup(d.camera, ds.cam);
-    ds.nodes = ctx->d_nodes.p; ds.primA = ctx->d_primA.p; ds.primB = ctx->d_primB.p; ds.primC = ctx->d_primC.p;
+    ds.nodes = ctx->d_nodes.p; ds.nodes_s = ctx->d_nodes_s.p; ds.primA = ctx->d_primA.p; ds.primB = ctx->d_primB.p; ds.primC = ctx->d_primC.p;
     ds.prim_obj = ctx->d_prim_obj.p; ds.prim_mat = ctx->d_prim_mat.p; ds.xforms = ctx->d_xforms.p; ds.mats = ctx->d_mats.p;
     ds.texs = ctx->d_texs.p; ds.images = ctx->d_images.p;
 
     // extend-kernel configuration: stage the whole BVH in shared memory when it leaves room for >= 2 CTAs per SM
-    const size_t bvh_bytes = sizeof(BvhNode) * (size_t)ds.n_nodes;
+    const size_t bvh_bytes = sizeof(BvhNodeS) * (size_t)ds.n_nodes;
     ctx->cfg.bvh_smem_bytes = 0;
     if (bvh_bytes <= ctx->smem_optin && bvh_bytes <= 100 * 1024) {
         if (extend_configure_smem(bvh_bytes) == cudaSuccess) ctx->cfg.bvh_smem_bytes = bvh_bytes;

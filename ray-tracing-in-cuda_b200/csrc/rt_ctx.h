@@ -49,7 +49,7 @@ struct rt_ctx {
     LbvhBuffers lb{};
     DevBuf<float> d_obmin, d_obmax, d_node_aabb, d_leaf_aabb; DevBuf<unsigned> d_bounds, d_hist;
     DevBuf<unsigned long long> d_keys[2]; DevBuf<int> d_vals[2], d_left, d_right, d_parent, d_flags, d_prim_obj, d_prim_mat;
-    DevBuf<BvhNode> d_nodes; DevBuf<float4> d_primA, d_primB, d_primC;
+    DevBuf<BvhNode> d_nodes; DevBuf<BvhNodeS> d_nodes_s; DevBuf<float4> d_primA, d_primB, d_primC;
     // wavefront
     Queues q{};
     DevBuf<float4> d_ray_o[2], d_ray_d[2], d_thr[2], d_radiance; DevBuf<int2> d_hits; DevBuf<int> d_bins, d_qcount, d_bincount, d_workctr;

@@ -67,148 +67,47 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
 // ------------------------------------------------------------------------------------------------
 // extend: closest hit for every ray of the bounce's queue (replaces hittable_list::hit, object.cuh:23-37).
 //
-// Persistent warps with PER-LANE dynamic ray fetch: a lane whose ray has terminated does not wait for the slowest
-// ray of its warp; as soon as RT_EXT_REFILL lanes are idle they are handed new rays from the warp's private batch
-// of queue indices (one global atomic per RT_EXT_BATCH rays).  Keeps SIMT lanes busy on incoherent bounces.
-// Box tests are one FFMA per slab plane (t = plane * (1/d) - o/d) with a conservative error margin; they only prune.
-// Leaf tests are the exact reference arithmetic (rt_scene.cuh), so the result equals the brute-force walk.
+// Persistent grid; a warp takes a private batch of consecutive queue indices with one global atomic (the batch size adapts
+// to the queue length, so short late-bounce queues still spread over every SM; CTAs that cannot get work leave before
+// staging the tree).  The whole tree is staged in shared memory in the sign-ordered layout when it fits, else the compact
+// 64-byte nodes are read through L1/L2.  Traversal itself: rt_traverse.cuh.  Output: 8 B per ray (t, leaf code).
+// Measured and rejected: per-lane refill of finished lanes, postponed/batched leaf tests, a 4-wide collapsed
+// tree with leaf ranges, binning rays by material here through global lists.
 // ------------------------------------------------------------------------------------------------
 #define RT_EXT_BLOCK 512
 #define RT_EXT_BATCH 256
-#define RT_EXT_REFILL 32
-#define RT_BOX_REL 9.5367431640625e-07f      // 2^-20: rcp.approx error + fma rounding, relative to t
-#define RT_BOX_ABS 2.384185791015625e-07f    // 2^-22 * max|o/d|: rounding of the hoisted o/d term
 
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf, int refill, int max_batch) {
+__global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf, int max_batch) {
     extern __shared__ float4 s_raw[];
     const int n = q.qcount[bounce];
     if (n == 0) return;
-    // batch of queue indices a warp takes per global atomic: large for long queues, small enough on short ones that
-    // every resident warp gets work; CTAs that cannot get any work leave before staging the BVH
     const int total_warps = gridDim.x * (RT_EXT_BLOCK / 32);
     int batch = (n + total_warps - 1) / total_warps;
     batch = batch < 32 ? 32 : (batch > max_batch ? max_batch : ((batch + 31) & ~31));
     if ((long long)blockIdx.x * (RT_EXT_BLOCK / 32) * batch >= n) return;
-    const BvhNode *nodes = sc.nodes;
+    const char *nodes = reinterpret_cast<const char *>(sc.nodes);
     if (SMEM) {
-        const float4 *src = reinterpret_cast<const float4 *>(sc.nodes);
-        for (int i = threadIdx.x; i < sc.n_nodes * 4; i += blockDim.x) s_raw[i] = __ldg(&src[i]);
+        const float4 *src = reinterpret_cast<const float4 *>(sc.nodes_s);
+        for (int i = threadIdx.x; i < sc.n_nodes * (int)(sizeof(BvhNodeS) / 16); i += blockDim.x) s_raw[i] = __ldg(&src[i]);
         __syncthreads();
-        nodes = reinterpret_cast<const BvhNode *>(s_raw);
+        nodes = reinterpret_cast<const char *>(s_raw);
     }
     int *cursor = &q.workctr[bounce * 2 + 0];
     const float4 *__restrict__ ray_o = q.ray_o[buf];
     const float4 *__restrict__ ray_d = q.ray_d[buf];
-    const bool no_prims = sc.n_prims == 0;
     TravCounters cnt = {};
-    int batch_next = 0, batch_end = 0;     // warp-uniform: this warp's private range of queue indices
-    bool exhausted = false;                // warp-uniform: the global cursor ran past the queue
-    // per-lane traversal state
-    bool active = false;
-    int ray_i = 0, cur = 0, sp = 0, best_code = -1;
-    float3 o = v3(0, 0, 0), d = v3(0, 0, 0), ood = v3(0, 0, 0), oo = v3(0, 0, 0);
-    float a = 1.0f, inv_a = 1.0f, E = 0.0f, best_t = FLT_MAX;
-    int2 stack[RT_TRAV_STACK];
-    const float tmin = 0.001f;
     for (;;) {
-        // ---- hand new rays to idle lanes ----
-        const unsigned idle = __ballot_sync(0xffffffffu, !active);
-        if (idle && !exhausted) {
-            if (batch_next == batch_end) {
-                const int base = warp_fetch(cursor, batch);
-                if (base >= n) { exhausted = true; batch_next = batch_end = 0; }
-                else { batch_next = base; batch_end = min(base + batch, n); }
-            }
-            const int take = min(__popc(idle), batch_end - batch_next);
-            if (!active) {
-                const int rank = __popc(idle & lanemask_lt());
-                if (rank < take) {
-                    ray_i = batch_next + rank;
-                    const float4 o4 = ray_o[ray_i], d4 = ray_d[ray_i];
-                    o = f4xyz(o4); d = f4xyz(d4);
-                    best_t = FLT_MAX; best_code = -1; sp = 0; cur = 0;
-                    a = dot3(d, d); inv_a = 1.0f / a;
-                    ood = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
-                    oo = v3(-(o.x * ood.x), -(o.y * ood.y), -(o.z * ood.z));
-                    float ex = fabsf(oo.x), ey = fabsf(oo.y), ez = fabsf(oo.z);
-                    ex = ex < INFINITY ? ex : 0.0f; ey = ey < INFINITY ? ey : 0.0f; ez = ez < INFINITY ? ez : 0.0f;
-                    E = RT_BOX_ABS * fmaxf(ex, fmaxf(ey, ez));
-                    active = true;
-                    if (no_prims) { q.hits[ray_i] = make_int2(__float_as_int(FLT_MAX), -1); active = false; }
-                }
-            }
-            batch_next += take;
+        const int base = warp_fetch(cursor, batch);
+        if (base >= n) break;
+        const int end = min(base + batch, n);
+#pragma unroll 1
+        for (int i = base + lane_id(); i < end; i += 32) {
+            const float4 o4 = ray_o[i], d4 = ray_d[i];
+            float t; int code;
+            traverse<SMEM, COUNT, false>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt);
+            q.hits[i] = make_int2(__float_as_int(t), code);
         }
-        if (!__any_sync(0xffffffffu, active)) {
-            if (exhausted) break;
-            continue;
-        }
-        // ---- traverse until enough lanes are idle again ----
-        const int thresh = exhausted ? 32 : refill;
-        do {
-            if (active) {
-                // next subtree that can still contain a closer (or equally close) hit; none left: the ray is done
-                auto pop_next = [&]() {
-                    for (;;) {
-                        if (sp == 0) {
-                            q.hits[ray_i] = make_int2(__float_as_int(best_t), best_code);
-                            active = false;
-                            break;
-                        }
-                        --sp;
-                        const int2 e = stack[sp];
-                        if (__int_as_float(e.y) <= best_t) { cur = e.x; break; }
-                    }
-                };
-                // leaf step first, inner step second: a lane that holds a leaf tests it, pops, and still takes part in
-                // this iteration's inner-node step (the two halves are executed by the warp anyway)
-                if (cur < 0) {
-                    const int code = ~cur;
-                    float t;
-                    const bool h = leaf_t(sc, code, o, d, a, inv_a, tmin, best_t, t);
-                    count_leaf<COUNT>(cnt, code, h);
-                    if (h) {
-                        bool take = t < best_t || best_code < 0;
-                        if (!take)   // t == best_t: the later object in the scene file wins (object.cuh:29-33)
-                            take = __ldg(&sc.prim_obj[code & RT_LEAF_SLOT_MASK]) > __ldg(&sc.prim_obj[best_code & RT_LEAF_SLOT_MASK]);
-                        if (take) { best_t = t; best_code = code; }
-                    }
-                    pop_next();
-                }
-                if (active && cur >= 0) {
-                    const float4 na = nodes[cur].a, nb = nodes[cur].b, nc = nodes[cur].c;
-                    const int4 nd = nodes[cur].d;
-                    if (COUNT) { cnt.box += 2; cnt.nodes++; }
-                    // left box: min (na.x na.y na.z) max (na.w nb.x nb.y); right box: min (nb.z nb.w nc.x) max (nc.y nc.z nc.w)
-                    float x0 = __fmaf_rn(na.x, ood.x, oo.x), x1 = __fmaf_rn(na.w, ood.x, oo.x);
-                    float y0 = __fmaf_rn(na.y, ood.y, oo.y), y1 = __fmaf_rn(nb.x, ood.y, oo.y);
-                    float z0 = __fmaf_rn(na.z, ood.z, oo.z), z1 = __fmaf_rn(nb.y, ood.z, oo.z);
-                    const float tnl = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
-                    const float tfl = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
-                    x0 = __fmaf_rn(nb.z, ood.x, oo.x); x1 = __fmaf_rn(nc.y, ood.x, oo.x);
-                    y0 = __fmaf_rn(nb.w, ood.y, oo.y); y1 = __fmaf_rn(nc.z, ood.y, oo.y);
-                    z0 = __fmaf_rn(nc.x, ood.z, oo.z); z1 = __fmaf_rn(nc.w, ood.z, oo.z);
-                    const float tnr = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
-                    const float tfr = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
-                    const bool hl = tnl <= __fmaf_rn(fabsf(tfl), RT_BOX_REL, tfl + E);
-                    const bool hr = tnr <= __fmaf_rn(fabsf(tfr), RT_BOX_REL, tfr + E);
-                    if (hl && hr) {
-                        const bool lfirst = tnl <= tnr;
-                        const float tfar = lfirst ? tnr : tnl;
-                        if (sp < RT_TRAV_STACK) {
-                            stack[sp] = make_int2(lfirst ? nd.y : nd.x, __float_as_int(__fmaf_rn(-fabsf(tfar), RT_BOX_REL, tfar) - E));
-                            ++sp;
-                        } else if (COUNT) cnt.overflow++;
-                        cur = lfirst ? nd.x : nd.y;
-                    } else if (hl || hr) {
-                        cur = hl ? nd.x : nd.y;
-                    } else {
-                        pop_next();
-                    }
-                }
-            }
-        } while (__popc(__ballot_sync(0xffffffffu, !active)) < thresh);
     }
     if (COUNT) {
         flush_counter<COUNT>(q.counters, CTR_BOX, cnt.box); flush_counter<COUNT>(q.counters, CTR_SPH_REJECT, cnt.sph_rej);
@@ -478,7 +377,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_aov(DScene sc, float *__restrict__
         float3 o, d;
         camera_ray(sc.cam, u, v, false, rng, o, d);
         float t; int code;
-        traverse<false, false>(sc, sc.nodes, o, d, 0.001f, FLT_MAX, t, code, cnt);
+        traverse<false, false, false>(sc, reinterpret_cast<const char *>(sc.nodes), o, d, 0.001f, FLT_MAX, t, code, cnt);
         float q[24];
 #pragma unroll
         for (int k = 0; k < 24; ++k) q[k] = 0.0f;
@@ -533,10 +432,9 @@ template <bool SMEM>
 static void launch_extend_t(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count) {
     const int grid = persistent_grid(c, c.extend_blocks_per_sm);
     const size_t sm = SMEM ? c.bvh_smem_bytes : 0;
-    static const int refill = getenv("RT_EXT_REFILL") ? atoi(getenv("RT_EXT_REFILL")) : RT_EXT_REFILL;
     static const int batch = getenv("RT_EXT_BATCH") ? atoi(getenv("RT_EXT_BATCH")) : RT_EXT_BATCH;
-    if (count) k_extend<SMEM, true><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, refill, batch);
-    else k_extend<SMEM, false><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, refill, batch);
+    if (count) k_extend<SMEM, true><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
+    else k_extend<SMEM, false><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
 }
 
 void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort) {

@@ -40,6 +40,7 @@ struct LbvhBuffers {                // all device pointers, sized for n objects
     float *node_aabb, *leaf_aabb;   // 6 floats per internal node / per sorted leaf
     // outputs consumed by traversal
     BvhNode *nodes;
+    BvhNodeS *nodes_s;
     float4 *primA, *primB, *primC;
     int *prim_obj, *prim_mat;
 };

@@ -289,7 +289,8 @@ __global__ void __launch_bounds__(256) k_refit(int n, const float *__restrict__ 
 // step 7: pack into 64-byte traversal nodes (both child boxes inline)
 __global__ void __launch_bounds__(256) k_pack(int n, const int *__restrict__ left, const int *__restrict__ right,
                                               const float *__restrict__ node_aabb, const float *__restrict__ leaf_aabb,
-                                              const int *__restrict__ sorted, const DObject *__restrict__ objects, BvhNode *nodes) {
+                                              const int *__restrict__ sorted, const DObject *__restrict__ objects, BvhNode *nodes,
+                                              BvhNodeS *nodes_s) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int n_nodes = n >= 2 ? n - 1 : 1;
     if (i >= n_nodes) return;
@@ -315,6 +316,11 @@ __global__ void __launch_bounds__(256) k_pack(int n, const int *__restrict__ lef
     nd.c = make_float4(rb[2], rb[3], rb[4], rb[5]);
     nd.d = make_int4(lc, rc, 0, 0);
     nodes[i] = nd;
+    BvhNodeS ns;
+    ns.lx = make_float4(lb[0], lb[3], lb[3], lb[0]); ns.ly = make_float4(lb[1], lb[4], lb[4], lb[1]); ns.lz = make_float4(lb[2], lb[5], lb[5], lb[2]);
+    ns.rx = make_float4(rb[0], rb[3], rb[3], rb[0]); ns.ry = make_float4(rb[1], rb[4], rb[4], rb[1]); ns.rz = make_float4(rb[2], rb[5], rb[5], rb[2]);
+    ns.link = make_int4(lc, rc, 0, 0); ns.pad = make_int4(0, 0, 0, 0);
+    nodes_s[i] = ns;
 }
 
 size_t lbvh_hist_words(int n) { return (size_t)256 * (size_t)((n + RS_TILE - 1) / RS_TILE > 0 ? (n + RS_TILE - 1) / RS_TILE : 1); }
@@ -346,5 +352,5 @@ void lbvh_build(const LaunchCfg &c, LbvhBuffers &b) {
             k_refit<<<g, 256, 0, s>>>(n, b.leaf_aabb, b.left, b.right, b.parent, b.flags, b.node_aabb); bump();
         }
     }
-    k_pack<<<g, 256, 0, s>>>(n, b.left, b.right, b.node_aabb, b.leaf_aabb, b.vals[0], b.objects, b.nodes); bump();
+    k_pack<<<g, 256, 0, s>>>(n, b.left, b.right, b.node_aabb, b.leaf_aabb, b.vals[0], b.objects, b.nodes, b.nodes_s); bump();
 }

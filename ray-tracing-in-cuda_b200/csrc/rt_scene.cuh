@@ -14,6 +14,15 @@ struct __align__(16) BvhNode {   // 64 B: both child boxes + child links; one no
     float4 c;   // r.min.z r.max.x r.max.y r.max.z
     int4 d;     // left, right, unused, unused.   child >= 0: internal node; child < 0: leaf, ~child = type<<28 | slot
 };
+// The same node laid out for the extend stage's sign-ordered slab test (128 B).  Per box and axis the two planes are stored
+// as (lo, hi, hi, lo): an 8-byte load at offset 0 yields (near, far) for a ray travelling in +axis, at offset 8 for -axis,
+// so the traversal needs no per-plane min/max or select — the ray's direction signs are folded into the load address.
+struct __align__(16) BvhNodeS {
+    float4 lx, ly, lz;   // left child box
+    float4 rx, ry, rz;   // right child box
+    int4 link;           // left, right (same encoding as BvhNode::d), unused, unused
+    int4 pad;
+};
 #define RT_LEAF_SLOT_MASK 0x0fffffff
 #define RT_LEAF_NONE (~(7 << 28))   // a leaf code that is never hit (its box is empty)
 
@@ -28,7 +37,8 @@ struct DScene {
     int width, height, max_depth, sampling, bg_mode, defocus;
     float3 background;
     DCamera cam;
-    const BvhNode *nodes;
+    const BvhNode *nodes;                  // AOV pass and build tests
+    const BvhNodeS *nodes_s;               // extend stage
     const float4 *primA, *primB, *primC;   // geometry by leaf slot
     const int *prim_obj;                   // slot -> object index in the scene file (closest-hit tie rule)
     const int *prim_mat;                   // slot -> material index

@@ -2,9 +2,17 @@
 //
 // Result contract = the reference's linear walk: the accepted hit is the smallest root over all objects, and on an
 // exact tie in t the object with the LARGER scene-file index wins ("last index wins": the walk tests
-// `t_max < root`, so an equal root replaces the earlier one).  Box tests only prune; they are made
-// conservative (far plane inflated by 4 ulp, stack-cull deflated) so that no hit the linear walk would
-// accept can be culled — tests compare against the brute-force oracle and expect zero mismatching pixels.
+// `t_max < root`, so an equal root replaces the earlier one).  Box tests only prune; they are conservative
+// (one FFMA per slab plane, t = plane * (1/d) - o/d, with the error margin |t| * 2^-20 + 2^-22 * max|o/d| applied to the
+// hit test and to the stack cull), so no hit the linear walk would accept can be culled — tests compare against the
+// brute-force oracle and expect zero mismatching pixels.  Leaf tests are the exact reference arithmetic (rt_scene.cuh).
+//
+// Two node layouts, one algorithm:
+//   SIGNED = true   BvhNodeS (128 B): plane pairs stored (lo, hi, hi, lo) per box and axis; the ray's direction signs pick
+//                   the 8-byte half that reads (near, far), so a box costs 6 FFMA + 2 three-input min/max + 2 min/max.
+//                   Used when the whole tree is staged in shared memory.
+//   SIGNED = false  BvhNode (64 B): both boxes in three float4; near/far by per-axis min/max.  Half the bytes per visit —
+//                   used when the tree is read from global memory (L1/L2), where bytes matter more than ALU slots.
 #pragma once
 #include "rt_wavefront.cuh"
 #include <cfloat>
@@ -23,65 +31,98 @@ __device__ __forceinline__ void count_leaf(TravCounters &c, int code, bool hit) 
     }
 }
 
-// nodes: the node array to read (shared-memory copy of the whole tree when it fits, else global memory).
-// Returns best_t / best_code (-1 = miss).  ANY_HIT: stop at the first accepted hit (shadow rays).
-template <bool COUNT, bool ANY_HIT>
-__device__ __forceinline__ void traverse(const DScene &sc, const BvhNode *__restrict__ nodes, float3 o, float3 d, float tmin,
+#define RT_BOX_REL 9.5367431640625e-07f      // 2^-20: reciprocal + fma rounding, relative to t
+#define RT_BOX_ABS 2.384185791015625e-07f    // 2^-22 * max|o/d|: rounding of the hoisted o/d term
+#define RT_TRAV_DONE ((int)0x80000000)
+
+// nodes: BvhNodeS array (SIGNED) or BvhNode array (!SIGNED), in shared or global memory.
+// Returns best_t / best_code (-1 = miss).  ANY_HIT: stop at the first accepted hit (occlusion rays).
+template <bool SIGNED, bool COUNT, bool ANY_HIT>
+__device__ __forceinline__ void traverse(const DScene &sc, const char *__restrict__ nodes, float3 o, float3 d, float tmin,
                                          float tmax, float &best_t, int &best_code, TravCounters &cnt) {
     best_t = tmax; best_code = -1;
     if (sc.n_prims == 0) return;
-    const float3 ood = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     const float a = dot3(d, d), inv_a = 1.0f / a;
-    int stack_node[RT_TRAV_STACK];
-    float stack_t[RT_TRAV_STACK];
-    int sp = 0;
-    int cur = 0;
-    for (;;) {
-        if (cur >= 0) {
-            const float4 na = nodes[cur].a, nb = nodes[cur].b, nc = nodes[cur].c;
-            const int4 nd = nodes[cur].d;
-            if (COUNT) { cnt.box += 2; cnt.nodes++; }
-            // left box: min (na.x na.y na.z) max (na.w nb.x nb.y); right box: min (nb.z nb.w nc.x) max (nc.y nc.z nc.w)
-            float x0 = (na.x - o.x) * ood.x, x1 = (na.w - o.x) * ood.x;
-            float y0 = (na.y - o.y) * ood.y, y1 = (nb.x - o.y) * ood.y;
-            float z0 = (na.z - o.z) * ood.z, z1 = (nb.y - o.z) * ood.z;
-            float tnl = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
-            float tfl = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
-            x0 = (nb.z - o.x) * ood.x; x1 = (nc.y - o.x) * ood.x;
-            y0 = (nb.w - o.y) * ood.y; y1 = (nc.z - o.y) * ood.y;
-            z0 = (nc.x - o.z) * ood.z; z1 = (nc.w - o.z) * ood.z;
-            float tnr = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
-            float tfr = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
-            const bool hl = tnl <= tfl * 1.0000005f, hr = tnr <= tfr * 1.0000005f;
-            if (hl && hr) {
-                const bool lfirst = tnl <= tnr;
-                const int nearc = lfirst ? nd.x : nd.y, farc = lfirst ? nd.y : nd.x;
-                if (sp < RT_TRAV_STACK) { stack_node[sp] = farc; stack_t[sp] = lfirst ? tnr : tnl; ++sp; }
-                else if (COUNT) cnt.overflow++;
-                cur = nearc;
-                continue;
-            }
-            if (hl) { cur = nd.x; continue; }
-            if (hr) { cur = nd.y; continue; }
-        } else {
+    const float3 ood = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    const float3 oo = v3(-(o.x * ood.x), -(o.y * ood.y), -(o.z * ood.z));
+    float ex = fabsf(oo.x), ey = fabsf(oo.y), ez = fabsf(oo.z);
+    ex = ex < INFINITY ? ex : 0.0f; ey = ey < INFINITY ? ey : 0.0f; ez = ez < INFINITY ? ez : 0.0f;
+    const float E = RT_BOX_ABS * fmaxf(ex, fmaxf(ey, ez));
+    // 8 where the ray travels in the negative axis direction: selects the (near, far) half of a plane quadruple
+    const int sx = (__float_as_int(d.x) >> 31) & 8, sy = (__float_as_int(d.y) >> 31) & 8, sz = (__float_as_int(d.z) >> 31) & 8;
+    int2 stack[RT_TRAV_STACK];
+    int sp = 0, cur = 0;
+    // next subtree that can still contain a closer (or equally close) hit; none left: done
+#define RT_POP()                                                                 \
+    for (;;) {                                                                   \
+        if (sp == 0) { cur = RT_TRAV_DONE; break; }                              \
+        --sp;                                                                    \
+        const int2 e_ = stack[sp];                                               \
+        if (__int_as_float(e_.y) <= best_t) { cur = e_.x; break; }               \
+    }
+    while (cur != RT_TRAV_DONE) {
+        // leaf step first, inner step second: a lane that holds a leaf tests it, pops, and still takes part in this
+        // iteration's inner-node step (a diverged warp executes both halves anyway)
+        if (cur < 0) {
             const int code = ~cur;
             float t;
             const bool h = leaf_t(sc, code, o, d, a, inv_a, tmin, best_t, t);
             count_leaf<COUNT>(cnt, code, h);
             if (h) {
                 bool take = t < best_t || best_code < 0;
-                if (!take) {   // t == best_t: the later object in the scene file wins (object.cuh:29-33)
+                if (!take)   // t == best_t: the later object in the scene file wins (object.cuh:29-33)
                     take = __ldg(&sc.prim_obj[code & RT_LEAF_SLOT_MASK]) > __ldg(&sc.prim_obj[best_code & RT_LEAF_SLOT_MASK]);
-                }
                 if (take) { best_t = t; best_code = code; if (ANY_HIT) return; }
             }
+            RT_POP()
         }
-        // pop, skipping subtrees that start beyond the current closest hit
-        for (;;) {
-            if (sp == 0) return;
-            --sp;
-            cur = stack_node[sp];
-            if (stack_t[sp] * 0.9999995f <= best_t) break;
+        if (cur >= 0) {
+            float tnl, tfl, tnr, tfr;
+            int2 nd;
+            if (SIGNED) {
+                const char *nb = nodes + (size_t)cur * sizeof(BvhNodeS);
+                const float2 lx = *reinterpret_cast<const float2 *>(nb + 0 + sx), ly = *reinterpret_cast<const float2 *>(nb + 16 + sy);
+                const float2 lz = *reinterpret_cast<const float2 *>(nb + 32 + sz), rx = *reinterpret_cast<const float2 *>(nb + 48 + sx);
+                const float2 ry = *reinterpret_cast<const float2 *>(nb + 64 + sy), rz = *reinterpret_cast<const float2 *>(nb + 80 + sz);
+                nd = *reinterpret_cast<const int2 *>(nb + 96);
+                tnl = fmaxf(fmaxf(__fmaf_rn(lx.x, ood.x, oo.x), __fmaf_rn(ly.x, ood.y, oo.y)), fmaxf(__fmaf_rn(lz.x, ood.z, oo.z), tmin));
+                tfl = fminf(fminf(__fmaf_rn(lx.y, ood.x, oo.x), __fmaf_rn(ly.y, ood.y, oo.y)), fminf(__fmaf_rn(lz.y, ood.z, oo.z), best_t));
+                tnr = fmaxf(fmaxf(__fmaf_rn(rx.x, ood.x, oo.x), __fmaf_rn(ry.x, ood.y, oo.y)), fmaxf(__fmaf_rn(rz.x, ood.z, oo.z), tmin));
+                tfr = fminf(fminf(__fmaf_rn(rx.y, ood.x, oo.x), __fmaf_rn(ry.y, ood.y, oo.y)), fminf(__fmaf_rn(rz.y, ood.z, oo.z), best_t));
+            } else {
+                const BvhNode *nb = reinterpret_cast<const BvhNode *>(nodes) + cur;
+                const float4 na = nb->a, nbb = nb->b, nc = nb->c;
+                const int4 nd4 = nb->d;
+                nd = make_int2(nd4.x, nd4.y);
+                // left box: min (na.x na.y na.z) max (na.w nbb.x nbb.y); right box: min (nbb.z nbb.w nc.x) max (nc.y nc.z nc.w)
+                float x0 = __fmaf_rn(na.x, ood.x, oo.x), x1 = __fmaf_rn(na.w, ood.x, oo.x);
+                float y0 = __fmaf_rn(na.y, ood.y, oo.y), y1 = __fmaf_rn(nbb.x, ood.y, oo.y);
+                float z0 = __fmaf_rn(na.z, ood.z, oo.z), z1 = __fmaf_rn(nbb.y, ood.z, oo.z);
+                tnl = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+                tfl = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
+                x0 = __fmaf_rn(nbb.z, ood.x, oo.x); x1 = __fmaf_rn(nc.y, ood.x, oo.x);
+                y0 = __fmaf_rn(nbb.w, ood.y, oo.y); y1 = __fmaf_rn(nc.z, ood.y, oo.y);
+                z0 = __fmaf_rn(nc.x, ood.z, oo.z); z1 = __fmaf_rn(nc.w, ood.z, oo.z);
+                tnr = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+                tfr = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
+            }
+            if (COUNT) { cnt.box += 2; cnt.nodes++; }
+            const bool hl = tnl <= __fmaf_rn(fabsf(tfl), RT_BOX_REL, tfl + E);
+            const bool hr = tnr <= __fmaf_rn(fabsf(tfr), RT_BOX_REL, tfr + E);
+            if (hl && hr) {
+                const bool lfirst = tnl <= tnr;
+                const float tfar = lfirst ? tnr : tnl;
+                if (sp < RT_TRAV_STACK) {
+                    stack[sp] = make_int2(lfirst ? nd.y : nd.x, __float_as_int(__fmaf_rn(-fabsf(tfar), RT_BOX_REL, tfar) - E));
+                    ++sp;
+                } else if (COUNT) cnt.overflow++;
+                cur = lfirst ? nd.x : nd.y;
+            } else if (hl || hr) {
+                cur = hl ? nd.x : nd.y;
+            } else {
+                RT_POP()
+            }
         }
     }
+#undef RT_POP
 }
