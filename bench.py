@@ -195,7 +195,7 @@ def main():
     ap.add_argument("--workload", default="rtiow_1080p_1024spp", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-sort", action="store_true")
+    ap.add_argument("--sort", action="store_true", help="sort shade chunks by material class (RT_RENDER_SORT)")
     ap.add_argument("--max-paths", type=int, default=0)
     args = ap.parse_args()
     if args.impl == "reference":
@@ -217,7 +217,7 @@ def main():
     upload, sdesc = make_upload(rt, args.workload)
     stream = torch.cuda.Stream()
     s0, s1 = multi_gpu.spp_slice(spp, rank, world)                 # this rank's slice of the sample indices
-    flags = capi.RT_RENDER_TIME_STAGES | (capi.RT_RENDER_NO_SORT if args.no_sort else 0)
+    flags = capi.RT_RENDER_TIME_STAGES | (capi.RT_RENDER_SORT if args.sort else 0)
 
     with torch.cuda.stream(stream):
         r = rt.Renderer(local, stream=stream.cuda_stream)

@@ -110,9 +110,11 @@ typedef struct rt_scene_desc {
 /* rt_render flags */
 enum { RT_RENDER_KEEP_ACCUM = 1,     /* add to the accumulation buffer instead of clearing it first */
        RT_RENDER_COUNT_EVENTS = 2,   /* fill the event counters of rt_stats (slower; counts are deterministic) */
-       RT_RENDER_NO_SORT = 4,        /* do not bin rays by material before shading (ablation switch) */
+       RT_RENDER_NO_SORT = 4,        /* accepted and ignored (sorting is opt-in, see RT_RENDER_SORT) */
        RT_RENDER_NEE = 8,            /* next-event estimation through the shadow stage (changes the estimator; default off) */
-       RT_RENDER_TIME_STAGES = 16 }; /* record CUDA events around every stage launch (no synchronisation); per-stage ms in rt_stats */
+       RT_RENDER_TIME_STAGES = 16,   /* record CUDA events around every stage launch (no synchronisation); per-stage ms in rt_stats */
+       RT_RENDER_SORT = 32 };        /* sort every shade chunk by material class in shared memory (same image; pays off only for scenes
+                                        with an even material mix — measured slower on the reference's scenes) */
 
 typedef struct rt_render_params {
     uint32_t seed;          /* Philox key word 0 */

@@ -386,7 +386,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     const int spp = prm->spp_count > 0 ? prm->spp_count : ctx->hs.d.samples_per_pixel;
     if (prm->spp_begin < 0) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: spp_begin < 0");
     const bool count = (prm->flags & RT_RENDER_COUNT_EVENTS) != 0;
-    const bool sort = (prm->flags & RT_RENDER_NO_SORT) == 0;
+    const bool sort = (prm->flags & RT_RENDER_SORT) != 0;
     // wavefront size: whole sample planes, at most max_paths_per_pass paths and at most 2^30 queue entries
     long long max_paths = prm->max_paths_per_pass;
     if (max_paths <= 0) {

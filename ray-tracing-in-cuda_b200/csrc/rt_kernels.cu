@@ -59,8 +59,8 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
         float3 o, d;
         camera_ray(sc.cam, u, v, sc.defocus != 0, rng, o, d);
         q.ray_o[0][i] = make_float4(o.x, o.y, o.z, __int_as_float(i));
-        q.ray_d[0][i] = make_float4(d.x, d.y, d.z, 0.0f);
-        q.thr[0][i] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+        q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // Philox key words travel with the path:
+        q.thr[0][i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(s_local));      // no divisions in the shade stage
     }
 }
 
@@ -198,7 +198,6 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
     const int n_chunks = (n + RT_SH_CHUNK - 1) / RT_SH_CHUNK;
     if ((int)blockIdx.x >= n_chunks) return;
     const int tid = threadIdx.x, lane = tid & 31;
-    const int np = sc.width * sc.height;
     int *next_count = &q.qcount[bounce + 1];
     if (tid == 0) {
         mbar_init(&sm.full[0], 1); mbar_init(&sm.full[1], 1);
@@ -251,11 +250,12 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
         bool alive = false;
         float3 no = v3(0, 0, 0), nd = v3(0, 0, 0), nthr = v3(0, 0, 0);
         int path_id = 0;
+        float key_pixel = 0.0f, key_sample = 0.0f;
         if (tid < cnt) {
             const float4 o4 = sm.in_o[st][j], d4 = sm.in_d[st][j], t4 = sm.in_thr[st][j];
             const int2 h = sm.in_hit[st][j];
             const float3 o = f4xyz(o4), d = f4xyz(d4), thr = f4xyz(t4);
-            path_id = __float_as_int(o4.w);
+            path_id = __float_as_int(o4.w); key_pixel = d4.w; key_sample = t4.w;
             float3 rad = v3(0, 0, 0);
             if (h.y < 0) {
                 rad = thr * background(sc, d);
@@ -268,8 +268,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
                     rad = thr * texture_value(sc, m.texture, rec.u, rec.v, rec.p);
                 } else {
-                    const int s_local = path_id / np, pixel = plane_to_pixel(sc.width, sc.height, path_id - s_local * np);
-                    Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), (unsigned)bounce + 1u, sc.sampling);
+                    Rng rng; rng.init(seed, (unsigned)__float_as_int(d4.w), (unsigned)(spp_begin + __float_as_int(t4.w)), (unsigned)bounce + 1u, sc.sampling);
                     float3 att, sd;
                     if (scatter(sc, m, d, rec, rng, att, sd) && !last_bounce) {
                         alive = true;
@@ -290,8 +289,8 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
             pos = __shfl_sync(0xffffffffu, pos, leader) + __popc(m & lanemask_lt());
             if (alive) {
                 sm.out_o[pos] = make_float4(no.x, no.y, no.z, __int_as_float(path_id));
-                sm.out_d[pos] = make_float4(nd.x, nd.y, nd.z, 0.0f);
-                sm.out_thr[pos] = make_float4(nthr.x, nthr.y, nthr.z, 0.0f);
+                sm.out_d[pos] = make_float4(nd.x, nd.y, nd.z, key_pixel);
+                sm.out_thr[pos] = make_float4(nthr.x, nthr.y, nthr.z, key_sample);
             }
         }
         fence_proxy_async();                          // make the generic-proxy writes visible to the TMA engine

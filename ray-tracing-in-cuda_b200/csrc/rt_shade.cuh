@@ -85,9 +85,12 @@ __device__ __forceinline__ float3 reflect3(float3 v, float3 n) {   // vec3.cuh:1
 template <class R>
 __device__ __forceinline__ bool scatter(const DScene &sc, const DMaterial &m, float3 rd, const HitRec &rec, R &rng,
                                         float3 &att, float3 &sd) {
+    // lambertian and metal draw the same random_in_unit_sphere(): one shared (convergent) rejection loop for both classes,
+    // then the short class-specific tails — a warp holding a mix of the two pays for the expensive part once
+    float3 r = v3(0, 0, 0);
+    if (m.type == RT_MAT_LAMBERTIAN || m.type == RT_MAT_METAL) r = random_in_unit_sphere(rng, sc.sampling);
     switch (m.type) {
     case RT_MAT_LAMBERTIAN: {
-        float3 r = random_in_unit_sphere(rng, sc.sampling);
         if (sc.sampling == RT_SAMPLING_REFERENCE_CPU) r = vunit(r);     // random_unit_vector (material.h:27)
         float3 dir = rec.n + r;
         if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = rec.n;
@@ -97,7 +100,6 @@ __device__ __forceinline__ bool scatter(const DScene &sc, const DMaterial &m, fl
     }
     case RT_MAT_METAL: {
         float3 refl = reflect3(vunit(rd), rec.n);
-        float3 r = random_in_unit_sphere(rng, sc.sampling);
         sd = vfma(m.fuzz, r, refl);
         att = f4xyz(m.albedo);
         return dot3(sd, rec.n) > 0.0f;

@@ -142,7 +142,7 @@ def test_render_options_do_not_change_the_image(rt):
     rt.override(width=W, height=H, spp=spp)
     rt.render(seed=5)
     base, _, _ = rt.download()
-    rt.render(seed=5, flags=capi.RT_RENDER_NO_SORT)
+    rt.render(seed=5, flags=capi.RT_RENDER_SORT)
     assert np.array_equal(rt.download()[0], base)
     rt.render(seed=5, max_paths_per_pass=W * H * 2)
     assert np.array_equal(rt.download()[0], base)
