@@ -34,6 +34,9 @@ WORKLOADS = {
     # config 4: procedural ~1M-triangle mesh (scenes.mesh_scene, seeded) under the GPU LBVH; "@" = tables, not a JSON file
     "mesh1m_4k_1024spp": ("@mesh:708", 3840, 2160, 1024),
     "mesh1m_1080p_64spp": ("@mesh:708", 1920, 1080, 64),
+    # config 5: blue2.py's moving-cylinder animation, frames dealt round-robin to the ranks (no collective)
+    "blue2_anim_240f_1080p_256spp": ("@anim:blue2:240", 1920, 1080, 256),
+    "blue2_anim_16f_1080p_64spp": ("@anim:blue2:16", 1920, 1080, 64),
 }
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "cmake_cpu_mt")
@@ -124,11 +127,19 @@ def run_reference_binary(width, height, spp, procs):
     return dt
 
 
+def _still_scene(workload):
+    """(scene file or @mesh tag, W, H, spp); an animation workload is represented by its base scene (frame rule not applied)."""
+    scene, W, H, spp = WORKLOADS[workload]
+    if scene.startswith("@anim"):
+        scene = {"blue2": "blue2.json", "blue": "blue.json", "dna": "dna_000.json"}[scene.split(":")[1]]
+    return scene, W, H, spp
+
+
 def oracle_sample(workload, threads, w, h, s):
     """The CPU restatement (oracle/, brute-force closest hit like the reference's hittable_list) on a bounded sample."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import orc
-    scene, W, H, spp = WORKLOADS[workload]
+    scene, W, H, spp = _still_scene(workload)
     if scene.startswith("@mesh"):
         rt = ge.load_package()
         from rt_b200 import scenes
@@ -144,7 +155,7 @@ def oracle_sample(workload, threads, w, h, s):
 def reference_sample(workload, procs):
     """A bounded sample of the workload for the CPU arm: same scene and camera, reduced size (the reference keeps the
     16:9 camera regardless of -w/-h, main.cpp:64,94).  Returns (samples, seconds, description, kind)."""
-    scene, W, H, spp = WORKLOADS[workload]
+    scene, W, H, spp = _still_scene(workload)
     if scene.startswith("@mesh"):      # the reference has no C++ mesh path at all: the oracle port is the CPU statement
         return oracle_sample(workload, procs, 32, 18, 1)
     if scene == "rtiow_486.json" and os.path.exists(REF_BIN):
@@ -187,6 +198,74 @@ def main_reference(args):
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
 
 
+def main_animation(args):
+    """Config 5.  One step = every frame of the animation once; rank r renders frames f with f % world == r, each frame
+    through the full host path (frame rule -> JSON text -> upload + LBVH build -> render -> RGB8 download -> PNG file).
+    `value` = samples / device time (CUDA events around each frame's render), `e2e` = samples / wall time of the step."""
+    import tempfile as tf
+    import torch
+    import torch.distributed as dist
+    rt = ge.load_package()
+    from rt_b200 import animation, multi_gpu
+    world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    scene, W, H, spp = WORKLOADS[args.workload]
+    _, name, n_frames = scene.split(":")
+    base_file, fn, _ = animation.FRAME_RULES[name]
+    base = json.load(open(os.path.join(GOLDEN, base_file)))
+    frames = multi_gpu.frames_for_rank(int(n_frames), rank, world)
+    r = rt.Renderer(local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        with tf.TemporaryDirectory() as td:
+            return animation.render_animation(r, base, fn, frames, td, W, H, spp, base_dir=GOLDEN, skip_existing=False)
+    for _ in range(args.warmup):
+        animation.render_animation(r, base, fn, frames[:2], None, W, H, spp, base_dir=GOLDEN)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    dev_ms, rays, launches = 0.0, 0, 0
+    for _ in range(args.steps):
+        res = step()
+        dev_ms += res["device_ms"]; rays += res["rays"]; launches += res["launches"]
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([dev_ms, wall * 1e3, float(rays)], device=f"cuda:{local}", dtype=torch.float64)
+    if world > 1:
+        mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        dev_ms, wall_ms, rays = float(mx[0]), float(mx[1]), float(sm[2])
+    else:
+        wall_ms = wall * 1e3
+    if rank == 0:
+        total = int(n_frames) * W * H * spp
+        line = {"metric": "samples_per_second", "value": total * args.steps / (dev_ms * 1e-3), "unit": "samples/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": args.workload, "scene": base_file, "frames": int(n_frames), "width": W, "height": H, "spp": spp,
+                           "partition": f"frames dealt round-robin over {world} GPU(s), no collective",
+                           "l2": "wavefront queues (GBs) exceed the 126 MB L2 every pass; no explicit flush needed"},
+                "mrays_per_s": rays / (dev_ms * 1e-3) / 1e6,
+                "e2e": {"value": total * args.steps / (wall_ms * 1e-3), "unit": "samples/s", "ms_per_step": wall_ms / args.steps,
+                        "h2d_bytes_per_step": int(n_frames) * 2048, "d2h_bytes_per_step": int(n_frames) * W * H * 3,
+                        "note": "frame rule + JSON text + upload/LBVH build + render + RGB8 download + PNG encode/write (8 host threads)"},
+                "gpu_launches": int(launches / args.steps), "clocks": clocks, "roofline": None}
+        print(json.dumps(line))
+    r.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -200,6 +279,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)
+    if WORKLOADS[args.workload][0].startswith("@anim"):
+        return main_animation(args)
 
     import numpy as np
     import torch

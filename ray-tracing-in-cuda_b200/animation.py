@@ -61,3 +61,61 @@ def blue2_frame(blue2_scene, frame):
 def frames_for_rank(n_frames, rank, world):
     """Frame partition of blue.py:23-32: frame f renders on GPU f % 8."""
     return [f for f in range(n_frames) if f % world == rank]
+
+
+# ---- in-process animation driver (replaces "write 360 JSON files, start one process per frame per GPU") ----
+FRAME_RULES = {
+    # name: (base scene file, frame function, number of frames the reference script renders)
+    "dna": ("basic_scene.json", dna_frame, 360),         # dna.py:17 (it writes 360 scenes; its render loop covers them all)
+    "blue": ("blue.json", blue_frame, 360),              # blue.py:14
+    "blue2": ("blue2.json", blue2_frame, 180),           # blue2.py:14
+}
+
+
+def render_animation(renderer, base_scene, frame_fn, frames, out_dir=None, width=0, height=0, spp=0, seed=0x2023,
+                     writer_threads=8, skip_existing=True, base_dir=None):
+    """Renders `frames` (an iterable of frame numbers — this rank's share, see frames_for_rank) on one Renderer.
+
+    Per frame: scene dict from the reference's rule -> JSON text -> rt_scene_upload_json_text (parse, flatten, LBVH build
+    on the device, ~0.2 ms) -> rt_render -> rt_download (tonemapped RGB8, rows flipped on the device) -> PNG encoding on a
+    pool of host threads, overlapped with the next frame's rendering.  Frames whose PNG already exists are skipped
+    (frame-level resume; the reference restarts from frame 0).  Returns a dict with counts and timings."""
+    import json
+    import os
+    import time
+    from concurrent.futures import ThreadPoolExecutor
+
+    from .renderer import write_png
+
+    t0 = time.perf_counter()
+    done, skipped, samples, rays, launches, device_ms, pending = 0, 0, 0, 0, 0, 0.0, []
+    pool = ThreadPoolExecutor(max_workers=max(1, writer_threads)) if out_dir else None
+    for f in frames:
+        scene = frame_fn(base_scene, f)
+        out = os.path.join(out_dir, os.path.basename(scene.get("output_file", f"frame_{f:04d}.png"))) if out_dir else None
+        if out and skip_existing and os.path.exists(out):
+            skipped += 1
+            continue
+        if "aspect_ratio" not in scene["camera"]:
+            scene["camera"]["aspect_ratio"] = scene["width"] / scene["height"]      # keep the framing under size overrides
+        if width:
+            scene["width"] = width
+        if height:
+            scene["height"] = height
+        if spp:
+            scene["samples_per_pixel"] = spp
+        renderer.stats_reset()
+        info = renderer.upload_json_text(json.dumps(scene), base_dir)
+        renderer.render(seed=seed)
+        _, rgb8, st = renderer.download(want_sum=False, gamma=0)
+        samples += info.width * info.height * info.samples_per_pixel
+        rays += st["rays"]; launches += st["launches"]; device_ms += st["ms_total"]
+        if pool:
+            pending.append(pool.submit(write_png, out, rgb8))
+        done += 1
+    for p in pending:
+        p.result()
+    if pool:
+        pool.shutdown()
+    dt = time.perf_counter() - t0
+    return {"frames": done, "skipped": skipped, "samples": samples, "rays": rays, "launches": launches, "seconds": dt, "device_ms": device_ms}

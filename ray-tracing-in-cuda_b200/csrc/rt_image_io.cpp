@@ -48,7 +48,7 @@ extern "C" int rt_write_png(const char *path, const unsigned char *rgb8, int wid
     for (int y = 0; y < height; ++y) { raw[(stride + 1) * y] = 0; memcpy(&raw[(stride + 1) * y + 1], rgb8 + stride * y, stride); }
     uLongf clen = compressBound((uLong)raw.size());
     std::vector<uint8_t> comp(clen);
-    if (compress2(comp.data(), &clen, raw.data(), (uLong)raw.size(), 6) != Z_OK) return RT_ERR_IO;
+    if (compress2(comp.data(), &clen, raw.data(), (uLong)raw.size(), 1) != Z_OK) return RT_ERR_IO;
     std::vector<uint8_t> out = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
     std::vector<uint8_t> ihdr;
     put32(ihdr, (uint32_t)width); put32(ihdr, (uint32_t)height);

@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
 //      reserves its output range with ONE global atomic per chunk and three TMA bulk stores write full lines.
 // ------------------------------------------------------------------------------------------------
 #ifndef RT_SH_CHUNK
-#define RT_SH_CHUNK 128
+#define RT_SH_CHUNK 256
 #endif
 #define RT_SH_CTAS_PER_SM (1024 / RT_SH_CHUNK)
 #define RT_SH_WARPS (RT_SH_CHUNK / 32)

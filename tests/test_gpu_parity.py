@@ -307,3 +307,23 @@ def test_million_triangle_mesh_builds_and_renders(rt):
     rt.render(seed=1)
     a2, _, _ = rt.download()
     assert np.array_equal(a, a2)
+
+
+def test_animation_driver_frames_resume_and_files(rt, tmp_path):
+    """blue2.py's rule in-process: every frame's PNG equals a stand-alone render of that frame's JSON; a second run
+    skips the frames already on disk (frame-level resume)."""
+    from PIL import Image
+    from rt_b200 import animation
+    base = json.load(open(scene_path("blue2")))
+    res = animation.render_animation(rt, base, animation.blue2_frame, [0, 3, 5], str(tmp_path), width=64, height=36, spp=2)
+    assert res["frames"] == 3 and res["skipped"] == 0 and res["samples"] == 3 * 64 * 36 * 2 and res["launches"] > 0
+    for f in (0, 3, 5):
+        d = animation.blue2_frame(base, f)
+        d["camera"]["aspect_ratio"] = d["width"] / d["height"]
+        d.update(width=64, height=36, samples_per_pixel=2)
+        rt.upload_json_text(json.dumps(d))
+        rt.render(seed=0x2023)
+        _, png8, _ = rt.download(gamma=0)
+        assert np.array_equal(np.asarray(Image.open(tmp_path / f"{f:03d}.png")), png8)
+    again = animation.render_animation(rt, base, animation.blue2_frame, [0, 3, 5, 6], str(tmp_path), width=64, height=36, spp=2)
+    assert again["frames"] == 1 and again["skipped"] == 3
