@@ -31,6 +31,8 @@ WORKLOADS = {
     "dna000_1080p_1024spp": ("dna_000.json", 1920, 1080, 1024),
     "blue2_1080p_256spp": ("blue2.json", 1920, 1080, 256),
     "sample_scene_1600x900_512spp": ("sample_scene.json", 1600, 900, 512),
+    # config 3 as BASELINE.json words it (boxes, rotate_y, image + checker textures, three emitters, OBJ mesh): our schema extensions
+    "sample_scene_ext_1600x900_512spp": ("sample_scene_ext.json", 1600, 900, 512),
     # config 4: procedural ~1M-triangle mesh (scenes.mesh_scene, seeded) under the GPU LBVH; "@" = tables, not a JSON file
     "mesh1m_4k_1024spp": ("@mesh:708", 3840, 2160, 1024),
     "mesh1m_1080p_64spp": ("@mesh:708", 1920, 1080, 64),

@@ -83,6 +83,31 @@ def read_image_rgb8(path):
     return np.ascontiguousarray(im)
 
 
+def expand_meshes(objs, base_dir):
+    """`mesh` objects -> triangles, in place in the object order (same rules as csrc/rt_json.cpp load_obj: v' = v*scale + t
+    in float32, 1-based / negative indices, v/vt/vn tokens, fan triangulation)."""
+    out = []
+    for o in objs:
+        if o["type"] != "mesh":
+            out.append(o)
+            continue
+        sc_, tr = np.float32(o.get("scale", 1.0)), np.array(o.get("translate", [0, 0, 0]), np.float32)
+        path = o["file"] if os.path.isabs(o["file"]) else os.path.join(base_dir or ".", o["file"])
+        v = []
+        for line in open(path):
+            t = line.split()
+            if not t:
+                continue
+            if t[0] == "v":
+                v.append([float(np.float32(np.float32(float(t[1 + k])) * sc_) + tr[k]) for k in range(3)])
+            elif t[0] == "f":
+                idx = [int(tok.split("/")[0]) for tok in t[1:]]
+                idx = [len(v) + i if i < 0 else i - 1 for i in idx]
+                for k in range(1, len(idx) - 1):
+                    out.append({"type": "triangle", "v0": v[idx[0]], "v1": v[idx[k]], "v2": v[idx[k + 1]], "material": o.get("material", 0)})
+    return out
+
+
 def load_scene(src, width=None, height=None, spp=None, max_depth=None, base_dir=None):
     """src: path to a JSON scene or an already parsed dict (schema of gpu-version/parser.hpp + extensions)."""
     if isinstance(src, (str, os.PathLike)):
@@ -112,7 +137,7 @@ def load_scene(src, width=None, height=None, spp=None, max_depth=None, base_dir=
     D.camera.focus_dist = cam.get("focus_dist", float(fd))
     sc.output_file = d.get("output_file", "main.png")
 
-    objs = d["object"]["data"]; mats = d["material"]["data"]; texs = d["texture"]["data"]
+    objs = expand_meshes(d["object"]["data"], base_dir); mats = d["material"]["data"]; texs = d["texture"]["data"]
     xforms = []
     OA = (capi.ObjectDesc * max(1, len(objs)))()
     for i, o in enumerate(objs):

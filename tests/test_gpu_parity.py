@@ -29,7 +29,7 @@ def scene_path(name):
     return f"{G}/{name}.json"
 
 
-@pytest.mark.parametrize("name", SCENES + ["basic_scene"])
+@pytest.mark.parametrize("name", SCENES + ["basic_scene", "sample_scene_ext"])
 def test_lbvh_bit_exact(rt, name):
     """GPU LBVH build vs the host twin: Morton keys, sorted order, Karras child/parent links bit-exact; boxes equal."""
     rt.upload_json(scene_path(name))
@@ -118,7 +118,8 @@ def test_aov_matches_oracle_and_reference(rt, name):
     assert np.abs(got[..., 13:22] - ref[..., 13:22])[same].max() <= 1e-5
 
 
-@pytest.mark.parametrize("name,spp", [("sample_scene", 8), ("blue", 4), ("blue2", 8), ("dna_000", 4), ("rtiow_486", 8), ("basic_scene", 3)])
+@pytest.mark.parametrize("name,spp", [("sample_scene", 8), ("blue", 4), ("blue2", 8), ("dna_000", 4), ("rtiow_486", 8), ("basic_scene", 3),
+                                      ("sample_scene_ext", 6)])
 def test_render_matches_oracle_sample_for_sample(rt, name, spp):
     """Full path tracing, same Philox streams: per-pixel radiance sums within 1e-5 per sample of the brute-force oracle,
     and exactly the same number of path segments."""
