@@ -328,3 +328,18 @@ def test_animation_driver_frames_resume_and_files(rt, tmp_path):
         assert np.array_equal(np.asarray(Image.open(tmp_path / f"{f:03d}.png")), png8)
     again = animation.render_animation(rt, base, animation.blue2_frame, [0, 3, 5, 6], str(tmp_path), width=64, height=36, spp=2)
     assert again["frames"] == 1 and again["skipped"] == 3
+
+
+@pytest.mark.parametrize("W,H,spp", [(67, 35, 3), (2, 2, 1), (9, 5, 7), (130, 3, 2)])
+def test_odd_image_sizes(rt, W, H, spp):
+    """Sizes that are not multiples of the 8x4 camera tile, of the shade chunk or of a 16-byte TMA copy (odd tails):
+    image and ray count still equal the oracle's, with and without the in-CTA material sort."""
+    rt.upload_json(scene_path("blue2"))
+    rt.override(width=W, height=H, spp=spp)
+    want, nrays = orc.render(orc.load_scene(scene_path("blue2"), width=W, height=H, spp=spp), seed=9)
+    for flags in (0, capi.RT_RENDER_SORT):
+        rt.stats_reset()
+        rt.render(seed=9, flags=flags)
+        got, _, st = rt.download()
+        assert st["rays"] == nrays
+        assert np.abs(got - want).max() <= 1e-5 * spp
