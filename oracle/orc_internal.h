@@ -86,6 +86,13 @@ v3 orc_emitted(const rt_scene_desc *sc, int mat, float u, float v, v3 p);
 int orc_scatter(const rt_scene_desc *sc, int mat, v3 rd, const orc_hit *rec, orc_rng *rng, v3 *att, v3 *so, v3 *sd);
 v3 orc_background(const rt_scene_desc *sc, v3 d);
 
+/* next-event estimation (orc_nee.c) */
+int orc_is_nee_light(const rt_scene_desc *sc, int i);
+float orc_light_area(const rt_scene_desc *sc, int i);
+int orc_light_list(const rt_scene_desc *sc, int *lights);
+int orc_nee_sample(const rt_scene_desc *sc, const int *lights, int n_lights, v3 x, v3 n, uint32_t seed, uint32_t pixel,
+                   uint32_t sample, uint32_t bounce, v3 *f, int64_t *shadow_rays);
+
 v3 orc_xform_point(const float m[12], v3 p);
 v3 orc_xform_vec(const float m[12], v3 p);
 v3 orc_xform_normal(const float minv[12], v3 p);

@@ -113,17 +113,29 @@ v3 orc_background(const rt_scene_desc *sc, v3 d) {
 
 /* ray_color, main.cu:17-70 / main.cpp:13-43.  Emission is non-zero only on diffuse_light, which never
  * scatters, so the radiance of a path is throughput * (E | background | 0) at its last vertex. */
-static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t pixel, uint32_t sample, int64_t *nrays) {
+typedef struct { int on, n_lights; const int *lights; const unsigned char *is_light; } nee_t;
+
+static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t pixel, uint32_t sample, int64_t *nrays,
+                    const nee_t *nee, int64_t *nshadow) {
     v3 thr = V(1, 1, 1), L = V(0, 0, 0);
+    int prev_nee = 0;       /* the previous vertex sampled the lights: do not count a sampled light again when hit */
     for (int bounce = 0; bounce < sc->max_depth; ++bounce) {
         orc_hit rec;
         ++*nrays;
         if (!orc_hit_world(sc, o, d, 0.001f, FLT_MAX, &rec)) { L = vadd(L, vmul(thr, orc_background(sc, d))); break; }
         v3 E = orc_emitted(sc, rec.mat, rec.u, rec.v, rec.p);
+        if (prev_nee && nee->is_light[rec.prim]) E = V(0, 0, 0);
         orc_rng rng; orc_rng_init(&rng, seed, pixel, sample, (uint32_t)bounce + 1u, sc->sampling);
         v3 att, so, sd;
         int ok = orc_scatter(sc, rec.mat, d, &rec, &rng, &att, &so, &sd);
         L = vadd(L, vmul(thr, E));
+        prev_nee = 0;
+        if (nee->on && nee->n_lights > 0 && sc->materials[rec.mat].type == RT_MAT_LAMBERTIAN) {
+            v3 f;
+            if (orc_nee_sample(sc, nee->lights, nee->n_lights, rec.p, rec.n, seed, pixel, sample, (uint32_t)bounce, &f, nshadow))
+                L = vadd(L, vmul(vmul(thr, att), f));
+            prev_nee = 1;
+        }
         if (!ok) break;
         thr = vmul(thr, att);
         o = so; d = sd;
@@ -133,14 +145,14 @@ static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t
 
 typedef struct {
     const rt_scene_desc *sc; orc_camera cam; uint32_t seed; int s0, sn; float *out;
-    int row_next; pthread_mutex_t mu; int64_t rays;
+    int row_next; pthread_mutex_t mu; int64_t rays, shadow; nee_t nee;
 } job_t;
 
 static void *worker(void *arg) {
     job_t *j = (job_t *)arg;
     const rt_scene_desc *sc = j->sc;
     const int W = sc->width, H = sc->height;
-    int64_t rays = 0;
+    int64_t rays = 0, shadow = 0;
     for (;;) {
         pthread_mutex_lock(&j->mu);
         int y = j->row_next++;
@@ -156,23 +168,32 @@ static void *worker(void *arg) {
                 v3 o, d;
                 int defocus = sc->sampling == RT_SAMPLING_REFERENCE_CPU && sc->camera.aperture > 0.0f;
                 orc_get_ray(&j->cam, u, v, defocus, &rng, &o, &d);
-                v3 c = ray_color(sc, o, d, j->seed, pixel, (uint32_t)s, &rays);
+                v3 c = ray_color(sc, o, d, j->seed, pixel, (uint32_t)s, &rays, &j->nee, &shadow);
                 sum = vadd(sum, c);                                   /* fixed order: ascending sample index */
             }
             float *q = j->out + 3 * (size_t)pixel;
             q[0] = sum.x; q[1] = sum.y; q[2] = sum.z;
         }
     }
-    pthread_mutex_lock(&j->mu); j->rays += rays; pthread_mutex_unlock(&j->mu);
+    pthread_mutex_lock(&j->mu); j->rays += rays; j->shadow += shadow; pthread_mutex_unlock(&j->mu);
     return NULL;
 }
 
-int orc_render(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
-               int64_t *n_rays) {
+int orc_render_ex(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
+                  int flags, int64_t *n_rays, int64_t *n_shadow_rays) {
     if (!sc || !rgb_sum || sc->width < 1 || sc->height < 1) return RT_ERR_INVALID;
+    if ((flags & RT_RENDER_NEE) && sc->sampling != RT_SAMPLING_REFERENCE_CPU) return RT_ERR_INVALID;
     job_t j; memset(&j, 0, sizeof j);
     j.sc = sc; j.seed = seed; j.s0 = spp_begin; j.sn = spp_count > 0 ? spp_count : sc->samples_per_pixel; j.out = rgb_sum;
     orc_camera_setup(&sc->camera, &j.cam);
+    int *lights = (int *)malloc(sizeof(int) * (size_t)(sc->n_objects > 0 ? sc->n_objects : 1));
+    unsigned char *is_light = (unsigned char *)calloc((size_t)(sc->n_objects > 0 ? sc->n_objects : 1), 1);
+    j.nee.on = (flags & RT_RENDER_NEE) != 0;
+    if (j.nee.on) {
+        j.nee.n_lights = orc_light_list(sc, lights);
+        for (int k = 0; k < j.nee.n_lights; ++k) is_light[lights[k]] = 1;
+    }
+    j.nee.lights = lights; j.nee.is_light = is_light;
     pthread_mutex_init(&j.mu, NULL);
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 256) n_threads = 256;
@@ -180,8 +201,15 @@ int orc_render(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_co
     for (int i = 0; i < n_threads; ++i) pthread_create(&th[i], NULL, worker, &j);
     for (int i = 0; i < n_threads; ++i) pthread_join(th[i], NULL);
     pthread_mutex_destroy(&j.mu);
+    free(lights); free(is_light);
     if (n_rays) *n_rays = j.rays;
+    if (n_shadow_rays) *n_shadow_rays = j.shadow;
     return 0;
+}
+
+int orc_render(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
+               int64_t *n_rays) {
+    return orc_render_ex(sc, seed, spp_begin, spp_count, rgb_sum, n_threads, 0, n_rays, NULL);
 }
 
 /* first-hit record per pixel: the "deterministic path" (pixel-centre ray, no lens offset, no scattering) */

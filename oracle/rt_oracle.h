@@ -33,6 +33,9 @@ extern "C" {
  * n_rays (may be NULL) receives the number of path segments traced. */
 int orc_render(const rt_scene_desc *scene, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum,
                int n_threads, int64_t *n_rays);
+/* as orc_render, with rt_render flags (RT_RENDER_NEE: next-event estimation, reference_cpu sampling only) */
+int orc_render_ex(const rt_scene_desc *scene, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum,
+                  int n_threads, int flags, int64_t *n_rays, int64_t *n_shadow_rays);
 /* first-hit record, 24 floats per pixel (same layout as oracle/ref_build/ref_gpu_harness.cpp `aov`) */
 int orc_aov(const rt_scene_desc *scene, float *aov);
 /* color.cuh:15-35 (gamma=0) / color.cuh:70-95 (gamma=1): rgb8 rows flipped so row 0 = top */

@@ -78,7 +78,8 @@ extern "C" void rt_destroy(rt_ctx *c) {
     c->d_obmin.release(); c->d_obmax.release(); c->d_node_aabb.release(); c->d_leaf_aabb.release(); c->d_bounds.release();
     c->d_hist.release(); c->d_keys[0].release(); c->d_keys[1].release(); c->d_vals[0].release(); c->d_vals[1].release();
     c->d_left.release(); c->d_right.release(); c->d_parent.release(); c->d_flags.release(); c->d_prim_obj.release();
-    c->d_prim_mat.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
+    c->d_prim_mat.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_light_slot.release(); c->d_light_type.release(); c->d_obj_light.release(); c->d_light_area.release();
+    c->d_sh_o.release(); c->d_sh_d.release(); c->d_sh_c.release(); c->d_shcount.release(); c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
     for (int k = 0; k < 2; ++k) { c->d_ray_o[k].release(); c->d_ray_d[k].release(); c->d_thr[k].release(); }
     c->d_radiance.release(); c->d_hits.release(); c->d_bins.release(); c->d_qcount.release(); c->d_bincount.release();
     c->d_workctr.release(); c->d_counters.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
@@ -246,6 +247,37 @@ static int upload_to_device(rt_ctx *ctx) {
     CU(cudaStreamSynchronize(s));       // the host vectors above go out of scope
     float ms = 0; cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1); ctx->stats.ms_build = ms;
 
+    // sampled lights for RT_RENDER_NEE: emissive spheres / rects / cylinders / triangles in scene-file order (oracle/orc_nee.c)
+    {
+        std::vector<int> obj_light((size_t)std::max(1, n), -1), ltype; std::vector<float> larea;
+        for (int i = 0; i < n; ++i) {
+            const rt_object_desc &o = hs.objects[i];
+            if (hs.materials[o.material].type != RT_MAT_DIFFUSE_LIGHT) continue;
+            const float *p = o.p; float area;
+            if (o.type == RT_OBJ_SPHERE) area = 4.0f * 3.14159274101257324f * (p[3] * p[3]);
+            else if (o.type == RT_OBJ_XY_RECT || o.type == RT_OBJ_XZ_RECT || o.type == RT_OBJ_YZ_RECT) area = fabsf((p[1] - p[0]) * (p[3] - p[2]));
+            else if (o.type == RT_OBJ_CYLINDER) area = 6.28318548202514648f * fabsf(p[0]) * fabsf(p[2] - p[1]);
+            else if (o.type == RT_OBJ_TRIANGLE) {
+                const float e1[3] = {p[3] - p[0], p[4] - p[1], p[5] - p[2]}, e2[3] = {p[6] - p[0], p[7] - p[1], p[8] - p[2]};
+                const float c[3] = {fmaf(e1[1], e2[2], -(e1[2] * e2[1])), fmaf(e1[2], e2[0], -(e1[0] * e2[2])), fmaf(e1[0], e2[1], -(e1[1] * e2[0]))};
+                area = 0.5f * sqrtf(fmaf(c[2], c[2], fmaf(c[1], c[1], c[0] * c[0])));
+            } else continue;                                   // emissive boxes are not sampled; they still emit when hit
+            obj_light[i] = (int)ltype.size(); ltype.push_back(o.type); larea.push_back(area);
+        }
+        const int nl = (int)ltype.size();
+        CU(ctx->d_obj_light.alloc(obj_light.size())); CU(ctx->d_light_type.alloc(std::max(1, nl)));
+        CU(ctx->d_light_area.alloc(std::max(1, nl))); CU(ctx->d_light_slot.alloc(std::max(1, nl)));
+        CU(cudaMemcpyAsync(ctx->d_obj_light.p, obj_light.data(), sizeof(int) * obj_light.size(), cudaMemcpyHostToDevice, s));
+        if (nl) {
+            CU(cudaMemcpyAsync(ctx->d_light_type.p, ltype.data(), sizeof(int) * nl, cudaMemcpyHostToDevice, s));
+            CU(cudaMemcpyAsync(ctx->d_light_area.p, larea.data(), sizeof(float) * nl, cudaMemcpyHostToDevice, s));
+            launch_light_slots(ctx->cfg, n, ctx->d_prim_obj.p, ctx->d_obj_light.p, ctx->d_light_slot.p);
+        }
+        CU(cudaStreamSynchronize(s));
+        ctx->ds.n_lights = nl; ctx->ds.light_slot = ctx->d_light_slot.p; ctx->ds.light_type = ctx->d_light_type.p;
+        ctx->ds.light_area = ctx->d_light_area.p; ctx->ds.obj_light = ctx->d_obj_light.p;
+    }
+
     // device scene header
     DScene &ds = ctx->ds;
     ds.n_prims = n; ds.n_nodes = n >= 2 ? n - 1 : 1;
@@ -356,7 +388,7 @@ static int ensure_queues(rt_ctx *ctx, long long cap) {
     for (int k = 0; k < 2; ++k) { CU(ctx->d_ray_o[k].alloc(cap)); CU(ctx->d_ray_d[k].alloc(cap)); CU(ctx->d_thr[k].alloc(cap)); }
     CU(ctx->d_radiance.alloc(cap)); CU(ctx->d_hits.alloc(cap + 2));   // +2: the TMA copy of an odd-sized tail rounds up to 16 B CU(ctx->d_bins.alloc((size_t)cap * RT_NUM_BINS));
     CU(ctx->d_counters.alloc(CTR_COUNT));
-    if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(1)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, sizeof(unsigned long long), ctx->stream)); }
+    if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(2)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 2 * sizeof(unsigned long long), ctx->stream)); }
     ctx->queue_cap = cap;
     Queues &q = ctx->q;
     for (int k = 0; k < 2; ++k) { q.ray_o[k] = ctx->d_ray_o[k].p; q.ray_d[k] = ctx->d_ray_d[k].p; q.thr[k] = ctx->d_thr[k].p; }
@@ -387,6 +419,9 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     if (prm->spp_begin < 0) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: spp_begin < 0");
     const bool count = (prm->flags & RT_RENDER_COUNT_EVENTS) != 0;
     const bool sort = (prm->flags & RT_RENDER_SORT) != 0;
+    const bool nee = (prm->flags & RT_RENDER_NEE) != 0;
+    if (nee && ds.sampling != RT_SAMPLING_REFERENCE_CPU)
+        return rt_fail(ctx, RT_ERR_INVALID, "rt_render: RT_RENDER_NEE needs the reference_cpu sampling convention (cosine-weighted lambertian)");
     // wavefront size: whole sample planes, at most max_paths_per_pass paths and at most 2^30 queue entries
     long long max_paths = prm->max_paths_per_pass;
     if (max_paths <= 0) {
@@ -403,11 +438,16 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     int rc = ensure_queues(ctx, cap); if (rc) return rc;
     rc = ensure_depth_buffers(ctx, ds.max_depth); if (rc) return rc;
     rc = ensure_accum(ctx); if (rc) return rc;
+    ctx->q.sh_o = nullptr; ctx->q.sh_d = nullptr; ctx->q.sh_c = nullptr; ctx->q.shcount = nullptr;
+    if (nee) {
+        CU(ctx->d_sh_o.alloc(cap)); CU(ctx->d_sh_d.alloc(cap)); CU(ctx->d_sh_c.alloc(cap)); CU(ctx->d_shcount.alloc(ds.max_depth + 1));
+        ctx->q.sh_o = ctx->d_sh_o.p; ctx->q.sh_d = ctx->d_sh_d.p; ctx->q.sh_c = ctx->d_sh_c.p; ctx->q.shcount = ctx->d_shcount.p;
+    }
     cudaStream_t s = ctx->stream;
     bool clear = !((prm->flags & RT_RENDER_KEEP_ACCUM) && ctx->accum_valid);
     if (count) CU(cudaMemsetAsync(ctx->d_counters.p, 0, sizeof(unsigned long long) * CTR_COUNT, s));
     long long passes = 0;
-    float ms_stage[4] = {0, 0, 0, 0};
+    float ms_stage[5] = {0, 0, 0, 0, 0};
     cudaEvent_t evs[2] = {nullptr, nullptr};
     if (count) { cudaEventCreate(&evs[0]); cudaEventCreate(&evs[1]); }
     const bool time_stages = !count && (prm->flags & RT_RENDER_TIME_STAGES) != 0;
@@ -429,11 +469,12 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         const int sn = std::min(s_pass, spp - done);
         const int n_paths = sn * np;
         launch_pass_init(ctx->cfg, ctx->q, ds.max_depth, n_paths);
-        timed(0, [&] { launch_generate(ctx->cfg, ds, ctx->q, prm->seed, prm->spp_begin + done, n_paths); });
+        timed(0, [&] { launch_generate(ctx->cfg, ds, ctx->q, prm->seed, prm->spp_begin + done, n_paths, nee); });
         int buf = 0;
         for (int b = 0; b < ds.max_depth; ++b) {
             timed(1, [&] { launch_extend(ctx->cfg, ds, ctx->q, b, buf, count, sort); });
-            timed(2, [&] { launch_shade(ctx->cfg, ds, ctx->q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort); });
+            timed(2, [&] { launch_shade(ctx->cfg, ds, ctx->q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort, nee); });
+            if (nee) timed(4, [&] { launch_shadow(ctx->cfg, ds, ctx->q, b); });
             buf ^= 1;
         }
         timed(3, [&] { launch_accumulate(ctx->cfg, ctx->q, ctx->d_accum.p, ds.width, ds.height, sn, clear, ds.max_depth, ctx->d_rays.p); });
@@ -453,7 +494,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         st.n_rect_tests += c[CTR_RECT]; st.n_cyl_reject += c[CTR_CYL_REJECT]; st.n_cyl_accept += c[CTR_CYL_ACCEPT];
         st.n_tri_tests += c[CTR_TRI]; st.n_boxprim_tests += c[CTR_BOXPRIM]; st.n_shade += c[CTR_SHADE];
         st.n_generate += (long long)spp * np; st.n_node_visits += c[CTR_NODE_VISITS];
-        st.ms_generate += ms_stage[0]; st.ms_extend += ms_stage[1]; st.ms_shade += ms_stage[2]; st.ms_accumulate += ms_stage[3];
+        st.ms_generate += ms_stage[0]; st.ms_extend += ms_stage[1]; st.ms_shade += ms_stage[2]; st.ms_accumulate += ms_stage[3]; st.ms_shadow += ms_stage[4];
         cudaEventDestroy(evs[0]); cudaEventDestroy(evs[1]);
         if (c[CTR_STACK_OVERFLOW]) return rt_fail(ctx, RT_ERR_INVALID, "traversal stack overflow (BVH deeper than RT_TRAV_STACK)");
     }
@@ -513,7 +554,7 @@ extern "C" int rt_stats_reset(rt_ctx *ctx) {
     ctx->stats.ms_build = ms_build;
     ctx->launches = 0;
     ctx->pending.clear();
-    if (ctx->d_rays.p) { CU(cudaSetDevice(ctx->device)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, sizeof(unsigned long long), ctx->stream)); }
+    if (ctx->d_rays.p) { CU(cudaSetDevice(ctx->device)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 2 * sizeof(unsigned long long), ctx->stream)); }
     return RT_OK;
 }
 
@@ -533,10 +574,10 @@ extern "C" int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigne
         CU(cudaMemcpyAsync(rgb8, ctx->d_rgb8.p, need, cudaMemcpyDeviceToHost, s));
     }
     if (rgb_sum) CU(cudaMemcpyAsync(rgb_sum, ctx->d_accum.p, sizeof(float) * need, cudaMemcpyDeviceToHost, s));
-    if (stats && ctx->d_rays.p) { unsigned long long r = 0; CU(cudaMemcpyAsync(&r, ctx->d_rays.p, sizeof r, cudaMemcpyDeviceToHost, s)); CU(cudaStreamSynchronize(s)); ctx->stats.rays = (long long)r; }
+    if (stats && ctx->d_rays.p) { unsigned long long r[2] = {0, 0}; CU(cudaMemcpyAsync(r, ctx->d_rays.p, sizeof r, cudaMemcpyDeviceToHost, s)); CU(cudaStreamSynchronize(s)); ctx->stats.rays = (long long)r[0]; ctx->stats.shadow_rays = (long long)r[1]; }
     CU(cudaStreamSynchronize(s));
     if (!ctx->pending.empty()) {
-        float *acc[4] = {&ctx->stats.ms_generate, &ctx->stats.ms_extend, &ctx->stats.ms_shade, &ctx->stats.ms_accumulate};
+        float *acc[5] = {&ctx->stats.ms_generate, &ctx->stats.ms_extend, &ctx->stats.ms_shade, &ctx->stats.ms_accumulate, &ctx->stats.ms_shadow};
         for (size_t k = 0; k < ctx->pending.size(); ++k) {
             float ms = 0;
             if (cudaEventElapsedTime(&ms, ctx->ev_pool[2 * k], ctx->ev_pool[2 * k + 1]) == cudaSuccess) *acc[ctx->pending[k]] += ms; else cudaGetLastError();

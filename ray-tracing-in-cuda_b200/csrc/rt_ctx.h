@@ -50,6 +50,9 @@ struct rt_ctx {
     DevBuf<float> d_obmin, d_obmax, d_node_aabb, d_leaf_aabb; DevBuf<unsigned> d_bounds, d_hist;
     DevBuf<unsigned long long> d_keys[2]; DevBuf<int> d_vals[2], d_left, d_right, d_parent, d_flags, d_prim_obj, d_prim_mat;
     DevBuf<BvhNode> d_nodes; DevBuf<BvhNodeS> d_nodes_s; DevBuf<float4> d_primA, d_primB, d_primC;
+    // sampled lights (next-event estimation)
+    DevBuf<int> d_light_slot, d_light_type, d_obj_light; DevBuf<float> d_light_area;
+    DevBuf<float4> d_sh_o, d_sh_d, d_sh_c; DevBuf<int> d_shcount; long long shadow_cap = 0;
     // wavefront
     Queues q{};
     DevBuf<float4> d_ray_o[2], d_ray_d[2], d_thr[2], d_radiance; DevBuf<int2> d_hits; DevBuf<int> d_bins, d_qcount, d_bincount, d_workctr;

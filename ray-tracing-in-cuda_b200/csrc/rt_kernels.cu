@@ -42,13 +42,14 @@ __global__ void k_pass_init(Queues q, int max_depth, int n_paths) {
     if (i <= max_depth) q.qcount[i] = i == 0 ? n_paths : 0;
     if (i < max_depth * RT_BIN_STRIDE) q.bincount[i] = 0;
     if (i < max_depth * 2) q.workctr[i] = 0;
+    if (q.shcount && i < max_depth) q.shcount[i] = 0;
 }
 
 // ------------------------------------------------------------------------------------------------
 // generate: one camera path per (pixel, sample) — main.cu:95-99.  Path id = s_local * n_pixels + pixel, so that
 // `accumulate` reads the radiance of one sample index as one contiguous, coalesced plane.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsigned seed, int spp_begin, int n_paths) {
+__global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsigned seed, int spp_begin, int n_paths, int zero_radiance) {
     const int np = sc.width * sc.height;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_paths; i += gridDim.x * blockDim.x) {
         const int s_local = i / np, pixel = plane_to_pixel(sc.width, sc.height, i - s_local * np);
@@ -59,6 +60,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
         float3 o, d;
         camera_ray(sc.cam, u, v, sc.defocus != 0, rng, o, d);
         q.ray_o[0][i] = make_float4(o.x, o.y, o.z, __int_as_float(i));
+        if (zero_radiance) q.radiance[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);      // NEE: several stages add to it
         q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // Philox key words travel with the path:
         q.thr[0][i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(s_local));      // no divisions in the shade stage
     }
@@ -133,7 +135,9 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
 #ifndef RT_SH_CHUNK
 #define RT_SH_CHUNK 256
 #endif
+#ifndef RT_SH_CTAS_PER_SM
 #define RT_SH_CTAS_PER_SM (1024 / RT_SH_CHUNK)
+#endif
 #define RT_SH_WARPS (RT_SH_CHUNK / 32)
 
 struct __align__(128) ShadeSmem {
@@ -189,7 +193,7 @@ __device__ __forceinline__ void shade_issue_loads(ShadeSmem &sm, const Queues &q
     tma_load_1d(sm.in_hit[stage], q.hits + first, b8, &sm.full[stage]);
 }
 
-template <bool COUNT>
+template <bool COUNT, bool NEE>
 __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene sc, Queues q, unsigned seed, int spp_begin, int bounce, int buf,
                                                          int last_bounce, int sort) {
     extern __shared__ __align__(128) unsigned char s_shade_raw[];
@@ -251,11 +255,16 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
         float3 no = v3(0, 0, 0), nd = v3(0, 0, 0), nthr = v3(0, 0, 0);
         int path_id = 0;
         float key_pixel = 0.0f, key_sample = 0.0f;
+        bool sh_on = false; int sh_flag = 0;
+        float3 sh_x = v3(0, 0, 0), sh_w = v3(0, 0, 0), sh_f = v3(0, 0, 0);
         if (tid < cnt) {
             const float4 o4 = sm.in_o[st][j], d4 = sm.in_d[st][j], t4 = sm.in_thr[st][j];
             const int2 h = sm.in_hit[st][j];
             const float3 o = f4xyz(o4), d = f4xyz(d4), thr = f4xyz(t4);
             path_id = __float_as_int(o4.w); key_pixel = d4.w; key_sample = t4.w;
+            // NEE: bit 30 of the path id = "the previous vertex sampled the lights" (do not count a sampled light again)
+            const bool prev_nee = NEE && (path_id & 0x40000000) != 0;
+            if (NEE) path_id &= 0x3fffffff;
             float3 rad = v3(0, 0, 0);
             if (h.y < 0) {
                 rad = thr * background(sc, d);
@@ -266,17 +275,43 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                 HitRec rec;
                 hit_record(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
-                    rad = thr * texture_value(sc, m.texture, rec.u, rec.v, rec.p);
+                    if (!(prev_nee && sc.obj_light[__ldg(&sc.prim_obj[slot])] >= 0))
+                        rad = thr * texture_value(sc, m.texture, rec.u, rec.v, rec.p);
                 } else {
                     Rng rng; rng.init(seed, (unsigned)__float_as_int(d4.w), (unsigned)(spp_begin + __float_as_int(t4.w)), (unsigned)bounce + 1u, sc.sampling);
                     float3 att, sd;
-                    if (scatter(sc, m, d, rec, rng, att, sd) && !last_bounce) {
+                    const bool ok = scatter(sc, m, d, rec, rng, att, sd);
+                    if (ok && !last_bounce) {
                         alive = true;
                         no = rec.p; nd = sd; nthr = thr * att;
                     }
+                    if (NEE && m.type == RT_MAT_LAMBERTIAN && sc.n_lights > 0) {      // shadow stage feed (oracle/orc_nee.c)
+                        Rng r2; r2.init(seed, (unsigned)__float_as_int(d4.w), (unsigned)(spp_begin + __float_as_int(t4.w)),
+                                        ((unsigned)bounce + 1u) | 0x10000u, sc.sampling);
+                        float3 f;
+                        if (light_sample(sc, rec.p, rec.n, r2, sh_w, f)) { sh_on = true; sh_x = rec.p; sh_f = (thr * att) * f; }
+                        sh_flag = 0x40000000;
+                    }
                 }
             }
-            if (!alive) q.radiance[path_id] = make_float4(rad.x, rad.y, rad.z, 0.0f);
+            if (!alive) {
+                if (NEE) { const float4 r0 = q.radiance[path_id]; rad = v3(r0.x + rad.x, r0.y + rad.y, r0.z + rad.z); }
+                q.radiance[path_id] = make_float4(rad.x, rad.y, rad.z, 0.0f);
+            }
+        }
+        if (NEE) {      // occlusion rays of this chunk -> shadow queue (one global atomic per warp)
+            const unsigned ms = __ballot_sync(0xffffffffu, sh_on);
+            if (ms) {
+                int pos = 0;
+                const int leader = __ffs(ms) - 1;
+                if (lane == leader) pos = atomicAdd(&q.shcount[bounce], __popc(ms));
+                pos = __shfl_sync(0xffffffffu, pos, leader) + __popc(ms & lanemask_lt());
+                if (sh_on) {
+                    q.sh_o[pos] = make_float4(sh_x.x, sh_x.y, sh_x.z, __int_as_float(path_id));
+                    q.sh_d[pos] = make_float4(sh_w.x, sh_w.y, sh_w.z, 0.0f);
+                    q.sh_c[pos] = make_float4(sh_f.x, sh_f.y, sh_f.z, 0.0f);
+                }
+            }
         }
         // ---- 3. compact the survivors into the staging area; one global atomic + three TMA stores per chunk ----
         if (tid == 0) tma_store_wait_read();          // the previous chunk's stores have finished reading the staging area
@@ -288,7 +323,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
             if (lane == leader) pos = atomicAdd(&sm.n_out, __popc(m));
             pos = __shfl_sync(0xffffffffu, pos, leader) + __popc(m & lanemask_lt());
             if (alive) {
-                sm.out_o[pos] = make_float4(no.x, no.y, no.z, __int_as_float(path_id));
+                sm.out_o[pos] = make_float4(no.x, no.y, no.z, __int_as_float(path_id | sh_flag));
                 sm.out_d[pos] = make_float4(nd.x, nd.y, nd.z, key_pixel);
                 sm.out_thr[pos] = make_float4(nthr.x, nthr.y, nthr.z, key_sample);
             }
@@ -312,17 +347,36 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
 }
 
 // ------------------------------------------------------------------------------------------------
+// shadow: occlusion test of the light samples taken by shade (any-hit traversal on t in [0.001, 0.999]); an unoccluded
+// sample adds its radiance to the path's slot.  One entry per path per bounce, so the add needs no atomic.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RT_BLOCK) k_shadow(DScene sc, Queues q, int bounce) {
+    const int n = q.shcount[bounce];
+    TravCounters cnt = {};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 o4 = q.sh_o[i], d4 = q.sh_d[i];
+        float t; int code;
+        traverse<false, false, true>(sc, reinterpret_cast<const char *>(sc.nodes), f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt);
+        if (code < 0) {
+            const int pid = __float_as_int(o4.w);
+            const float4 c = q.sh_c[i], r = q.radiance[pid];
+            q.radiance[pid] = make_float4(r.x + c.x, r.y + c.y, r.z + c.z, 0.0f);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // accumulate: accum[pixel] += sum over this pass's samples, in ascending sample order (fixed order => the image is
 // bit-reproducible; replaces the register sum of main.cu:95-104).  One thread per pixel, S coalesced plane reads.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restrict__ radiance, float *__restrict__ accum, int W, int H,
                                                          int n_samples, int clear, const int *__restrict__ qcount, int max_depth,
-                                                         unsigned long long *total_rays) {
+                                                         unsigned long long *total_rays, const int *__restrict__ shcount) {
     const int np = W * H;
     if (blockIdx.x == 0 && threadIdx.x == 0) {     // rays traced this pass = sum of the per-bounce queue lengths
-        unsigned long long r = 0;
-        for (int b = 0; b < max_depth; ++b) r += (unsigned long long)qcount[b];
-        *total_rays += r;
+        unsigned long long r = 0, sh = 0;
+        for (int b = 0; b < max_depth; ++b) { r += (unsigned long long)qcount[b]; if (shcount) sh += (unsigned long long)shcount[b]; }
+        total_rays[0] += r; total_rays[1] += sh;
     }
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < np; k += gridDim.x * blockDim.x) {
         const int p = plane_to_pixel(W, H, k);
@@ -420,10 +474,10 @@ void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_
     bump(c);
 }
 
-void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths) {
+void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths, bool zero_radiance) {
     long long blocks = ((long long)n_paths + RT_BLOCK - 1) / RT_BLOCK;
     int grid = (int)(blocks < (long long)c.num_sms * 16 ? blocks : (long long)c.num_sms * 16);
-    k_generate<<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, n_paths);
+    k_generate<<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, n_paths, zero_radiance ? 1 : 0);
     bump(c);
 }
 
@@ -459,23 +513,46 @@ int extend_max_blocks_per_sm(size_t smem_bytes) {
 }
 
 void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
-                  bool last_bounce, bool count, bool sort) {
+                  bool last_bounce, bool count, bool sort, bool nee) {
     static bool configured = false;
     if (!configured) {
-        cudaFuncSetAttribute(k_shade<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
         configured = true;
     }
     const int grid = persistent_grid(c, RT_SH_CTAS_PER_SM);
-    if (count) k_shade<true><<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort);
-    else k_shade<false><<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort);
+#define RT_SHADE_ARGS <<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort)
+    if (count) { if (nee) k_shade<true, true> RT_SHADE_ARGS; else k_shade<true, false> RT_SHADE_ARGS; }
+    else { if (nee) k_shade<false, true> RT_SHADE_ARGS; else k_shade<false, false> RT_SHADE_ARGS; }
+#undef RT_SHADE_ARGS
+    bump(c);
+}
+
+// light -> leaf slot (the LBVH build decides the slots on the device): one thread per slot
+__global__ void k_light_slots(int n, const int *__restrict__ prim_obj, const int *__restrict__ obj_light, int *light_slot) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int k = obj_light[prim_obj[j]];
+    if (k >= 0) light_slot[k] = j;
+}
+
+void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const int *obj_light, int *light_slot) {
+    if (n <= 0) return;
+    k_light_slots<<<(n + 255) / 256, 256, 0, c.stream>>>(n, prim_obj, obj_light, light_slot);
+    bump(c);
+}
+
+void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce) {
+    k_shadow<<<persistent_grid(c, 8), RT_BLOCK, 0, c.stream>>>(sc, q, bounce);
     bump(c);
 }
 
 void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W, int H, int n_samples, bool clear, int max_depth,
                        unsigned long long *total_rays) {
     int blocks = (W * H + RT_BLOCK - 1) / RT_BLOCK;
-    k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, accum, W, H, n_samples, clear ? 1 : 0, q.qcount, max_depth, total_rays);
+    k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, accum, W, H, n_samples, clear ? 1 : 0, q.qcount, max_depth, total_rays, q.shcount);
     bump(c);
 }
 

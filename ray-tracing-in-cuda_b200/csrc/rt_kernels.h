@@ -11,10 +11,12 @@ struct LaunchCfg {
 };
 
 void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_paths);
-void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths);
+void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths, bool zero_radiance);
 void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort);
 void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
-                  bool last_bounce, bool count, bool sort);
+                  bool last_bounce, bool count, bool sort, bool nee);
+void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const int *obj_light, int *light_slot);
+void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce);
 void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W, int H, int n_samples, bool clear, int max_depth,
                        unsigned long long *total_rays);
 void launch_sum_ordered(const LaunchCfg &c, float *accum, const float *const *partials_dev, int n_partials, long long n);

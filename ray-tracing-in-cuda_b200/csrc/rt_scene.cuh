@@ -44,6 +44,12 @@ struct DScene {
     const int *prim_mat;                   // slot -> material index
     const float4 *xforms;                  // 6 float4 per transform: rows of m (3x4) then rows of m_inv (3x4)
     const DMaterial *mats;
+    // next-event estimation (RT_RENDER_NEE): sampled lights in scene-file order
+    int n_lights;
+    const int *light_slot;                 // light -> leaf slot
+    const int *light_type;                 // light -> RT_OBJ_*
+    const float *light_area;               // light -> surface area
+    const int *obj_light;                  // object index -> light index or -1
     const DTexture *texs;
     const DImage *images;
 };

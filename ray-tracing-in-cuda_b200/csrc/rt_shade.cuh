@@ -152,6 +152,73 @@ __device__ __forceinline__ int plane_to_pixel(int W, int H, int k) {
     return y * W + x;
 }
 
+// ---- next-event estimation: one point on one light (same operation order as oracle/orc_nee.c) ----
+__device__ __forceinline__ float rt_cosf(float x) { return rt_sinf(x + RT_PIO2_F); }
+
+// Samples light k's surface with (u1, u2).  Returns false when x cannot receive light from the sampled point; else
+// w = y - x (the occlusion ray, to be tested on t in [0.001, 0.999]) and f = Le(y) * cos_x * cos_y / |w|^2 * area * n_lights / pi.
+template <class R>
+__device__ __forceinline__ bool light_sample(const DScene &sc, float3 x, float3 n, R &rng, float3 &w, float3 &f) {
+    const float u0 = rng.next(), u1 = rng.next(), u2 = rng.next();
+    int k = (int)(u0 * (float)sc.n_lights);
+    if (k > sc.n_lights - 1) k = sc.n_lights - 1;
+    const int slot = sc.light_slot[k];
+    const int type = sc.light_type[k];
+    const float4 A = sc.primA[slot];
+    float3 y, ny; float tu = 0.0f, tv = 0.0f;
+    switch (type) {
+    case RT_OBJ_SPHERE: {
+        const float z = __fmaf_rn(-2.0f, u1, 1.0f);
+        const float r = sqrtf(fmaxf(0.0f, __fmaf_rn(-z, z, 1.0f)));
+        const float phi = RT_2PI_F * u2;
+        const float3 dir = v3(r * rt_cosf(phi), r * rt_sinf(phi), z);
+        ny = dir;
+        y = vfma(fabsf(A.w), dir, f4xyz(A));
+        const float theta = rt_acosf(-dir.y), ph = rt_atan2f(-dir.z, dir.x) + RT_PI_F;
+        tu = ph * RT_INV_2PI_F; tv = theta * RT_INV_PI_F;
+        break;
+    }
+    case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: {
+        const float a = __fmaf_rn(u1, A.y - A.x, A.x), b = __fmaf_rn(u2, A.w - A.z, A.z), kk = sc.primB[slot].x;
+        if (type == RT_OBJ_XY_RECT) { y = v3(a, b, kk); ny = v3(0, 0, 1); }
+        else if (type == RT_OBJ_XZ_RECT) { y = v3(a, kk, b); ny = v3(0, 1, 0); }
+        else { y = v3(kk, a, b); ny = v3(1, 0, 0); }
+        tu = (a - A.x) / (A.y - A.x); tv = (b - A.z) / (A.w - A.z);
+        break;
+    }
+    case RT_OBJ_CYLINDER: {
+        const float4 *xf = sc.xforms + 6 * __float_as_int(A.w);
+        const float phi = RT_2PI_F * u1, z = __fmaf_rn(u2, A.z - A.y, A.y);
+        const float c = rt_cosf(phi), s = rt_sinf(phi);
+        const float3 op = v3(A.x * c, A.x * s, z);
+        y = xf_point(xf, op);
+        ny = vunit(xf_normal(xf + 3, v3(c, s, 0.0f)));
+        tu = (rt_atan2f(op.y, op.x) + RT_2PI_F) * RT_INV_4PI_F; tv = (z - A.y) / (A.z - A.y);
+        break;
+    }
+    default: {   // RT_OBJ_TRIANGLE: A = v0, B = e1, C = e2
+        const float3 e1 = f4xyz(sc.primB[slot]), e2 = f4xyz(sc.primC[slot]);
+        const float su = sqrtf(u1);
+        const float b1 = u2 * su, b2 = 1.0f - su;
+        y = vfma(b2, e2, vfma(b1, e1, f4xyz(A)));
+        const float3 c = v3(__fmaf_rn(e1.y, e2.z, -(e1.z * e2.y)), __fmaf_rn(e1.z, e2.x, -(e1.x * e2.z)), __fmaf_rn(e1.x, e2.y, -(e1.y * e2.x)));
+        ny = vunit(c);
+        tu = b1; tv = b2;
+        break;
+    }
+    }
+    w = y - x;
+    const float d2 = dot3(w, w);
+    if (!(d2 > 0.0f)) return false;
+    const float inv_d = 1.0f / sqrtf(d2);
+    const float cs = dot3(n, w) * inv_d, cl = fabsf(dot3(ny, w)) * inv_d;
+    if (!(cs > 0.0f) || !(cl > 0.0f)) return false;
+    const float g = ((cs * cl) / d2) * (sc.light_area[k] * ((float)sc.n_lights * RT_INV_PI_F));
+    const DMaterial m = sc.mats[sc.prim_mat[slot]];
+    f = g * texture_value(sc, m.texture, tu, tv, y);
+    return true;
+}
+
 // miss colour: constant background (main.cu:61-63) or the RTIOW sky gradient (cmake-cpu-version/main.cpp:36-38)
 __device__ __forceinline__ float3 background(const DScene &sc, float3 d) {
     if (sc.bg_mode == RT_BG_SKY_GRADIENT) {

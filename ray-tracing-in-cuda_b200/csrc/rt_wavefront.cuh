@@ -22,6 +22,9 @@ struct Queues {
     int *qcount;           // [max_depth + 1] queue length per bounce
     int *bincount;         // [max_depth][RT_BIN_STRIDE]
     int *workctr;          // [max_depth][2] dynamic work-fetch cursors (extend, shade)
+    // shadow stage (RT_RENDER_NEE): occlusion rays written by shade, consumed by k_shadow right after it
+    float4 *sh_o, *sh_d, *sh_c;   // origin.xyz + path id | direction y - x | radiance carried if unoccluded
+    int *shcount;                 // [max_depth] shadow-queue length per bounce
     unsigned long long *counters;   // [CTR_COUNT]
     long long cap;
 };

@@ -30,6 +30,7 @@ def lib():
         P = C.POINTER
         fp = P(C.c_float)
         L.orc_render.argtypes = [P(capi.SceneDesc), C.c_uint32, C.c_int, C.c_int, fp, C.c_int, P(C.c_int64)]
+        L.orc_render_ex.argtypes = [P(capi.SceneDesc), C.c_uint32, C.c_int, C.c_int, fp, C.c_int, C.c_int, P(C.c_int64), P(C.c_int64)]
         L.orc_aov.argtypes = [P(capi.SceneDesc), fp]
         L.orc_tonemap.argtypes = [fp, C.c_int, C.c_int, C.c_int, C.c_int, P(C.c_ubyte)]
         L.orc_tonemap.restype = None
@@ -212,6 +213,16 @@ def render(sc, seed=0x2023, spp_begin=0, spp_count=0, threads=None):
     rc = lib().orc_render(sc.ptr, seed, spp_begin, spp_count, fptr(out), threads or os.cpu_count() or 1, C.byref(nr))
     assert rc == 0
     return out, nr.value
+
+
+def render_ex(sc, seed=0x2023, spp_begin=0, spp_count=0, threads=None, flags=0):
+    """orc_render with rt_render flags (RT_RENDER_NEE); returns (image, rays, shadow_rays)."""
+    W, H = sc.desc.width, sc.desc.height
+    out = np.zeros((H, W, 3), np.float32)
+    nr, ns = C.c_int64(0), C.c_int64(0)
+    rc = lib().orc_render_ex(sc.ptr, seed, spp_begin, spp_count, fptr(out), threads or os.cpu_count() or 1, flags, C.byref(nr), C.byref(ns))
+    assert rc == 0, rc
+    return out, nr.value, ns.value
 
 
 def aov(sc):

@@ -343,3 +343,59 @@ def test_odd_image_sizes(rt, W, H, spp):
         got, _, st = rt.download()
         assert st["rays"] == nrays
         assert np.abs(got - want).max() <= 1e-5 * spp
+
+
+def _nee_scene(extra_lights=True):
+    with open(scene_path("sample_scene_ext")) as f:
+        d = json.load(f)
+    d["sampling"] = "reference_cpu"
+    if extra_lights:     # a triangle light (sampled) and an emissive box (not sampled, still emits when hit)
+        light = next(i for i, m in enumerate(d["material"]["data"]) if m["type"] == "diffuse_light")
+        d["object"]["data"].append({"type": "triangle", "v0": [-3.0, 2.5, -2.0], "v1": [-2.0, 2.5, -2.0], "v2": [-2.5, 2.9, -1.2], "material": light})
+        d["object"]["data"].append({"type": "box", "min": [2.6, -0.4, 1.0], "max": [2.9, -0.1, 1.3], "material": light})
+    return d
+
+
+@pytest.mark.parametrize("extra,depth", [(False, 0), (True, 0), (True, 3)])
+def test_nee_matches_oracle_sample_for_sample(rt, extra, depth):
+    """RT_RENDER_NEE (the shadow stage): light sampling at every lambertian vertex + any-hit occlusion rays, same
+    Philox streams as oracle/orc_nee.c: radiance within 1e-5 per sample, equal path-segment and shadow-ray counts."""
+    W, H, spp = 96, 54, 5
+    d = _nee_scene(extra)
+    rt.upload_json_text(json.dumps(d), base_dir=G)
+    rt.override(width=W, height=H, spp=spp, max_depth=depth)
+    rt.stats_reset()
+    rt.render(seed=0x77, flags=capi.RT_RENDER_NEE)
+    got, _, st = rt.download()
+    want, nrays, nshadow = orc.render_ex(orc.load_scene(d, width=W, height=H, spp=spp, max_depth=depth or None, base_dir=G), seed=0x77,
+                                         flags=capi.RT_RENDER_NEE)
+    assert nshadow > 0 and st["shadow_rays"] == nshadow and st["rays"] == nrays
+    err = np.abs(got - want)
+    bad = (err > 1e-5 * spp * max(1.0, want.max() / spp)).any(-1).sum()
+    assert bad == 0, f"{bad} pixels differ, max {err.max()}"
+    # scheduling options leave the NEE image unchanged too
+    rt.render(seed=0x77, flags=capi.RT_RENDER_NEE | capi.RT_RENDER_SORT, max_paths_per_pass=W * H * 2)
+    assert np.array_equal(rt.download()[0], got)
+
+
+def test_nee_same_expectation_lower_variance(rt):
+    """NEE and the plain estimator converge to the same image; on a scene lit by small lights NEE is the less noisy one."""
+    W, H, spp = 64, 36, 256
+    d = _nee_scene(True)
+    d["background"] = [0.02, 0.02, 0.03]
+    rt.upload_json_text(json.dumps(d), base_dir=G)
+    rt.override(width=W, height=H, spp=spp)
+    rt.render(seed=1); plain = rt.download()[0] / spp
+    rt.render(seed=1, flags=capi.RT_RENDER_NEE); nee = rt.download()[0] / spp
+    assert abs(nee.mean() - plain.mean()) <= 0.03 * plain.mean()
+    rt.render(seed=2, flags=capi.RT_RENDER_NEE); nee2 = rt.download()[0] / spp
+    rt.render(seed=2); plain2 = rt.download()[0] / spp
+    assert np.mean((nee - nee2) ** 2) < np.mean((plain - plain2) ** 2)
+
+
+def test_nee_needs_cpu_sampling_convention(rt):
+    rt.upload_json(scene_path("sample_scene_ext"))
+    rt.override(width=32, height=18, spp=1)
+    with pytest.raises(RtError):
+        rt.render(flags=capi.RT_RENDER_NEE)
+    rt.render()            # the context stays usable
