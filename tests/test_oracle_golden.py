@@ -189,3 +189,25 @@ def test_lbvh_host_invariants():
                 seen[~c] += 1
     assert np.all(seen == 1)
     assert r["parent"][0] == -1
+
+
+def test_oracle_nee_same_expectation_as_plain_estimator():
+    """orc_nee.c (our definition of the shadow stage) is an unbiased variant of the plain estimator: on a scene lit by
+    small lights the two converge to the same mean, NEE with the lower pixel variance; NEE needs the CPU convention."""
+    import json
+    from rt_b200 import capi
+    with open(f"{orc.GOLDEN}/sample_scene_ext.json") as f:
+        d = json.load(f)
+    d["background"] = [0.02, 0.02, 0.03]
+    W, H, spp = 48, 27, 96
+    with pytest.raises(AssertionError):
+        orc.render_ex(orc.load_scene(d, width=W, height=H, spp=1, base_dir=orc.GOLDEN), flags=capi.RT_RENDER_NEE)
+    d["sampling"] = "reference_cpu"
+    sc = orc.load_scene(d, width=W, height=H, spp=spp, base_dir=orc.GOLDEN)
+    plain, _, ns0 = orc.render_ex(sc, seed=3)
+    nee, _, ns = orc.render_ex(sc, seed=3, flags=capi.RT_RENDER_NEE)
+    assert ns0 == 0 and ns > 0
+    assert abs(nee.mean() - plain.mean()) <= 0.05 * plain.mean()
+    plain2, _, _ = orc.render_ex(sc, seed=4)
+    nee2, _, _ = orc.render_ex(sc, seed=4, flags=capi.RT_RENDER_NEE)
+    assert np.mean((nee - nee2) ** 2) < np.mean((plain - plain2) ** 2)
