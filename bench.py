@@ -300,7 +300,7 @@ def main():
     upload, sdesc = make_upload(rt, args.workload)
     stream = torch.cuda.Stream()
     s0, s1 = multi_gpu.spp_slice(spp, rank, world)                 # this rank's slice of the sample indices
-    flags = capi.RT_RENDER_TIME_STAGES | (capi.RT_RENDER_SORT if args.sort else 0)
+    flags = capi.RT_RENDER_SORT if args.sort else 0       # timed region: the default schedule (two passes in flight)
 
     with torch.cuda.stream(stream):
         r = rt.Renderer(local, stream=stream.cuda_stream)
@@ -343,7 +343,13 @@ def main():
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         ms_step = float(ms.item()) / args.steps
-        _, _, st = r.download(want_sum=False, want_rgb8=False)       # resolves the per-stage events of the timed region
+        _, _, st = r.download(want_sum=False, want_rgb8=False)       # rays and launches of the timed region
+        # per-stage times: one extra step right after the timed region with a CUDA-event pair around every launch, which
+        # needs one pass at a time (RT_RENDER_TIME_STAGES serialises the two pass streams)
+        r.stats_reset()
+        r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=flags | capi.RT_RENDER_TIME_STAGES, max_paths_per_pass=args.max_paths)
+        _, _, sg = r.download(want_sum=False, want_rgb8=False)
+        barrier()
 
         # ---- e2e: host JSON text -> upload (+BVH build) -> render -> reduce -> download to host, every step ----
         def step_e2e():
@@ -358,7 +364,7 @@ def main():
         barrier()
         t0 = time.perf_counter()
         e0.record(stream)
-        for _ in range(max(1, args.steps // 2)):
+        for _ in range(max(2, args.steps // 2)):
             out = step_e2e()
         e1.record(stream)
         barrier()
@@ -366,7 +372,7 @@ def main():
         ms2 = torch.tensor([max(e0.elapsed_time(e1), wall * 1e3)], device=f"cuda:{local}")
         if world > 1:
             dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
-        ms_e2e = float(ms2.item()) / max(1, args.steps // 2)
+        ms_e2e = float(ms2.item()) / max(2, args.steps // 2)
 
     if rank == 0:
         total_samples = W * H * spp
@@ -374,8 +380,8 @@ def main():
         rays = st["rays"] / args.steps * world            # rank 0 traced 1/world of them
         ext_flops, shade_flops = flop_model(counts)
         ext_flops *= scale; shade_flops *= scale
-        ms_extend = st["ms_extend"] / args.steps
-        ms_other = (st["ms_generate"] + st["ms_shade"] + st["ms_accumulate"]) / args.steps
+        ms_extend = sg["ms_extend"]
+        ms_other = sg["ms_generate"] + sg["ms_shade"] + sg["ms_accumulate"]
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         ach = ext_flops / (ms_extend * 1e-3) / 1e12 if ms_extend > 0 else 0.0
@@ -392,12 +398,13 @@ def main():
                        "objects": sdesc["objects"], "partition": f"spp split over {world} GPU(s), one NCCL reduce of the float accumulation buffer",
                        "l2": "wavefront queues (GBs) exceed the 126 MB L2 every pass; no explicit flush needed"},
             "mrays_per_s": rays / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays / total_samples,
-            "stage_ms_per_step": {"generate": st["ms_generate"] / args.steps, "extend": ms_extend, "shade": st["ms_shade"] / args.steps,
-                                  "accumulate": st["ms_accumulate"] / args.steps},
+            "stage_ms_per_step": {"generate": sg["ms_generate"], "extend": ms_extend, "shade": sg["ms_shade"], "accumulate": sg["ms_accumulate"],
+                                  "serial_total": sg["ms_total"],
+                                  "note": "one extra step with per-launch CUDA events, one pass at a time; the timed steps keep two passes in flight"},
             "roofline": {"bound": "fp32", "kernel": "k_extend", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": ach / fp32_peak if fp32_peak else None, "traffic": None,
                          "note": "algorithmic FLOPs (SURVEY §8(d) model, device event counters) / CUDA-event time of the extend launches "
-                                 "in the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)"},
+                                 "of one step run right after the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)"},
             "roofline_hbm": {"bound": "hbm", "kernel": "generate+shade+accumulate", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s",
                              "frac": hbm_ach / hbm_peak, "note": ("104 B/ray + 32 B/sample (DESIGN.md §6) / CUDA-event time of those stages; peak from MEASURED_PEAKS.json (of measured)" if peaks else "of fallback")},
             "e2e": {"value": total_samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,

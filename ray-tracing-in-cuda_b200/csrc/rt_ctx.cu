@@ -1,6 +1,7 @@
 // rt_ctx.cu — C ABI implementation (include/rt.h): context, scene upload (flatten + GPU LBVH build), the wavefront
 // pass loop, download/tonemap.  Replaces jsonmain() of gpu-version/main.cu:448-522 minus file I/O.
 #include "rt_ctx.h"
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -58,6 +59,9 @@ extern "C" int rt_create(rt_ctx **out, int device, void *stream) {
         c->own_stream = true;
     }
     cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1);
+    cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+    for (int k = 0; k < 2; ++k) cudaEventCreateWithFlags(&c->qs[k].ev_acc, cudaEventDisableTiming);
     c->cfg.stream = c->stream; c->cfg.num_sms = c->num_sms; c->cfg.launches = &c->launches;
     *out = c;
     return RT_OK;
@@ -79,10 +83,11 @@ extern "C" void rt_destroy(rt_ctx *c) {
     c->d_hist.release(); c->d_keys[0].release(); c->d_keys[1].release(); c->d_vals[0].release(); c->d_vals[1].release();
     c->d_left.release(); c->d_right.release(); c->d_parent.release(); c->d_flags.release(); c->d_prim_obj.release();
     c->d_prim_mat.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_light_slot.release(); c->d_light_type.release(); c->d_obj_light.release(); c->d_light_area.release();
-    c->d_sh_o.release(); c->d_sh_d.release(); c->d_sh_c.release(); c->d_shcount.release(); c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
-    for (int k = 0; k < 2; ++k) { c->d_ray_o[k].release(); c->d_ray_d[k].release(); c->d_thr[k].release(); }
-    c->d_radiance.release(); c->d_hits.release(); c->d_bins.release(); c->d_qcount.release(); c->d_bincount.release();
-    c->d_workctr.release(); c->d_counters.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
+    c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
+    for (int k = 0; k < 2; ++k) { c->qs[k].release(); if (c->qs[k].ev_acc) cudaEventDestroy(c->qs[k].ev_acc); }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->stream2) cudaStreamDestroy(c->stream2);
+    c->d_counters.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
     c->d_partials.release(); c->d_rays.release();
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -383,22 +388,22 @@ extern "C" int rt_scene_override(rt_ctx *ctx, int width, int height, int spp, in
 }
 
 // ---- wavefront queues ----
-static int ensure_queues(rt_ctx *ctx, long long cap) {
-    if (cap <= ctx->queue_cap && ctx->d_qcount.p) return RT_OK;
-    for (int k = 0; k < 2; ++k) { CU(ctx->d_ray_o[k].alloc(cap)); CU(ctx->d_ray_d[k].alloc(cap)); CU(ctx->d_thr[k].alloc(cap)); }
-    CU(ctx->d_radiance.alloc(cap)); CU(ctx->d_hits.alloc(cap + 2));   // +2: the TMA copy of an odd-sized tail rounds up to 16 B CU(ctx->d_bins.alloc((size_t)cap * RT_NUM_BINS));
+static int ensure_queues(rt_ctx *ctx, QueueSet &S, long long cap, int max_depth, bool nee) {
+    for (int k = 0; k < 2; ++k) { CU(S.ray_o[k].alloc(cap)); CU(S.ray_d[k].alloc(cap)); CU(S.thr[k].alloc(cap)); }
+    CU(S.radiance.alloc(cap)); CU(S.hits.alloc(cap + 2));   // +2: the TMA copy of an odd-sized tail rounds up to 16 B
+    CU(S.qcount.alloc(max_depth + 2)); CU(S.workctr.alloc((size_t)max_depth * 2));
     CU(ctx->d_counters.alloc(CTR_COUNT));
     if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(2)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 2 * sizeof(unsigned long long), ctx->stream)); }
-    ctx->queue_cap = cap;
-    Queues &q = ctx->q;
-    for (int k = 0; k < 2; ++k) { q.ray_o[k] = ctx->d_ray_o[k].p; q.ray_d[k] = ctx->d_ray_d[k].p; q.thr[k] = ctx->d_thr[k].p; }
-    q.hits = ctx->d_hits.p; q.bins = ctx->d_bins.p; q.radiance = ctx->d_radiance.p; q.counters = ctx->d_counters.p; q.cap = cap;
-    return RT_OK;
-}
-
-static int ensure_depth_buffers(rt_ctx *ctx, int max_depth) {
-    CU(ctx->d_qcount.alloc(max_depth + 2)); CU(ctx->d_bincount.alloc((size_t)max_depth * RT_BIN_STRIDE)); CU(ctx->d_workctr.alloc((size_t)max_depth * 2));
-    ctx->q.qcount = ctx->d_qcount.p; ctx->q.bincount = ctx->d_bincount.p; ctx->q.workctr = ctx->d_workctr.p;
+    S.cap = std::max(S.cap, cap);
+    Queues &q = S.q;
+    for (int k = 0; k < 2; ++k) { q.ray_o[k] = S.ray_o[k].p; q.ray_d[k] = S.ray_d[k].p; q.thr[k] = S.thr[k].p; }
+    q.hits = S.hits.p; q.bins = nullptr; q.bincount = nullptr; q.radiance = S.radiance.p; q.counters = ctx->d_counters.p; q.cap = cap;
+    q.qcount = S.qcount.p; q.workctr = S.workctr.p;
+    q.sh_o = nullptr; q.sh_d = nullptr; q.sh_c = nullptr; q.shcount = nullptr;
+    if (nee) {
+        CU(S.sh_o.alloc(cap)); CU(S.sh_d.alloc(cap)); CU(S.sh_c.alloc(cap)); CU(S.shcount.alloc(max_depth + 1));
+        q.sh_o = S.sh_o.p; q.sh_d = S.sh_d.p; q.sh_c = S.sh_c.p; q.shcount = S.shcount.p;
+    }
     return RT_OK;
 }
 
@@ -422,26 +427,32 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     const bool nee = (prm->flags & RT_RENDER_NEE) != 0;
     if (nee && ds.sampling != RT_SAMPLING_REFERENCE_CPU)
         return rt_fail(ctx, RT_ERR_INVALID, "rt_render: RT_RENDER_NEE needs the reference_cpu sampling convention (cosine-weighted lambertian)");
-    // wavefront size: whole sample planes, at most max_paths_per_pass paths and at most 2^30 queue entries
+    static const bool trace = getenv("RT_TRACE") != nullptr;      // host-side timing of this call on stderr
+    const auto t_enter = std::chrono::steady_clock::now();
+    const bool time_stages = !count && (prm->flags & RT_RENDER_TIME_STAGES) != 0;
+    // Two passes in flight on two streams (unless a diagnostic mode wants serial stage times): the bounce loop ends in
+    // dozens of short launches that cannot fill the GPU; the other pass's long early-bounce launches fill it meanwhile.
+    const int n_sets = (count || time_stages || (prm->flags & RT_RENDER_SERIAL) || spp < 2) ? 1 : 2;
+    // wavefront size: whole sample planes, at most max_paths_per_pass paths and at most 2^30 queue entries per set
     long long max_paths = prm->max_paths_per_pass;
     if (max_paths <= 0) {
         size_t free_b = 0, total_b = 0;
         cudaMemGetInfo(&free_b, &total_b);
-        const long long per_path = 2 * 48 + 16 + 8 + 4 * RT_NUM_BINS;            // bytes per queue entry
-        long long by_mem = (long long)((double)(free_b + ctx->queue_cap * per_path) * 0.5 / per_path);
-        max_paths = std::min<long long>(by_mem, 64ll << 20);
+        const long long per_path = 2 * 48 + 16 + 8 + (nee ? 48 : 0);            // bytes per queue entry
+        const long long held = (ctx->qs[0].cap + ctx->qs[1].cap) * per_path;
+        long long by_mem = (long long)((double)(free_b + held) * 0.5 / per_path) / n_sets;
+        // big wavefronts amortise the ~100 short late-bounce launches of a pass: 2 x 128 M paths = 32 GB of the 180 GB
+        max_paths = std::min<long long>(by_mem, (256ll << 20) / n_sets);
     }
     max_paths = std::min<long long>(max_paths, 1ll << 30);
     int s_pass = (int)std::max<long long>(1, std::min<long long>(spp, max_paths / np));
+    if (n_sets == 2) s_pass = std::min(s_pass, (spp + 1) / 2);                    // at least two passes to overlap
     const long long cap = (long long)s_pass * np;
-    if (cap > (1ll << 31) - 64) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: image too large for one wavefront pass");
-    int rc = ensure_queues(ctx, cap); if (rc) return rc;
-    rc = ensure_depth_buffers(ctx, ds.max_depth); if (rc) return rc;
-    rc = ensure_accum(ctx); if (rc) return rc;
-    ctx->q.sh_o = nullptr; ctx->q.sh_d = nullptr; ctx->q.sh_c = nullptr; ctx->q.shcount = nullptr;
-    if (nee) {
-        CU(ctx->d_sh_o.alloc(cap)); CU(ctx->d_sh_d.alloc(cap)); CU(ctx->d_sh_c.alloc(cap)); CU(ctx->d_shcount.alloc(ds.max_depth + 1));
-        ctx->q.sh_o = ctx->d_sh_o.p; ctx->q.sh_d = ctx->d_sh_d.p; ctx->q.sh_c = ctx->d_sh_c.p; ctx->q.shcount = ctx->d_shcount.p;
+    if (cap > (1ll << 30) - 64) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: image too large for one wavefront pass");
+    int rc = ensure_accum(ctx); if (rc) return rc;
+    for (int k = 0; k < n_sets; ++k) {
+        rc = ensure_queues(ctx, ctx->qs[k], cap, ds.max_depth, nee); if (rc) return rc;
+        ctx->qs[k].cfg = ctx->cfg; ctx->qs[k].cfg.stream = k == 0 ? ctx->stream : ctx->stream2;
     }
     cudaStream_t s = ctx->stream;
     bool clear = !((prm->flags & RT_RENDER_KEEP_ACCUM) && ctx->accum_valid);
@@ -450,10 +461,9 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     float ms_stage[5] = {0, 0, 0, 0, 0};
     cudaEvent_t evs[2] = {nullptr, nullptr};
     if (count) { cudaEventCreate(&evs[0]); cudaEventCreate(&evs[1]); }
-    const bool time_stages = !count && (prm->flags & RT_RENDER_TIME_STAGES) != 0;
     if (time_stages) {          // event pairs are recorded without synchronising and resolved in rt_download
         const size_t n_passes = (size_t)((spp + s_pass - 1) / s_pass);
-        const size_t need = ctx->pending.size() + n_passes * (2 + 2 * (size_t)ds.max_depth);
+        const size_t need = ctx->pending.size() + n_passes * (2 + 3 * (size_t)ds.max_depth);
         while (ctx->ev_pool.size() < 2 * need) { cudaEvent_t e; if (cudaEventCreate(&e) != cudaSuccess) return rt_fail(ctx, RT_ERR_CUDA, "cudaEventCreate"); ctx->ev_pool.push_back(e); }
     }
     auto timed = [&](int stage, auto &&fn) {
@@ -464,24 +474,47 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         if (time_stages) cudaEventRecord(ctx->ev_pool[2 * slot + 1], s);
         if (count) { cudaEventRecord(evs[1], s); cudaEventSynchronize(evs[1]); float ms = 0; cudaEventElapsedTime(&ms, evs[0], evs[1]); ms_stage[stage] += ms; }
     };
+    const auto t_prep = std::chrono::steady_clock::now();
     CU(cudaEventRecord(ctx->ev0, s));
+    if (n_sets == 2) {          // the second stream starts after everything already queued on the caller's stream
+        CU(cudaEventRecord(ctx->ev_fork, s));
+        CU(cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
+    }
+    int last_set = 0;
     for (int done = 0; done < spp; done += s_pass) {
         const int sn = std::min(s_pass, spp - done);
         const int n_paths = sn * np;
-        launch_pass_init(ctx->cfg, ctx->q, ds.max_depth, n_paths);
-        timed(0, [&] { launch_generate(ctx->cfg, ds, ctx->q, prm->seed, prm->spp_begin + done, n_paths, nee); });
+        const int k = (int)(passes % n_sets);
+        QueueSet &S = ctx->qs[k];
+        const LaunchCfg &cfg = S.cfg;
+        launch_pass_init(cfg, S.q, ds.max_depth, n_paths);
+        timed(0, [&] { launch_generate(cfg, ds, S.q, prm->seed, prm->spp_begin + done, n_paths, nee); });
         int buf = 0;
         for (int b = 0; b < ds.max_depth; ++b) {
-            timed(1, [&] { launch_extend(ctx->cfg, ds, ctx->q, b, buf, count, sort); });
-            timed(2, [&] { launch_shade(ctx->cfg, ds, ctx->q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort, nee); });
-            if (nee) timed(4, [&] { launch_shadow(ctx->cfg, ds, ctx->q, b); });
+            timed(1, [&] { launch_extend(cfg, ds, S.q, b, buf, count, sort); });
+            timed(2, [&] { launch_shade(cfg, ds, S.q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort, nee); });
+            if (nee) timed(4, [&] { launch_shadow(cfg, ds, S.q, b); });
             buf ^= 1;
         }
-        timed(3, [&] { launch_accumulate(ctx->cfg, ctx->q, ctx->d_accum.p, ds.width, ds.height, sn, clear, ds.max_depth, ctx->d_rays.p); });
+        // samples are added to the image in ascending order whatever the stream: pass p's accumulate follows pass p-1's
+        if (n_sets == 2 && passes > 0) CU(cudaStreamWaitEvent(cfg.stream, ctx->qs[k ^ 1].ev_acc, 0));
+        timed(3, [&] { launch_accumulate(cfg, S.q, ctx->d_accum.p, ds.width, ds.height, sn, clear, ds.max_depth, ctx->d_rays.p); });
+        if (n_sets == 2) CU(cudaEventRecord(S.ev_acc, cfg.stream));
         clear = false;
+        last_set = k;
         ++passes;
     }
+    if (n_sets == 2) {          // join: the caller's stream continues after both pass streams
+        // (a last pass on the caller's stream has already waited for the other stream's final accumulate)
+        if (last_set == 1) CU(cudaStreamWaitEvent(s, ctx->qs[1].ev_acc, 0));
+    }
     CU(cudaEventRecord(ctx->ev1, s));
+    if (trace) {
+        const auto t_done = std::chrono::steady_clock::now();
+        fprintf(stderr, "[rt_render] prep %.2f ms, enqueue %.2f ms, %lld passes of %d spp on %d stream(s)\n",
+                std::chrono::duration<double, std::milli>(t_prep - t_enter).count(), std::chrono::duration<double, std::milli>(t_done - t_prep).count(),
+                passes, s_pass, n_sets);
+    }
     CU(cudaGetLastError());
     ctx->accum_valid = true;
     rt_stats &st = ctx->stats;

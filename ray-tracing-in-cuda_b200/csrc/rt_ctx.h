@@ -28,6 +28,19 @@ template <class T> struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
 };
 
+struct QueueSet {
+    Queues q{};
+    DevBuf<float4> ray_o[2], ray_d[2], thr[2], radiance, sh_o, sh_d, sh_c; DevBuf<int2> hits; DevBuf<int> qcount, workctr, shcount;
+    long long cap = 0;
+    LaunchCfg cfg{};                    // the context's launch configuration on this set's stream
+    cudaEvent_t ev_acc = nullptr;       // recorded after this set's accumulate: orders the accumulation across streams
+    void release() {
+        for (int k = 0; k < 2; ++k) { ray_o[k].release(); ray_d[k].release(); thr[k].release(); }
+        radiance.release(); sh_o.release(); sh_d.release(); sh_c.release(); hits.release(); qcount.release(); workctr.release(); shcount.release();
+        cap = 0;
+    }
+};
+
 struct rt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -52,13 +65,13 @@ struct rt_ctx {
     DevBuf<BvhNode> d_nodes; DevBuf<BvhNodeS> d_nodes_s; DevBuf<float4> d_primA, d_primB, d_primC;
     // sampled lights (next-event estimation)
     DevBuf<int> d_light_slot, d_light_type, d_obj_light; DevBuf<float> d_light_area;
-    DevBuf<float4> d_sh_o, d_sh_d, d_sh_c; DevBuf<int> d_shcount; long long shadow_cap = 0;
-    // wavefront
-    Queues q{};
-    DevBuf<float4> d_ray_o[2], d_ray_d[2], d_thr[2], d_radiance; DevBuf<int2> d_hits; DevBuf<int> d_bins, d_qcount, d_bincount, d_workctr;
+    // wavefront: two independent queue sets, one per stream, so that the short late-bounce launches of one pass overlap
+    // the long early-bounce launches of the next (rt_render)
+    QueueSet qs[2];
+    cudaStream_t stream2 = nullptr;     // second pass stream (ours; the first is `stream`)
+    cudaEvent_t ev_fork = nullptr;
     DevBuf<unsigned long long> d_counters, d_rays;
     DevBuf<float> d_accum; DevBuf<unsigned char> d_rgb8; DevBuf<float> d_aov; DevBuf<const float *> d_partials;
-    long long queue_cap = 0;
     // stats
     rt_stats stats{};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;

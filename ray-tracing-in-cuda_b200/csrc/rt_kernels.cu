@@ -40,7 +40,6 @@ __device__ __forceinline__ void flush_counter(unsigned long long *counters, int 
 __global__ void k_pass_init(Queues q, int max_depth, int n_paths) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i <= max_depth) q.qcount[i] = i == 0 ? n_paths : 0;
-    if (i < max_depth * RT_BIN_STRIDE) q.bincount[i] = 0;
     if (i < max_depth * 2) q.workctr[i] = 0;
     if (q.shcount && i < max_depth) q.shcount[i] = 0;
 }
@@ -469,7 +468,7 @@ static inline int persistent_grid(const LaunchCfg &c, int per_sm) { return c.num
 static inline void bump(const LaunchCfg &c) { if (c.launches) ++*c.launches; }
 
 void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_paths) {
-    int n = max_depth * RT_BIN_STRIDE + 1;
+    int n = max_depth * 2 + 2;
     k_pass_init<<<(n + 255) / 256, 256, 0, c.stream>>>(q, max_depth, n_paths);
     bump(c);
 }

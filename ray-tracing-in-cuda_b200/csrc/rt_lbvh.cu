@@ -319,7 +319,8 @@ __global__ void __launch_bounds__(256) k_pack(int n, const int *__restrict__ lef
     BvhNodeS ns;
     ns.lx = make_float4(lb[0], lb[3], lb[3], lb[0]); ns.ly = make_float4(lb[1], lb[4], lb[4], lb[1]); ns.lz = make_float4(lb[2], lb[5], lb[5], lb[2]);
     ns.rx = make_float4(rb[0], rb[3], rb[3], rb[0]); ns.ry = make_float4(rb[1], rb[4], rb[4], rb[1]); ns.rz = make_float4(rb[2], rb[5], rb[5], rb[2]);
-    ns.link = make_int4(lc, rc, 0, 0); ns.pad = make_int4(0, 0, 0, 0);
+    // inner children as byte offsets into the node array (the traversal adds them to a shared-memory address)
+    ns.link = make_int4(lc >= 0 ? lc << 7 : lc, rc >= 0 ? rc << 7 : rc, 0, 0); ns.pad = make_int4(0, 0, 0, 0);
     nodes_s[i] = ns;
 }
 

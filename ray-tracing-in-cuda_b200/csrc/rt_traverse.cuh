@@ -3,7 +3,7 @@
 // Result contract = the reference's linear walk: the accepted hit is the smallest root over all objects, and on an
 // exact tie in t the object with the LARGER scene-file index wins ("last index wins": the walk tests
 // `t_max < root`, so an equal root replaces the earlier one).  Box tests only prune; they are conservative
-// (one FFMA per slab plane, t = plane * (1/d) - o/d, with the error margin |t| * 2^-20 + 2^-22 * max|o/d| applied to the
+// (one FFMA per slab plane, t = plane * (1/d) - o/d, with the error margin |t| * 2^-20 + 2^-21 * max|o/d| applied to the
 // hit test and to the stack cull), so no hit the linear walk would accept can be culled — tests compare against the
 // brute-force oracle and expect zero mismatching pixels.  Leaf tests are the exact reference arithmetic (rt_scene.cuh).
 //
@@ -32,11 +32,28 @@ __device__ __forceinline__ void count_leaf(TravCounters &c, int code, bool hit) 
 }
 
 #define RT_BOX_REL 9.5367431640625e-07f      // 2^-20: reciprocal + fma rounding, relative to t
-#define RT_BOX_ABS 2.384185791015625e-07f    // 2^-22 * max|o/d|: rounding of the hoisted o/d term
+#define RT_BOX_ABS 4.76837158203125e-07f     // 2^-21 * max|o/d|: rounding of the hoisted o/d term (and of the inflated copies)
 #define RT_TRAV_DONE ((int)0x80000000)
+#define RT_NODE_S_SHIFT 7                    // BvhNodeS links of inner children are byte offsets (index << 7)
 
-// nodes: BvhNodeS array (SIGNED) or BvhNode array (!SIGNED), in shared or global memory.
+__device__ __forceinline__ float2 lds_f2(unsigned addr) {
+    float2 v;
+    asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ int2 lds_i2(unsigned addr) {
+    int2 v;
+    asm("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
+
+// nodes: BvhNodeS array in SHARED memory (SIGNED) or BvhNode array in global memory (!SIGNED).
 // Returns best_t / best_code (-1 = miss).  ANY_HIT: stop at the first accepted hit (occlusion rays).
+//
+// Margins without per-node work (SIGNED): far planes are evaluated with an inflated copy of the ray constants,
+//   t_far' = plane * (ood (1+r)) + (oo (1+r) + E) = t_far (1+r) + E      (t_far > 0; boxes behind the origin never pass),
+// and the current best distance is kept twice: best_t (exact, for the leaf tests) and best_f = best_t (1+r) + E (for the box
+// tests and the stack cull), refreshed only when a leaf is accepted.
 template <bool SIGNED, bool COUNT, bool ANY_HIT>
 __device__ __forceinline__ void traverse(const DScene &sc, const char *__restrict__ nodes, float3 o, float3 d, float tmin,
                                          float tmax, float &best_t, int &best_code, TravCounters &cnt) {
@@ -48,8 +65,17 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
     float ex = fabsf(oo.x), ey = fabsf(oo.y), ez = fabsf(oo.z);
     ex = ex < INFINITY ? ex : 0.0f; ey = ey < INFINITY ? ey : 0.0f; ez = ez < INFINITY ? ez : 0.0f;
     const float E = RT_BOX_ABS * fmaxf(ex, fmaxf(ey, ez));
+    const float G = 1.0f + RT_BOX_REL;
+    const float3 oodf = v3(ood.x * G, ood.y * G, ood.z * G);
+    const float3 oof = v3(__fmaf_rn(oo.x, G, E), __fmaf_rn(oo.y, G, E), __fmaf_rn(oo.z, G, E));
+    float best_f = __fmaf_rn(best_t, G, E);
     // 8 where the ray travels in the negative axis direction: selects the (near, far) half of a plane quadruple
-    const int sx = (__float_as_int(d.x) >> 31) & 8, sy = (__float_as_int(d.y) >> 31) & 8, sz = (__float_as_int(d.z) >> 31) & 8;
+    unsigned al = 96, ax = (__float_as_int(d.x) >> 31) & 8, ay = (__float_as_int(d.y) >> 31) & 8, az = (__float_as_int(d.z) >> 31) & 8;
+    if (SIGNED) {
+        const unsigned sbase = (unsigned)__cvta_generic_to_shared(nodes);
+        ax += sbase; ay += sbase + 16; az += sbase + 32; al += sbase;
+        asm("" : "+r"(al));        // opaque: keeps the compiler from re-deriving the shared window base every iteration
+    }
     int2 stack[RT_TRAV_STACK];
     int sp = 0, cur = 0;
     // next subtree that can still contain a closer (or equally close) hit; none left: done
@@ -58,7 +84,7 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
         if (sp == 0) { cur = RT_TRAV_DONE; break; }                              \
         --sp;                                                                    \
         const int2 e_ = stack[sp];                                               \
-        if (__int_as_float(e_.y) <= best_t) { cur = e_.x; break; }               \
+        if (__int_as_float(e_.y) <= best_f) { cur = e_.x; break; }               \
     }
     while (cur != RT_TRAV_DONE) {
         // leaf step first, inner step second: a lane that holds a leaf tests it, pops, and still takes part in this
@@ -72,7 +98,7 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
                 bool take = t < best_t || best_code < 0;
                 if (!take)   // t == best_t: the later object in the scene file wins (object.cuh:29-33)
                     take = __ldg(&sc.prim_obj[code & RT_LEAF_SLOT_MASK]) > __ldg(&sc.prim_obj[best_code & RT_LEAF_SLOT_MASK]);
-                if (take) { best_t = t; best_code = code; if (ANY_HIT) return; }
+                if (take) { best_t = t; best_code = code; best_f = __fmaf_rn(t, G, E); if (ANY_HIT) return; }
             }
             RT_POP()
         }
@@ -80,15 +106,14 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
             float tnl, tfl, tnr, tfr;
             int2 nd;
             if (SIGNED) {
-                const char *nb = nodes + (size_t)cur * sizeof(BvhNodeS);
-                const float2 lx = *reinterpret_cast<const float2 *>(nb + 0 + sx), ly = *reinterpret_cast<const float2 *>(nb + 16 + sy);
-                const float2 lz = *reinterpret_cast<const float2 *>(nb + 32 + sz), rx = *reinterpret_cast<const float2 *>(nb + 48 + sx);
-                const float2 ry = *reinterpret_cast<const float2 *>(nb + 64 + sy), rz = *reinterpret_cast<const float2 *>(nb + 80 + sz);
-                nd = *reinterpret_cast<const int2 *>(nb + 96);
+                const unsigned c = (unsigned)cur;                 // byte offset of the node
+                const float2 lx = lds_f2(ax + c), ly = lds_f2(ay + c), lz = lds_f2(az + c);
+                const float2 rx = lds_f2(ax + c + 48), ry = lds_f2(ay + c + 48), rz = lds_f2(az + c + 48);
+                nd = lds_i2(al + c);
                 tnl = fmaxf(fmaxf(__fmaf_rn(lx.x, ood.x, oo.x), __fmaf_rn(ly.x, ood.y, oo.y)), fmaxf(__fmaf_rn(lz.x, ood.z, oo.z), tmin));
-                tfl = fminf(fminf(__fmaf_rn(lx.y, ood.x, oo.x), __fmaf_rn(ly.y, ood.y, oo.y)), fminf(__fmaf_rn(lz.y, ood.z, oo.z), best_t));
+                tfl = fminf(fminf(__fmaf_rn(lx.y, oodf.x, oof.x), __fmaf_rn(ly.y, oodf.y, oof.y)), fminf(__fmaf_rn(lz.y, oodf.z, oof.z), best_f));
                 tnr = fmaxf(fmaxf(__fmaf_rn(rx.x, ood.x, oo.x), __fmaf_rn(ry.x, ood.y, oo.y)), fmaxf(__fmaf_rn(rz.x, ood.z, oo.z), tmin));
-                tfr = fminf(fminf(__fmaf_rn(rx.y, ood.x, oo.x), __fmaf_rn(ry.y, ood.y, oo.y)), fminf(__fmaf_rn(rz.y, ood.z, oo.z), best_t));
+                tfr = fminf(fminf(__fmaf_rn(rx.y, oodf.x, oof.x), __fmaf_rn(ry.y, oodf.y, oof.y)), fminf(__fmaf_rn(rz.y, oodf.z, oof.z), best_f));
             } else {
                 const BvhNode *nb = reinterpret_cast<const BvhNode *>(nodes) + cur;
                 const float4 na = nb->a, nbb = nb->b, nc = nb->c;
@@ -105,15 +130,16 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
                 z0 = __fmaf_rn(nc.x, ood.z, oo.z); z1 = __fmaf_rn(nc.w, ood.z, oo.z);
                 tnr = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
                 tfr = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
+                tfl = __fmaf_rn(fabsf(tfl), RT_BOX_REL, tfl + E);
+                tfr = __fmaf_rn(fabsf(tfr), RT_BOX_REL, tfr + E);
             }
             if (COUNT) { cnt.box += 2; cnt.nodes++; }
-            const bool hl = tnl <= __fmaf_rn(fabsf(tfl), RT_BOX_REL, tfl + E);
-            const bool hr = tnr <= __fmaf_rn(fabsf(tfr), RT_BOX_REL, tfr + E);
+            const bool hl = tnl <= tfl;
+            const bool hr = tnr <= tfr;
             if (hl && hr) {
                 const bool lfirst = tnl <= tnr;
-                const float tfar = lfirst ? tnr : tnl;
                 if (sp < RT_TRAV_STACK) {
-                    stack[sp] = make_int2(lfirst ? nd.y : nd.x, __float_as_int(__fmaf_rn(-fabsf(tfar), RT_BOX_REL, tfar) - E));
+                    stack[sp] = make_int2(lfirst ? nd.y : nd.x, __float_as_int(lfirst ? tnr : tnl));
                     ++sp;
                 } else if (COUNT) cnt.overflow++;
                 cur = lfirst ? nd.x : nd.y;

@@ -147,6 +147,12 @@ def test_render_options_do_not_change_the_image(rt):
     assert np.array_equal(rt.download()[0], base)
     rt.render(seed=5, max_paths_per_pass=W * H * 2)
     assert np.array_equal(rt.download()[0], base)
+    rt.render(seed=5, flags=capi.RT_RENDER_SERIAL)                       # one stream instead of two passes in flight
+    assert np.array_equal(rt.download()[0], base)
+    rt.render(seed=5, flags=capi.RT_RENDER_SERIAL, max_paths_per_pass=W * H)
+    assert np.array_equal(rt.download()[0], base)
+    rt.render(seed=5, max_paths_per_pass=W * H)                           # six one-sample passes alternating between the streams
+    assert np.array_equal(rt.download()[0], base)
     rt.render(seed=5, flags=capi.RT_RENDER_COUNT_EVENTS)
     img, _, st = rt.download()
     assert np.array_equal(img, base) and st["n_box_tests"] > 0 and st["n_shade"] > 0
