@@ -49,19 +49,26 @@ __global__ void k_pass_init(Queues q, int max_depth, int n_paths) {
 // `accumulate` reads the radiance of one sample index as one contiguous, coalesced plane.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsigned seed, int spp_begin, int n_paths, int zero_radiance) {
-    const int np = sc.width * sc.height;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_paths; i += gridDim.x * blockDim.x) {
-        const int s_local = i / np, pixel = plane_to_pixel(sc.width, sc.height, i - s_local * np);
+    // one thread per (tile-ordered) pixel slot and group of samples: the pixel arithmetic is done once, the sample planes are
+    // written with stride n_pixels (each plane coalesced across the warp)
+    const int np = sc.width * sc.height, n_s = n_paths / np;
+    const float div_w = (float)(sc.width - 1), div_h = (float)(sc.height - 1);      // divisors of camera.cuh's (i + r) / (W - 1)
+    const int groups = gridDim.y;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < np; k += gridDim.x * blockDim.x) {
+        const int pixel = plane_to_pixel(sc.width, sc.height, k);
         const int y = pixel / sc.width, x = pixel - y * sc.width;
-        Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), 0u, sc.sampling);
-        const float u = ((float)x + rng.next()) / (float)(sc.width - 1);
-        const float v = ((float)y + rng.next()) / (float)(sc.height - 1);
-        float3 o, d;
-        camera_ray(sc.cam, u, v, sc.defocus != 0, rng, o, d);
-        q.ray_o[0][i] = make_float4(o.x, o.y, o.z, __int_as_float(i));
-        if (zero_radiance) q.radiance[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);      // NEE: several stages add to it
-        q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // Philox key words travel with the path:
-        q.thr[0][i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(s_local));      // no divisions in the shade stage
+        for (int s_local = blockIdx.y; s_local < n_s; s_local += groups) {
+            const int i = s_local * np + k;
+            Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), 0u, sc.sampling);
+            const float u = ((float)x + rng.next()) / div_w;
+            const float v = ((float)y + rng.next()) / div_h;
+            float3 o, d;
+            camera_ray(sc.cam, u, v, sc.defocus != 0, rng, o, d);
+            q.ray_o[0][i] = make_float4(o.x, o.y, o.z, __int_as_float(i));
+            if (zero_radiance) q.radiance[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);      // NEE: several stages add to it
+            q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // Philox key words travel with the path:
+            q.thr[0][i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(s_local));      // no divisions in the shade stage
+        }
     }
 }
 
@@ -474,9 +481,12 @@ void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_
 }
 
 void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths, bool zero_radiance) {
-    long long blocks = ((long long)n_paths + RT_BLOCK - 1) / RT_BLOCK;
-    int grid = (int)(blocks < (long long)c.num_sms * 16 ? blocks : (long long)c.num_sms * 16);
-    k_generate<<<grid, RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, n_paths, zero_radiance ? 1 : 0);
+    const int np = sc.width * sc.height, n_s = n_paths / np;
+    const int bx = (np + RT_BLOCK - 1) / RT_BLOCK;
+    // enough CTAs to fill the GPU: pixel blocks x sample groups
+    int gy = (c.num_sms * 16 + bx - 1) / bx;
+    gy = gy < 1 ? 1 : (gy > n_s ? n_s : gy);
+    k_generate<<<dim3(bx, gy), RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, n_paths, zero_radiance ? 1 : 0);
     bump(c);
 }
 
@@ -513,7 +523,9 @@ int extend_max_blocks_per_sm(size_t smem_bytes) {
 
 void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
                   bool last_bounce, bool count, bool sort, bool nee) {
-    static bool configured = false;
+    static bool configured_dev[64] = {};         // the attribute is per device
+    int dev = 0; cudaGetDevice(&dev);
+    bool &configured = configured_dev[dev & 63];
     if (!configured) {
         cudaFuncSetAttribute(k_shade<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
         cudaFuncSetAttribute(k_shade<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
