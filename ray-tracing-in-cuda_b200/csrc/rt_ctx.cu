@@ -59,9 +59,9 @@ extern "C" int rt_create(rt_ctx **out, int device, void *stream) {
         c->own_stream = true;
     }
     cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1);
-    cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking);
+    for (int k = 1; k < RT_MAX_SETS; ++k) cudaStreamCreateWithFlags(&c->extra_stream[k], cudaStreamNonBlocking);
     cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
-    for (int k = 0; k < 2; ++k) cudaEventCreateWithFlags(&c->qs[k].ev_acc, cudaEventDisableTiming);
+    for (int k = 0; k < RT_MAX_SETS; ++k) cudaEventCreateWithFlags(&c->qs[k].ev_acc, cudaEventDisableTiming);
     c->cfg.stream = c->stream; c->cfg.num_sms = c->num_sms; c->cfg.launches = &c->launches;
     *out = c;
     return RT_OK;
@@ -84,9 +84,9 @@ extern "C" void rt_destroy(rt_ctx *c) {
     c->d_left.release(); c->d_right.release(); c->d_parent.release(); c->d_flags.release(); c->d_prim_obj.release();
     c->d_prim_mat.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_light_slot.release(); c->d_light_type.release(); c->d_obj_light.release(); c->d_light_area.release();
     c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
-    for (int k = 0; k < 2; ++k) { c->qs[k].release(); if (c->qs[k].ev_acc) cudaEventDestroy(c->qs[k].ev_acc); }
+    for (int k = 0; k < RT_MAX_SETS; ++k) { c->qs[k].release(); if (c->qs[k].ev_acc) cudaEventDestroy(c->qs[k].ev_acc); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    if (c->stream2) cudaStreamDestroy(c->stream2);
+    for (int k = 1; k < RT_MAX_SETS; ++k) if (c->extra_stream[k]) cudaStreamDestroy(c->extra_stream[k]);
     c->d_counters.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
     c->d_partials.release(); c->d_rays.release();
     for (auto e : c->ev_pool) cudaEventDestroy(e);
@@ -432,27 +432,29 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     const bool time_stages = !count && (prm->flags & RT_RENDER_TIME_STAGES) != 0;
     // Two passes in flight on two streams (unless a diagnostic mode wants serial stage times): the bounce loop ends in
     // dozens of short launches that cannot fill the GPU; the other pass's long early-bounce launches fill it meanwhile.
-    const int n_sets = (count || time_stages || (prm->flags & RT_RENDER_SERIAL) || spp < 2) ? 1 : 2;
+    static const int want_sets = getenv("RT_STREAMS") ? std::max(1, std::min(RT_MAX_SETS, atoi(getenv("RT_STREAMS")))) : 2;
+    const int n_sets = (count || time_stages || (prm->flags & RT_RENDER_SERIAL)) ? 1 : std::min(want_sets, spp);
     // wavefront size: whole sample planes, at most max_paths_per_pass paths and at most 2^30 queue entries per set
     long long max_paths = prm->max_paths_per_pass;
     if (max_paths <= 0) {
         size_t free_b = 0, total_b = 0;
         cudaMemGetInfo(&free_b, &total_b);
         const long long per_path = 2 * 48 + 16 + 8 + (nee ? 48 : 0);            // bytes per queue entry
-        const long long held = (ctx->qs[0].cap + ctx->qs[1].cap) * per_path;
+        long long held = 0;
+        for (int k = 0; k < RT_MAX_SETS; ++k) held += ctx->qs[k].cap * per_path;
         long long by_mem = (long long)((double)(free_b + held) * 0.5 / per_path) / n_sets;
         // big wavefronts amortise the ~100 short late-bounce launches of a pass: 2 x 128 M paths = 32 GB of the 180 GB
         max_paths = std::min<long long>(by_mem, (256ll << 20) / n_sets);
     }
     max_paths = std::min<long long>(max_paths, 1ll << 30);
     int s_pass = (int)std::max<long long>(1, std::min<long long>(spp, max_paths / np));
-    if (n_sets == 2) s_pass = std::min(s_pass, (spp + 1) / 2);                    // at least two passes to overlap
+    if (n_sets > 1) s_pass = std::min(s_pass, (spp + n_sets - 1) / n_sets);        // at least one pass per stream
     const long long cap = (long long)s_pass * np;
     if (cap > (1ll << 30) - 64) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: image too large for one wavefront pass");
     int rc = ensure_accum(ctx); if (rc) return rc;
     for (int k = 0; k < n_sets; ++k) {
         rc = ensure_queues(ctx, ctx->qs[k], cap, ds.max_depth, nee); if (rc) return rc;
-        ctx->qs[k].cfg = ctx->cfg; ctx->qs[k].cfg.stream = k == 0 ? ctx->stream : ctx->stream2;
+        ctx->qs[k].cfg = ctx->cfg; ctx->qs[k].cfg.stream = k == 0 ? ctx->stream : ctx->extra_stream[k];
     }
     cudaStream_t s = ctx->stream;
     bool clear = !((prm->flags & RT_RENDER_KEEP_ACCUM) && ctx->accum_valid);
@@ -476,9 +478,9 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     };
     const auto t_prep = std::chrono::steady_clock::now();
     CU(cudaEventRecord(ctx->ev0, s));
-    if (n_sets == 2) {          // the second stream starts after everything already queued on the caller's stream
+    if (n_sets > 1) {           // the extra streams start after everything already queued on the caller's stream
         CU(cudaEventRecord(ctx->ev_fork, s));
-        CU(cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
+        for (int k = 1; k < n_sets; ++k) CU(cudaStreamWaitEvent(ctx->extra_stream[k], ctx->ev_fork, 0));
     }
     int last_set = 0;
     for (int done = 0; done < spp; done += s_pass) {
@@ -497,16 +499,16 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
             buf ^= 1;
         }
         // samples are added to the image in ascending order whatever the stream: pass p's accumulate follows pass p-1's
-        if (n_sets == 2 && passes > 0) CU(cudaStreamWaitEvent(cfg.stream, ctx->qs[k ^ 1].ev_acc, 0));
+        if (n_sets > 1 && passes > 0) CU(cudaStreamWaitEvent(cfg.stream, ctx->qs[last_set].ev_acc, 0));
         timed(3, [&] { launch_accumulate(cfg, S.q, ctx->d_accum.p, ds.width, ds.height, sn, clear, ds.max_depth, ctx->d_rays.p); });
-        if (n_sets == 2) CU(cudaEventRecord(S.ev_acc, cfg.stream));
+        if (n_sets > 1) CU(cudaEventRecord(S.ev_acc, cfg.stream));
         clear = false;
         last_set = k;
         ++passes;
     }
-    if (n_sets == 2) {          // join: the caller's stream continues after both pass streams
+    if (n_sets > 1) {           // join: the caller's stream continues after both pass streams
         // (a last pass on the caller's stream has already waited for the other stream's final accumulate)
-        if (last_set == 1) CU(cudaStreamWaitEvent(s, ctx->qs[1].ev_acc, 0));
+        if (last_set != 0) CU(cudaStreamWaitEvent(s, ctx->qs[last_set].ev_acc, 0));
     }
     CU(cudaEventRecord(ctx->ev1, s));
     if (trace) {

@@ -28,6 +28,7 @@ template <class T> struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
 };
 
+#define RT_MAX_SETS 4
 struct QueueSet {
     Queues q{};
     DevBuf<float4> ray_o[2], ray_d[2], thr[2], radiance, sh_o, sh_d, sh_c; DevBuf<int2> hits; DevBuf<int> qcount, workctr, shcount;
@@ -67,8 +68,8 @@ struct rt_ctx {
     DevBuf<int> d_light_slot, d_light_type, d_obj_light; DevBuf<float> d_light_area;
     // wavefront: two independent queue sets, one per stream, so that the short late-bounce launches of one pass overlap
     // the long early-bounce launches of the next (rt_render)
-    QueueSet qs[2];
-    cudaStream_t stream2 = nullptr;     // second pass stream (ours; the first is `stream`)
+    QueueSet qs[RT_MAX_SETS];
+    cudaStream_t extra_stream[RT_MAX_SETS] = {};   // pass streams 1.. (ours; pass stream 0 is `stream`)
     cudaEvent_t ev_fork = nullptr;
     DevBuf<unsigned long long> d_counters, d_rays;
     DevBuf<float> d_accum; DevBuf<unsigned char> d_rgb8; DevBuf<float> d_aov; DevBuf<const float *> d_partials;
