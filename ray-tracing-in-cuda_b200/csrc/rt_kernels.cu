@@ -436,10 +436,18 @@ __global__ void __launch_bounds__(RT_BLOCK) k_aov(DScene sc, float *__restrict__
         float3 o, d;
         camera_ray(sc.cam, u, v, false, rng, o, d);
         float t; int code;
+#ifdef RT_AOV_COST      // development builds (tools/build_variant.py): channel 23 = BVH nodes visited by this pixel's ray
+        cnt.nodes = 0;
+        traverse<false, true, false>(sc, reinterpret_cast<const char *>(sc.nodes), o, d, 0.001f, FLT_MAX, t, code, cnt);
+#else
         traverse<false, false, false>(sc, reinterpret_cast<const char *>(sc.nodes), o, d, 0.001f, FLT_MAX, t, code, cnt);
+#endif
         float q[24];
 #pragma unroll
         for (int k = 0; k < 24; ++k) q[k] = 0.0f;
+#ifdef RT_AOV_COST
+        q[23] = (float)cnt.nodes;
+#endif
         if (code >= 0) {
             const int type = (unsigned)code >> 28, slot = code & RT_LEAF_SLOT_MASK;
             const int mi = sc.prim_mat[slot];

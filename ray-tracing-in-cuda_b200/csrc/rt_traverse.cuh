@@ -3,15 +3,16 @@
 // Result contract = the reference's linear walk: the accepted hit is the smallest root over all objects, and on an
 // exact tie in t the object with the LARGER scene-file index wins ("last index wins": the walk tests
 // `t_max < root`, so an equal root replaces the earlier one).  Box tests only prune; they are conservative
-// (one FFMA per slab plane, t = plane * (1/d) - o/d, with the error margin |t| * 2^-20 + 2^-21 * max|o/d| applied to the
-// hit test and to the stack cull), so no hit the linear walk would accept can be culled — tests compare against the
-// brute-force oracle and expect zero mismatching pixels.  Leaf tests are the exact reference arithmetic (rt_scene.cuh).
+// (one FFMA per slab plane, t = plane * (1/d) - o/d, evaluated with ray constants that already carry the error margin
+// |t| * 2^-20 + 2^-21 * |o/d| of their axis: near planes rounded down, far planes rounded up), so no hit the linear walk
+// would accept can be culled — tests compare against the brute-force oracle and expect zero mismatching pixels.
+// Leaf tests are the exact reference arithmetic (rt_scene.cuh).
 //
 // Two node layouts, one algorithm:
 //   SIGNED = true   BvhNodeS (128 B): plane pairs stored (lo, hi, hi, lo) per box and axis; the ray's direction signs pick
 //                   the 8-byte half that reads (near, far), so a box costs 6 FFMA + 2 three-input min/max + 2 min/max.
 //                   Used when the whole tree is staged in shared memory.
-//   SIGNED = false  BvhNode (64 B): both boxes in three float4; near/far by per-axis min/max.  Half the bytes per visit —
+//   SIGNED = false  BvhNode (64 B): both boxes in three float4; near/far planes picked by the sign predicates.  Half the bytes per visit —
 //                   used when the tree is read from global memory (L1/L2), where bytes matter more than ALU slots.
 #pragma once
 #include "rt_wavefront.cuh"
@@ -32,7 +33,9 @@ __device__ __forceinline__ void count_leaf(TravCounters &c, int code, bool hit) 
 }
 
 #define RT_BOX_REL 9.5367431640625e-07f      // 2^-20: reciprocal + fma rounding, relative to t
-#define RT_BOX_ABS 4.76837158203125e-07f     // 2^-21 * max|o/d|: rounding of the hoisted o/d term (and of the inflated copies)
+#define RT_BOX_ABS 4.76837158203125e-07f     // 2^-21 * |o/d| per axis: rounding of the hoisted o/d term and of the scaled copies
+#define RT_BOX_OOD_MAX 1e18f                 // |1/d| clamp: beyond it the ray counts as parallel to the slab pair
+#define RT_BOX_PAR 1e10f                     // absolute margin of a parallel axis (t units; larger than any scene distance)
 #define RT_TRAV_DONE ((int)0x80000000)
 #define RT_NODE_S_SHIFT 7                    // BvhNodeS links of inner children are byte offsets (index << 7)
 
@@ -50,27 +53,35 @@ __device__ __forceinline__ int2 lds_i2(unsigned addr) {
 // nodes: BvhNodeS array in SHARED memory (SIGNED) or BvhNode array in global memory (!SIGNED).
 // Returns best_t / best_code (-1 = miss).  ANY_HIT: stop at the first accepted hit (occlusion rays).
 //
-// Margins without per-node work (SIGNED): far planes are evaluated with an inflated copy of the ray constants,
-//   t_far' = plane * (ood (1+r)) + (oo (1+r) + E) = t_far (1+r) + E      (t_far > 0; boxes behind the origin never pass),
-// and the current best distance is kept twice: best_t (exact, for the leaf tests) and best_f = best_t (1+r) + E (for the box
-// tests and the stack cull), refreshed only when a leaf is accepted.
+// Conservative slabs without per-node work: every plane is evaluated twice-over-constant, never with a per-node margin —
+//   near planes with  (ood (1-r), oo (1-r) - c|oo|)   so that  t_near' <= exact t_near,
+//   far  planes with  (ood (1+r), oo (1+r) + c|oo|)   so that  t_far'  >= exact t_far      (r = 2^-20, c = 2^-21),
+// per axis (an axis the ray is almost parallel to has a huge |oo|; its own margin grows, the other axes keep theirs).
+// |1/d| is clamped to 1e18; a clamped axis (d = 0 or denormal: the ray is parallel to that slab pair) gets an absolute
+// margin of 1e10 instead, which keeps the slab pair as an inside/outside test without NaNs — before, 0 * inf dropped the
+// slab and such a ray visited every node along its projection (one ray in ~10^4 of the centre column of a camera placed at
+// x = 0: 15 000 node visits, a multi-millisecond tail on the 1 M-triangle mesh).
 template <bool SIGNED, bool COUNT, bool ANY_HIT>
 __device__ __forceinline__ void traverse(const DScene &sc, const char *__restrict__ nodes, float3 o, float3 d, float tmin,
                                          float tmax, float &best_t, int &best_code, TravCounters &cnt) {
     best_t = tmax; best_code = -1;
     if (sc.n_prims == 0) return;
     const float a = dot3(d, d), inv_a = 1.0f / a;
-    const float3 ood = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    float3 ood = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    const bool px = !(fabsf(ood.x) <= RT_BOX_OOD_MAX), py = !(fabsf(ood.y) <= RT_BOX_OOD_MAX), pz = !(fabsf(ood.z) <= RT_BOX_OOD_MAX);
+    if (px) ood.x = copysignf(RT_BOX_OOD_MAX, d.x);
+    if (py) ood.y = copysignf(RT_BOX_OOD_MAX, d.y);
+    if (pz) ood.z = copysignf(RT_BOX_OOD_MAX, d.z);
     const float3 oo = v3(-(o.x * ood.x), -(o.y * ood.y), -(o.z * ood.z));
-    float ex = fabsf(oo.x), ey = fabsf(oo.y), ez = fabsf(oo.z);
-    ex = ex < INFINITY ? ex : 0.0f; ey = ey < INFINITY ? ey : 0.0f; ez = ez < INFINITY ? ez : 0.0f;
-    const float E = RT_BOX_ABS * fmaxf(ex, fmaxf(ey, ez));
-    const float G = 1.0f + RT_BOX_REL;
-    const float3 oodf = v3(ood.x * G, ood.y * G, ood.z * G);
-    const float3 oof = v3(__fmaf_rn(oo.x, G, E), __fmaf_rn(oo.y, G, E), __fmaf_rn(oo.z, G, E));
-    float best_f = __fmaf_rn(best_t, G, E);
-    // 8 where the ray travels in the negative axis direction: selects the (near, far) half of a plane quadruple
-    unsigned al = 96, ax = (__float_as_int(d.x) >> 31) & 8, ay = (__float_as_int(d.y) >> 31) & 8, az = (__float_as_int(d.z) >> 31) & 8;
+    const float3 ca = v3(__fmaf_rn(RT_BOX_ABS, fabsf(oo.x), px ? RT_BOX_PAR : 0.0f), __fmaf_rn(RT_BOX_ABS, fabsf(oo.y), py ? RT_BOX_PAR : 0.0f),
+                         __fmaf_rn(RT_BOX_ABS, fabsf(oo.z), pz ? RT_BOX_PAR : 0.0f));
+    const float GN = 1.0f - RT_BOX_REL, GF = 1.0f + RT_BOX_REL;
+    const float3 oodn = v3(ood.x * GN, ood.y * GN, ood.z * GN), oodf = v3(ood.x * GF, ood.y * GF, ood.z * GF);
+    const float3 oon = v3(__fmaf_rn(oo.x, GN, -ca.x), __fmaf_rn(oo.y, GN, -ca.y), __fmaf_rn(oo.z, GN, -ca.z));
+    const float3 oof = v3(__fmaf_rn(oo.x, GF, ca.x), __fmaf_rn(oo.y, GF, ca.y), __fmaf_rn(oo.z, GF, ca.z));
+    const bool ngx = __float_as_int(d.x) < 0, ngy = __float_as_int(d.y) < 0, ngz = __float_as_int(d.z) < 0;
+    // SIGNED: 8 where the ray travels in the negative axis direction selects the (near, far) half of a plane quadruple
+    unsigned al = 96, ax = ngx ? 8 : 0, ay = ngy ? 8 : 0, az = ngz ? 8 : 0;
     if (SIGNED) {
         const unsigned sbase = (unsigned)__cvta_generic_to_shared(nodes);
         ax += sbase; ay += sbase + 16; az += sbase + 32; al += sbase;
@@ -84,7 +95,7 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
         if (sp == 0) { cur = RT_TRAV_DONE; break; }                              \
         --sp;                                                                    \
         const int2 e_ = stack[sp];                                               \
-        if (__int_as_float(e_.y) <= best_f) { cur = e_.x; break; }               \
+        if (__int_as_float(e_.y) <= best_t) { cur = e_.x; break; }               \
     }
     while (cur != RT_TRAV_DONE) {
         // leaf step first, inner step second: a lane that holds a leaf tests it, pops, and still takes part in this
@@ -98,7 +109,7 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
                 bool take = t < best_t || best_code < 0;
                 if (!take)   // t == best_t: the later object in the scene file wins (object.cuh:29-33)
                     take = __ldg(&sc.prim_obj[code & RT_LEAF_SLOT_MASK]) > __ldg(&sc.prim_obj[best_code & RT_LEAF_SLOT_MASK]);
-                if (take) { best_t = t; best_code = code; best_f = __fmaf_rn(t, G, E); if (ANY_HIT) return; }
+                if (take) { best_t = t; best_code = code; if (ANY_HIT) return; }
             }
             RT_POP()
         }
@@ -110,28 +121,25 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
                 const float2 lx = lds_f2(ax + c), ly = lds_f2(ay + c), lz = lds_f2(az + c);
                 const float2 rx = lds_f2(ax + c + 48), ry = lds_f2(ay + c + 48), rz = lds_f2(az + c + 48);
                 nd = lds_i2(al + c);
-                tnl = fmaxf(fmaxf(__fmaf_rn(lx.x, ood.x, oo.x), __fmaf_rn(ly.x, ood.y, oo.y)), fmaxf(__fmaf_rn(lz.x, ood.z, oo.z), tmin));
-                tfl = fminf(fminf(__fmaf_rn(lx.y, oodf.x, oof.x), __fmaf_rn(ly.y, oodf.y, oof.y)), fminf(__fmaf_rn(lz.y, oodf.z, oof.z), best_f));
-                tnr = fmaxf(fmaxf(__fmaf_rn(rx.x, ood.x, oo.x), __fmaf_rn(ry.x, ood.y, oo.y)), fmaxf(__fmaf_rn(rz.x, ood.z, oo.z), tmin));
-                tfr = fminf(fminf(__fmaf_rn(rx.y, oodf.x, oof.x), __fmaf_rn(ry.y, oodf.y, oof.y)), fminf(__fmaf_rn(rz.y, oodf.z, oof.z), best_f));
+                tnl = fmaxf(fmaxf(__fmaf_rn(lx.x, oodn.x, oon.x), __fmaf_rn(ly.x, oodn.y, oon.y)), fmaxf(__fmaf_rn(lz.x, oodn.z, oon.z), tmin));
+                tfl = fminf(fminf(__fmaf_rn(lx.y, oodf.x, oof.x), __fmaf_rn(ly.y, oodf.y, oof.y)), fminf(__fmaf_rn(lz.y, oodf.z, oof.z), best_t));
+                tnr = fmaxf(fmaxf(__fmaf_rn(rx.x, oodn.x, oon.x), __fmaf_rn(ry.x, oodn.y, oon.y)), fmaxf(__fmaf_rn(rz.x, oodn.z, oon.z), tmin));
+                tfr = fminf(fminf(__fmaf_rn(rx.y, oodf.x, oof.x), __fmaf_rn(ry.y, oodf.y, oof.y)), fminf(__fmaf_rn(rz.y, oodf.z, oof.z), best_t));
             } else {
                 const BvhNode *nb = reinterpret_cast<const BvhNode *>(nodes) + cur;
                 const float4 na = nb->a, nbb = nb->b, nc = nb->c;
                 const int4 nd4 = nb->d;
                 nd = make_int2(nd4.x, nd4.y);
-                // left box: min (na.x na.y na.z) max (na.w nbb.x nbb.y); right box: min (nbb.z nbb.w nc.x) max (nc.y nc.z nc.w)
-                float x0 = __fmaf_rn(na.x, ood.x, oo.x), x1 = __fmaf_rn(na.w, ood.x, oo.x);
-                float y0 = __fmaf_rn(na.y, ood.y, oo.y), y1 = __fmaf_rn(nbb.x, ood.y, oo.y);
-                float z0 = __fmaf_rn(na.z, ood.z, oo.z), z1 = __fmaf_rn(nbb.y, ood.z, oo.z);
-                tnl = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
-                tfl = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
-                x0 = __fmaf_rn(nbb.z, ood.x, oo.x); x1 = __fmaf_rn(nc.y, ood.x, oo.x);
-                y0 = __fmaf_rn(nbb.w, ood.y, oo.y); y1 = __fmaf_rn(nc.z, ood.y, oo.y);
-                z0 = __fmaf_rn(nc.x, ood.z, oo.z); z1 = __fmaf_rn(nc.w, ood.z, oo.z);
-                tnr = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
-                tfr = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
-                tfl = __fmaf_rn(fabsf(tfl), RT_BOX_REL, tfl + E);
-                tfr = __fmaf_rn(fabsf(tfr), RT_BOX_REL, tfr + E);
+                // left box: min (na.x na.y na.z) max (na.w nbb.x nbb.y); right box: min (nbb.z nbb.w nc.x) max (nc.y nc.z nc.w);
+                // the direction signs pick the (near, far) plane of every pair
+                tnl = fmaxf(fmaxf(__fmaf_rn(ngx ? na.w : na.x, oodn.x, oon.x), __fmaf_rn(ngy ? nbb.x : na.y, oodn.y, oon.y)),
+                            fmaxf(__fmaf_rn(ngz ? nbb.y : na.z, oodn.z, oon.z), tmin));
+                tfl = fminf(fminf(__fmaf_rn(ngx ? na.x : na.w, oodf.x, oof.x), __fmaf_rn(ngy ? na.y : nbb.x, oodf.y, oof.y)),
+                            fminf(__fmaf_rn(ngz ? na.z : nbb.y, oodf.z, oof.z), best_t));
+                tnr = fmaxf(fmaxf(__fmaf_rn(ngx ? nc.y : nbb.z, oodn.x, oon.x), __fmaf_rn(ngy ? nc.z : nbb.w, oodn.y, oon.y)),
+                            fmaxf(__fmaf_rn(ngz ? nc.w : nc.x, oodn.z, oon.z), tmin));
+                tfr = fminf(fminf(__fmaf_rn(ngx ? nbb.z : nc.y, oodf.x, oof.x), __fmaf_rn(ngy ? nbb.w : nc.z, oodf.y, oof.y)),
+                            fminf(__fmaf_rn(ngz ? nc.x : nc.w, oodf.z, oof.z), best_t));
             }
             if (COUNT) { cnt.box += 2; cnt.nodes++; }
             const bool hl = tnl <= tfl;

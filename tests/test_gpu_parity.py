@@ -405,3 +405,47 @@ def test_nee_needs_cpu_sampling_convention(rt):
     with pytest.raises(RtError):
         rt.render(flags=capi.RT_RENDER_NEE)
     rt.render()            # the context stays usable
+
+
+def test_axis_parallel_rays_and_faces_on_the_ray_plane(rt):
+    """Rays with a direction component of exactly 0 (centre column / centre row of an axis-aligned camera at the origin of
+    that axis) against geometry whose box faces lie exactly in the ray's plane: the slab pair of the parallel axis must act
+    as an inside/outside test (no NaN, nothing culled that the linear walk accepts).  Also a full render for the counts."""
+    W, H = 96, 54           # even sizes: pixel column 47 / row 26 have u = v = 0.5 exactly
+    tri = lambda a, b, c, m: {"type": "triangle", "v0": a, "v1": b, "v2": c, "material": m}
+    objs = []
+    for k in range(-3, 3):  # a strip of triangle pairs sharing edges on the plane x = 0 and on the plane y = 0
+        z = float(k)
+        objs += [tri([0, -1, z], [1, -1, z], [0, 1, z - 0.5], 0), tri([0, -1, z], [0, 1, z - 0.5], [-1, -1, z], 1),
+                 tri([-2, 0, z], [2, 0, z], [0, 0, z - 0.9], 2)]
+    objs += [{"type": "box", "min": [0, 0, -6], "max": [1.5, 1.5, -5], "material": 0},
+             {"type": "box", "min": [-1.5, -1.5, -6], "max": [0, 0, -5], "material": 1},
+             {"type": "xy_rect", "x0": -4, "x1": 0, "y0": 0, "y1": 3, "k": -7, "material": 2},
+             {"type": "xy_rect", "x0": 0, "x1": 4, "y0": -3, "y1": 0, "k": -7, "material": 0},
+             {"type": "sphere", "center": [0, 0, -9], "radius": 1.0, "material": 3},
+             {"type": "yz_rect", "y0": -3, "y1": 3, "z0": -12, "z1": 4, "k": 0.0, "material": 1},      # edge-on in the plane x = 0
+             {"type": "xz_rect", "x0": -3, "x1": 3, "z0": -12, "z1": 4, "k": 0.0, "material": 2}]      # edge-on in the plane y = 0
+    d = {"output_file": "t.png", "background": [0.6, 0.7, 0.9], "max_depth": 8, "samples_per_pixel": 4, "width": W, "height": H,
+         "camera": {"lookfrom": [0, 0, 5], "lookat": [0, 0, 0], "vup": [0, 1, 0], "vfov": 40, "aperture": 0.0},
+         "object": {"data": objs},
+         "material": {"data": [{"type": "lambertian", "texture": 0}, {"type": "lambertian", "texture": 1},
+                               {"type": "metal", "albedo": [0.8, 0.8, 0.8], "fuzz": 0.1}, {"type": "dielectric", "index_of_refraction": 1.5}]},
+         "texture": {"data": [{"type": "solid_color", "color": [0.8, 0.3, 0.3]}, {"type": "solid_color", "color": [0.3, 0.8, 0.3]}]}}
+    rt.upload_json_text(json.dumps(d))
+    got = rt.render_aov()
+    osc = orc.load_scene(d)
+    want = orc.aov(osc)
+    # rays that lie IN the plane of an edge-on rect get t = 0/0 = NaN from the reference's rect test (object.cuh:105-110
+    # accepts it: NaN fails both range comparisons); the one ray in BOTH planes has two NaN hits and no defined winner
+    ok = ~np.isnan(want[..., 1])
+    assert np.array_equal(np.isnan(got[..., 1]), ~ok)
+    assert np.array_equal(got[..., 0], want[..., 0]) and np.array_equal(got[..., 11][ok], want[..., 11][ok])
+    assert (got[..., 11] != want[..., 11]).sum() <= 1
+    assert np.abs(got - want)[ok].max() <= 1e-5 * max(1.0, np.abs(want[ok]).max())
+    assert want[:, 47, 0].sum() > 0 and want[26, :, 0].sum() > 0          # the degenerate column / row do hit things
+    rt.stats_reset()
+    rt.render(seed=9)
+    img, _, st = rt.download()
+    ref, nrays = orc.render(osc, seed=9)
+    assert st["rays"] == nrays
+    assert (np.abs(img - ref) > 1e-5 * 4).any(-1).sum() == 0
