@@ -163,7 +163,8 @@ def test_render_options_do_not_change_the_image(rt):
     assert not np.array_equal(rt.download()[0], base)
 
 
-@pytest.mark.parametrize("seed", [11, 12])
+# RT_SOAK=n: n more seeded scenes (a wider sweep for one-off runs after traversal changes)
+@pytest.mark.parametrize("seed", [11, 12] + list(range(100, 100 + int(os.environ.get("RT_SOAK", "0")))))
 def test_random_scenes_all_primitives(rt, seed):
     """Every primitive type incl. box/triangle extensions, duplicates (exact ties) and negative radii vs the oracle."""
     sc = random_scene(np.random.default_rng(seed), 60)
