@@ -397,7 +397,7 @@ static int ensure_queues(rt_ctx *ctx, QueueSet &S, long long cap, int max_depth,
     S.cap = std::max(S.cap, cap);
     Queues &q = S.q;
     for (int k = 0; k < 2; ++k) { q.ray_o[k] = S.ray_o[k].p; q.ray_d[k] = S.ray_d[k].p; q.thr[k] = S.thr[k].p; }
-    q.hits = S.hits.p; q.bins = nullptr; q.bincount = nullptr; q.radiance = S.radiance.p; q.counters = ctx->d_counters.p; q.cap = cap;
+    q.hits = S.hits.p; q.radiance = S.radiance.p; q.counters = ctx->d_counters.p; q.cap = cap;
     q.qcount = S.qcount.p; q.workctr = S.workctr.p;
     q.sh_o = nullptr; q.sh_d = nullptr; q.sh_c = nullptr; q.shcount = nullptr;
     if (nee) {

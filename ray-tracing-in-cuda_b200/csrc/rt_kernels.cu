@@ -85,10 +85,13 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
 #define RT_EXT_BLOCK 512
 #define RT_EXT_BATCH 256
 
-template <bool SMEM, bool COUNT>
+// SHADOW = true: the same kernel walks the bounce's occlusion-ray queue (RT_RENDER_NEE) with an any-hit traversal on
+// t in [0.001, 0.999] of the unnormalised segment; an unoccluded sample adds its radiance to the path's slot (one entry per
+// path and bounce, so the add needs no atomic).
+template <bool SMEM, bool COUNT, bool SHADOW>
 __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf, int max_batch) {
     extern __shared__ float4 s_raw[];
-    const int n = q.qcount[bounce];
+    const int n = SHADOW ? q.shcount[bounce] : q.qcount[bounce];
     if (n == 0) return;
     const int total_warps = gridDim.x * (RT_EXT_BLOCK / 32);
     int batch = (n + total_warps - 1) / total_warps;
@@ -101,9 +104,9 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
         __syncthreads();
         nodes = reinterpret_cast<const char *>(s_raw);
     }
-    int *cursor = &q.workctr[bounce * 2 + 0];
-    const float4 *__restrict__ ray_o = q.ray_o[buf];
-    const float4 *__restrict__ ray_d = q.ray_d[buf];
+    int *cursor = &q.workctr[bounce * 2 + (SHADOW ? 1 : 0)];
+    const float4 *__restrict__ ray_o = SHADOW ? q.sh_o : q.ray_o[buf];
+    const float4 *__restrict__ ray_d = SHADOW ? q.sh_d : q.ray_d[buf];
     TravCounters cnt = {};
     for (;;) {
         const int base = warp_fetch(cursor, batch);
@@ -113,8 +116,17 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
         for (int i = base + lane_id(); i < end; i += 32) {
             const float4 o4 = ray_o[i], d4 = ray_d[i];
             float t; int code;
-            traverse<SMEM, COUNT, false>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt);
-            q.hits[i] = make_int2(__float_as_int(t), code);
+            if (SHADOW) {
+                traverse<SMEM, COUNT, true>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt);
+                if (code < 0) {
+                    const int pid = __float_as_int(o4.w);
+                    const float4 c = q.sh_c[i], r = q.radiance[pid];
+                    q.radiance[pid] = make_float4(r.x + c.x, r.y + c.y, r.z + c.z, 0.0f);
+                }
+            } else {
+                traverse<SMEM, COUNT, false>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt);
+                q.hits[i] = make_int2(__float_as_int(t), code);
+            }
         }
     }
     if (COUNT) {
@@ -353,25 +365,6 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
 }
 
 // ------------------------------------------------------------------------------------------------
-// shadow: occlusion test of the light samples taken by shade (any-hit traversal on t in [0.001, 0.999]); an unoccluded
-// sample adds its radiance to the path's slot.  One entry per path per bounce, so the add needs no atomic.
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(RT_BLOCK) k_shadow(DScene sc, Queues q, int bounce) {
-    const int n = q.shcount[bounce];
-    TravCounters cnt = {};
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 o4 = q.sh_o[i], d4 = q.sh_d[i];
-        float t; int code;
-        traverse<false, false, true>(sc, reinterpret_cast<const char *>(sc.nodes), f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt);
-        if (code < 0) {
-            const int pid = __float_as_int(o4.w);
-            const float4 c = q.sh_c[i], r = q.radiance[pid];
-            q.radiance[pid] = make_float4(r.x + c.x, r.y + c.y, r.z + c.z, 0.0f);
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
 // accumulate: accum[pixel] += sum over this pass's samples, in ascending sample order (fixed order => the image is
 // bit-reproducible; replaces the register sum of main.cu:95-104).  One thread per pixel, S coalesced plane reads.
 // ------------------------------------------------------------------------------------------------
@@ -498,34 +491,41 @@ void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsi
     bump(c);
 }
 
-template <bool SMEM>
+template <bool SMEM, bool SHADOW>
 static void launch_extend_t(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count) {
     const int grid = persistent_grid(c, c.extend_blocks_per_sm);
     const size_t sm = SMEM ? c.bvh_smem_bytes : 0;
     static const int batch = getenv("RT_EXT_BATCH") ? atoi(getenv("RT_EXT_BATCH")) : RT_EXT_BATCH;
-    if (count) k_extend<SMEM, true><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
-    else k_extend<SMEM, false><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
+    if (count) k_extend<SMEM, true, SHADOW><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
+    else k_extend<SMEM, false, SHADOW><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
 }
 
 void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort) {
     (void)sort;
-    if (c.bvh_smem_bytes) launch_extend_t<true>(c, sc, q, bounce, buf, count);
-    else launch_extend_t<false>(c, sc, q, bounce, buf, count);
+    if (c.bvh_smem_bytes) launch_extend_t<true, false>(c, sc, q, bounce, buf, count);
+    else launch_extend_t<false, false>(c, sc, q, bounce, buf, count);
+    bump(c);
+}
+
+// shadow stage (RT_RENDER_NEE): the extend kernel in any-hit mode over the occlusion-ray queue shade has just written
+void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce) {
+    if (c.bvh_smem_bytes) launch_extend_t<true, true>(c, sc, q, bounce, 0, false);
+    else launch_extend_t<false, true>(c, sc, q, bounce, 0, false);
     bump(c);
 }
 
 cudaError_t extend_configure_smem(size_t smem_bytes) {
     cudaError_t e = cudaSuccess;
 #define SET(K) if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes)
-    SET((k_extend<true, false>)); SET((k_extend<true, true>));
+    SET((k_extend<true, false, false>)); SET((k_extend<true, true, false>)); SET((k_extend<true, false, true>)); SET((k_extend<true, true, true>));
 #undef SET
     return e;
 }
 
 int extend_max_blocks_per_sm(size_t smem_bytes) {
     int nb = 0;
-    if (smem_bytes) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<true, false>, RT_EXT_BLOCK, smem_bytes);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<false, false>, RT_EXT_BLOCK, 0);
+    if (smem_bytes) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<true, false, false>, RT_EXT_BLOCK, smem_bytes);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<false, false, false>, RT_EXT_BLOCK, 0);
     return nb;
 }
 
@@ -560,11 +560,6 @@ __global__ void k_light_slots(int n, const int *__restrict__ prim_obj, const int
 void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const int *obj_light, int *light_slot) {
     if (n <= 0) return;
     k_light_slots<<<(n + 255) / 256, 256, 0, c.stream>>>(n, prim_obj, obj_light, light_slot);
-    bump(c);
-}
-
-void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce) {
-    k_shadow<<<persistent_grid(c, 8), RT_BLOCK, 0, c.stream>>>(sc, q, bounce);
     bump(c);
 }
 

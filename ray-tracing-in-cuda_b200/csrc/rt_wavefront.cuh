@@ -3,7 +3,6 @@
 #include "rt_shade.cuh"
 
 #define RT_NUM_BINS 5          // miss, lambertian, metal, dielectric, diffuse_light
-#define RT_BIN_STRIDE 8
 #define RT_TRAV_STACK 64
 #define RT_BLOCK 256
 
@@ -14,15 +13,13 @@ enum { CTR_BOX = 0, CTR_SPH_REJECT, CTR_SPH_ACCEPT, CTR_RECT, CTR_CYL_REJECT, CT
 // SoA ray queues: every per-ray field is one float4 array, read and written with coalesced 16-byte accesses.
 struct Queues {
     float4 *ray_o[2];      // origin.xyz, path id (int bits)            — ping-pong between bounces
-    float4 *ray_d[2];      // direction.xyz (unnormalised, as the reference keeps it), unused
-    float4 *thr[2];        // throughput rgb, unused
+    float4 *ray_d[2];      // direction.xyz (unnormalised, as the reference keeps it), pixel index (Philox key word)
+    float4 *thr[2];        // throughput rgb, sample index within the pass
     int2 *hits;            // (t bits, leaf code or -1) per queue entry, written by extend, read by shade
-    int *bins;             // RT_NUM_BINS index lists of capacity `cap` each: queue entries grouped by material class
-    float4 *radiance;      // per path id: the radiance this sample contributes (written exactly once)
+    float4 *radiance;      // per path id: the radiance this sample contributes (written exactly once; NEE: accumulated)
     int *qcount;           // [max_depth + 1] queue length per bounce
-    int *bincount;         // [max_depth][RT_BIN_STRIDE]
     int *workctr;          // [max_depth][2] dynamic work-fetch cursors (extend, shade)
-    // shadow stage (RT_RENDER_NEE): occlusion rays written by shade, consumed by k_shadow right after it
+    // shadow stage (RT_RENDER_NEE): occlusion rays written by shade, consumed by the extend kernel in any-hit mode (launch_shadow) right after it
     float4 *sh_o, *sh_d, *sh_c;   // origin.xyz + path id | direction y - x | radiance carried if unoccluded
     int *shcount;                 // [max_depth] shadow-queue length per bounce
     unsigned long long *counters;   // [CTR_COUNT]
