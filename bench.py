@@ -391,6 +391,14 @@ def main():
         queue_bytes = 48.0 * samples_rank + 56.0 * rays_rank + 48.0 * (rays_rank - samples_rank) + 16.0 * samples_rank + 16.0 * samples_rank
         hbm_ach = queue_bytes / (ms_other * 1e-3) / 1e9 if ms_other > 0 else 0.0
         h2d = sdesc["h2d"]
+        # DRAM traffic of the dominant kernel per launch, from the committed ncu capture (bytes per ray x rays per launch)
+        traffic, traffic_note = None, ""
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        n_ext_launches = max(1, int(sg["passes"]) * int(sdesc["max_depth"])) if "passes" in sg else 0
+        if args.workload == "rtiow_1080p_1024spp" and os.path.exists(tpath) and n_ext_launches:
+            tj = json.load(open(tpath))
+            traffic = tj["k_extend_dram_bytes_per_ray"] * rays_rank / n_ext_launches
+            traffic_note = "; traffic = %.1f B/ray (ncu, profiles/traffic.json) x mean rays per extend launch, bytes" % tj["k_extend_dram_bytes_per_ray"]
         line = {
             "metric": "samples_per_second", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -402,9 +410,9 @@ def main():
                                   "serial_total": sg["ms_total"],
                                   "note": "one extra step with per-launch CUDA events, one pass at a time; the timed steps keep two passes in flight"},
             "roofline": {"bound": "fp32", "kernel": "k_extend", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s",
-                         "frac": ach / fp32_peak if fp32_peak else None, "traffic": None,
+                         "frac": ach / fp32_peak if fp32_peak else None, "traffic": traffic,
                          "note": "algorithmic FLOPs (SURVEY §8(d) model, device event counters) / CUDA-event time of the extend launches "
-                                 "of one step run right after the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)"},
+                                 "of one step run right after the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)" + traffic_note},
             "roofline_hbm": {"bound": "hbm", "kernel": "generate+shade+accumulate", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s",
                              "frac": hbm_ach / hbm_peak, "note": ("104 B/ray + 32 B/sample (DESIGN.md §6) / CUDA-event time of those stages; peak from MEASURED_PEAKS.json (of measured)" if peaks else "of fallback")},
             "e2e": {"value": total_samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
