@@ -352,12 +352,15 @@ def main():
         barrier()
 
         # ---- e2e: host JSON text -> upload (+BVH build) -> render -> reduce -> download to host, every step ----
+        pin_sum = r.pinned_empty((H, W, 3), np.float32) if rank == 0 else None      # page-locked download targets
+        pin_rgb8 = r.pinned_empty((H, W, 3), np.uint8) if rank == 0 else None
+
         def step_e2e():
             upload(r)
             r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=0, max_paths_per_pass=args.max_paths)
             multi_gpu.reduce_image(accum, dst=0)
             if rank == 0:
-                return r.download(gamma=0)
+                return r.download(gamma=0, out_sum=pin_sum, out_rgb8=pin_rgb8)
             r.synchronize()
             return None
         step_e2e()

@@ -184,6 +184,12 @@ int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigned char *rgb
 int rt_synchronize(rt_ctx *ctx);
 int rt_stats_reset(rt_ctx *ctx);
 
+/* Page-locked host buffers for rt_download targets (optional: any host pointer works, a pinned one is copied at the full
+ * host-link rate and without a staging copy).  Takes the place of the reference's managed image allocation, which the
+ * host reads after cudaDeviceSynchronize (main.cu:487-489, 509-514). */
+int rt_host_alloc(rt_ctx *ctx, void **ptr, size_t bytes);
+int rt_host_free(rt_ctx *ctx, void *ptr);
+
 /* LBVH introspection for the bit-exact build tests.  n_prims leaves, n_prims-1 internal nodes (0 if n_prims < 2).
  * Any output pointer may be NULL.  child encoding: >= 0 internal node index, < 0 leaf ~index into the sorted order. */
 int rt_bvh_download(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left,

@@ -655,3 +655,17 @@ extern "C" int rt_bvh_download(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_s
 }
 
 extern "C" void rt_free(void *p) { free(p); }
+
+extern "C" int rt_host_alloc(rt_ctx *ctx, void **ptr, size_t bytes) {
+    if (!ctx || !ptr) return RT_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    *ptr = nullptr;
+    CU(cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocDefault));
+    return RT_OK;
+}
+
+extern "C" int rt_host_free(rt_ctx *ctx, void *ptr) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (ptr) CU(cudaFreeHost(ptr));
+    return RT_OK;
+}

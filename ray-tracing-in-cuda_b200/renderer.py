@@ -36,6 +36,9 @@ class Renderer:
 
     def close(self):
         if getattr(self, "ctx", None):
+            for ptr in getattr(self, "_pinned", []):
+                self.lib.rt_host_free(self.ctx, ptr)
+            self._pinned = []
             self.lib.rt_destroy(self.ctx)
             self.ctx = None
 
@@ -94,11 +97,30 @@ class Renderer:
         self._check(self.lib.rt_accum_sum_ordered(self.ctx, arr, len(device_ptrs)), "rt_accum_sum_ordered")
 
     # ---- image out ----
-    def download(self, total_spp=0, gamma=0, want_sum=True, want_rgb8=True):
-        """Returns (rgb_sum[H,W,3] float32 with row 0 = bottom, rgb8[H,W,3] uint8 with row 0 = top, stats dict)."""
+    def pinned_empty(self, shape, dtype):
+        """numpy array over page-locked host memory (rt_host_alloc); freed when the renderer is closed."""
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        self._check(self.lib.rt_host_alloc(self.ctx, C.byref(p), n), "rt_host_alloc")
+        if not hasattr(self, "_pinned"):
+            self._pinned = []
+        self._pinned.append(p)
+        return np.ctypeslib.as_array((C.c_ubyte * max(n, 1)).from_address(p.value))[:n].view(dtype).reshape(shape)
+
+    def download(self, total_spp=0, gamma=0, want_sum=True, want_rgb8=True, out_sum=None, out_rgb8=None):
+        """Returns (rgb_sum[H,W,3] float32 with row 0 = bottom, rgb8[H,W,3] uint8 with row 0 = top, stats dict).
+        out_sum / out_rgb8: caller-owned target arrays of those shapes (e.g. from pinned_empty), reused across calls."""
         i = self.info()
-        rgb_sum = np.zeros((i.height, i.width, 3), np.float32) if want_sum else None
-        rgb8 = np.zeros((i.height, i.width, 3), np.uint8) if want_rgb8 else None
+        if want_sum:
+            rgb_sum = out_sum if out_sum is not None else np.empty((i.height, i.width, 3), np.float32)
+            assert rgb_sum.shape == (i.height, i.width, 3) and rgb_sum.dtype == np.float32 and rgb_sum.flags.c_contiguous
+        else:
+            rgb_sum = None
+        if want_rgb8:
+            rgb8 = out_rgb8 if out_rgb8 is not None else np.empty((i.height, i.width, 3), np.uint8)
+            assert rgb8.shape == (i.height, i.width, 3) and rgb8.dtype == np.uint8 and rgb8.flags.c_contiguous
+        else:
+            rgb8 = None
         st = capi.Stats()
         self._check(self.lib.rt_download(
             self.ctx, rgb_sum.ctypes.data_as(C.POINTER(C.c_float)) if want_sum else None, rgb_sum.size if want_sum else 0,
