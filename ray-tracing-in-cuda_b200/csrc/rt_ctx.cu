@@ -432,7 +432,10 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     const bool time_stages = !count && (prm->flags & RT_RENDER_TIME_STAGES) != 0;
     // Two passes in flight on two streams (unless a diagnostic mode wants serial stage times): the bounce loop ends in
     // dozens of short launches that cannot fill the GPU; the other pass's long early-bounce launches fill it meanwhile.
-    static const int want_sets = getenv("RT_STREAMS") ? std::max(1, std::min(RT_MAX_SETS, atoi(getenv("RT_STREAMS")))) : 2;
+    // (measured: RTIOW -4.5 %, blue2 -3 % with two streams; a tree read from global memory — the 1 M-triangle mesh — gets 8 %
+    // SLOWER, two passes thrash each other's L1/L2 working set, so it keeps one stream unless RT_STREAMS says otherwise)
+    static const int env_sets = getenv("RT_STREAMS") ? std::max(1, std::min(RT_MAX_SETS, atoi(getenv("RT_STREAMS")))) : 0;
+    const int want_sets = env_sets ? env_sets : (ctx->cfg.bvh_smem_bytes ? 2 : 1);
     const int n_sets = (count || time_stages || (prm->flags & RT_RENDER_SERIAL)) ? 1 : std::min(want_sets, spp);
     // wavefront size: whole sample planes, at most max_paths_per_pass paths and at most 2^30 queue entries per set
     long long max_paths = prm->max_paths_per_pass;
