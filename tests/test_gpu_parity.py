@@ -450,3 +450,18 @@ def test_axis_parallel_rays_and_faces_on_the_ray_plane(rt):
     ref, nrays = orc.render(osc, seed=9)
     assert st["rays"] == nrays
     assert (np.abs(img - ref) > 1e-5 * 4).any(-1).sum() == 0
+
+
+def test_download_into_pinned_buffers(rt):
+    """rt_host_alloc targets: same bytes as a download into ordinary numpy arrays; buffers are reusable across renders."""
+    rt.upload_json(scene_path("blue2"))
+    rt.override(width=64, height=36, spp=3)
+    rt.render(seed=4)
+    a_sum, a_rgb, _ = rt.download(gamma=1)
+    p_sum, p_rgb = rt.pinned_empty((36, 64, 3), np.float32), rt.pinned_empty((36, 64, 3), np.uint8)
+    b_sum, b_rgb, _ = rt.download(gamma=1, out_sum=p_sum, out_rgb8=p_rgb)
+    assert b_sum is p_sum and b_rgb is p_rgb
+    assert np.array_equal(a_sum, p_sum) and np.array_equal(a_rgb, p_rgb)
+    rt.render(seed=5)
+    rt.download(gamma=1, out_sum=p_sum, out_rgb8=p_rgb)
+    assert not np.array_equal(a_sum, p_sum)
