@@ -115,8 +115,10 @@ enum { RT_RENDER_KEEP_ACCUM = 1,     /* add to the accumulation buffer instead o
        RT_RENDER_TIME_STAGES = 16,   /* record CUDA events around every stage launch (no synchronisation); per-stage ms in rt_stats */
        RT_RENDER_SORT = 32,          /* sort every shade chunk by material class in shared memory (same image; pays off only for scenes
                                         with an even material mix — measured slower on the reference's scenes) */
-       RT_RENDER_SERIAL = 64 };      /* one pass at a time on the context's stream (default: two passes in flight on two streams, so the
+       RT_RENDER_SERIAL = 64,      /* one pass at a time on the context's stream (default: two passes in flight on two streams, so the
                                         short late-bounce launches of one overlap the other; same image either way) */
+       RT_RENDER_NO_TILE_LISTS = 256 }; /* traverse the tree for bounce 0 too (default: the generate stage resolves bounce-0 hits from the
+                                        per-tile candidate lists of the camera beams; same image either way) */
 
 typedef struct rt_render_params {
     uint32_t seed;          /* Philox key word 0 */

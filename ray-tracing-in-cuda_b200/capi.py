@@ -15,6 +15,7 @@ RT_BG_CONSTANT, RT_BG_SKY_GRADIENT = range(2)
 RT_SAMPLING_REFERENCE_GPU, RT_SAMPLING_REFERENCE_CPU = range(2)
 RT_RENDER_KEEP_ACCUM, RT_RENDER_COUNT_EVENTS, RT_RENDER_NO_SORT, RT_RENDER_NEE, RT_RENDER_TIME_STAGES, RT_RENDER_SORT = 1, 2, 4, 8, 16, 32
 RT_RENDER_SERIAL = 64
+RT_RENDER_NO_TILE_LISTS = 256
 
 
 class ObjectDesc(C.Structure):

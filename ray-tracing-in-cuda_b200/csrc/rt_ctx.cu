@@ -87,7 +87,7 @@ extern "C" void rt_destroy(rt_ctx *c) {
     for (int k = 0; k < RT_MAX_SETS; ++k) { c->qs[k].release(); if (c->qs[k].ev_acc) cudaEventDestroy(c->qs[k].ev_acc); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     for (int k = 1; k < RT_MAX_SETS; ++k) if (c->extra_stream[k]) cudaStreamDestroy(c->extra_stream[k]);
-    c->d_counters.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
+    c->d_counters.release(); c->d_tile_list.release(); c->d_tile_cnt.release(); c->d_tile_bad.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
     c->d_partials.release(); c->d_rays.release();
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -305,6 +305,7 @@ static int upload_to_device(rt_ctx *ctx) {
     if (per_sm < 1) { ctx->cfg.bvh_smem_bytes = 0; per_sm = extend_max_blocks_per_sm(0); }
     ctx->cfg.extend_blocks_per_sm = per_sm < 1 ? 1 : per_sm;
     ctx->have_scene = true;
+    ctx->tiles_dirty = true;
     ctx->accum_valid = false;
     return RT_OK;
 }
@@ -384,6 +385,29 @@ extern "C" int rt_scene_override(rt_ctx *ctx, int width, int height, int spp, in
     // the camera keeps the aspect the scene was loaded with (the reference ties it to the JSON's width/height, parser.hpp:122)
     ctx->ds.width = d.width; ctx->ds.height = d.height; ctx->ds.max_depth = d.max_depth;
     ctx->accum_valid = false;
+    ctx->tiles_dirty = true;
+    return RT_OK;
+}
+
+// ---- primary-ray candidate lists (k_tile_lists): once per scene / image size ----
+static int ensure_tile_lists(rt_ctx *ctx) {
+    DScene &ds = ctx->ds;
+    if (!ctx->tiles_dirty) return RT_OK;
+    ds.tile_mode = 0; ds.tile_list = nullptr; ds.tile_cnt = nullptr;
+    ctx->tiles_dirty = false;
+    static const bool off = getenv("RT_NO_TILE_LISTS") != nullptr;
+    const int n_tiles = ((ds.width & ~7) >> 3) * ((ds.height & ~3) >> 2);
+    if (off || n_tiles == 0) return RT_OK;
+    CU(ctx->d_tile_list.alloc((size_t)n_tiles * RT_TILE_K)); CU(ctx->d_tile_cnt.alloc(n_tiles)); CU(ctx->d_tile_bad.alloc(1));
+    CU(cudaMemsetAsync(ctx->d_tile_bad.p, 0, sizeof(int), ctx->stream));
+    launch_tile_lists(ctx->cfg, ds, ctx->d_tile_list.p, ctx->d_tile_cnt.p, ctx->d_tile_bad.p);
+    int bad = 0;
+    CU(cudaMemcpyAsync(&bad, ctx->d_tile_bad.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (getenv("RT_TRACE")) fprintf(stderr, "[tile lists] %d tiles, %d over RT_TILE_K, defocus %d\n", n_tiles, bad, ds.defocus);
+    if (bad * 4 > n_tiles) return RT_OK;                      // most beams touch more than RT_TILE_K leaves (dense meshes): not worth it
+    ds.tile_list = ctx->d_tile_list.p; ds.tile_cnt = ctx->d_tile_cnt.p;
+    ds.tile_mode = (bad == 0 && n_tiles * 32 == ds.width * ds.height) ? 1 : 2;
     return RT_OK;
 }
 
@@ -455,6 +479,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     const long long cap = (long long)s_pass * np;
     if (cap > (1ll << 30) - 64) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: image too large for one wavefront pass");
     int rc = ensure_accum(ctx); if (rc) return rc;
+    rc = ensure_tile_lists(ctx); if (rc) return rc;
     for (int k = 0; k < n_sets; ++k) {
         rc = ensure_queues(ctx, ctx->qs[k], cap, ds.max_depth, nee); if (rc) return rc;
         ctx->qs[k].cfg = ctx->cfg; ctx->qs[k].cfg.stream = k == 0 ? ctx->stream : ctx->extra_stream[k];
@@ -493,10 +518,12 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         QueueSet &S = ctx->qs[k];
         const LaunchCfg &cfg = S.cfg;
         launch_pass_init(cfg, S.q, ds.max_depth, n_paths);
-        timed(0, [&] { launch_generate(cfg, ds, S.q, prm->seed, prm->spp_begin + done, n_paths, nee); });
+        // bounce 0: generate resolves the hits of every path whose tile has a candidate list (ds.tile_mode; k_generate)
+        const int tile_mode = (prm->flags & RT_RENDER_NO_TILE_LISTS) ? 0 : ds.tile_mode;
+        timed(0, [&] { launch_generate(cfg, ds, S.q, prm->seed, prm->spp_begin + done, n_paths, nee, tile_mode != 0, count); });
         int buf = 0;
         for (int b = 0; b < ds.max_depth; ++b) {
-            timed(1, [&] { launch_extend(cfg, ds, S.q, b, buf, count, sort); });
+            if (b > 0 || tile_mode != 1) timed(1, [&] { launch_extend(cfg, ds, S.q, b, buf, count, b == 0 && tile_mode == 2); });
             timed(2, [&] { launch_shade(cfg, ds, S.q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort, nee); });
             if (nee) timed(4, [&] { launch_shadow(cfg, ds, S.q, b); });
             buf ^= 1;

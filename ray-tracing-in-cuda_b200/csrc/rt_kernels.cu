@@ -48,15 +48,27 @@ __global__ void k_pass_init(Queues q, int max_depth, int n_paths) {
 // generate: one camera path per (pixel, sample) — main.cu:95-99.  Path id = s_local * n_pixels + pixel, so that
 // `accumulate` reads the radiance of one sample index as one contiguous, coalesced plane.
 // ------------------------------------------------------------------------------------------------
+// HITS: bounce 0 needs no traversal.  All samples of the 32 pixels of a tile leave the camera inside one thin beam, and
+// k_tile_lists has already found every leaf that beam can touch (2.5 on average for the RTIOW scene, never more than 8),
+// so the thread tests those few leaves with the exact leaf arithmetic right here and writes the bounce-0 hit record next
+// to the ray: the bounce-0 extend launch disappears.  Paths it cannot cover (margin pixels outside the 8x4 tiling, tiles
+// with more than RT_TILE_K candidates) get the RT_HIT_TODO mark and are traversed by a fix-up extend launch.
+#define RT_HIT_TODO ((int)0x80000001)
+template <bool HITS, bool COUNT>
 __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsigned seed, int spp_begin, int n_paths, int zero_radiance) {
     // one thread per (tile-ordered) pixel slot and group of samples: the pixel arithmetic is done once, the sample planes are
     // written with stride n_pixels (each plane coalesced across the warp)
     const int np = sc.width * sc.height, n_s = n_paths / np;
     const float div_w = (float)(sc.width - 1), div_h = (float)(sc.height - 1);      // divisors of camera.cuh's (i + r) / (W - 1)
     const int groups = gridDim.y;
+    const int n_tiled = (sc.width & ~7) * (sc.height & ~3);
+    TravCounters cnt = {};
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < np; k += gridDim.x * blockDim.x) {
         const int pixel = plane_to_pixel(sc.width, sc.height, k);
         const int y = pixel / sc.width, x = pixel - y * sc.width;
+        int n_cand = -1;
+        const int *cand = nullptr;
+        if (HITS && k < n_tiled) { n_cand = __ldg(&sc.tile_cnt[k >> 5]); cand = sc.tile_list + (size_t)(k >> 5) * RT_TILE_K; }
         for (int s_local = blockIdx.y; s_local < n_s; s_local += groups) {
             const int i = s_local * np + k;
             Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), 0u, sc.sampling);
@@ -68,8 +80,102 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
             if (zero_radiance) q.radiance[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);      // NEE: several stages add to it
             q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // Philox key words travel with the path:
             q.thr[0][i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(s_local));      // no divisions in the shade stage
+            if (HITS) {
+                float best_t = FLT_MAX; int best_code = RT_HIT_TODO;
+                if (n_cand >= 0) {
+                    best_code = -1;
+                    const float a = dot3(d, d), inv_a = 1.0f / a;
+                    for (int c = 0; c < n_cand; ++c) leaf_visit<COUNT>(sc, __ldg(&cand[c]), o, d, a, inv_a, 0.001f, best_t, best_code, cnt);
+                }
+                q.hits[i] = make_int2(__float_as_int(best_t), best_code);
+            }
         }
     }
+    if (HITS && COUNT) {
+        flush_counter<COUNT>(q.counters, CTR_SPH_REJECT, cnt.sph_rej); flush_counter<COUNT>(q.counters, CTR_SPH_ACCEPT, cnt.sph_acc);
+        flush_counter<COUNT>(q.counters, CTR_RECT, cnt.rect); flush_counter<COUNT>(q.counters, CTR_CYL_REJECT, cnt.cyl_rej);
+        flush_counter<COUNT>(q.counters, CTR_CYL_ACCEPT, cnt.cyl_acc); flush_counter<COUNT>(q.counters, CTR_TRI, cnt.tri);
+        flush_counter<COUNT>(q.counters, CTR_BOXPRIM, cnt.boxprim);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// tile_lists: per 8x4 pixel tile, the leaves whose box the tile's camera beam can touch.  The beam = every ray the camera
+// can produce for the tile's pixels (jitter included): directions affine in (u, v), so their componentwise range over the
+// tile is the range over its four corners; with a thin lens the origin ranges over the box of the lens disk and the
+// direction range widens by the same offsets (o and d taken as independent ranges: conservative).  Interval slab test per axis:
+//   t_near(d) >= min over the range, t_far(d) <= max over the range  =>  "max of the minima <= min of the maxima" holds for
+// every box a single ray of the beam hits (necessary condition; boxes are never missed, some extra ones are listed).
+// One thread per tile, plain stack traversal of the 64-byte nodes; runs once per uploaded scene / size override.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool beam_box(float3 ol, float3 oh, float3 dl, float3 dh, float3 lo, float3 hi) {
+    float tn = 0.0f, tf = INFINITY;
+    const float ovl[3] = {ol.x, ol.y, ol.z}, ovh[3] = {oh.x, oh.y, oh.z}, l[3] = {dl.x, dl.y, dl.z}, h[3] = {dh.x, dh.y, dh.z};
+    const float bl[3] = {lo.x, lo.y, lo.z}, bh[3] = {hi.x, hi.y, hi.z};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float A = bl[k] - ovh[k], B = bh[k] - ovl[k];      // smallest lo - o and largest hi - o over the origin range
+        float n, f;
+        if (l[k] > 0.0f) { n = fminf(A / l[k], A / h[k]); f = fmaxf(B / l[k], B / h[k]); }
+        else if (h[k] < 0.0f) { n = fminf(B / l[k], B / h[k]); f = fmaxf(A / l[k], A / h[k]); }
+        else if (A <= 0.0f && B >= 0.0f) { n = -INFINITY; f = INFINITY; }
+        else if (A > 0.0f) { n = h[k] > 0.0f ? A / h[k] : INFINITY; f = INFINITY; }
+        else { n = l[k] < 0.0f ? B / l[k] : INFINITY; f = INFINITY; }
+        // rounding of the subtractions and divisions: widen by 2^-16 relative (and a small absolute term)
+        n = n - fabsf(n) * 1.52587890625e-05f - 1e-6f; f = f + fabsf(f) * 1.52587890625e-05f + 1e-6f;
+        if (n == n) tn = fmaxf(tn, n);         // NaN (0 * inf, inf - inf): no constraint from this axis
+        if (f == f) tf = fminf(tf, f);
+    }
+    return tn <= tf;
+}
+
+__global__ void __launch_bounds__(128) k_tile_lists(DScene sc, int *__restrict__ list, int *__restrict__ tile_cnt, int *__restrict__ n_bad) {
+    const int tiles_x = (sc.width & ~7) >> 3, n_tiles = tiles_x * ((sc.height & ~3) >> 2);
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tiles) return;
+    const int ty = t / tiles_x, tx = t - ty * tiles_x;
+    const DCamera &cam = sc.cam;
+    // u = (x + xi) / (W - 1) with xi in [0, 1]: the tile spans x in [8 tx, 8 tx + 8]; a hair wider for the rounding of u, v
+    const float u0 = (float)(tx * 8) / (float)(sc.width - 1) - 1e-6f, u1 = (float)(tx * 8 + 8) / (float)(sc.width - 1) + 1e-6f;
+    const float v0 = (float)(ty * 4) / (float)(sc.height - 1) - 1e-6f, v1 = (float)(ty * 4 + 4) / (float)(sc.height - 1) + 1e-6f;
+    float3 dl = v3(INFINITY, INFINITY, INFINITY), dh = v3(-INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const float u = (c & 1) ? u1 : u0, v = (c & 2) ? v1 : v0;
+        const float3 d = vfma(v, cam.vertical, vfma(u, cam.horizontal, cam.llc)) - cam.origin;
+        dl = v3(fminf(dl.x, d.x), fminf(dl.y, d.y), fminf(dl.z, d.z)); dh = v3(fmaxf(dh.x, d.x), fmaxf(dh.y, d.y), fmaxf(dh.z, d.z));
+    }
+    // rounding of camera_ray's own evaluation (three fma / subtractions on terms of this size)
+    const float3 pad = v3(1e-5f * (fabsf(cam.llc.x) + fabsf(cam.horizontal.x) + fabsf(cam.vertical.x) + fabsf(cam.origin.x)) + 1e-30f,
+                          1e-5f * (fabsf(cam.llc.y) + fabsf(cam.horizontal.y) + fabsf(cam.vertical.y) + fabsf(cam.origin.y)) + 1e-30f,
+                          1e-5f * (fabsf(cam.llc.z) + fabsf(cam.horizontal.z) + fabsf(cam.vertical.z) + fabsf(cam.origin.z)) + 1e-30f);
+    dl = dl - pad; dh = dh + pad;
+    float3 ol = cam.origin, oh = cam.origin;
+    if (sc.defocus) {      // camera_ray: off = u rx + v ry with (rx, ry) in the lens disk; o = origin + off, d = d0 - off
+        const float r = cam.lens_radius * 1.00001f;
+        const float3 lens = v3(r * (fabsf(cam.u.x) + fabsf(cam.v.x)), r * (fabsf(cam.u.y) + fabsf(cam.v.y)), r * (fabsf(cam.u.z) + fabsf(cam.v.z)));
+        ol = ol - lens; oh = oh + lens; dl = dl - lens; dh = dh + lens;
+    }
+    int stack[64];
+    int sp = 0, n = 0;
+    bool bad = false;
+    int *out = list + (size_t)t * RT_TILE_K;
+    if (sc.n_prims > 0) stack[sp++] = 0;
+    while (sp > 0 && !bad) {
+        const BvhNode nd = sc.nodes[stack[--sp]];
+#pragma unroll
+        for (int side = 0; side < 2; ++side) {
+            const float3 lo = side ? v3(nd.b.z, nd.b.w, nd.c.x) : v3(nd.a.x, nd.a.y, nd.a.z);
+            const float3 hi = side ? v3(nd.c.y, nd.c.z, nd.c.w) : v3(nd.a.w, nd.b.x, nd.b.y);
+            const int child = side ? nd.d.y : nd.d.x;
+            if (!beam_box(ol, oh, dl, dh, lo, hi)) continue;
+            if (child < 0) { if (n < RT_TILE_K) out[n++] = ~child; else bad = true; }
+            else if (sp < 64) stack[sp++] = child;
+            else bad = true;
+        }
+    }
+    tile_cnt[t] = bad ? -1 : n;
+    if (bad) atomicAdd(n_bad, 1);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -88,8 +194,11 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
 // SHADOW = true: the same kernel walks the bounce's occlusion-ray queue (RT_RENDER_NEE) with an any-hit traversal on
 // t in [0.001, 0.999] of the unnormalised segment; an unoccluded sample adds its radiance to the path's slot (one entry per
 // path and bounce, so the add needs no atomic).
+// max_batch < 0 (bounce 0 after a generate launch that resolved most hits itself): only entries carrying RT_HIT_TODO.
 template <bool SMEM, bool COUNT, bool SHADOW>
 __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf, int max_batch) {
+    const bool fixup = max_batch < 0;
+    if (fixup) max_batch = -max_batch;
     extern __shared__ float4 s_raw[];
     const int n = SHADOW ? q.shcount[bounce] : q.qcount[bounce];
     if (n == 0) return;
@@ -114,6 +223,7 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
         const int end = min(base + batch, n);
 #pragma unroll 1
         for (int i = base + lane_id(); i < end; i += 32) {
+            if (!SHADOW && fixup && q.hits[i].y != RT_HIT_TODO) continue;
             const float4 o4 = ray_o[i], d4 = ray_d[i];
             float t; int code;
             if (SHADOW) {
@@ -481,29 +591,43 @@ void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_
     bump(c);
 }
 
-void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths, bool zero_radiance) {
+void launch_tile_lists(const LaunchCfg &c, const DScene &sc, int *list, int *tile_cnt, int *n_bad) {
+    const int n_tiles = ((sc.width & ~7) >> 3) * ((sc.height & ~3) >> 2);
+    if (n_tiles <= 0) return;
+    k_tile_lists<<<(n_tiles + 127) / 128, 128, 0, c.stream>>>(sc, list, tile_cnt, n_bad);
+    bump(c);
+}
+
+// hits: also resolve the bounce-0 hit records from the tile candidate lists (sc.tile_mode != 0)
+void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths, bool zero_radiance,
+                     bool hits, bool count) {
     const int np = sc.width * sc.height, n_s = n_paths / np;
     const int bx = (np + RT_BLOCK - 1) / RT_BLOCK;
     // enough CTAs to fill the GPU: pixel blocks x sample groups
     int gy = (c.num_sms * 16 + bx - 1) / bx;
     gy = gy < 1 ? 1 : (gy > n_s ? n_s : gy);
-    k_generate<<<dim3(bx, gy), RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, n_paths, zero_radiance ? 1 : 0);
+#define RT_GEN_ARGS <<<dim3(bx, gy), RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, n_paths, zero_radiance ? 1 : 0)
+    if (!hits) k_generate<false, false> RT_GEN_ARGS;
+    else if (count) k_generate<true, true> RT_GEN_ARGS;
+    else k_generate<true, false> RT_GEN_ARGS;
+#undef RT_GEN_ARGS
     bump(c);
 }
 
 template <bool SMEM, bool SHADOW>
-static void launch_extend_t(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count) {
+static void launch_extend_t(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool fixup = false) {
     const int grid = persistent_grid(c, c.extend_blocks_per_sm);
     const size_t sm = SMEM ? c.bvh_smem_bytes : 0;
-    static const int batch = getenv("RT_EXT_BATCH") ? atoi(getenv("RT_EXT_BATCH")) : RT_EXT_BATCH;
+    static const int batch0 = getenv("RT_EXT_BATCH") ? atoi(getenv("RT_EXT_BATCH")) : RT_EXT_BATCH;
+    const int batch = fixup ? -batch0 : batch0;
     if (count) k_extend<SMEM, true, SHADOW><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
     else k_extend<SMEM, false, SHADOW><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
 }
 
-void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort) {
-    (void)sort;
-    if (c.bvh_smem_bytes) launch_extend_t<true, false>(c, sc, q, bounce, buf, count);
-    else launch_extend_t<false, false>(c, sc, q, bounce, buf, count);
+// fixup: bounce 0 after a generate launch that wrote the hit records itself; only entries marked RT_HIT_TODO are traversed
+void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool fixup) {
+    if (c.bvh_smem_bytes) launch_extend_t<true, false>(c, sc, q, bounce, buf, count, fixup);
+    else launch_extend_t<false, false>(c, sc, q, bounce, buf, count, fixup);
     bump(c);
 }
 

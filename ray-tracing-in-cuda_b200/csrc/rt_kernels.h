@@ -11,8 +11,10 @@ struct LaunchCfg {
 };
 
 void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_paths);
-void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths, bool zero_radiance);
-void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool sort);
+void launch_tile_lists(const LaunchCfg &c, const DScene &sc, int *list, int *tile_cnt, int *n_bad);
+void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths, bool zero_radiance,
+                     bool hits, bool count);
+void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool fixup);
 void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
                   bool last_bounce, bool count, bool sort, bool nee);
 void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const int *obj_light, int *light_slot);

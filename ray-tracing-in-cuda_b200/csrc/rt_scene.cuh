@@ -30,6 +30,7 @@ struct DMaterial { int type; int texture; float fuzz; float ior; float4 albedo; 
 struct DTexture { int type; int even; int odd; int image; float4 color; };            // 32 B
 struct DImage { cudaTextureObject_t tex; int width, height; };
 
+#define RT_TILE_K 16
 struct DCamera { float3 origin, llc, horizontal, vertical, u, v, w; float lens_radius; };
 
 struct DScene {
@@ -50,6 +51,9 @@ struct DScene {
     const int *light_type;                 // light -> RT_OBJ_*
     const float *light_area;               // light -> surface area
     const int *obj_light;                  // object index -> light index or -1
+    // primary-ray candidate lists (rt_kernels.cu:k_tile_lists): per 8x4 pixel tile the leaves its camera beam can touch
+    int tile_mode;                         // 0: none, 1: every path of a pass is covered, 2: covered where tile_cnt >= 0
+    const int *tile_list, *tile_cnt;       // [n_tiles * RT_TILE_K] leaf codes, [n_tiles] count or -1 (too many: fix-up pass)
     const DTexture *texs;
     const DImage *images;
 };

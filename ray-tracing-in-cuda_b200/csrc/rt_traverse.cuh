@@ -39,6 +39,22 @@ __device__ __forceinline__ void count_leaf(TravCounters &c, int code, bool hit) 
 #define RT_TRAV_DONE ((int)0x80000000)
 #define RT_NODE_S_SHIFT 7                    // BvhNodeS links of inner children are byte offsets (index << 7)
 
+// One exact leaf test with the closest-hit bookkeeping of the linear walk (object.cuh:23-37): a root equal to the current
+// best replaces it when the object comes later in the scene file.  Returns true when the hit was taken.
+template <bool COUNT>
+__device__ __forceinline__ bool leaf_visit(const DScene &sc, int code, float3 o, float3 d, float a, float inv_a, float tmin,
+                                           float &best_t, int &best_code, TravCounters &cnt) {
+    float t;
+    const bool h = leaf_t(sc, code, o, d, a, inv_a, tmin, best_t, t);
+    count_leaf<COUNT>(cnt, code, h);
+    if (!h) return false;
+    bool take = t < best_t || best_code < 0;
+    if (!take)   // t == best_t: the later object in the scene file wins (object.cuh:29-33)
+        take = __ldg(&sc.prim_obj[code & RT_LEAF_SLOT_MASK]) > __ldg(&sc.prim_obj[best_code & RT_LEAF_SLOT_MASK]);
+    if (take) { best_t = t; best_code = code; }
+    return take;
+}
+
 __device__ __forceinline__ float2 lds_f2(unsigned addr) {
     float2 v;
     asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
@@ -101,16 +117,7 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
         // leaf step first, inner step second: a lane that holds a leaf tests it, pops, and still takes part in this
         // iteration's inner-node step (a diverged warp executes both halves anyway)
         if (cur < 0) {
-            const int code = ~cur;
-            float t;
-            const bool h = leaf_t(sc, code, o, d, a, inv_a, tmin, best_t, t);
-            count_leaf<COUNT>(cnt, code, h);
-            if (h) {
-                bool take = t < best_t || best_code < 0;
-                if (!take)   // t == best_t: the later object in the scene file wins (object.cuh:29-33)
-                    take = __ldg(&sc.prim_obj[code & RT_LEAF_SLOT_MASK]) > __ldg(&sc.prim_obj[best_code & RT_LEAF_SLOT_MASK]);
-                if (take) { best_t = t; best_code = code; if (ANY_HIT) return; }
-            }
+            if (leaf_visit<COUNT>(sc, ~cur, o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
             RT_POP()
         }
         if (cur >= 0) {

@@ -149,6 +149,8 @@ def test_render_options_do_not_change_the_image(rt):
     assert np.array_equal(rt.download()[0], base)
     rt.render(seed=5, flags=capi.RT_RENDER_SERIAL)                       # one stream instead of two passes in flight
     assert np.array_equal(rt.download()[0], base)
+    rt.render(seed=5, flags=capi.RT_RENDER_NO_TILE_LISTS)                # bounce 0 through the tree instead of the beam lists
+    assert np.array_equal(rt.download()[0], base)
     rt.render(seed=5, flags=capi.RT_RENDER_SERIAL, max_paths_per_pass=W * H)
     assert np.array_equal(rt.download()[0], base)
     rt.render(seed=5, max_paths_per_pass=W * H)                           # six one-sample passes alternating between the streams
@@ -465,3 +467,26 @@ def test_download_into_pinned_buffers(rt):
     rt.render(seed=5)
     rt.download(gamma=1, out_sum=p_sum, out_rgb8=p_rgb)
     assert not np.array_equal(a_sum, p_sum)
+
+
+@pytest.mark.parametrize("name,W,H", [("rtiow_486", 256, 144), ("rtiow_486", 200, 120), ("sample_scene_ext", 64, 36), ("blue2", 72, 44), ("dna_000", 64, 36)])
+def test_primary_hits_from_tile_beams(rt, name, W, H):
+    """Bounce-0 hits resolved in the generate stage from the per-tile candidate lists (thin-lens beams for rtiow_486):
+    identical to full traversal (flag) and to the brute-force oracle, on fully tiled images (at
+    low resolutions some beams exceed RT_TILE_K candidates and go through the fix-up launch, which is covered as well)."""
+    spp = 6
+    rt.upload_json(scene_path(name))
+    rt.override(width=W, height=H, spp=spp)
+    rt.stats_reset()
+    rt.render(seed=21, flags=capi.RT_RENDER_COUNT_EVENTS)
+    got, _, st = rt.download()
+    rt.stats_reset()
+    rt.render(seed=21, flags=capi.RT_RENDER_COUNT_EVENTS | capi.RT_RENDER_NO_TILE_LISTS)
+    full, _, st2 = rt.download()
+    assert np.array_equal(got, full) and st["rays"] == st2["rays"]
+    assert st["n_box_tests"] < st2["n_box_tests"]        # bounce 0 really skipped the tree (where its tile has a list)
+    rt.render(seed=21)                                   # the default schedule (two pass streams) gives the same image
+    assert np.array_equal(rt.download()[0], got)
+    want, nrays = orc.render(orc.load_scene(scene_path(name), width=W, height=H, spp=spp), seed=21)
+    assert st["rays"] == nrays
+    assert (np.abs(got - want) > 1e-5 * spp).any(-1).sum() == 0
