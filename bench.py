@@ -397,10 +397,16 @@ def main():
         # DRAM traffic of the dominant kernel per launch, from the committed ncu capture (bytes per ray x rays per launch)
         traffic, traffic_note = None, ""
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        n_ext_launches = max(1, int(sg["passes"]) * int(sdesc["max_depth"])) if "passes" in sg else 0
-        if args.workload == "rtiow_1080p_1024spp" and os.path.exists(tpath) and n_ext_launches:
+        depth = int(sdesc["max_depth"])
+        passes_sg = max(1, int(sg.get("passes", 1)))
+        # per pass: pass_init + generate + accumulate + `depth` shade launches + the extend launches
+        ext_per_pass = int(sg["launches"]) // passes_sg - 3 - depth
+        bounce0_in_generate = ext_per_pass == depth - 1       # primary hits resolved from the tile candidate lists
+        ext_rays = rays_rank - (samples_rank if bounce0_in_generate else 0.0)
+        n_ext_launches = passes_sg * max(1, ext_per_pass)
+        if args.workload == "rtiow_1080p_1024spp" and os.path.exists(tpath):
             tj = json.load(open(tpath))
-            traffic = tj["k_extend_dram_bytes_per_ray"] * rays_rank / n_ext_launches
+            traffic = tj["k_extend_dram_bytes_per_ray"] * ext_rays / n_ext_launches
             traffic_note = "; traffic = %.1f B/ray (ncu, profiles/traffic.json) x mean rays per extend launch, bytes" % tj["k_extend_dram_bytes_per_ray"]
         line = {
             "metric": "samples_per_second", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
