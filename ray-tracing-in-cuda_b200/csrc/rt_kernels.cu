@@ -1,15 +1,17 @@
 // rt_kernels.cu — the wavefront path-tracing kernels for sm_100a:
-//   generate -> [ extend (LBVH traversal) -> shade (+ stream compaction) ] x max_depth -> accumulate ; tonemap
+//   tile_lists (once per scene) ; generate (+ bounce-0 hits) -> [ extend (LBVH traversal) -> shade (+ stream compaction)
+//   (-> shadow) ] x max_depth -> accumulate ; tonemap
 // They replace the reference's megakernel (gpu-version/main.cu:72-105 `render` + 17-70 `ray_color`), which runs one
 // thread per pixel, serial over samples, with virtual dispatch through device-heap pointers.
 //
-// Design for B200 (148 SMs, 228 KB smem/SM, 126 MB L2):
-//   * persistent grids (SM count x resident CTAs) pulling work in warp-sized chunks from a device-side cursor,
-//     so queue lengths never travel to the host and nearly-empty late bounces cost one tiny launch each;
-//   * SoA float4 ray queues (coalesced 16-byte accesses), hit records of 8 bytes;
-//   * the whole BVH is staged in shared memory when it fits (RTIOW: 485 nodes = 31 KB), else read via L1/L2;
-//   * warp-ballot / popc / shfl compaction with one atomic per warp per destination queue;
-//   * rays binned by material class at the end of extend so that shade warps are (almost) divergence-free;
+// Design for B200 (148 SMs, 228 KB smem/SM, 126 MB L2, 180 GB HBM3e):
+//   * persistent grids (SM count x resident CTAs); extend warps pull batches from a device-side cursor, shade CTAs own
+//     256-entry chunks — queue lengths never travel to the host, nearly-empty late bounces cost one tiny launch each;
+//   * SoA float4 ray queues (coalesced 16-byte accesses / TMA bulk copies), hit records of 8 bytes, 128 M paths per pass;
+//   * the whole BVH is staged in shared memory in a sign-ordered 128-byte layout when it fits (RTIOW: 485 nodes = 62 KB),
+//     else 64-byte nodes are read via L1/L2; primary rays skip the tree through per-tile camera-beam candidate lists;
+//   * shade: TMA bulk loads/stores through shared staging, ballot/popc compaction, one global atomic per chunk, optional
+//     in-CTA sort by material class (RT_RENDER_SORT);
 //   * Philox4x32-10 keyed (pixel, sample, bounce): no RNG state in memory;
 //   * radiance is written once per path and summed per pixel in sample order by `accumulate` (no float atomics).
 #include "rt_kernels.h"
