@@ -54,6 +54,7 @@ typedef struct {
 
 void orc_rng_init(orc_rng *r, uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t bounce, int sampling);
 float orc_rng_next(orc_rng *r);
+void orc_rng_block(orc_rng *r, uint32_t out[4]);
 
 /* ---- prepared scene ---- */
 typedef struct {

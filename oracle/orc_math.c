@@ -95,6 +95,12 @@ float orc_rng_next(orc_rng *r) {
     return (float)x * 5.9604644775390625e-08f;
 }
 
+/* the next whole block of the stream (unread words of the current block are dropped; the next draw starts a new block) */
+void orc_rng_block(orc_rng *r, uint32_t out[4]) {
+    orc_philox4x32_10(r->ctr, r->key, out);
+    r->ctr[2]++; r->idx = 4;
+}
+
 void orc_uniforms(uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t bounce, int sampling, int count, float *out) {
     orc_rng r; orc_rng_init(&r, seed, pixel, sample, bounce, sampling);
     for (int i = 0; i < count; ++i) out[i] = orc_rng_next(&r);

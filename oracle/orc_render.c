@@ -36,14 +36,45 @@ v3 orc_emitted(const rt_scene_desc *sc, int mat, float u, float v, v3 p) {   /* 
     return V(0, 0, 0);
 }
 
-/* random_in_unit_sphere: vec3.cuh:133-141 (positive octant, GPU semantics) | vec3.h:121-129 (full cube, CPU semantics) */
+/* random_in_unit_sphere: vec3.cuh:133-141 (positive octant, GPU semantics) | vec3.h:121-129 (full cube, CPU semantics).
+ * The rejection loop is the reference's; how uniforms are cut out of the Philox stream is ours (the reference draws from
+ * XORWOW / mt19937): the sampler consumes whole 128-bit blocks, two trials of three 21-bit uniforms per block — trial 1 =
+ * the low 21 bits of words 0..2, trial 2 = their high 11 bits extended by bits 0-9 / 10-19 / 20-29 of word 3 — and the
+ * next draw after it starts a new block.  Replayed uniforms (known-answer tests) are taken three per trial as they come. */
+static int ball_trial(const orc_rng *rng, float a, float b, float c, v3 *p) {
+    *p = rng->sampling == RT_SAMPLING_REFERENCE_GPU ? V(a, b, c)
+                                                    : V(fmaf(2.0f, a, -1.0f), fmaf(2.0f, b, -1.0f), fmaf(2.0f, c, -1.0f));
+    return !(dot3(*p, *p) >= 1.0f);
+}
+static float u21(const orc_rng *rng, uint32_t x) {
+    if (rng->sampling == RT_SAMPLING_REFERENCE_GPU) x += 1u;     /* (0,1] | [0,1), as orc_rng_next */
+    return (float)x * 4.76837158203125e-07f;                     /* 2^-21 */
+}
 static v3 random_in_unit_sphere(orc_rng *rng) {
+    v3 p;
+    if (rng->replay) {
+        for (;;) {
+            float a = orc_rng_next(rng), b = orc_rng_next(rng), c = orc_rng_next(rng);
+            if (ball_trial(rng, a, b, c, &p)) return p;
+        }
+    }
     for (;;) {
-        float a = orc_rng_next(rng), b = orc_rng_next(rng), c = orc_rng_next(rng);
-        v3 p = rng->sampling == RT_SAMPLING_REFERENCE_GPU ? V(a, b, c)
-                                                          : V(fmaf(2.0f, a, -1.0f), fmaf(2.0f, b, -1.0f), fmaf(2.0f, c, -1.0f));
-        if (dot3(p, p) >= 1.0f) continue;
-        return p;
+        uint32_t w[4];
+        orc_rng_block(rng, w);
+        rng->draws += 3;
+        if (ball_trial(rng, u21(rng, w[0] & 0x1fffffu), u21(rng, w[1] & 0x1fffffu), u21(rng, w[2] & 0x1fffffu), &p)) return p;
+        rng->draws += 3;
+        if (ball_trial(rng, u21(rng, (w[0] >> 21) | ((w[3] & 0x3ffu) << 11)), u21(rng, (w[1] >> 21) | (((w[3] >> 10) & 0x3ffu) << 11)),
+                       u21(rng, (w[2] >> 21) | (((w[3] >> 20) & 0x3ffu) << 11)), &p)) return p;
+    }
+}
+
+/* test hook: n points of the sampler, one stream per point (pixel = first_pixel + i) */
+void orc_ball_samples(uint32_t seed, uint32_t first_pixel, uint32_t sample, uint32_t bounce, int sampling, int n, float *out) {
+    for (int i = 0; i < n; ++i) {
+        orc_rng r; orc_rng_init(&r, seed, first_pixel + (uint32_t)i, sample, bounce, sampling);
+        v3 p = random_in_unit_sphere(&r);
+        out[3 * i] = p.x; out[3 * i + 1] = p.y; out[3 * i + 2] = p.z;
     }
 }
 

@@ -49,6 +49,8 @@ void orc_make_xform(const float axis[3], double angle_deg, int has_rotate, const
 void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
 /* the n-th..(n+count-1)-th uniforms of stream (seed, pixel, sample, bounce) in the given sampling mode */
 void orc_uniforms(uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t bounce, int sampling, int count, float *out);
+/* n points of random_in_unit_sphere, stream (seed, first_pixel + i, sample, bounce) each: out[3n] */
+void orc_ball_samples(uint32_t seed, uint32_t first_pixel, uint32_t sample, uint32_t bounce, int sampling, int n, float *out);
 
 /* known-answer entry points; record formats identical to ref_gpu_harness.cpp kat_* modes */
 void orc_kat_sphere(const float *in, float *out, int n);

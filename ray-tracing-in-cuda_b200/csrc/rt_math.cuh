@@ -93,9 +93,12 @@ __device__ __forceinline__ float rt_atan2f(float y, float x) {
 // ---- Philox4x32-10, keyed (seed, pixel) with counter (sample, bounce, block, 'RT') ----
 // Replaces the reference's per-pixel XORWOW state array (gpu-version/main.cu:120-125: 48 B/pixel in global
 // memory, one RMW per draw) by a stateless counter-based generator: nothing to initialise, nothing to store.
+#ifndef RT_PHILOX_ROUNDS
+#define RT_PHILOX_ROUNDS 10      // tuning builds only (tools/build_variant.py): the oracle states 10 rounds
+#endif
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 #pragma unroll
-    for (int i = 0; i < 10; ++i) {
+    for (int i = 0; i < RT_PHILOX_ROUNDS; ++i) {
         uint32_t h0 = __umulhi(0xD2511F53u, c.x), l0 = 0xD2511F53u * c.x;
         uint32_t h1 = __umulhi(0xCD9E8D57u, c.z), l1 = 0xCD9E8D57u * c.z;
         c = make_uint4(h1 ^ c.y ^ k.x, l1, h0 ^ c.w ^ k.y, l0);
@@ -120,8 +123,6 @@ struct Rng {
         ++idx;
         return (float)((x >> 8) + inc) * 5.9604644775390625e-08f;
     }
-    // block-wise access for samplers that consume whole blocks with compile-time word indices (same stream as next())
-    __device__ __forceinline__ bool at_block_start() const { return idx == 4; }
+    // block-wise access for samplers that consume whole blocks (rt_shade.cuh:random_in_unit_sphere)
     __device__ __forceinline__ uint4 next_block() { uint4 r = philox4x32_10(make_uint4(sample, bounce, block, 0x5254u), key); ++block; return r; }
-    __device__ __forceinline__ float to_uniform(uint32_t x) const { return (float)((x >> 8) + inc) * 5.9604644775390625e-08f; }
 };

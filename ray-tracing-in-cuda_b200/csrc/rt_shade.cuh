@@ -53,26 +53,23 @@ __device__ __forceinline__ float3 random_in_unit_sphere(R &rng, int sampling) {
         if (ball_trial(a, b, c, sampling, p)) return p;
     }
 }
-// Same draws in the same order for a generator standing at a block boundary (every scatter() call: the stream is keyed
-// per bounce), consumed as whole Philox blocks with compile-time word indices: trials 4k..4k+3 use blocks 3k..3k+2.
+// Philox stream: the rejection sampler consumes WHOLE blocks and cuts every 128-bit block into two trials of three 21-bit
+// uniforms (oracle/orc_render.c:random_in_unit_sphere states the same packing).  Trial 1 = the low 21 bits of words x, y, z;
+// trial 2 = their high 11 bits extended by 10 bits each of word w.  21-bit uniforms convert to float exactly, 2u-1 is
+// exact as well, and a trial costs half a Philox block instead of three quarters: the loop (acceptance pi/6 per trial, the
+// warp waits for its slowest lane) is the largest instruction block of k_shade.  Draws after the sampler start a new block.
+__device__ __forceinline__ float u21(uint32_t x, uint32_t inc) { return (float)(x + inc) * 4.76837158203125e-07f; }
 template <>
 __device__ __forceinline__ float3 random_in_unit_sphere<Rng>(Rng &rng, int sampling) {
     float3 p;
-    if (!rng.at_block_start()) {
-        for (;;) {
-            float a = rng.next(), b = rng.next(), c = rng.next();
-            if (ball_trial(a, b, c, sampling, p)) return p;
-        }
-    }
     for (;;) {
-        const uint4 A = rng.next_block();
-        if (ball_trial(rng.to_uniform(A.x), rng.to_uniform(A.y), rng.to_uniform(A.z), sampling, p)) return p;
         const uint4 B = rng.next_block();
-        if (ball_trial(rng.to_uniform(A.w), rng.to_uniform(B.x), rng.to_uniform(B.y), sampling, p)) return p;
-        const uint4 C = rng.next_block();
-        if (ball_trial(rng.to_uniform(B.z), rng.to_uniform(B.w), rng.to_uniform(C.x), sampling, p)) return p;
-        if (ball_trial(rng.to_uniform(C.y), rng.to_uniform(C.z), rng.to_uniform(C.w), sampling, p)) return p;
+        if (ball_trial(u21(B.x & 0x1fffffu, rng.inc), u21(B.y & 0x1fffffu, rng.inc), u21(B.z & 0x1fffffu, rng.inc), sampling, p)) break;
+        if (ball_trial(u21((B.x >> 21) | ((B.w & 0x3ffu) << 11), rng.inc), u21((B.y >> 21) | ((B.w & 0xffc00u) << 1), rng.inc),
+                       u21((B.z >> 21) | ((B.w >> 9) & 0x1ff800u), rng.inc), sampling, p)) break;
     }
+    rng.idx = 4;
+    return p;
 }
 
 __device__ __forceinline__ float3 reflect3(float3 v, float3 n) {   // vec3.cuh:121-123

@@ -40,6 +40,8 @@ def lib():
         L.orc_philox4x32_10.restype = None
         L.orc_uniforms.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, fp]
         L.orc_uniforms.restype = None
+        L.orc_ball_samples.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, fp]
+        L.orc_ball_samples.restype = None
         for k in ("sphere", "rect", "cyl", "camera", "xform"):
             f = getattr(L, "orc_kat_" + k); f.argtypes = [fp, fp, C.c_int]; f.restype = None
         L.orc_kat_scatter.argtypes = [fp, fp, C.c_int, C.c_int]; L.orc_kat_scatter.restype = None

@@ -47,6 +47,31 @@ def test_uniform_ranges():
     assert abs(cpu.mean() - 0.5) < 0.02
 
 
+def test_ball_sampler_distribution():
+    """random_in_unit_sphere with two 21-bit trials per Philox block: uniform in the ball (CPU semantics, vec3.h:121-129)
+    or in its positive octant (GPU semantics, vec3.cuh:133-141).  Moments of the uniform ball: E[x]=0, E[x^2]=1/5,
+    E[|p|^2]=3/5, P(|p|<r)=r^3; octant: E[x]=3/8.  n = 2e5 -> standard errors ~1e-3."""
+    L = orc.lib()
+    n = 200000
+    out = np.zeros(3 * n, np.float32)
+    L.orc_ball_samples(7, 0, 3, 1, capi.RT_SAMPLING_REFERENCE_CPU, n, orc.fptr(out))
+    p = out.reshape(n, 3).astype(np.float64)
+    r2 = (p * p).sum(1)
+    assert r2.max() < 1.0
+    assert np.abs(p.mean(0)).max() < 5e-3
+    assert np.abs((p * p).mean(0) - 0.2).max() < 3e-3
+    assert abs(r2.mean() - 0.6) < 3e-3
+    for r in (0.25, 0.5, 0.75):
+        assert abs((r2 < r * r).mean() - r ** 3) < 4e-3
+    assert np.abs(np.corrcoef(p.T) - np.eye(3)).max() < 0.01
+    # every 21-bit lattice value is a multiple of 2^-20 after 2u-1
+    assert np.all(p * 2 ** 20 == np.round(p * 2 ** 20))
+    L.orc_ball_samples(7, 0, 3, 1, capi.RT_SAMPLING_REFERENCE_GPU, n, orc.fptr(out))
+    q = out.reshape(n, 3).astype(np.float64)
+    assert q.min() > 0.0 and (q * q).sum(1).max() < 1.0
+    assert np.abs(q.mean(0) - 0.375).max() < 3e-3
+
+
 def test_transcendentals_against_libm():
     L = orc.lib()
     rng = np.random.default_rng(0)
