@@ -80,8 +80,8 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
             camera_ray(sc.cam, u, v, sc.defocus != 0, rng, o, d);
             q.ray_o[0][i] = make_float4(o.x, o.y, o.z, __int_as_float(i));
             if (zero_radiance) q.radiance[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);      // NEE: several stages add to it
-            q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // Philox key words travel with the path:
-            q.thr[0][i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(s_local));      // no divisions in the shade stage
+            q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // the Philox key word travels with the path
+            // no throughput record at bounce 0: it is (1, 1, 1) and the sample index is i / n_pixels — k_shade knows both
             if (HITS) {
                 float best_t = FLT_MAX; int best_code = RT_HIT_TODO;
                 if (n_cand >= 0) {
@@ -277,6 +277,7 @@ struct __align__(128) ShadeSmem {
     unsigned long long full[2];       // mbarriers: "stage s has landed"
     int cls_count[8];
     int n_out, out_base;
+    int cam_s[2], cam_rem[2];         // camera paths: sample index and position inside its plane of the stage's first entry
     unsigned short perm[RT_SH_CHUNK];
 };
 
@@ -312,18 +313,21 @@ __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.b
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-__device__ __forceinline__ void shade_issue_loads(ShadeSmem &sm, const Queues &q, int buf, int chunk, int n, int stage) {
+// with_thr = false at bounce 0: camera paths carry no throughput record (generate does not write one)
+__device__ __forceinline__ void shade_issue_loads(ShadeSmem &sm, const Queues &q, int buf, int chunk, int n, int stage, bool with_thr,
+                                                  int q_n_pixels) {
     const int first = chunk * RT_SH_CHUNK;
     const int cnt = min(RT_SH_CHUNK, n - first);
     const unsigned b16 = (unsigned)cnt * 16u, b8 = ((unsigned)cnt * 8u + 15u) & ~15u;
-    mbar_expect_tx(&sm.full[stage], 3u * b16 + b8);
+    if (!with_thr) { const int s0 = first / q_n_pixels; sm.cam_s[stage] = s0; sm.cam_rem[stage] = first - s0 * q_n_pixels; }   // before the arrive (release)
+    mbar_expect_tx(&sm.full[stage], (with_thr ? 3u : 2u) * b16 + b8);
     tma_load_1d(sm.in_o[stage], q.ray_o[buf] + first, b16, &sm.full[stage]);
     tma_load_1d(sm.in_d[stage], q.ray_d[buf] + first, b16, &sm.full[stage]);
-    tma_load_1d(sm.in_thr[stage], q.thr[buf] + first, b16, &sm.full[stage]);
+    if (with_thr) tma_load_1d(sm.in_thr[stage], q.thr[buf] + first, b16, &sm.full[stage]);
     tma_load_1d(sm.in_hit[stage], q.hits + first, b8, &sm.full[stage]);
 }
 
-template <bool COUNT, bool NEE>
+template <bool COUNT, bool NEE, bool CAM>
 __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene sc, Queues q, unsigned seed, int spp_begin, int bounce, int buf,
                                                          int last_bounce, int sort) {
     extern __shared__ __align__(128) unsigned char s_shade_raw[];
@@ -341,13 +345,15 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
         for (int b = 0; b < 8; ++b) sm.cls_count[b] = 0;
     }
     __syncthreads();
-    if (tid == 0) shade_issue_loads(sm, q, buf, blockIdx.x, n, 0);
+    constexpr bool camera_paths = CAM;            // bounce 0: queue position = path id, throughput (1, 1, 1), no record in memory
+    const int n_pixels = sc.width * sc.height;
+    if (tid == 0) shade_issue_loads(sm, q, buf, blockIdx.x, n, 0, !camera_paths, n_pixels);
     unsigned n_shaded = 0;
     int it = 0;
     for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x, ++it) {
         const int st = it & 1;
         const int cnt = min(RT_SH_CHUNK, n - chunk * RT_SH_CHUNK);
-        if (tid == 0 && chunk + (int)gridDim.x < n_chunks) shade_issue_loads(sm, q, buf, chunk + gridDim.x, n, st ^ 1);
+        if (tid == 0 && chunk + (int)gridDim.x < n_chunks) shade_issue_loads(sm, q, buf, chunk + gridDim.x, n, st ^ 1, !camera_paths, n_pixels);
         mbar_wait(&sm.full[st], (unsigned)(it >> 1) & 1u);
         // ---- 1. sort the chunk by material class (shared memory only) ----
         int j = tid;                                   // the entry this thread shades
@@ -388,7 +394,13 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
         bool sh_on = false; int sh_flag = 0;
         float3 sh_x = v3(0, 0, 0), sh_w = v3(0, 0, 0), sh_f = v3(0, 0, 0);
         if (tid < cnt) {
-            const float4 o4 = sm.in_o[st][j], d4 = sm.in_d[st][j], t4 = sm.in_thr[st][j];
+            const float4 o4 = sm.in_o[st][j], d4 = sm.in_d[st][j];
+            float4 t4;
+            if (camera_paths) {        // sample index of queue position i = i / n_pixels (thread 0 divided once per chunk)
+                int s_local = sm.cam_s[st], rem = sm.cam_rem[st] + j;
+                while (rem >= n_pixels) { rem -= n_pixels; ++s_local; }
+                t4 = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(s_local));
+            } else t4 = sm.in_thr[st][j];
             const int2 h = sm.in_hit[st][j];
             const float3 o = f4xyz(o4), d = f4xyz(d4), thr = f4xyz(t4);
             path_id = __float_as_int(o4.w); key_pixel = d4.w; key_sample = t4.w;
@@ -661,16 +673,22 @@ void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigne
     int dev = 0; cudaGetDevice(&dev);
     bool &configured = configured_dev[dev & 63];
     if (!configured) {
-        cudaFuncSetAttribute(k_shade<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
+        cudaFuncSetAttribute(k_shade<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
         configured = true;
     }
     const int grid = persistent_grid(c, RT_SH_CTAS_PER_SM);
 #define RT_SHADE_ARGS <<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort)
-    if (count) { if (nee) k_shade<true, true> RT_SHADE_ARGS; else k_shade<true, false> RT_SHADE_ARGS; }
-    else { if (nee) k_shade<false, true> RT_SHADE_ARGS; else k_shade<false, false> RT_SHADE_ARGS; }
+#define RT_SHADE_CAM(C_, N_) { if (bounce == 0) k_shade<C_, N_, true> RT_SHADE_ARGS; else k_shade<C_, N_, false> RT_SHADE_ARGS; }
+    if (count) { if (nee) RT_SHADE_CAM(true, true) else RT_SHADE_CAM(true, false) }
+    else { if (nee) RT_SHADE_CAM(false, true) else RT_SHADE_CAM(false, false) }
+#undef RT_SHADE_CAM
 #undef RT_SHADE_ARGS
     bump(c);
 }
