@@ -393,21 +393,28 @@ extern "C" int rt_scene_override(rt_ctx *ctx, int width, int height, int spp, in
 static int ensure_tile_lists(rt_ctx *ctx) {
     DScene &ds = ctx->ds;
     if (!ctx->tiles_dirty) return RT_OK;
-    ds.tile_mode = 0; ds.tile_list = nullptr; ds.tile_cnt = nullptr;
-    ctx->tiles_dirty = false;
+    ds.tile_mode = 0; ds.tile_list = nullptr; ds.tile_cnt = nullptr; ds.tile_empty_prefix = nullptr;
+    ctx->tiles_dirty = false; ctx->tiles_all_empty = false;
     static const bool off = getenv("RT_NO_TILE_LISTS") != nullptr;
     const int n_tiles = ((ds.width & ~7) >> 3) * ((ds.height & ~3) >> 2);
     if (off || n_tiles == 0) return RT_OK;
     CU(ctx->d_tile_list.alloc((size_t)n_tiles * RT_TILE_K)); CU(ctx->d_tile_cnt.alloc(n_tiles)); CU(ctx->d_tile_bad.alloc(1));
+    CU(ctx->d_tile_prefix.alloc((size_t)n_tiles + 1));
     CU(cudaMemsetAsync(ctx->d_tile_bad.p, 0, sizeof(int), ctx->stream));
     launch_tile_lists(ctx->cfg, ds, ctx->d_tile_list.p, ctx->d_tile_cnt.p, ctx->d_tile_bad.p);
-    int bad = 0;
+    launch_tile_prefix(ctx->cfg, ctx->d_tile_cnt.p, n_tiles, ctx->d_tile_prefix.p);
+    int bad = 0, n_empty = 0;
     CU(cudaMemcpyAsync(&bad, ctx->d_tile_bad.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(&n_empty, ctx->d_tile_prefix.p + n_tiles, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
-    if (getenv("RT_TRACE")) fprintf(stderr, "[tile lists] %d tiles, %d over RT_TILE_K, defocus %d\n", n_tiles, bad, ds.defocus);
+    if (getenv("RT_TRACE")) fprintf(stderr, "[tile lists] %d tiles, %d empty, %d over RT_TILE_K, defocus %d\n", n_tiles, n_empty, bad, ds.defocus);
     if (bad * 4 > n_tiles) return RT_OK;                      // most beams touch more than RT_TILE_K leaves (dense meshes): not worth it
     ds.tile_list = ctx->d_tile_list.p; ds.tile_cnt = ctx->d_tile_cnt.p;
     ds.tile_mode = (bad == 0 && n_tiles * 32 == ds.width * ds.height) ? 1 : 2;
+    // tiles whose beam touches nothing: their paths skip the queues (k_generate / k_shade / k_accumulate)
+    static const bool keep_empty = getenv("RT_NO_EMPTY_TILES") != nullptr;
+    if (n_empty > 0 && !keep_empty) ds.tile_empty_prefix = ctx->d_tile_prefix.p;
+    ctx->tiles_all_empty = ds.tile_empty_prefix && ds.tile_mode == 1 && n_empty == n_tiles;
     return RT_OK;
 }
 
@@ -520,17 +527,23 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         launch_pass_init(cfg, S.q, ds.max_depth, n_paths);
         // bounce 0: generate resolves the hits of every path whose tile has a candidate list (ds.tile_mode; k_generate)
         const int tile_mode = (prm->flags & RT_RENDER_NO_TILE_LISTS) ? 0 : ds.tile_mode;
-        timed(0, [&] { launch_generate(cfg, ds, S.q, prm->seed, prm->spp_begin + done, n_paths, nee, tile_mode != 0, count); });
+        DScene dsp = ds;                 // this pass's view of the scene: no tile data when the candidate lists are switched off
+        if (tile_mode == 0) { dsp.tile_mode = 0; dsp.tile_list = nullptr; dsp.tile_cnt = nullptr; dsp.tile_empty_prefix = nullptr; }
+        timed(0, [&] { launch_generate(cfg, dsp, S.q, prm->seed, prm->spp_begin + done, n_paths, nee, tile_mode != 0, count); });
         int buf = 0;
-        for (int b = 0; b < ds.max_depth; ++b) {
-            if (b > 0 || tile_mode != 1) timed(1, [&] { launch_extend(cfg, ds, S.q, b, buf, count, b == 0 && tile_mode == 2); });
-            timed(2, [&] { launch_shade(cfg, ds, S.q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort, nee); });
-            if (nee) timed(4, [&] { launch_shadow(cfg, ds, S.q, b); });
+        // every tile's beam misses everything (empty scene, camera looking away): no path enters the queues
+        const bool no_paths = tile_mode == 1 && ctx->tiles_all_empty;
+        for (int b = 0; b < ds.max_depth && !no_paths; ++b) {
+            if (b > 0 || tile_mode != 1) timed(1, [&] { launch_extend(cfg, dsp, S.q, b, buf, count, b == 0 && tile_mode == 2); });
+            timed(2, [&] { launch_shade(cfg, dsp, S.q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort, nee); });
+            if (nee) timed(4, [&] { launch_shadow(cfg, dsp, S.q, b); });
             buf ^= 1;
         }
         // samples are added to the image in ascending order whatever the stream: pass p's accumulate follows pass p-1's
         if (n_sets > 1 && passes > 0) CU(cudaStreamWaitEvent(cfg.stream, ctx->qs[last_set].ev_acc, 0));
-        timed(3, [&] { launch_accumulate(cfg, S.q, ctx->d_accum.p, ds.width, ds.height, sn, clear, ds.max_depth, ctx->d_rays.p); });
+        const int *const_tiles = (dsp.tile_empty_prefix && ds.bg_mode != RT_BG_SKY_GRADIENT) ? dsp.tile_cnt : nullptr;
+        timed(3, [&] { launch_accumulate(cfg, S.q, ctx->d_accum.p, ds.width, ds.height, sn, clear, ds.max_depth, ctx->d_rays.p, const_tiles,
+                                         ds.background); });
         if (n_sets > 1) CU(cudaEventRecord(S.ev_acc, cfg.stream));
         clear = false;
         last_set = k;

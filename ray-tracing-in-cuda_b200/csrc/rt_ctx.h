@@ -73,7 +73,7 @@ struct rt_ctx {
     cudaEvent_t ev_fork = nullptr;
     DevBuf<unsigned long long> d_counters, d_rays;
     // primary-ray candidate lists per 8x4 tile (rebuilt after an upload or a size override)
-    DevBuf<int> d_tile_list, d_tile_cnt, d_tile_bad; bool tiles_dirty = true;
+    DevBuf<int> d_tile_list, d_tile_cnt, d_tile_bad, d_tile_prefix; bool tiles_dirty = true, tiles_all_empty = false;
     DevBuf<float> d_accum; DevBuf<unsigned char> d_rgb8; DevBuf<float> d_aov; DevBuf<const float *> d_partials;
     // stats
     rt_stats stats{};

@@ -39,9 +39,9 @@ __device__ __forceinline__ void flush_counter(unsigned long long *counters, int 
 // ------------------------------------------------------------------------------------------------
 // pass_init: zero the per-bounce cursors/counters of a pass and publish the length of the bounce-0 queue
 // ------------------------------------------------------------------------------------------------
-__global__ void k_pass_init(Queues q, int max_depth, int n_paths) {
+__global__ void k_pass_init(Queues q, int max_depth, int n_queue0) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i <= max_depth) q.qcount[i] = i == 0 ? n_paths : 0;
+    if (i <= max_depth) q.qcount[i] = i == 0 ? n_queue0 : 0;
     if (i < max_depth * 2) q.workctr[i] = 0;
     if (q.shcount && i < max_depth) q.shcount[i] = 0;
 }
@@ -59,38 +59,53 @@ __global__ void k_pass_init(Queues q, int max_depth, int n_paths) {
 template <bool HITS, bool COUNT>
 __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsigned seed, int spp_begin, int n_paths, int zero_radiance) {
     // one thread per (tile-ordered) pixel slot and group of samples: the pixel arithmetic is done once, the sample planes are
-    // written with stride n_pixels (each plane coalesced across the warp)
+    // written with stride n_pixels (each plane coalesced across the warp).  The grid covers every pixel slot in x.
     const int np = sc.width * sc.height, n_s = n_paths / np;
     const float div_w = (float)(sc.width - 1), div_h = (float)(sc.height - 1);      // divisors of camera.cuh's (i + r) / (W - 1)
     const int groups = gridDim.y;
     const int n_tiled = (sc.width & ~7) * (sc.height & ~3);
     TravCounters cnt = {};
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < np; k += gridDim.x * blockDim.x) {
-        const int pixel = plane_to_pixel(sc.width, sc.height, k);
-        const int y = pixel / sc.width, x = pixel - y * sc.width;
-        int n_cand = -1;
-        const int *cand = nullptr;
+    // HITS: a tile whose beam touches no leaf box at all (tile_cnt == 0: sky, backdrop) has nothing but misses.  Its paths
+    // never enter the queues: with a constant background nothing is written here (k_accumulate adds the constant, sample by
+    // sample), with the sky gradient only the radiance record is written.  k_shade skips such entries of the bounce-0 queue
+    // (whole chunks through sc.tile_empty_prefix), so their ray / hit records are never read either.  One warp = one tile.
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    int pixel = 0, x = 0, y = 0, n_cand = -1;
+    const int *cand = nullptr;
+    if (k < np) {
+        pixel = plane_to_pixel(sc.width, sc.height, k);
+        y = pixel / sc.width; x = pixel - y * sc.width;
         if (HITS && k < n_tiled) { n_cand = __ldg(&sc.tile_cnt[k >> 5]); cand = sc.tile_list + (size_t)(k >> 5) * RT_TILE_K; }
-        for (int s_local = blockIdx.y; s_local < n_s; s_local += groups) {
-            const int i = s_local * np + k;
-            Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), 0u, sc.sampling);
-            const float u = ((float)x + rng.next()) / div_w;
-            const float v = ((float)y + rng.next()) / div_h;
-            float3 o, d;
-            camera_ray(sc.cam, u, v, sc.defocus != 0, rng, o, d);
-            q.ray_o[0][i] = make_float4(o.x, o.y, o.z, __int_as_float(i));
-            if (zero_radiance) q.radiance[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);      // NEE: several stages add to it
-            q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // the Philox key word travels with the path
-            // no throughput record at bounce 0: it is (1, 1, 1) and the sample index is i / n_pixels — k_shade knows both
-            if (HITS) {
-                float best_t = FLT_MAX; int best_code = RT_HIT_TODO;
-                if (n_cand >= 0) {
-                    best_code = -1;
-                    const float a = dot3(d, d), inv_a = 1.0f / a;
-                    for (int c = 0; c < n_cand; ++c) leaf_visit<COUNT>(sc, __ldg(&cand[c]), o, d, a, inv_a, 0.001f, best_t, best_code, cnt);
-                }
-                q.hits[i] = make_int2(__float_as_int(best_t), best_code);
+    }
+    const bool empty_tile = HITS && n_cand == 0 && sc.tile_empty_prefix != nullptr, gradient = sc.bg_mode == RT_BG_SKY_GRADIENT;
+    // nothing to do at all: pixel slots past the image, and empty tiles under a constant background when no fix-up extend runs
+    const bool idle = k >= np || (empty_tile && !gradient && sc.tile_mode == 1);
+    for (int s_local = blockIdx.y; s_local < n_s && !idle; s_local += groups) {
+        const int i = s_local * np + k;
+        if (empty_tile && sc.tile_mode == 2) q.hits[i] = make_int2(__float_as_int(FLT_MAX), -1);   // the fix-up extend scans every hit record
+        if (empty_tile && !gradient) continue;
+        Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s_local), 0u, sc.sampling);
+        const float u = ((float)x + rng.next()) / div_w;
+        const float v = ((float)y + rng.next()) / div_h;
+        float3 o, d;
+        camera_ray(sc.cam, u, v, sc.defocus != 0, rng, o, d);
+        if (empty_tile) {             // main.cu:61-63 with throughput 1
+            const float3 bg = background(sc, d);
+            q.radiance[i] = make_float4(bg.x, bg.y, bg.z, 0.0f);
+            continue;
+        }
+        q.ray_o[0][i] = make_float4(o.x, o.y, o.z, __int_as_float(i));
+        if (zero_radiance) q.radiance[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);      // NEE: several stages add to it
+        q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // the Philox key word travels with the path
+        // no throughput record at bounce 0: it is (1, 1, 1) and the sample index is path id / n_pixels — k_shade knows both
+        if (HITS) {
+            float best_t = FLT_MAX; int best_code = RT_HIT_TODO;
+            if (n_cand >= 0) {
+                best_code = -1;
+                const float a = dot3(d, d), inv_a = 1.0f / a;
+                for (int c = 0; c < n_cand; ++c) leaf_visit<COUNT>(sc, __ldg(&cand[c]), o, d, a, inv_a, 0.001f, best_t, best_code, cnt);
             }
+            q.hits[i] = make_int2(__float_as_int(best_t), best_code);
         }
     }
     if (HITS && COUNT) {
@@ -270,6 +285,26 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
 #endif
 #define RT_SH_WARPS (RT_SH_CHUNK / 32)
 
+// Camera-path entries of the bounce-0 queue (position = path id = sample * n_pixels + plane position), plane positions
+// k0, k0 + 1, ... (wrapping at n_pixels), cnt of them: 1 when every one belongs to a tile whose beam touches nothing (generate
+// wrote no record for them), 0 when none does, 2 when the chunk is mixed.
+__device__ __forceinline__ int cam_range_state(const DScene &sc, int k0, int cnt, int n_pixels) {
+    const int n_tiled = (sc.width & ~7) * (sc.height & ~3);
+    int left = cnt, empties = 0, tiles = 0;
+    bool margin = false;
+    while (left > 0) {                        // at most two plane segments unless the image is smaller than a chunk
+        const int k1 = min(k0 + left, n_pixels), kt = min(k1, n_tiled);
+        if (k1 > n_tiled) margin = true;      // margin pixels outside the tiling are never "empty"
+        if (kt > k0) {
+            const int t0 = k0 >> 5, t1 = (kt + 31) >> 5;
+            empties += __ldg(&sc.tile_empty_prefix[t1]) - __ldg(&sc.tile_empty_prefix[t0]); tiles += t1 - t0;
+        }
+        left -= k1 - k0; k0 = 0;
+    }
+    if (empties == 0) return 0;
+    return (empties == tiles && !margin) ? 1 : 2;
+}
+
 struct __align__(128) ShadeSmem {
     float4 in_o[2][RT_SH_CHUNK], in_d[2][RT_SH_CHUNK], in_thr[2][RT_SH_CHUNK];
     int2 in_hit[2][RT_SH_CHUNK];
@@ -277,7 +312,8 @@ struct __align__(128) ShadeSmem {
     unsigned long long full[2];       // mbarriers: "stage s has landed"
     int cls_count[8];
     int n_out, out_base;
-    int cam_s[2], cam_rem[2];         // camera paths: sample index and position inside its plane of the stage's first entry
+    int cam_state[2], cam_k0[2];      // camera paths: 1 = the stage's chunk holds entries of empty tiles only (nothing was loaded),
+                                      // 2 = some of them, 0 = none; plane position of the chunk's first entry
     unsigned short perm[RT_SH_CHUNK];
 };
 
@@ -314,12 +350,17 @@ __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bu
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // with_thr = false at bounce 0: camera paths carry no throughput record (generate does not write one)
-__device__ __forceinline__ void shade_issue_loads(ShadeSmem &sm, const Queues &q, int buf, int chunk, int n, int stage, bool with_thr,
-                                                  int q_n_pixels) {
+__device__ __forceinline__ void shade_issue_loads(ShadeSmem &sm, const DScene &sc, const Queues &q, int buf, int chunk, int n, int stage,
+                                                  bool with_thr) {
     const int first = chunk * RT_SH_CHUNK;
     const int cnt = min(RT_SH_CHUNK, n - first);
     const unsigned b16 = (unsigned)cnt * 16u, b8 = ((unsigned)cnt * 8u + 15u) & ~15u;
-    if (!with_thr) { const int s0 = first / q_n_pixels; sm.cam_s[stage] = s0; sm.cam_rem[stage] = first - s0 * q_n_pixels; }   // before the arrive (release)
+    if (!with_thr && sc.tile_empty_prefix) {      // written before the arrive below (release), read after the wait (acquire)
+        const int np = sc.width * sc.height, k0 = first % np;
+        const int state = cam_range_state(sc, k0, cnt, np);
+        sm.cam_state[stage] = state; sm.cam_k0[stage] = k0;
+        if (state == 1) { mbar_expect_tx(&sm.full[stage], 0u); return; }
+    }
     mbar_expect_tx(&sm.full[stage], (with_thr ? 3u : 2u) * b16 + b8);
     tma_load_1d(sm.in_o[stage], q.ray_o[buf] + first, b16, &sm.full[stage]);
     tma_load_1d(sm.in_d[stage], q.ray_d[buf] + first, b16, &sm.full[stage]);
@@ -347,17 +388,21 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
     __syncthreads();
     constexpr bool camera_paths = CAM;            // bounce 0: queue position = path id, throughput (1, 1, 1), no record in memory
     const int n_pixels = sc.width * sc.height;
-    if (tid == 0) shade_issue_loads(sm, q, buf, blockIdx.x, n, 0, !camera_paths, n_pixels);
+    const float inv_np = 1.0f / (float)n_pixels;
+    if (tid == 0) shade_issue_loads(sm, sc, q, buf, blockIdx.x, n, 0, !camera_paths);
     unsigned n_shaded = 0;
     int it = 0;
     for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x, ++it) {
         const int st = it & 1;
         const int cnt = min(RT_SH_CHUNK, n - chunk * RT_SH_CHUNK);
-        if (tid == 0 && chunk + (int)gridDim.x < n_chunks) shade_issue_loads(sm, q, buf, chunk + gridDim.x, n, st ^ 1, !camera_paths, n_pixels);
+        if (tid == 0 && chunk + (int)gridDim.x < n_chunks) shade_issue_loads(sm, sc, q, buf, chunk + gridDim.x, n, st ^ 1, !camera_paths);
         mbar_wait(&sm.full[st], (unsigned)(it >> 1) & 1u);
+        const int cam_state = (camera_paths && sc.tile_empty_prefix) ? sm.cam_state[st] : 0;
+        if (cam_state == 1) { __syncthreads(); continue; }      // uniform: only empty-tile entries, nothing was loaded
+        // (the barrier keeps thread 0 from re-using sm.cam_state[st] for the chunk after next before everyone has read it)
         // ---- 1. sort the chunk by material class (shared memory only) ----
         int j = tid;                                   // the entry this thread shades
-        if (sort) {
+        if (sort && cam_state == 0) {     // (a mixed camera chunk holds unwritten records)
             int cls = -1;
             if (tid < cnt) {
                 const int code = sm.in_hit[st][tid].y;
@@ -394,10 +439,19 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
         bool sh_on = false; int sh_flag = 0;
         float3 sh_x = v3(0, 0, 0), sh_w = v3(0, 0, 0), sh_f = v3(0, 0, 0);
         if (tid < cnt) {
+            bool live = true;
+            if (cam_state == 2) {     // an entry of an empty tile inside a mixed chunk: no record was written
+                int kpos = sm.cam_k0[st] + j;
+                while (kpos >= n_pixels) kpos -= n_pixels;
+                live = kpos >= (sc.width & ~7) * (sc.height & ~3) || __ldg(&sc.tile_cnt[kpos >> 5]) != 0;
+            }
+            if (live) {
             const float4 o4 = sm.in_o[st][j], d4 = sm.in_d[st][j];
             float4 t4;
-            if (camera_paths) {        // sample index of queue position i = i / n_pixels (thread 0 divided once per chunk)
-                int s_local = sm.cam_s[st], rem = sm.cam_rem[st] + j;
+            if (camera_paths) {        // sample index = path id / n_pixels: float estimate (off by one at most), exact fix-up
+                const int pid = __float_as_int(o4.w);
+                int s_local = (int)((float)pid * inv_np), rem = pid - s_local * n_pixels;
+                while (rem < 0) { rem += n_pixels; --s_local; }
                 while (rem >= n_pixels) { rem -= n_pixels; ++s_local; }
                 t4 = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(s_local));
             } else t4 = sm.in_thr[st][j];
@@ -439,6 +493,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
             if (!alive) {
                 if (NEE) { const float4 r0 = q.radiance[path_id]; rad = v3(r0.x + rad.x, r0.y + rad.y, r0.z + rad.z); }
                 q.radiance[path_id] = make_float4(rad.x, rad.y, rad.z, 0.0f);
+            }
             }
         }
         if (NEE) {      // occlusion rays of this chunk -> shadow queue (one global atomic per warp)
@@ -492,19 +547,27 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
 // accumulate: accum[pixel] += sum over this pass's samples, in ascending sample order (fixed order => the image is
 // bit-reproducible; replaces the register sum of main.cu:95-104).  One thread per pixel, S coalesced plane reads.
 // ------------------------------------------------------------------------------------------------
+// const_tiles: tile_cnt of a pass whose generate skipped the empty tiles under a constant background (else nullptr) — their
+// pixels get the constant added once per sample, in the same order as the sum over radiance records would.
 __global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restrict__ radiance, float *__restrict__ accum, int W, int H,
                                                          int n_samples, int clear, const int *__restrict__ qcount, int max_depth,
-                                                         unsigned long long *total_rays, const int *__restrict__ shcount) {
+                                                         unsigned long long *total_rays, const int *__restrict__ shcount,
+                                                         const int *__restrict__ const_tiles, float3 bg) {
     const int np = W * H;
     if (blockIdx.x == 0 && threadIdx.x == 0) {     // rays traced this pass = sum of the per-bounce queue lengths
         unsigned long long r = 0, sh = 0;
-        for (int b = 0; b < max_depth; ++b) { r += (unsigned long long)qcount[b]; if (shcount) sh += (unsigned long long)shcount[b]; }
+        // every camera path is one ray (the bounce-0 queue may hold fewer: paths that miss everything end in generate)
+        r = (unsigned long long)np * (unsigned long long)n_samples;
+        for (int b = 0; b < max_depth; ++b) { if (b > 0) r += (unsigned long long)qcount[b]; if (shcount) sh += (unsigned long long)shcount[b]; }
         total_rays[0] += r; total_rays[1] += sh;
     }
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < np; k += gridDim.x * blockDim.x) {
         const int p = plane_to_pixel(W, H, k);
         float r = 0.0f, g = 0.0f, b = 0.0f;
         if (!clear) { r = accum[3 * p]; g = accum[3 * p + 1]; b = accum[3 * p + 2]; }
+        if (const_tiles && k < (W & ~7) * (H & ~3) && __ldg(&const_tiles[k >> 5]) == 0) {
+            for (int s = 0; s < n_samples; ++s) { r += bg.x; g += bg.y; b += bg.z; }
+        } else
         for (int s = 0; s < n_samples; ++s) {
             const float4 c = radiance[(long long)s * np + k];
             r += c.x; g += c.y; b += c.z;
@@ -599,9 +662,34 @@ __global__ void __launch_bounds__(RT_BLOCK) k_aov(DScene sc, float *__restrict__
 static inline int persistent_grid(const LaunchCfg &c, int per_sm) { return c.num_sms * per_sm; }
 static inline void bump(const LaunchCfg &c) { if (c.launches) ++*c.launches; }
 
-void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_paths) {
+// n_queue0: length of the bounce-0 queue = all camera paths of the pass (dense: position = path id)
+void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_queue0) {
     int n = max_depth * 2 + 2;
-    k_pass_init<<<(n + 255) / 256, 256, 0, c.stream>>>(q, max_depth, n_paths);
+    k_pass_init<<<(n + 255) / 256, 256, 0, c.stream>>>(q, max_depth, n_queue0);
+    bump(c);
+}
+
+// exclusive prefix count of empty tiles (tile_cnt == 0): prefix[t] = number of empty tiles among [0, t); one block
+__global__ void __launch_bounds__(1024) k_tile_prefix(const int *__restrict__ tile_cnt, int n_tiles, int *__restrict__ prefix) {
+    __shared__ int part[1024];
+    const int per = (n_tiles + 1023) / 1024, t0 = threadIdx.x * per, t1 = min(t0 + per, n_tiles);
+    int c = 0;
+    for (int t = t0; t < t1; ++t) c += tile_cnt[t] == 0;
+    part[threadIdx.x] = c;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {       // inclusive Hillis-Steele scan of the per-thread counts
+        const int v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    int run = part[threadIdx.x] - c;
+    for (int t = t0; t < t1; ++t) { prefix[t] = run; run += tile_cnt[t] == 0; }
+    if (threadIdx.x == 1023) prefix[n_tiles] = part[1023];
+}
+
+void launch_tile_prefix(const LaunchCfg &c, const int *tile_cnt, int n_tiles, int *prefix) {
+    k_tile_prefix<<<1, 1024, 0, c.stream>>>(tile_cnt, n_tiles, prefix);
     bump(c);
 }
 
@@ -708,9 +796,10 @@ void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const in
 }
 
 void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W, int H, int n_samples, bool clear, int max_depth,
-                       unsigned long long *total_rays) {
+                       unsigned long long *total_rays, const int *const_tiles, float3 bg) {
     int blocks = (W * H + RT_BLOCK - 1) / RT_BLOCK;
-    k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, accum, W, H, n_samples, clear ? 1 : 0, q.qcount, max_depth, total_rays, q.shcount);
+    k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, accum, W, H, n_samples, clear ? 1 : 0, q.qcount, max_depth, total_rays, q.shcount,
+                                                    const_tiles, bg);
     bump(c);
 }
 

@@ -10,8 +10,9 @@ struct LaunchCfg {
     long long *launches;          // counter of kernels launched (rt_stats.launches)
 };
 
-void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_paths);
+void launch_pass_init(const LaunchCfg &c, const Queues &q, int max_depth, int n_queue0);
 void launch_tile_lists(const LaunchCfg &c, const DScene &sc, int *list, int *tile_cnt, int *n_bad);
+void launch_tile_prefix(const LaunchCfg &c, const int *tile_cnt, int n_tiles, int *prefix);
 void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int n_paths, bool zero_radiance,
                      bool hits, bool count);
 void launch_extend(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool fixup);
@@ -20,7 +21,7 @@ void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigne
 void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const int *obj_light, int *light_slot);
 void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce);
 void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W, int H, int n_samples, bool clear, int max_depth,
-                       unsigned long long *total_rays);
+                       unsigned long long *total_rays, const int *const_tiles, float3 bg);
 void launch_sum_ordered(const LaunchCfg &c, float *accum, const float *const *partials_dev, int n_partials, long long n);
 void launch_tonemap(const LaunchCfg &c, const float *accum, unsigned char *rgb8, int W, int H, int spp, int gamma);
 void launch_aov(const LaunchCfg &c, const DScene &sc, float *out);

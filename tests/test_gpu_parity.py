@@ -490,3 +490,30 @@ def test_primary_hits_from_tile_beams(rt, name, W, H):
     want, nrays = orc.render(orc.load_scene(scene_path(name), width=W, height=H, spp=spp), seed=21)
     assert st["rays"] == nrays
     assert (np.abs(got - want) > 1e-5 * spp).any(-1).sum() == 0
+
+
+@pytest.mark.parametrize("name,W,H,spp", [("basic_scene", 128, 72, 5), ("dna_000", 256, 144, 4), ("rtiow_486", 256, 144, 4),
+                                          ("rtiow_486", 16, 12, 40), ("blue2", 40, 28, 9), ("dna_000", 200, 100, 3)])
+def test_empty_tiles_skip_the_queues(rt, name, W, H, spp):
+    """Tiles whose camera beam touches no leaf box (background only) never enter the queues: generate writes at most their
+    radiance, shade skips their chunks, accumulate adds a constant background sample by sample.  Same image bit for bit
+    and same ray count as the plain schedule (every path through the tree), small passes included (chunks that span
+    several sample planes, images smaller than a chunk, partial tiles)."""
+    rt.upload_json(scene_path(name))
+    rt.override(width=W, height=H, spp=spp)
+    rt.stats_reset()
+    rt.render(seed=33, flags=capi.RT_RENDER_NO_TILE_LISTS)
+    full, _, st_full = rt.download()
+    for kw in ({}, {"max_paths_per_pass": W * H * 2}, {"flags": capi.RT_RENDER_SERIAL, "max_paths_per_pass": W * H}):
+        rt.stats_reset()
+        rt.render(seed=33, **kw)
+        got, _, st = rt.download()
+        assert np.array_equal(got, full), kw
+        assert st["rays"] == st_full["rays"], kw
+    if name == "basic_scene":       # no objects: every pixel is spp x background, added one sample at a time (main.cu:95-104)
+        bg = np.array(json.load(open(scene_path(name)))["background"], np.float32)
+        acc = np.zeros(3, np.float32)
+        for _ in range(spp):
+            acc = acc + bg
+        assert np.array_equal(full, np.broadcast_to(acc, full.shape))
+        assert st_full["rays"] == W * H * spp
