@@ -388,11 +388,7 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         ach = ext_flops / (ms_extend * 1e-3) / 1e12 if ms_extend > 0 else 0.0
-        # algorithmic bytes of the queue stages on this rank: generate W48/sample; shade R56/ray + W48 per
-        # survivor (rays - samples) + W16 per finished path; accumulate R16/sample (+12 B/pixel RMW per pass, ignored)
         rays_rank, samples_rank = st["rays"] / args.steps, total_samples / world
-        queue_bytes = 48.0 * samples_rank + 56.0 * rays_rank + 48.0 * (rays_rank - samples_rank) + 16.0 * samples_rank + 16.0 * samples_rank
-        hbm_ach = queue_bytes / (ms_other * 1e-3) / 1e9 if ms_other > 0 else 0.0
         h2d = sdesc["h2d"]
         # DRAM traffic of the dominant kernel per launch, from the committed ncu capture (bytes per ray x rays per launch)
         traffic, traffic_note = None, ""
@@ -404,6 +400,13 @@ def main():
         bounce0_in_generate = ext_per_pass == depth - 1       # primary hits resolved from the tile candidate lists
         ext_rays = rays_rank - (samples_rank if bounce0_in_generate else 0.0)
         n_ext_launches = passes_sg * max(1, ext_per_pass)
+        # algorithmic bytes of the queue stages on this rank: generate W32/sample (ray_o, ray_d; camera paths carry
+        # no throughput record) + W8/sample when it also resolves the bounce-0 hits; shade R56/ray minus the 16-byte throughput
+        # record at bounce 0, + W48 per survivor (rays - samples) + W16 per finished path; accumulate R16/sample (+12 B/pixel RMW
+        # per pass, ignored).  Paths of empty camera tiles move fewer bytes than this (not subtracted: no such tile in RTIOW).
+        queue_bytes = ((32.0 + (8.0 if bounce0_in_generate else 0.0)) * samples_rank + 56.0 * rays_rank - 16.0 * samples_rank
+                       + 48.0 * (rays_rank - samples_rank) + 16.0 * samples_rank + 16.0 * samples_rank)
+        hbm_ach = queue_bytes / (ms_other * 1e-3) / 1e9 if ms_other > 0 else 0.0
         if args.workload == "rtiow_1080p_1024spp" and os.path.exists(tpath):
             tj = json.load(open(tpath))
             traffic = tj["k_extend_dram_bytes_per_ray"] * ext_rays / n_ext_launches
@@ -423,7 +426,7 @@ def main():
                          "note": "algorithmic FLOPs (SURVEY §8(d) model, device event counters) / CUDA-event time of the extend launches "
                                  "of one step run right after the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)" + traffic_note},
             "roofline_hbm": {"bound": "hbm", "kernel": "generate+shade+accumulate", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": hbm_ach / hbm_peak, "note": ("104 B/ray + 32 B/sample (DESIGN.md §6) / CUDA-event time of those stages; peak from MEASURED_PEAKS.json (of measured)" if peaks else "of fallback")},
+                             "frac": hbm_ach / hbm_peak, "note": ("104 B/ray (+ 8 B/sample when generate writes the bounce-0 hit records; DESIGN.md §6) / CUDA-event time of those stages; peak from MEASURED_PEAKS.json (of measured)" if peaks else "of fallback")},
             "e2e": {"value": total_samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": W * H * 3 * 4 + W * H * 3, "ms_per_step": ms_e2e},
             "gpu_launches": int(st["launches"] / args.steps), "clocks": clocks,

@@ -407,7 +407,29 @@ static int ensure_tile_lists(rt_ctx *ctx) {
     CU(cudaMemcpyAsync(&bad, ctx->d_tile_bad.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(&n_empty, ctx->d_tile_prefix.p + n_tiles, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
-    if (getenv("RT_TRACE")) fprintf(stderr, "[tile lists] %d tiles, %d empty, %d over RT_TILE_K, defocus %d\n", n_tiles, n_empty, bad, ds.defocus);
+    if (getenv("RT_TRACE")) {
+        std::vector<int> h((size_t)n_tiles);
+        CU(cudaMemcpy(h.data(), ctx->d_tile_cnt.p, (size_t)n_tiles * sizeof(int), cudaMemcpyDeviceToHost));
+        int hist[RT_TILE_K + 2] = {};
+        for (int c : h) hist[c < 0 ? RT_TILE_K + 1 : c]++;
+        fprintf(stderr, "[tile lists] %d tiles, %d empty, %d over RT_TILE_K, defocus %d; candidates per tile:", n_tiles, n_empty, bad, ds.defocus);
+        for (int c = 0; c <= RT_TILE_K + 1; ++c) if (hist[c]) fprintf(stderr, " %d:%d", c, hist[c]);
+        fprintf(stderr, "\n");
+        if (getenv("RT_TRACE_TILE")) {          // candidates of one tile (development aid)
+            const int t = atoi(getenv("RT_TRACE_TILE"));
+            if (t >= 0 && t < n_tiles) {
+                int cand[RT_TILE_K];
+                CU(cudaMemcpy(cand, ctx->d_tile_list.p + (size_t)t * RT_TILE_K, sizeof cand, cudaMemcpyDeviceToHost));
+                fprintf(stderr, "[tile %d] %d candidates:", t, h[t]);
+                for (int c = 0; c < h[t] && c < RT_TILE_K; ++c) {
+                    int obj = -1;
+                    CU(cudaMemcpy(&obj, ctx->d_prim_obj.p + (cand[c] & RT_LEAF_SLOT_MASK), sizeof(int), cudaMemcpyDeviceToHost));
+                    fprintf(stderr, " type %d object %d", (unsigned)cand[c] >> 28, obj);
+                }
+                fprintf(stderr, "\n");
+            }
+        }
+    }
     if (bad * 4 > n_tiles) return RT_OK;                      // most beams touch more than RT_TILE_K leaves (dense meshes): not worth it
     ds.tile_list = ctx->d_tile_list.p; ds.tile_cnt = ctx->d_tile_cnt.p;
     ds.tile_mode = (bad == 0 && n_tiles * 32 == ds.width * ds.height) ? 1 : 2;
