@@ -297,7 +297,7 @@ static int upload_to_device(rt_ctx *ctx) {
     // extend-kernel configuration: stage the whole BVH in shared memory when it leaves room for >= 2 CTAs per SM
     const size_t bvh_bytes = sizeof(BvhNodeS) * (size_t)ds.n_nodes;
     ctx->cfg.bvh_smem_bytes = 0;
-    if (bvh_bytes <= ctx->smem_optin && bvh_bytes <= 100 * 1024) {
+    if (bvh_bytes + RT_SSTACK_BYTES <= ctx->smem_optin && bvh_bytes + RT_SSTACK_BYTES <= 112 * 1024) {      // two CTAs per SM: tree + stack each
         if (extend_configure_smem(bvh_bytes) == cudaSuccess) ctx->cfg.bvh_smem_bytes = bvh_bytes;
         else cudaGetLastError();
     }

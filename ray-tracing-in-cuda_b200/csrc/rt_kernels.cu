@@ -205,7 +205,6 @@ __global__ void __launch_bounds__(128) k_tile_lists(DScene sc, int *__restrict__
 // Measured and rejected: per-lane refill of finished lanes, postponed/batched leaf tests, a 4-wide collapsed
 // tree with leaf ranges, binning rays by material here through global lists.
 // ------------------------------------------------------------------------------------------------
-#define RT_EXT_BLOCK 512
 #define RT_EXT_BATCH 256
 
 // SHADOW = true: the same kernel walks the bounce's occlusion-ray queue (RT_RENDER_NEE) with an any-hit traversal on
@@ -230,6 +229,9 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
         __syncthreads();
         nodes = reinterpret_cast<const char *>(s_raw);
     }
+    // this thread's column of the shared-memory traversal stack, behind the tree (dynamic smem = tree bytes + RT_SSTACK_BYTES)
+    const unsigned sstack = (unsigned)__cvta_generic_to_shared(s_raw) + (SMEM ? (unsigned)sc.n_nodes * (unsigned)sizeof(BvhNodeS) : 0u) +
+                            threadIdx.x * 8u;
     int *cursor = &q.workctr[bounce * 2 + (SHADOW ? 1 : 0)];
     const float4 *__restrict__ ray_o = SHADOW ? q.sh_o : q.ray_o[buf];
     const float4 *__restrict__ ray_d = SHADOW ? q.sh_d : q.ray_d[buf];
@@ -242,16 +244,22 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
         for (int i = base + lane_id(); i < end; i += 32) {
             if (!SHADOW && fixup && q.hits[i].y != RT_HIT_TODO) continue;
             const float4 o4 = ray_o[i], d4 = ray_d[i];
+#ifdef RT_EXT_PREFETCH
+            if (i + 32 < end) {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(ray_o + i + 32));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(ray_d + i + 32));
+            }
+#endif
             float t; int code;
             if (SHADOW) {
-                traverse<SMEM, COUNT, true>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt);
+                traverse<SMEM, COUNT, true, RT_SSTACK>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt, sstack);
                 if (code < 0) {
                     const int pid = __float_as_int(o4.w);
                     const float4 c = q.sh_c[i], r = q.radiance[pid];
                     q.radiance[pid] = make_float4(r.x + c.x, r.y + c.y, r.z + c.z, 0.0f);
                 }
             } else {
-                traverse<SMEM, COUNT, false>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt);
+                traverse<SMEM, COUNT, false, RT_SSTACK>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt, sstack);
                 q.hits[i] = make_int2(__float_as_int(t), code);
             }
         }
@@ -719,7 +727,7 @@ void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsi
 template <bool SMEM, bool SHADOW>
 static void launch_extend_t(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce, int buf, bool count, bool fixup = false) {
     const int grid = persistent_grid(c, c.extend_blocks_per_sm);
-    const size_t sm = SMEM ? c.bvh_smem_bytes : 0;
+    const size_t sm = (SMEM ? c.bvh_smem_bytes : 0) + RT_SSTACK_BYTES;
     static const int batch0 = getenv("RT_EXT_BATCH") ? atoi(getenv("RT_EXT_BATCH")) : RT_EXT_BATCH;
     const int batch = fixup ? -batch0 : batch0;
     if (count) k_extend<SMEM, true, SHADOW><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
@@ -740,18 +748,25 @@ void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bo
     bump(c);
 }
 
+// smem_bytes: size of the staged tree; the kernel's shared-memory traversal stack comes on top
 cudaError_t extend_configure_smem(size_t smem_bytes) {
     cudaError_t e = cudaSuccess;
-#define SET(K) if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes)
-    SET((k_extend<true, false, false>)); SET((k_extend<true, true, false>)); SET((k_extend<true, false, true>)); SET((k_extend<true, true, true>));
+#define SET(K, B) if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(B))
+    const size_t tot = smem_bytes + RT_SSTACK_BYTES;
+    SET((k_extend<true, false, false>), tot); SET((k_extend<true, true, false>), tot); SET((k_extend<true, false, true>), tot);
+    SET((k_extend<true, true, true>), tot);
+    if (RT_SSTACK_BYTES > 48 * 1024) {
+        SET((k_extend<false, false, false>), RT_SSTACK_BYTES); SET((k_extend<false, true, false>), RT_SSTACK_BYTES);
+        SET((k_extend<false, false, true>), RT_SSTACK_BYTES); SET((k_extend<false, true, true>), RT_SSTACK_BYTES);
+    }
 #undef SET
     return e;
 }
 
 int extend_max_blocks_per_sm(size_t smem_bytes) {
     int nb = 0;
-    if (smem_bytes) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<true, false, false>, RT_EXT_BLOCK, smem_bytes);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<false, false, false>, RT_EXT_BLOCK, 0);
+    if (smem_bytes) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<true, false, false>, RT_EXT_BLOCK, smem_bytes + RT_SSTACK_BYTES);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_extend<false, false, false>, RT_EXT_BLOCK, RT_SSTACK_BYTES);
     return nb;
 }
 

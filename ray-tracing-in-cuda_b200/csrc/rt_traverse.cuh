@@ -60,9 +60,18 @@ __device__ __forceinline__ float2 lds_f2(unsigned addr) {
     asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
     return v;
 }
+__device__ __forceinline__ void sts_i2(unsigned addr, int2 v) {
+    asm volatile("st.shared.v2.s32 [%0], {%1, %2};" ::"r"(addr), "r"(v.x), "r"(v.y));
+}
 __device__ __forceinline__ int2 lds_i2(unsigned addr) {
     int2 v;
     asm("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
+// stack accesses: volatile, so that the compiler keeps them in program order with respect to each other
+__device__ __forceinline__ int2 lds_stack(unsigned addr) {
+    int2 v;
+    asm volatile("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
     return v;
 }
 
@@ -77,9 +86,15 @@ __device__ __forceinline__ int2 lds_i2(unsigned addr) {
 // margin of 1e10 instead, which keeps the slab pair as an inside/outside test without NaNs — before, 0 * inf dropped the
 // slab and such a ray visited every node along its projection (one ray in ~10^4 of the centre column of a camera placed at
 // x = 0: 15 000 node visits, a multi-millisecond tail on the 1 M-triangle mesh).
-template <bool SIGNED, bool COUNT, bool ANY_HIT>
+//
+// Traversal stack: the first SD levels live in SHARED memory (sstack = shared-window address of this thread's column, one
+// 8-byte entry per level, levels RT_SSTACK_STRIDE bytes apart: bank = thread, so any mix of levels across the lanes of a warp
+// is conflict-free), deeper levels in the per-thread local-memory array.  ncu (r01f) had the pop loop at 17 % of the warp
+// samples of k_extend, waiting on local-memory loads at ~6 active lanes; mean stack depth on the reference scenes is < SD.
+// SD = 0 (k_aov, k_tile_lists callers): local memory only.
+template <bool SIGNED, bool COUNT, bool ANY_HIT, int SD = 0>
 __device__ __forceinline__ void traverse(const DScene &sc, const char *__restrict__ nodes, float3 o, float3 d, float tmin,
-                                         float tmax, float &best_t, int &best_code, TravCounters &cnt) {
+                                         float tmax, float &best_t, int &best_code, TravCounters &cnt, unsigned sstack = 0) {
     best_t = tmax; best_code = -1;
     if (sc.n_prims == 0) return;
     const float a = dot3(d, d), inv_a = 1.0f / a;
@@ -110,7 +125,9 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
     for (;;) {                                                                   \
         if (sp == 0) { cur = RT_TRAV_DONE; break; }                              \
         --sp;                                                                    \
-        const int2 e_ = stack[sp];                                               \
+        int2 e_;                                                                 \
+        if (SD > 0 && sp < SD) e_ = lds_stack(sstack + (unsigned)sp * RT_SSTACK_STRIDE); \
+        else e_ = stack[sp - SD];                                                \
         if (__int_as_float(e_.y) <= best_t) { cur = e_.x; break; }               \
     }
     while (cur != RT_TRAV_DONE) {
@@ -153,10 +170,10 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
             const bool hr = tnr <= tfr;
             if (hl && hr) {
                 const bool lfirst = tnl <= tnr;
-                if (sp < RT_TRAV_STACK) {
-                    stack[sp] = make_int2(lfirst ? nd.y : nd.x, __float_as_int(lfirst ? tnr : tnl));
-                    ++sp;
-                } else if (COUNT) cnt.overflow++;
+                const int2 far_ = make_int2(lfirst ? nd.y : nd.x, __float_as_int(lfirst ? tnr : tnl));
+                if (SD > 0 && sp < SD) { sts_i2(sstack + (unsigned)sp * RT_SSTACK_STRIDE, far_); ++sp; }
+                else if (sp - SD < RT_TRAV_STACK) { stack[sp - SD] = far_; ++sp; }
+                else if (COUNT) cnt.overflow++;
                 cur = lfirst ? nd.x : nd.y;
             } else if (hl || hr) {
                 cur = hl ? nd.x : nd.y;
