@@ -54,39 +54,87 @@ def flop_model(st):
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock, power and throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe: the nvidia-smi clocks
+    line).  Read through NVML in this process every 50 ms — the same counters nvidia-smi prints, without starting a process
+    inside the timed region (its start-up takes driver locks for tens of ms and showed up as 45 -> 60 ms steps on the
+    launch-bound workloads); `nvidia-smi -lms` is the fallback when the NVML binding is missing."""
+
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
     def __init__(self, index):
-        self.rows = []
+        self.rows = []          # (sm_mhz, sm_max_mhz, power_w, reasons bitmask)
         self.proc = None
         self.index = index
+        self.source = None
+        self._stop = threading.Event()
+        self._thread = None
+
+    def _nvml_handle(self):
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            import torch
+            uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            return pynvml, pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+        except Exception:
+            return pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.index)
 
     def start(self):
+        try:
+            nv, h = self._nvml_handle()
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+
+            def loop():
+                while not self._stop.is_set():
+                    try:
+                        try:
+                            rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                        except Exception:
+                            rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        self.rows.append((float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), float(mx),
+                                          nv.nvmlDeviceGetPowerUsage(h) / 1000.0, int(rs)))
+                    except Exception:
+                        pass
+                    self._stop.wait(0.05)
+            self.source = "nvml"
+            self._thread = threading.Thread(target=loop, daemon=True)
+            self._thread.start()
+            return
+        except Exception:
+            self.source = None
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "200"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.source = "nvidia-smi"
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
             self.proc = None
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            c = [x.strip() for x in line.split(",")]
+            try:
+                mask = sum(bit for k, (_, bit) in enumerate(self.REASONS) if len(c) > 3 + k and c[3 + k].lower().startswith("active"))
+                self.rows.append((float(c[0]), float(c[1]), float(c[2]), mask))
+            except (ValueError, IndexError):
+                pass
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.25)
-        self.proc.terminate()
-        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for k, n in enumerate(names) if any(len(r) > 3 + k and r[3 + k].lower().startswith("active") for r in self.rows)]
-        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "power_w_max": max(pw) if pw else None, "samples": len(self.rows)}
+        if self.source is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampling unavailable"]}
+        if self.source == "nvml":
+            time.sleep(0.06)
+            self._stop.set()
+            self._thread.join(timeout=1.0)
+        else:
+            time.sleep(0.25)
+            self.proc.terminate()
+        sm = sorted(r[0] for r in self.rows)
+        reasons = [n for n, bit in self.REASONS if any(r[3] & bit for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max((r[1] for r in self.rows), default=None), "reasons": reasons,
+                "power_w_max": max((r[2] for r in self.rows), default=None), "samples": len(self.rows), "source": self.source}
 
 
 def scene_text(name, width, height, spp):
