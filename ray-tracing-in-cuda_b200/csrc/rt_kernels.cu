@@ -9,10 +9,11 @@
 //     256-entry chunks — queue lengths never travel to the host, nearly-empty late bounces cost one tiny launch each;
 //   * SoA float4 ray queues (coalesced 16-byte accesses / TMA bulk copies), hit records of 8 bytes, 128 M paths per pass;
 //   * the whole BVH is staged in shared memory in a sign-ordered 128-byte layout when it fits (RTIOW: 485 nodes = 62 KB),
-//     else 64-byte nodes are read via L1/L2; primary rays skip the tree through per-tile camera-beam candidate lists;
+//     else 64-byte nodes are read via L1/L2; the first traversal-stack levels live in shared memory too; primary rays skip
+//     the tree through per-tile camera-beam candidate lists, and tiles whose beam touches nothing skip the queues altogether;
 //   * shade: TMA bulk loads/stores through shared staging, ballot/popc compaction, one global atomic per chunk, optional
 //     in-CTA sort by material class (RT_RENDER_SORT);
-//   * Philox4x32-10 keyed (pixel, sample, bounce): no RNG state in memory;
+//   * Philox4x32-10 keyed (pixel, sample, bounce): no RNG state in memory; camera paths carry no throughput record;
 //   * radiance is written once per path and summed per pixel in sample order by `accumulate` (no float atomics).
 #include "rt_kernels.h"
 #include "rt_traverse.cuh"
@@ -244,12 +245,6 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
         for (int i = base + lane_id(); i < end; i += 32) {
             if (!SHADOW && fixup && q.hits[i].y != RT_HIT_TODO) continue;
             const float4 o4 = ray_o[i], d4 = ray_d[i];
-#ifdef RT_EXT_PREFETCH
-            if (i + 32 < end) {
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(ray_o + i + 32));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(ray_d + i + 32));
-            }
-#endif
             float t; int code;
             if (SHADOW) {
                 traverse<SMEM, COUNT, true, RT_SSTACK>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt, sstack);
