@@ -33,6 +33,9 @@ WORKLOADS = {
     "sample_scene_1600x900_512spp": ("sample_scene.json", 1600, 900, 512),
     # config 3 as BASELINE.json words it (boxes, rotate_y, image + checker textures, three emitters, OBJ mesh): our schema extensions
     "sample_scene_ext_1600x900_512spp": ("sample_scene_ext.json", 1600, 900, 512),
+    # config 3 at its full sample count (4096 spp, 512 per GPU on 8)
+    "sample_scene_1600x900_4096spp": ("sample_scene.json", 1600, 900, 4096),
+    "sample_scene_ext_1600x900_4096spp": ("sample_scene_ext.json", 1600, 900, 4096),
     # config 4: procedural ~1M-triangle mesh (scenes.mesh_scene, seeded) under the GPU LBVH; "@" = tables, not a JSON file
     "mesh1m_4k_1024spp": ("@mesh:708", 3840, 2160, 1024),
     "mesh1m_1080p_64spp": ("@mesh:708", 1920, 1080, 64),

@@ -304,6 +304,10 @@ static int upload_to_device(rt_ctx *ctx) {
     int per_sm = extend_max_blocks_per_sm(ctx->cfg.bvh_smem_bytes);
     if (per_sm < 1) { ctx->cfg.bvh_smem_bytes = 0; per_sm = extend_max_blocks_per_sm(0); }
     ctx->cfg.extend_blocks_per_sm = per_sm < 1 ? 1 : per_sm;
+    // a scene whose objects are all emitters (dna.py frames) ends every path at its first vertex: one bounce is the whole job
+    ctx->scene_scatters = false;
+    for (int i = 0; i < d.n_objects; ++i)
+        if (hs.materials[hs.objects[i].material].type != RT_MAT_DIFFUSE_LIGHT) { ctx->scene_scatters = true; break; }
     ctx->have_scene = true;
     ctx->tiles_dirty = true;
     ctx->accum_valid = false;
@@ -555,7 +559,8 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         int buf = 0;
         // every tile's beam misses everything (empty scene, camera looking away): no path enters the queues
         const bool no_paths = tile_mode == 1 && ctx->tiles_all_empty;
-        for (int b = 0; b < ds.max_depth && !no_paths; ++b) {
+        const int depth_needed = ctx->scene_scatters ? ds.max_depth : 1;      // nothing survives the first vertex of an all-emitter scene
+        for (int b = 0; b < depth_needed && !no_paths; ++b) {
             if (b > 0 || tile_mode != 1) timed(1, [&] { launch_extend(cfg, dsp, S.q, b, buf, count, b == 0 && tile_mode == 2); });
             timed(2, [&] { launch_shade(cfg, dsp, S.q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort, nee); });
             if (nee) timed(4, [&] { launch_shadow(cfg, dsp, S.q, b); });

@@ -52,6 +52,7 @@ struct rt_ctx {
     long long launches = 0;
 
     bool have_scene = false;
+    bool scene_scatters = true;      // false: every material referenced by an object is a diffuse_light (paths end at their first vertex)
     HostScene hs;
     DScene ds{};
     LaunchCfg cfg{};

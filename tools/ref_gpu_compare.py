@@ -2,10 +2,10 @@
 gpu-version/main.cu compiled for sm_100 (oracle/_ref/parallel_compute_ref, recipe: oracle/Makefile target `refgpu`)
 against this library on the same JSON scene files, on the same B200.
 
-The reference binary prints no timings, so its render time is the slope of whole-process wall time between two
-sample counts (start-up, parse, move_to_device and image writing cancel); ours is the CUDA-event-free wall time of
-rt_render + rt_synchronize on a resident scene, and — like for like — the whole-process wall time of our
-`parallel_compute` CLI on the same file.
+The reference binary prints progress lines on (unbuffered) stderr: its render time is the wall time between the arrival of
+"Start rendering" and "Finish rendering" (main.cu:499-508: the render<<<>>> launch and the cudaDeviceSynchronize after it);
+ours is the wall time of rt_render + rt_synchronize on a resident scene, and — like for like — the whole-process wall time
+of our `parallel_compute` CLI on the same file next to the reference's.
 
 Usage (GPU box):  python tools/ref_gpu_compare.py [--out gpurun_out/ref_gpu_compare.json]
 Test infrastructure: only this tool and bench.py execute anything under oracle/_ref.
@@ -42,10 +42,26 @@ def reference_schema(scene):
 
 
 def run_wall(cmd, cwd, timeout):
+    """Returns (whole-process wall s, exit code, stderr tail, seconds between the 'Start rendering' and 'Finish rendering' lines)."""
     t0 = time.perf_counter()
-    p = subprocess.run(cmd, cwd=cwd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, timeout=timeout)
+    p = subprocess.Popen(cmd, cwd=cwd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
+    t_start = t_finish = None
+    tail = []
+    for raw in p.stderr:                      # the reference writes these lines with fprintf(stderr, ...): unbuffered
+        now = time.perf_counter()
+        line = raw.decode(errors="replace")
+        tail.append(line)
+        if "Start rendering" in line:
+            t_start = now
+        elif "Finish rendering" in line:
+            t_finish = now
+        if now - t0 > timeout:
+            p.kill()
+            break
+    rc = p.wait()
     dt = time.perf_counter() - t0
-    return dt, p.returncode, p.stderr.decode(errors="replace")[-400:]
+    render = (t_finish - t_start) if (t_start is not None and t_finish is not None) else None
+    return dt, rc, "".join(tail)[-400:], render
 
 
 def main():
@@ -58,7 +74,7 @@ def main():
 
     # (scene file, width, height, reference spp pair, our spp)
     cases = [
-        ("rtiow_486.json", 1920, 1080, (4, 12), 64),
+        ("rtiow_486.json", 1920, 1080, (4, 16), 64),
         ("blue2.json", 1920, 1080, (64, 256), 256),
         ("sample_scene.json", 1600, 900, (128, 512), 512),
     ]
@@ -78,13 +94,13 @@ def main():
                 fn = os.path.join(td, f"ref_{spp}.json")
                 json.dump(ref_scene, open(fn, "w"))
                 if os.path.exists(REF_BIN):
-                    dt, rc, err = run_wall([REF_BIN, "-f", fn], td, a.timeout)
-                    walls[spp] = dt
-                    rec.setdefault("reference_runs", []).append({"spp": spp, "wall_s": dt, "exit": rc, "stderr_tail": err if rc else ""})
-            if len(walls) == 2 and all(r["exit"] == 0 for r in rec["reference_runs"]):
-                slope = (walls[s2] - walls[s1]) / (s2 - s1)           # seconds per sample-per-pixel
-                rec["reference_render_s_per_spp"] = slope
-                rec["reference_samples_per_s"] = W * H / slope if slope > 0 else None
+                    dt, rc, err, render = run_wall([REF_BIN, "-f", fn], td, a.timeout)
+                    walls[spp] = render
+                    rec.setdefault("reference_runs", []).append({"spp": spp, "wall_s": dt, "render_s": render, "exit": rc,
+                                                                 "stderr_tail": err if rc else ""})
+            if walls.get(s2) and all(r["exit"] == 0 for r in rec["reference_runs"]):
+                rec["reference_render_s_per_spp"] = walls[s2] / s2    # the larger run
+                rec["reference_samples_per_s"] = W * H * s2 / walls[s2]
             # ours, resident scene, same file (reference schema: same objects, constant background)
             ref_scene["samples_per_pixel"] = ours_spp
             fn = os.path.join(td, "ours.json")
@@ -109,7 +125,7 @@ def main():
             fn2 = os.path.join(td, f"ours_{s2}.json")
             json.dump(ref_scene, open(fn2, "w"))
             if os.path.exists(OUR_CLI):
-                dt, rc, err = run_wall([OUR_CLI, "-f", fn2], td, a.timeout)
+                dt, rc, err, _ = run_wall([OUR_CLI, "-f", fn2], td, a.timeout)
                 rec["ours_cli_wall_s"] = {"spp": s2, "wall_s": dt, "exit": rc}
             if rec.get("reference_samples_per_s"):
                 rec["speedup_render"] = rec["ours_samples_per_s"] / rec["reference_samples_per_s"]
