@@ -304,6 +304,8 @@ static int upload_to_device(rt_ctx *ctx) {
     int per_sm = extend_max_blocks_per_sm(ctx->cfg.bvh_smem_bytes);
     if (per_sm < 1) { ctx->cfg.bvh_smem_bytes = 0; per_sm = extend_max_blocks_per_sm(0); }
     ctx->cfg.extend_blocks_per_sm = per_sm < 1 ? 1 : per_sm;
+    ds.only_type = d.n_objects > 0 ? hs.objects[0].type : -1;
+    for (int i = 1; i < d.n_objects; ++i) if (hs.objects[i].type != ds.only_type) { ds.only_type = -1; break; }
     // a scene whose objects are all emitters (dna.py frames) ends every path at its first vertex: one bounce is the whole job
     ctx->scene_scatters = false;
     for (int i = 0; i < d.n_objects; ++i)

@@ -212,7 +212,8 @@ __global__ void __launch_bounds__(128) k_tile_lists(DScene sc, int *__restrict__
 // t in [0.001, 0.999] of the unnormalised segment; an unoccluded sample adds its radiance to the path's slot (one entry per
 // path and bounce, so the add needs no atomic).
 // max_batch < 0 (bounce 0 after a generate launch that resolved most hits itself): only entries carrying RT_HIT_TODO.
-template <bool SMEM, bool COUNT, bool SHADOW>
+// ONLY: RT_OBJ_SPHERE when every primitive of the scene is a sphere (no leaf dispatch in the loop), else -1.
+template <bool SMEM, bool COUNT, bool SHADOW, int ONLY = -1>
 __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf, int max_batch) {
     const bool fixup = max_batch < 0;
     if (fixup) max_batch = -max_batch;
@@ -247,14 +248,14 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
             const float4 o4 = ray_o[i], d4 = ray_d[i];
             float t; int code;
             if (SHADOW) {
-                traverse<SMEM, COUNT, true, RT_SSTACK>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt, sstack);
+                traverse<SMEM, COUNT, true, RT_SSTACK, ONLY>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt, sstack);
                 if (code < 0) {
                     const int pid = __float_as_int(o4.w);
                     const float4 c = q.sh_c[i], r = q.radiance[pid];
                     q.radiance[pid] = make_float4(r.x + c.x, r.y + c.y, r.z + c.z, 0.0f);
                 }
             } else {
-                traverse<SMEM, COUNT, false, RT_SSTACK>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt, sstack);
+                traverse<SMEM, COUNT, false, RT_SSTACK, ONLY>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt, sstack);
                 q.hits[i] = make_int2(__float_as_int(t), code);
             }
         }
@@ -725,7 +726,9 @@ static void launch_extend_t(const LaunchCfg &c, const DScene &sc, const Queues &
     const size_t sm = (SMEM ? c.bvh_smem_bytes : 0) + RT_SSTACK_BYTES;
     static const int batch0 = getenv("RT_EXT_BATCH") ? atoi(getenv("RT_EXT_BATCH")) : RT_EXT_BATCH;
     const int batch = fixup ? -batch0 : batch0;
+    const bool spheres = SMEM && sc.only_type == RT_OBJ_SPHERE;      // the specialised loop exists for the shared-memory tree
     if (count) k_extend<SMEM, true, SHADOW><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
+    else if (spheres) k_extend<true, false, SHADOW, RT_OBJ_SPHERE><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
     else k_extend<SMEM, false, SHADOW><<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, bounce, buf, batch);
 }
 
@@ -750,6 +753,7 @@ cudaError_t extend_configure_smem(size_t smem_bytes) {
     const size_t tot = smem_bytes + RT_SSTACK_BYTES;
     SET((k_extend<true, false, false>), tot); SET((k_extend<true, true, false>), tot); SET((k_extend<true, false, true>), tot);
     SET((k_extend<true, true, true>), tot);
+    SET((k_extend<true, false, false, RT_OBJ_SPHERE>), tot); SET((k_extend<true, false, true, RT_OBJ_SPHERE>), tot);
     if (RT_SSTACK_BYTES > 48 * 1024) {
         SET((k_extend<false, false, false>), RT_SSTACK_BYTES); SET((k_extend<false, true, false>), RT_SSTACK_BYTES);
         SET((k_extend<false, false, true>), RT_SSTACK_BYTES); SET((k_extend<false, true, true>), RT_SSTACK_BYTES);

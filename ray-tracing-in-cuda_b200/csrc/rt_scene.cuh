@@ -52,6 +52,7 @@ struct DScene {
     const float *light_area;               // light -> surface area
     const int *obj_light;                  // object index -> light index or -1
     // primary-ray candidate lists (rt_kernels.cu:k_tile_lists): per 8x4 pixel tile the leaves its camera beam can touch
+    int only_type;                         // RT_OBJ_* when every primitive has that type (k_extend specialisation), else -1
     int tile_mode;                         // 0: none, 1: every path of a pass is covered, 2: covered where tile_cnt >= 0
     const int *tile_list, *tile_cnt;       // [n_tiles * RT_TILE_K] leaf codes, [n_tiles] count or -1 (too many: fix-up pass)
     const int *tile_empty_prefix;          // [n_tiles + 1] number of tiles with count 0 before tile t (their paths skip the queues), or null
@@ -187,9 +188,12 @@ __device__ __forceinline__ bool triangle_t(float3 v0, float3 e1, float3 e2, floa
 }
 
 // One leaf test for the extend stage.  code = ~child = type<<28 | slot.
+// ONLY >= 0: the scene holds primitives of that one type (spheres: the RTIOW scene) — no dispatch, the other tests are not compiled in.
+template <int ONLY = -1>
 __device__ __forceinline__ bool leaf_t(const DScene &sc, int code, float3 o, float3 d, float a, float inv_a, float tmin, float tmax, float &t) {
     const int type = (unsigned)code >> 28, slot = code & RT_LEAF_SLOT_MASK;
     const float4 A = __ldg(&sc.primA[slot]);
+    if (ONLY == RT_OBJ_SPHERE) return sphere_t(A, o, d, a, inv_a, tmin, tmax, t);
     switch (type) {
     case RT_OBJ_SPHERE: return sphere_t(A, o, d, a, inv_a, tmin, tmax, t);
     case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT:

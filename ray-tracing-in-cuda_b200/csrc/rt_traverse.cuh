@@ -41,11 +41,11 @@ __device__ __forceinline__ void count_leaf(TravCounters &c, int code, bool hit) 
 
 // One exact leaf test with the closest-hit bookkeeping of the linear walk (object.cuh:23-37): a root equal to the current
 // best replaces it when the object comes later in the scene file.  Returns true when the hit was taken.
-template <bool COUNT>
+template <bool COUNT, int ONLY = -1>
 __device__ __forceinline__ bool leaf_visit(const DScene &sc, int code, float3 o, float3 d, float a, float inv_a, float tmin,
                                            float &best_t, int &best_code, TravCounters &cnt) {
     float t;
-    const bool h = leaf_t(sc, code, o, d, a, inv_a, tmin, best_t, t);
+    const bool h = leaf_t<ONLY>(sc, code, o, d, a, inv_a, tmin, best_t, t);
     count_leaf<COUNT>(cnt, code, h);
     if (!h) return false;
     bool take = t < best_t || best_code < 0;
@@ -92,7 +92,7 @@ __device__ __forceinline__ int2 lds_stack(unsigned addr) {
 // is conflict-free), deeper levels in the per-thread local-memory array.  ncu (r01f) had the pop loop at 17 % of the warp
 // samples of k_extend, waiting on local-memory loads at ~6 active lanes; mean stack depth on the reference scenes is < SD.
 // SD = 0 (k_aov, k_tile_lists callers): local memory only.
-template <bool SIGNED, bool COUNT, bool ANY_HIT, int SD = 0>
+template <bool SIGNED, bool COUNT, bool ANY_HIT, int SD = 0, int ONLY = -1>
 __device__ __forceinline__ void traverse(const DScene &sc, const char *__restrict__ nodes, float3 o, float3 d, float tmin,
                                          float tmax, float &best_t, int &best_code, TravCounters &cnt, unsigned sstack = 0) {
     best_t = tmax; best_code = -1;
@@ -134,7 +134,7 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
         // leaf step first, inner step second: a lane that holds a leaf tests it, pops, and still takes part in this
         // iteration's inner-node step (a diverged warp executes both halves anyway)
         if (cur < 0) {
-            if (leaf_visit<COUNT>(sc, ~cur, o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
+            if (leaf_visit<COUNT, ONLY>(sc, ~cur, o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
             RT_POP()
         }
         if (cur >= 0) {
