@@ -189,6 +189,12 @@ static int upload_to_device(rt_ctx *ctx) {
         dm.ior = m.ior;
         const bool uv = (m.type == RT_MAT_LAMBERTIAN || m.type == RT_MAT_DIFFUSE_LIGHT) && texture_reads_uv(hs, m.texture);
         dm.albedo = make_float4(m.albedo[0], m.albedo[1], m.albedo[2], uv ? 1.0f : 0.0f);
+        // a plain solid_color texture is resolved here: the material carries the colour, the kernels skip the texture table
+        if ((m.type == RT_MAT_LAMBERTIAN || m.type == RT_MAT_DIFFUSE_LIGHT) && hs.textures[m.texture].type == RT_TEX_SOLID) {
+            const rt_texture_desc &t = hs.textures[m.texture];
+            dm.albedo = make_float4(t.color[0], t.color[1], t.color[2], 0.0f);
+            dm.texture = -1;
+        }
         mats[i] = dm;
     }
     CU(ctx->d_mats.alloc(mats.size()));

@@ -476,7 +476,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                 hit_record(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
                     if (!(prev_nee && sc.obj_light[__ldg(&sc.prim_obj[slot])] >= 0))
-                        rad = thr * texture_value(sc, m.texture, rec.u, rec.v, rec.p);
+                        rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
                 } else {
                     Rng rng; rng.init(seed, (unsigned)__float_as_int(d4.w), (unsigned)(spp_begin + __float_as_int(t4.w)), (unsigned)bounce + 1u, sc.sampling);
                     float3 att, sd;
@@ -643,7 +643,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_aov(DScene sc, float *__restrict__
             q[11] = (float)sc.prim_obj[slot]; q[12] = (float)mi;
             float3 att = v3(0, 0, 0), E = v3(0, 0, 0);
             bool ok = false;
-            if (m.type == RT_MAT_DIFFUSE_LIGHT) E = texture_value(sc, m.texture, rec.u, rec.v, rec.p);
+            if (m.type == RT_MAT_DIFFUSE_LIGHT) E = material_color(sc, m, rec.u, rec.v, rec.p);
             else {
                 // fixed uniforms 0.5,0.5,0.5,... as in the oracle/reference harness: only `att` and `ok` are recorded
                 FixedRng fr;

@@ -30,6 +30,12 @@ __device__ __forceinline__ float3 texture_value(const DScene &sc, int tex, float
     return v3(0, 0, 0);
 }
 
+// Colour of a lambertian / diffuse_light material at (u, v, p).  A material whose texture is a plain solid_color carries the colour
+// itself (texture < 0, resolved at upload): one dependent table load less per shaded vertex.
+__device__ __forceinline__ float3 material_color(const DScene &sc, const DMaterial &m, float u, float v, float3 p) {
+    return m.texture < 0 ? f4xyz(m.albedo) : texture_value(sc, m.texture, u, v, p);
+}
+
 // replayed uniforms for the deterministic AOV pass (same sequence as the oracle and the reference harness)
 struct FixedRng {
     int pos = 0;
@@ -92,7 +98,7 @@ __device__ __forceinline__ bool scatter(const DScene &sc, const DMaterial &m, fl
         float3 dir = rec.n + r;
         if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = rec.n;
         sd = dir;
-        att = texture_value(sc, m.texture, rec.u, rec.v, rec.p);
+        att = material_color(sc, m, rec.u, rec.v, rec.p);
         return true;
     }
     case RT_MAT_METAL: {
@@ -212,7 +218,7 @@ __device__ __forceinline__ bool light_sample(const DScene &sc, float3 x, float3 
     if (!(cs > 0.0f) || !(cl > 0.0f)) return false;
     const float g = ((cs * cl) / d2) * (sc.light_area[k] * ((float)sc.n_lights * RT_INV_PI_F));
     const DMaterial m = sc.mats[sc.prim_mat[slot]];
-    f = g * texture_value(sc, m.texture, tu, tv, y);
+    f = g * material_color(sc, m, tu, tv, y);
     return true;
 }
 

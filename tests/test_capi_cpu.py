@@ -106,3 +106,18 @@ def test_cli_keeps_the_reference_exit_code_without_a_device(lib, tmp_path):
     assert not (tmp_path / "main.ppm").exists()
     p = subprocess.run([cli, "--bogus"], cwd=tmp_path, capture_output=True, text=True)
     assert p.returncode == 99
+
+
+def test_bench_clock_sampler_degrades_without_a_gpu():
+    """bench.py samples clocks through NVML (nvidia-smi as fallback); without a GPU it must report that, not raise."""
+    import importlib.util
+    import time
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    s = bench.ClockSampler(0)
+    s.start()
+    time.sleep(0.1)
+    out = s.stop()
+    assert "reasons" in out and "sm_mhz" in out
