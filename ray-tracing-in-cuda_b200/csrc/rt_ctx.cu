@@ -511,8 +511,9 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         long long held = 0;
         for (int k = 0; k < RT_MAX_SETS; ++k) held += ctx->qs[k].cap * per_path;
         long long by_mem = (long long)((double)(free_b + held) * 0.5 / per_path) / n_sets;
-        // big wavefronts amortise the ~100 short late-bounce launches of a pass: 2 x 128 M paths = 32 GB of the 180 GB
-        max_paths = std::min<long long>(by_mem, (256ll << 20) / n_sets);
+        // big wavefronts amortise the ~100 short late-bounce launches of a pass: 2 x 256 M paths = 61 GB of the 180 GB
+        // (RTIOW 1080p 1024 spp: 508.9 / 498.3 / 493.3 ms per step at 64 / 128 / 256 M paths per stream)
+        max_paths = std::min<long long>(by_mem, (512ll << 20) / n_sets);
     }
     max_paths = std::min<long long>(max_paths, 1ll << 30);
     int s_pass = (int)std::max<long long>(1, std::min<long long>(spp, max_paths / np));
