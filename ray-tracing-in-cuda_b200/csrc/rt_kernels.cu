@@ -7,7 +7,7 @@
 // Design for B200 (148 SMs, 228 KB smem/SM, 126 MB L2, 180 GB HBM3e):
 //   * persistent grids (SM count x resident CTAs); extend warps pull batches from a device-side cursor, shade CTAs own
 //     256-entry chunks — queue lengths never travel to the host, nearly-empty late bounces cost one tiny launch each;
-//   * SoA float4 ray queues (coalesced 16-byte accesses / TMA bulk copies), hit records of 8 bytes, 128 M paths per pass;
+//   * SoA float4 ray queues (coalesced 16-byte accesses / TMA bulk copies), hit records of 8 bytes, 256 M paths per pass and stream;
 //   * the whole BVH is staged in shared memory in a sign-ordered 128-byte layout when it fits (RTIOW: 485 nodes = 62 KB),
 //     else 64-byte nodes are read via L1/L2; the first traversal-stack levels live in shared memory too; primary rays skip
 //     the tree through per-tile camera-beam candidate lists, and tiles whose beam touches nothing skip the queues altogether;
