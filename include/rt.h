@@ -192,11 +192,17 @@ int rt_stats_reset(rt_ctx *ctx);
 int rt_host_alloc(rt_ctx *ctx, void **ptr, size_t bytes);
 int rt_host_free(rt_ctx *ctx, void *ptr);
 
-/* LBVH introspection for the bit-exact build tests.  n_prims leaves, n_prims-1 internal nodes (0 if n_prims < 2).
- * Any output pointer may be NULL.  child encoding: >= 0 internal node index, < 0 leaf ~index into the sorted order. */
+/* LBVH introspection for the bit-exact build tests.  Arrays are sized for n_prims leaves (n_prims-1 internal nodes); the tree
+ * itself has n_tree <= n_prims leaves (rt_bvh_info): objects that span more than a quarter of the scene ("giants") are kept out
+ * of it, sorted behind the others, and tested by every ray before the walk — left/right/node_aabb hold n_tree-1 entries, parent
+ * 2*n_tree-1.  Any output pointer may be NULL.  child encoding: >= 0 internal node index, < 0 leaf ~index into the sorted order. */
 int rt_bvh_download(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left,
                     int32_t *right, int32_t *parent, float *node_aabb /* 6 per internal node */,
                     float *leaf_aabb /* 6 per sorted leaf */, float *scene_aabb /* 6 */);
+
+/* n_tree leaves in the tree, n_giants objects tested up front (sorted slots n_tree ..), depth = internal nodes on the longest
+ * root-to-leaf path (an upload whose tree is deeper than the traversal stack fails with RT_ERR_INVALID). */
+int rt_bvh_info(rt_ctx *ctx, int32_t *n_tree, int32_t *n_giants, int32_t *depth);
 
 /* Host image writers (row 0 of rgb8 = top).  PPM is the reference's P3 text format (color.cuh:70-95). */
 int rt_write_ppm(const char *path, const unsigned char *rgb8, int width, int height);

@@ -9,9 +9,22 @@
  *   topology: Karras 2012, delta(i,j) = clz(m_i ^ m_j), ties broken by 64 + clz(i ^ j)
  *   boxes:    leaf = object box padded by 2^-10 * (largest object extent) + 2^-20 * (largest scene extent);
  *             internal = union of children
+ *   giants:   an object whose largest box extent exceeds a quarter of the scene's (the r = 1000 ground sphere of the RTIOW
+ *             scene, cmake-cpu-version/main.cpp:125-172; the 200 x 200 rects of blue2.json) would make every box on its
+ *             ancestor chain cover the whole scene.  Up to ORC_MAX_GIANTS such objects stay OUT of the tree: they get the key
+ *             2^63 (behind every 63-bit Morton code; the stable sort keeps them in scene-file order), occupy the last
+ *             n_giants leaf slots, and the traversal tests them before it walks the tree (the "last index wins" tie rule of
+ *             object.cuh:29-33 does not depend on the order of the tests).  Morton codes are normalised to the centroid
+ *             bounds of the other objects.  A giant sphere's box (read only by the camera-beam tile lists) is padded by the
+ *             float error bound of sphere::hit for rays that start at the camera instead of 2^-10 of its extent.
  */
 #include "orc_internal.h"
 #include <float.h>
+
+#ifndef ORC_MAX_GIANTS
+#define ORC_MAX_GIANTS 16
+#endif
+#define ORC_GIANT_KEY 0x8000000000000000ULL
 
 void orc_object_aabb(const rt_scene_desc *sc, int i, float bmin[3], float bmax[3]) {
     const rt_object_desc *ob = &sc->objects[i];
@@ -100,80 +113,110 @@ static inline int delta(const uint64_t *m, int n, int i, int j) {
     return 64 + __builtin_clz((uint32_t)(i ^ j));     /* i != j here */
 }
 
-int orc_lbvh_build(const rt_scene_desc *sc, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left, int32_t *right,
-                   int32_t *parent, float *node_aabb, float *leaf_aabb, float *scene_aabb) {
+/* Giant-sphere box padding: largest distance m by which a ray starting within D of the centre can miss the sphere while the float
+ * discriminant of sphere::hit (object.cuh:51-58) still comes out >= 0, and by which an accepted hit point can lie off the surface:
+ * m^2 + 2 r m <= K (D^2 + r^2) with K = 2^-18 (64 ulp of the largest term, a loose bound on the ~20 roundings involved). */
+static float giant_sphere_pad(float r, float D) {
+    float x = 3.814697265625e-06f * (D * D + r * r);
+    return x / (sqrtf(r * r + x) + r);
+}
+
+int orc_lbvh_build_ex(const rt_scene_desc *sc, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left, int32_t *right,
+                      int32_t *parent, float *node_aabb, float *leaf_aabb, float *scene_aabb, int32_t *info) {
     const int n = sc->n_objects;
+    if (info) { info[0] = 0; info[1] = 0; info[2] = 0; info[3] = 0; }
     if (n <= 0) return 0;
     float *bmin = (float *)malloc(sizeof(float) * 3 * (size_t)n), *bmax = (float *)malloc(sizeof(float) * 3 * (size_t)n);
     float smin[3] = {INFINITY, INFINITY, INFINITY}, smax[3] = {-INFINITY, -INFINITY, -INFINITY};
-    float cmin[3] = {INFINITY, INFINITY, INFINITY}, cmax[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (int i = 0; i < n; ++i) {
         orc_object_aabb(sc, i, bmin + 3 * i, bmax + 3 * i);
+        for (int k = 0; k < 3; ++k) { smin[k] = fminf(smin[k], bmin[3 * i + k]); smax[k] = fmaxf(smax[k], bmax[3 * i + k]); }
+    }
+    if (scene_aabb) for (int k = 0; k < 3; ++k) { scene_aabb[k] = smin[k]; scene_aabb[3 + k] = smax[k]; }
+    const float sext = fmaxf(smax[0] - smin[0], fmaxf(smax[1] - smin[1], smax[2] - smin[2]));
+    /* giants: largest extent > sext / 4; none when more than ORC_MAX_GIANTS qualify (a scene made of large pieces) */
+    unsigned char *giant = (unsigned char *)calloc((size_t)n, 1);
+    int ng = 0;
+    for (int i = 0; i < n; ++i) {
+        float e = fmaxf(bmax[3 * i] - bmin[3 * i], fmaxf(bmax[3 * i + 1] - bmin[3 * i + 1], bmax[3 * i + 2] - bmin[3 * i + 2]));
+        giant[i] = e > 0.25f * sext;
+        ng += giant[i];
+    }
+    if (ng > ORC_MAX_GIANTS) { memset(giant, 0, (size_t)n); ng = 0; }
+    const int nt = n - ng;                      /* leaves of the tree */
+    float cmin[3] = {INFINITY, INFINITY, INFINITY}, cmax[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = 0; i < n; ++i) {
+        if (giant[i]) continue;
         for (int k = 0; k < 3; ++k) {
             float c = 0.5f * (bmin[3 * i + k] + bmax[3 * i + k]);
-            smin[k] = fminf(smin[k], bmin[3 * i + k]); smax[k] = fmaxf(smax[k], bmax[3 * i + k]);
             cmin[k] = fminf(cmin[k], c); cmax[k] = fmaxf(cmax[k], c);
         }
     }
-    if (scene_aabb) for (int k = 0; k < 3; ++k) { scene_aabb[k] = smin[k]; scene_aabb[3 + k] = smax[k]; }
     uint64_t *keys = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)n);
     int32_t *vals = (int32_t *)malloc(sizeof(int32_t) * (size_t)n);
     for (int i = 0; i < n; ++i) {
+        vals[i] = i;
+        if (giant[i]) { keys[i] = ORC_GIANT_KEY; continue; }
         uint32_t q[3];
         for (int k = 0; k < 3; ++k) {
             float c = 0.5f * (bmin[3 * i + k] + bmax[3 * i + k]);
             q[k] = quant21(c, cmin[k], cmax[k] - cmin[k]);
         }
         keys[i] = expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
-        vals[i] = i;
     }
     orc_radix_sort_pairs(keys, vals, n);
     if (morton_sorted) memcpy(morton_sorted, keys, sizeof(uint64_t) * (size_t)n);
     if (prim_sorted) memcpy(prim_sorted, vals, sizeof(int32_t) * (size_t)n);
 
-    float sext = fmaxf(smax[0] - smin[0], fmaxf(smax[1] - smin[1], smax[2] - smin[2]));
     float pad_abs = sext * 9.5367431640625e-07f;                     /* 2^-20 */
     float *lb = (float *)malloc(sizeof(float) * 6 * (size_t)n);
     for (int j = 0; j < n; ++j) {
         int i = vals[j];
         float e = fmaxf(bmax[3 * i] - bmin[3 * i], fmaxf(bmax[3 * i + 1] - bmin[3 * i + 1], bmax[3 * i + 2] - bmin[3 * i + 2]));
         float pad = fmaf(e, 9.765625e-04f, pad_abs);                  /* 2^-10 */
+        if (giant[i] && sc->objects[i].type == RT_OBJ_SPHERE) {        /* camera rays only: error bound instead of 2^-10 e */
+            const float *p = sc->objects[i].p, *cf = sc->camera.lookfrom;
+            float dx = cf[0] - p[0], dy = cf[1] - p[1], dz = cf[2] - p[2];
+            float D = sqrtf(dx * dx + dy * dy + dz * dz) + 0.5f * fabsf(sc->camera.aperture);
+            pad = giant_sphere_pad(fabsf(p[3]), D) + pad_abs;
+        }
         for (int k = 0; k < 3; ++k) { lb[6 * j + k] = bmin[3 * i + k] - pad; lb[6 * j + 3 + k] = bmax[3 * i + k] + pad; }
     }
     if (leaf_aabb) memcpy(leaf_aabb, lb, sizeof(float) * 6 * (size_t)n);
 
-    if (n >= 2) {
-        int32_t *L = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n - 1)), *R = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n - 1));
-        int32_t *P = (int32_t *)malloc(sizeof(int32_t) * (size_t)(2 * n - 1));
+    int depth = nt >= 1 ? 1 : 0;
+    if (nt >= 2) {
+        int32_t *L = (int32_t *)malloc(sizeof(int32_t) * (size_t)(nt - 1)), *R = (int32_t *)malloc(sizeof(int32_t) * (size_t)(nt - 1));
+        int32_t *P = (int32_t *)malloc(sizeof(int32_t) * (size_t)(2 * nt - 1));
         P[0] = -1;
-        for (int i = 0; i < n - 1; ++i) {     /* Karras 2012, Algorithm "construct internal nodes" */
-            int d = delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
-            int dmin = delta(keys, n, i, i - d);
+        for (int i = 0; i < nt - 1; ++i) {     /* Karras 2012, Algorithm "construct internal nodes" */
+            int d = delta(keys, nt, i, i + 1) - delta(keys, nt, i, i - 1) >= 0 ? 1 : -1;
+            int dmin = delta(keys, nt, i, i - d);
             int lmax = 2;
-            while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+            while (delta(keys, nt, i, i + lmax * d) > dmin) lmax *= 2;
             int l = 0;
             for (int t = lmax / 2; t >= 1; t /= 2)
-                if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+                if (delta(keys, nt, i, i + (l + t) * d) > dmin) l += t;
             int j = i + l * d;
-            int dnode = delta(keys, n, i, j);
+            int dnode = delta(keys, nt, i, j);
             int s = 0, t = l;
             do {
                 t = (t + 1) >> 1;
-                if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+                if (delta(keys, nt, i, i + (s + t) * d) > dnode) s += t;
             } while (t > 1);
             int gamma = i + s * d + (d < 0 ? -1 : 0);
             int lo = i < j ? i : j, hi = i < j ? j : i;
             L[i] = lo == gamma ? ~gamma : gamma;
             R[i] = hi == gamma + 1 ? ~(gamma + 1) : gamma + 1;
-            if (L[i] >= 0) P[L[i]] = i; else P[n - 1 + ~L[i]] = i;
-            if (R[i] >= 0) P[R[i]] = i; else P[n - 1 + ~R[i]] = i;
+            if (L[i] >= 0) P[L[i]] = i; else P[nt - 1 + ~L[i]] = i;
+            if (R[i] >= 0) P[R[i]] = i; else P[nt - 1 + ~R[i]] = i;
         }
         /* refit bottom-up: process nodes in an order where children come first (iterate until all done) */
-        float *nb = (float *)malloc(sizeof(float) * 6 * (size_t)(n - 1));
-        unsigned char *done = (unsigned char *)calloc((size_t)(n - 1), 1);
-        int remaining = n - 1;
+        float *nb = (float *)malloc(sizeof(float) * 6 * (size_t)(nt - 1));
+        unsigned char *done = (unsigned char *)calloc((size_t)(nt - 1), 1);
+        int remaining = nt - 1;
         while (remaining > 0) {
-            for (int i = n - 2; i >= 0; --i) {
+            for (int i = nt - 2; i >= 0; --i) {
                 if (done[i]) continue;
                 if ((L[i] >= 0 && !done[L[i]]) || (R[i] >= 0 && !done[R[i]])) continue;
                 const float *a = L[i] >= 0 ? nb + 6 * L[i] : lb + 6 * (~L[i]);
@@ -182,12 +225,24 @@ int orc_lbvh_build(const rt_scene_desc *sc, uint64_t *morton_sorted, int32_t *pr
                 done[i] = 1; --remaining;
             }
         }
-        if (left) memcpy(left, L, sizeof(int32_t) * (size_t)(n - 1));
-        if (right) memcpy(right, R, sizeof(int32_t) * (size_t)(n - 1));
-        if (parent) memcpy(parent, P, sizeof(int32_t) * (size_t)(2 * n - 1));
-        if (node_aabb) memcpy(node_aabb, nb, sizeof(float) * 6 * (size_t)(n - 1));
+        /* depth = the largest number of internal nodes between the root and a leaf (the traversal stack never holds more) */
+        for (int j = 0; j < nt; ++j) {
+            int dpt = 0;
+            for (int c = P[nt - 1 + j]; c >= 0; c = P[c]) ++dpt;
+            if (dpt > depth) depth = dpt;
+        }
+        if (left) memcpy(left, L, sizeof(int32_t) * (size_t)(nt - 1));
+        if (right) memcpy(right, R, sizeof(int32_t) * (size_t)(nt - 1));
+        if (parent) memcpy(parent, P, sizeof(int32_t) * (size_t)(2 * nt - 1));
+        if (node_aabb) memcpy(node_aabb, nb, sizeof(float) * 6 * (size_t)(nt - 1));
         free(L); free(R); free(P); free(nb); free(done);
     } else if (parent) parent[0] = -1;
-    free(bmin); free(bmax); free(keys); free(vals); free(lb);
+    if (info) { info[0] = nt; info[1] = ng; info[2] = depth; }
+    free(bmin); free(bmax); free(keys); free(vals); free(lb); free(giant);
     return 0;
+}
+
+int orc_lbvh_build(const rt_scene_desc *sc, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left, int32_t *right,
+                   int32_t *parent, float *node_aabb, float *leaf_aabb, float *scene_aabb) {
+    return orc_lbvh_build_ex(sc, morton_sorted, prim_sorted, left, right, parent, node_aabb, leaf_aabb, scene_aabb, NULL);
 }

@@ -98,6 +98,13 @@ v3 orc_xform_point(const float m[12], v3 p);
 v3 orc_xform_vec(const float m[12], v3 p);
 v3 orc_xform_normal(const float minv[12], v3 p);
 
+/* host twin of the device traversal (orc_trav.c): the LBVH of lbvh_host.c walked with the device's box arithmetic and order */
+typedef struct orc_bvh orc_bvh;
+typedef struct { int64_t box, nodes, sph_rej, sph_acc, rect, cyl_rej, cyl_acc, tri, boxprim, overflow; int max_stack; } orc_trav_counters;
+orc_bvh *orc_bvh_create(const rt_scene_desc *sc);
+void orc_bvh_destroy(orc_bvh *b);
+int orc_bvh_hit(const orc_bvh *b, v3 o, v3 d, float tmin, float tmax, int any_hit, orc_hit *rec, orc_trav_counters *cnt);
+
 /* object AABB exactly as the GPU build computes it (lbvh_host.c) */
 void orc_object_aabb(const rt_scene_desc *sc, int i, float bmin[3], float bmax[3]);
 

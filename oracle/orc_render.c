@@ -147,13 +147,14 @@ v3 orc_background(const rt_scene_desc *sc, v3 d) {
 typedef struct { int on, n_lights; const int *lights; const unsigned char *is_light; } nee_t;
 
 static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t pixel, uint32_t sample, int64_t *nrays,
-                    const nee_t *nee, int64_t *nshadow) {
+                    const nee_t *nee, int64_t *nshadow, const orc_bvh *bvh, orc_trav_counters *cnt) {
     v3 thr = V(1, 1, 1), L = V(0, 0, 0);
     int prev_nee = 0;       /* the previous vertex sampled the lights: do not count a sampled light again when hit */
     for (int bounce = 0; bounce < sc->max_depth; ++bounce) {
         orc_hit rec;
         ++*nrays;
-        if (!orc_hit_world(sc, o, d, 0.001f, FLT_MAX, &rec)) { L = vadd(L, vmul(thr, orc_background(sc, d))); break; }
+        const int hit = bvh ? orc_bvh_hit(bvh, o, d, 0.001f, FLT_MAX, 0, &rec, cnt) : orc_hit_world(sc, o, d, 0.001f, FLT_MAX, &rec);
+        if (!hit) { L = vadd(L, vmul(thr, orc_background(sc, d))); break; }
         v3 E = orc_emitted(sc, rec.mat, rec.u, rec.v, rec.p);
         if (prev_nee && nee->is_light[rec.prim]) E = V(0, 0, 0);
         orc_rng rng; orc_rng_init(&rng, seed, pixel, sample, (uint32_t)bounce + 1u, sc->sampling);
@@ -177,6 +178,7 @@ static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t
 typedef struct {
     const rt_scene_desc *sc; orc_camera cam; uint32_t seed; int s0, sn; float *out;
     int row_next; pthread_mutex_t mu; int64_t rays, shadow; nee_t nee;
+    const orc_bvh *bvh; orc_trav_counters cnt;
 } job_t;
 
 static void *worker(void *arg) {
@@ -184,6 +186,7 @@ static void *worker(void *arg) {
     const rt_scene_desc *sc = j->sc;
     const int W = sc->width, H = sc->height;
     int64_t rays = 0, shadow = 0;
+    orc_trav_counters cnt; memset(&cnt, 0, sizeof cnt);
     for (;;) {
         pthread_mutex_lock(&j->mu);
         int y = j->row_next++;
@@ -199,19 +202,24 @@ static void *worker(void *arg) {
                 v3 o, d;
                 int defocus = sc->sampling == RT_SAMPLING_REFERENCE_CPU && sc->camera.aperture > 0.0f;
                 orc_get_ray(&j->cam, u, v, defocus, &rng, &o, &d);
-                v3 c = ray_color(sc, o, d, j->seed, pixel, (uint32_t)s, &rays, &j->nee, &shadow);
+                v3 c = ray_color(sc, o, d, j->seed, pixel, (uint32_t)s, &rays, &j->nee, &shadow, j->bvh, &cnt);
                 sum = vadd(sum, c);                                   /* fixed order: ascending sample index */
             }
             float *q = j->out + 3 * (size_t)pixel;
             q[0] = sum.x; q[1] = sum.y; q[2] = sum.z;
         }
     }
-    pthread_mutex_lock(&j->mu); j->rays += rays; j->shadow += shadow; pthread_mutex_unlock(&j->mu);
+    pthread_mutex_lock(&j->mu);
+    j->rays += rays; j->shadow += shadow;
+    j->cnt.box += cnt.box; j->cnt.nodes += cnt.nodes; j->cnt.sph_rej += cnt.sph_rej; j->cnt.sph_acc += cnt.sph_acc; j->cnt.rect += cnt.rect;
+    j->cnt.cyl_rej += cnt.cyl_rej; j->cnt.cyl_acc += cnt.cyl_acc; j->cnt.tri += cnt.tri; j->cnt.boxprim += cnt.boxprim;
+    j->cnt.overflow += cnt.overflow; if (cnt.max_stack > j->cnt.max_stack) j->cnt.max_stack = cnt.max_stack;
+    pthread_mutex_unlock(&j->mu);
     return NULL;
 }
 
-int orc_render_ex(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
-                  int flags, int64_t *n_rays, int64_t *n_shadow_rays) {
+static int render_impl(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
+                       int flags, int64_t *n_rays, int64_t *n_shadow_rays, int use_bvh, int64_t *counters) {
     if (!sc || !rgb_sum || sc->width < 1 || sc->height < 1) return RT_ERR_INVALID;
     if ((flags & RT_RENDER_NEE) && sc->sampling != RT_SAMPLING_REFERENCE_CPU) return RT_ERR_INVALID;
     job_t j; memset(&j, 0, sizeof j);
@@ -225,6 +233,8 @@ int orc_render_ex(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp
         for (int k = 0; k < j.nee.n_lights; ++k) is_light[lights[k]] = 1;
     }
     j.nee.lights = lights; j.nee.is_light = is_light;
+    orc_bvh *bvh = use_bvh ? orc_bvh_create(sc) : NULL;
+    j.bvh = bvh;
     pthread_mutex_init(&j.mu, NULL);
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 256) n_threads = 256;
@@ -233,9 +243,24 @@ int orc_render_ex(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp
     for (int i = 0; i < n_threads; ++i) pthread_join(th[i], NULL);
     pthread_mutex_destroy(&j.mu);
     free(lights); free(is_light);
+    orc_bvh_destroy(bvh);
     if (n_rays) *n_rays = j.rays;
     if (n_shadow_rays) *n_shadow_rays = j.shadow;
+    if (counters) {
+        counters[0] = j.cnt.box; counters[1] = j.cnt.nodes; counters[2] = j.cnt.sph_rej; counters[3] = j.cnt.sph_acc; counters[4] = j.cnt.rect;
+        counters[5] = j.cnt.cyl_rej; counters[6] = j.cnt.cyl_acc; counters[7] = j.cnt.tri; counters[8] = j.cnt.boxprim; counters[9] = j.cnt.max_stack;
+    }
     return 0;
+}
+
+int orc_render_ex(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
+                  int flags, int64_t *n_rays, int64_t *n_shadow_rays) {
+    return render_impl(sc, seed, spp_begin, spp_count, rgb_sum, n_threads, flags, n_rays, n_shadow_rays, 0, NULL);
+}
+
+int orc_render_bvh(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
+                   int flags, int64_t *n_rays, int64_t *counters) {
+    return render_impl(sc, seed, spp_begin, spp_count, rgb_sum, n_threads, flags, n_rays, NULL, 1, counters);
 }
 
 int orc_render(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,

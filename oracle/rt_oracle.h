@@ -68,6 +68,14 @@ float orc_atan2f(float y, float x);
  * parent has 2n-1 entries (n-1 internal nodes then n leaves). */
 int orc_lbvh_build(const rt_scene_desc *scene, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left,
                    int32_t *right, int32_t *parent, float *node_aabb, float *leaf_aabb, float *scene_aabb);
+/* as orc_lbvh_build; info[4] = { leaves in the tree, giants kept out of it (they occupy the last leaf slots), tree depth, 0 } */
+int orc_lbvh_build_ex(const rt_scene_desc *scene, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left,
+                      int32_t *right, int32_t *parent, float *node_aabb, float *leaf_aabb, float *scene_aabb, int32_t *info);
+/* orc_render_ex with the closest hit found by the host twin of the device traversal (orc_trav.c) instead of the linear walk;
+ * counters[10] (may be NULL) = box tests, inner-node visits, sphere reject / accept, rect, cylinder reject / accept, triangle,
+ * box-primitive tests, deepest stack — the serial statement of the device's event counters (rt_stats). */
+int orc_render_bvh(const rt_scene_desc *scene, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
+                   int flags, int64_t *n_rays, int64_t *counters);
 /* stable LSD radix sort of (key, value) pairs — the host statement of the device sort, exposed for tests */
 void orc_radix_sort_pairs(uint64_t *keys, int32_t *vals, int n);
 

@@ -85,7 +85,7 @@ class SceneInfo(C.Structure):
 RT_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_scene_upload", "rt_scene_upload_json",
               "rt_scene_upload_json_text", "rt_scene_info_get", "rt_scene_override", "rt_render", "rt_render_aov",
               "rt_accum_device_ptr", "rt_accum_sum_ordered", "rt_download", "rt_synchronize", "rt_stats_reset",
-              "rt_bvh_download", "rt_write_ppm", "rt_write_png", "rt_read_png", "rt_free", "rt_probe_fp32_peak", "rt_host_alloc",
+              "rt_bvh_download", "rt_bvh_info", "rt_write_ppm", "rt_write_png", "rt_read_png", "rt_free", "rt_probe_fp32_peak", "rt_host_alloc",
               "rt_host_free"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -125,6 +125,7 @@ def load_library(path=None):
     lib.rt_host_free.argtypes = [vp, C.c_void_p]
     lib.rt_bvh_download.argtypes = [vp, P(C.c_int32), P(C.c_uint64), P(C.c_int32), P(C.c_int32), P(C.c_int32),
                                     P(C.c_int32), P(C.c_float), P(C.c_float), P(C.c_float)]
+    lib.rt_bvh_info.argtypes = [vp, P(C.c_int32), P(C.c_int32), P(C.c_int32)]
     lib.rt_write_ppm.argtypes = [C.c_char_p, P(C.c_ubyte), C.c_int, C.c_int]
     lib.rt_write_png.argtypes = [C.c_char_p, P(C.c_ubyte), C.c_int, C.c_int]
     lib.rt_read_png.argtypes = [C.c_char_p, P(P(C.c_ubyte)), P(C.c_int), P(C.c_int)]

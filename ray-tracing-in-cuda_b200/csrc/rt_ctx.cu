@@ -58,11 +58,13 @@ extern "C" int rt_create(rt_ctx **out, int device, void *stream) {
         if (e != cudaSuccess) { delete c; return rt_fail(nullptr, RT_ERR_CUDA, cudaGetErrorString(e)); }
         c->own_stream = true;
     }
-    cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1);
+    cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1); cudaEventCreate(&c->ev_count[0]); cudaEventCreate(&c->ev_count[1]);
     for (int k = 1; k < RT_MAX_SETS; ++k) cudaStreamCreateWithFlags(&c->extra_stream[k], cudaStreamNonBlocking);
     cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
     for (int k = 0; k < RT_MAX_SETS; ++k) cudaEventCreateWithFlags(&c->qs[k].ev_acc, cudaEventDisableTiming);
     c->cfg.stream = c->stream; c->cfg.num_sms = c->num_sms; c->cfg.launches = &c->launches;
+    e = kernels_configure_device(device, c->smem_optin);
+    if (e != cudaSuccess) { std::string m = std::string("kernel configuration: ") + cudaGetErrorString(e); rt_destroy(c); return rt_fail(nullptr, RT_ERR_CUDA, m); }
     *out = c;
     return RT_OK;
 }
@@ -82,7 +84,7 @@ extern "C" void rt_destroy(rt_ctx *c) {
     c->d_obmin.release(); c->d_obmax.release(); c->d_node_aabb.release(); c->d_leaf_aabb.release(); c->d_bounds.release();
     c->d_hist.release(); c->d_keys[0].release(); c->d_keys[1].release(); c->d_vals[0].release(); c->d_vals[1].release();
     c->d_left.release(); c->d_right.release(); c->d_parent.release(); c->d_flags.release(); c->d_prim_obj.release();
-    c->d_prim_mat.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_light_slot.release(); c->d_light_type.release(); c->d_obj_light.release(); c->d_light_area.release();
+    c->d_prim_mat.release(); c->d_giant.release(); c->d_lbvh_info.release(); c->d_tile_prefix.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_light_slot.release(); c->d_light_type.release(); c->d_obj_light.release(); c->d_light_area.release();
     c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
     for (int k = 0; k < RT_MAX_SETS; ++k) { c->qs[k].release(); if (c->qs[k].ev_acc) cudaEventDestroy(c->qs[k].ev_acc); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -90,6 +92,7 @@ extern "C" void rt_destroy(rt_ctx *c) {
     c->d_counters.release(); c->d_tile_list.release(); c->d_tile_cnt.release(); c->d_tile_bad.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
     c->d_partials.release(); c->d_rays.release();
     for (auto e : c->ev_pool) cudaEventDestroy(e);
+    for (int k = 0; k < 2; ++k) if (c->ev_count[k]) cudaEventDestroy(c->ev_count[k]);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -243,8 +246,10 @@ static int upload_to_device(rt_ctx *ctx) {
     CU(ctx->d_left.alloc(nn)); CU(ctx->d_right.alloc(nn)); CU(ctx->d_parent.alloc(2 * nn)); CU(ctx->d_flags.alloc(nn));
     CU(ctx->d_node_aabb.alloc(6 * nn)); CU(ctx->d_leaf_aabb.alloc(6 * nn));
     CU(ctx->d_nodes.alloc(nn)); CU(ctx->d_nodes_s.alloc(nn)); CU(ctx->d_primA.alloc(nn)); CU(ctx->d_primB.alloc(nn)); CU(ctx->d_primC.alloc(nn));
-    CU(ctx->d_prim_obj.alloc(nn)); CU(ctx->d_prim_mat.alloc(nn));
+    CU(ctx->d_prim_obj.alloc(nn)); CU(ctx->d_prim_mat.alloc(nn)); CU(ctx->d_giant.alloc(nn)); CU(ctx->d_lbvh_info.alloc(RT_LBVH_INFO_WORDS));
     LbvhBuffers &lb = ctx->lb;
+    lb.giant = ctx->d_giant.p; lb.info = ctx->d_lbvh_info.p;
+    lb.cam = make_float4(d.camera.lookfrom[0], d.camera.lookfrom[1], d.camera.lookfrom[2], 0.5f * fabsf(d.camera.aperture));
     lb.n = n; lb.objects = ctx->d_objects.p; lb.xforms = ctx->d_xforms.p; lb.obj_bmin = ctx->d_obmin.p; lb.obj_bmax = ctx->d_obmax.p;
     lb.bounds = ctx->d_bounds.p; lb.keys[0] = ctx->d_keys[0].p; lb.keys[1] = ctx->d_keys[1].p; lb.vals[0] = ctx->d_vals[0].p;
     lb.vals[1] = ctx->d_vals[1].p; lb.hist = ctx->d_hist.p; lb.left = ctx->d_left.p; lb.right = ctx->d_right.p;
@@ -255,8 +260,18 @@ static int upload_to_device(rt_ctx *ctx) {
     lbvh_build(ctx->cfg, lb);
     CU(cudaEventRecord(ctx->ev1, s));
     CU(cudaGetLastError());
+    int info[RT_LBVH_INFO_WORDS] = {};
+    CU(cudaMemcpyAsync(info, ctx->d_lbvh_info.p, sizeof info, cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));       // the host vectors above go out of scope
     float ms = 0; cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1); ctx->stats.ms_build = ms;
+    ctx->bvh_depth = info[2];
+    // the traversal stacks hold one entry per level at most (rt_traverse.cuh, k_tile_lists): a deeper tree (tens of thousands of
+    // objects sharing one Morton cell) would drop subtrees silently, so the upload fails instead
+    if (info[2] > RT_TRAV_STACK) {
+        ctx->have_scene = false;
+        return rt_fail(ctx, RT_ERR_INVALID, "scene: LBVH depth " + std::to_string(info[2]) + " exceeds the traversal stack (" + std::to_string(RT_TRAV_STACK) +
+                                            " levels): too many objects share one Morton cell");
+    }
 
     // sampled lights for RT_RENDER_NEE: emissive spheres / rects / cylinders / triangles in scene-file order (oracle/orc_nee.c)
     {
@@ -291,7 +306,9 @@ static int upload_to_device(rt_ctx *ctx) {
 
     // device scene header
     DScene &ds = ctx->ds;
-    ds.n_prims = n; ds.n_nodes = n >= 2 ? n - 1 : 1;
+    ds.n_prims = n; ds.n_tree = info[0]; ds.n_giants = info[1]; ds.n_nodes = ds.n_tree >= 2 ? ds.n_tree - 1 : 1;
+    for (int g = 0; g < RT_MAX_GIANTS; ++g) ds.giant_code[g] = g < ds.n_giants ? info[4 + g] : 0;
+    ds.leaf_aabb = ctx->d_leaf_aabb.p;
     ds.width = d.width; ds.height = d.height; ds.max_depth = d.max_depth; ds.sampling = d.sampling; ds.bg_mode = d.background_mode;
     ds.defocus = (d.sampling == RT_SAMPLING_REFERENCE_CPU && d.camera.aperture > 0.0f) ? 1 : 0;
     ds.background = make_float3(d.background[0], d.background[1], d.background[2]);
@@ -303,10 +320,8 @@ static int upload_to_device(rt_ctx *ctx) {
     // extend-kernel configuration: stage the whole BVH in shared memory when it leaves room for >= 2 CTAs per SM
     const size_t bvh_bytes = sizeof(BvhNodeS) * (size_t)ds.n_nodes;
     ctx->cfg.bvh_smem_bytes = 0;
-    if (bvh_bytes + RT_SSTACK_BYTES <= ctx->smem_optin && bvh_bytes + RT_SSTACK_BYTES <= 112 * 1024) {      // two CTAs per SM: tree + stack each
-        if (extend_configure_smem(bvh_bytes) == cudaSuccess) ctx->cfg.bvh_smem_bytes = bvh_bytes;
-        else cudaGetLastError();
-    }
+    if (bvh_bytes + RT_SSTACK_BYTES <= ctx->smem_optin && bvh_bytes + RT_SSTACK_BYTES <= 112 * 1024)      // two CTAs per SM: tree + stack each
+        ctx->cfg.bvh_smem_bytes = bvh_bytes;
     int per_sm = extend_max_blocks_per_sm(ctx->cfg.bvh_smem_bytes);
     if (per_sm < 1) { ctx->cfg.bvh_smem_bytes = 0; per_sm = extend_max_blocks_per_sm(0); }
     ctx->cfg.extend_blocks_per_sm = per_sm < 1 ? 1 : per_sm;
@@ -531,8 +546,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     if (count) CU(cudaMemsetAsync(ctx->d_counters.p, 0, sizeof(unsigned long long) * CTR_COUNT, s));
     long long passes = 0;
     float ms_stage[5] = {0, 0, 0, 0, 0};
-    cudaEvent_t evs[2] = {nullptr, nullptr};
-    if (count) { cudaEventCreate(&evs[0]); cudaEventCreate(&evs[1]); }
+    cudaEvent_t *evs = ctx->ev_count;       // COUNT_EVENTS: one synchronising event pair per stage launch (owned by the context)
     if (time_stages) {          // event pairs are recorded without synchronising and resolved in rt_download
         const size_t n_passes = (size_t)((spp + s_pass - 1) / s_pass);
         const size_t need = ctx->pending.size() + n_passes * (2 + 3 * (size_t)ds.max_depth);
@@ -609,7 +623,6 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         st.n_tri_tests += c[CTR_TRI]; st.n_boxprim_tests += c[CTR_BOXPRIM]; st.n_shade += c[CTR_SHADE];
         st.n_generate += (long long)spp * np; st.n_node_visits += c[CTR_NODE_VISITS];
         st.ms_generate += ms_stage[0]; st.ms_extend += ms_stage[1]; st.ms_shade += ms_stage[2]; st.ms_accumulate += ms_stage[3]; st.ms_shadow += ms_stage[4];
-        cudaEventDestroy(evs[0]); cudaEventDestroy(evs[1]);
         if (c[CTR_STACK_OVERFLOW]) return rt_fail(ctx, RT_ERR_INVALID, "traversal stack overflow (BVH deeper than RT_TRAV_STACK)");
     }
     return RT_OK;
@@ -724,12 +737,22 @@ extern "C" int rt_bvh_download(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_s
         CU(cudaMemcpy(b, ctx->d_bounds.p, sizeof b, cudaMemcpyDeviceToHost));
         for (int k = 0; k < 6; ++k) { unsigned u = b[k]; u ^= (u >> 31) ? 0x80000000u : 0xffffffffu; memcpy(&scene_aabb[k], &u, 4); }
     }
-    if (n >= 2) {
-        if (left) CU(cudaMemcpy(left, ctx->d_left.p, sizeof(int) * (n - 1), cudaMemcpyDeviceToHost));
-        if (right) CU(cudaMemcpy(right, ctx->d_right.p, sizeof(int) * (n - 1), cudaMemcpyDeviceToHost));
-        if (parent) CU(cudaMemcpy(parent, ctx->d_parent.p, sizeof(int) * (2 * n - 1), cudaMemcpyDeviceToHost));
-        if (node_aabb) CU(cudaMemcpy(node_aabb, ctx->d_node_aabb.p, sizeof(float) * 6 * (n - 1), cudaMemcpyDeviceToHost));
+    const int nt = ctx->ds.n_tree;      // leaves of the tree; the giants occupy the sorted slots behind them
+    if (nt >= 2) {
+        if (left) CU(cudaMemcpy(left, ctx->d_left.p, sizeof(int) * (nt - 1), cudaMemcpyDeviceToHost));
+        if (right) CU(cudaMemcpy(right, ctx->d_right.p, sizeof(int) * (nt - 1), cudaMemcpyDeviceToHost));
+        if (parent) CU(cudaMemcpy(parent, ctx->d_parent.p, sizeof(int) * (2 * nt - 1), cudaMemcpyDeviceToHost));
+        if (node_aabb) CU(cudaMemcpy(node_aabb, ctx->d_node_aabb.p, sizeof(float) * 6 * (nt - 1), cudaMemcpyDeviceToHost));
     } else if (parent) parent[0] = -1;
+    return RT_OK;
+}
+
+extern "C" int rt_bvh_info(rt_ctx *ctx, int32_t *n_tree, int32_t *n_giants, int32_t *depth) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "rt_bvh_info: no scene uploaded");
+    if (n_tree) *n_tree = ctx->ds.n_tree;
+    if (n_giants) *n_giants = ctx->ds.n_giants;
+    if (depth) *depth = ctx->bvh_depth;
     return RT_OK;
 }
 

@@ -63,7 +63,9 @@ struct rt_ctx {
     // LBVH
     LbvhBuffers lb{};
     DevBuf<float> d_obmin, d_obmax, d_node_aabb, d_leaf_aabb; DevBuf<unsigned> d_bounds, d_hist;
-    DevBuf<unsigned long long> d_keys[2]; DevBuf<int> d_vals[2], d_left, d_right, d_parent, d_flags, d_prim_obj, d_prim_mat;
+    DevBuf<unsigned long long> d_keys[2]; DevBuf<int> d_vals[2], d_left, d_right, d_parent, d_flags, d_prim_obj, d_prim_mat, d_lbvh_info;
+    DevBuf<unsigned char> d_giant;
+    int bvh_depth = 0;
     DevBuf<BvhNode> d_nodes; DevBuf<BvhNodeS> d_nodes_s; DevBuf<float4> d_primA, d_primB, d_primC;
     // sampled lights (next-event estimation)
     DevBuf<int> d_light_slot, d_light_type, d_obj_light; DevBuf<float> d_light_area;
@@ -78,7 +80,7 @@ struct rt_ctx {
     DevBuf<float> d_accum; DevBuf<unsigned char> d_rgb8; DevBuf<float> d_aov; DevBuf<const float *> d_partials;
     // stats
     rt_stats stats{};
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_count[2] = {nullptr, nullptr};
     std::vector<cudaEvent_t> ev_pool;   // RT_RENDER_TIME_STAGES: (start, stop) pairs, resolved in rt_download
     std::vector<int> pending;           // stage id per recorded pair
     bool accum_valid = false;

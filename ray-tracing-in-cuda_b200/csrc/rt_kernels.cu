@@ -18,6 +18,7 @@
 #include "rt_kernels.h"
 #include "rt_traverse.cuh"
 #include <cstdlib>
+#include <mutex>
 
 __device__ __forceinline__ unsigned lanemask_lt() { unsigned m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
@@ -178,7 +179,11 @@ __global__ void __launch_bounds__(128) k_tile_lists(DScene sc, int *__restrict__
     int sp = 0, n = 0;
     bool bad = false;
     int *out = list + (size_t)t * RT_TILE_K;
-    if (sc.n_prims > 0) stack[sp++] = 0;
+    for (int g = 0; g < sc.n_giants; ++g) {       // the giants are not in the tree: their padded boxes sit in the last leaf slots
+        const float *bx = sc.leaf_aabb + 6 * (size_t)(sc.n_tree + g);
+        if (beam_box(ol, oh, dl, dh, v3(bx[0], bx[1], bx[2]), v3(bx[3], bx[4], bx[5]))) out[n++] = sc.giant_code[g];
+    }
+    if (sc.n_tree > 0) stack[sp++] = 0;
     while (sp > 0 && !bad) {
         const BvhNode nd = sc.nodes[stack[--sp]];
 #pragma unroll
@@ -750,20 +755,29 @@ void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bo
     bump(c);
 }
 
-// smem_bytes: size of the staged tree; the kernel's shared-memory traversal stack comes on top
-cudaError_t extend_configure_smem(size_t smem_bytes) {
-    cudaError_t e = cudaSuccess;
+// The dynamic shared-memory limit is a property of the kernel on a device, shared by every context (and host thread) that uses
+// the device: it is raised ONCE per device to the opt-in maximum for every k_extend / k_shade instance, never to one scene's tree
+// size (a second context uploading a smaller tree must not lower the limit under the first one's launches).
+static std::once_flag g_smem_once[RT_MAX_DEVICES];
+static cudaError_t g_smem_err[RT_MAX_DEVICES];
+cudaError_t kernels_configure_device(int dev, size_t smem_optin) {
+    if (dev < 0 || dev >= RT_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::call_once(g_smem_once[dev], [&] {
+        cudaError_t e = cudaSuccess;
 #define SET(K, B) if (e == cudaSuccess) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(B))
-    const size_t tot = smem_bytes + RT_SSTACK_BYTES;
-    SET((k_extend<true, false, false>), tot); SET((k_extend<true, true, false>), tot); SET((k_extend<true, false, true>), tot);
-    SET((k_extend<true, true, true>), tot);
-    SET((k_extend<true, false, false, RT_OBJ_SPHERE>), tot); SET((k_extend<true, false, true, RT_OBJ_SPHERE>), tot);
-    if (RT_SSTACK_BYTES > 48 * 1024) {
-        SET((k_extend<false, false, false>), RT_SSTACK_BYTES); SET((k_extend<false, true, false>), RT_SSTACK_BYTES);
-        SET((k_extend<false, false, true>), RT_SSTACK_BYTES); SET((k_extend<false, true, true>), RT_SSTACK_BYTES);
-    }
+        SET((k_extend<true, false, false>), smem_optin); SET((k_extend<true, true, false>), smem_optin); SET((k_extend<true, false, true>), smem_optin);
+        SET((k_extend<true, true, true>), smem_optin);
+        SET((k_extend<true, false, false, RT_OBJ_SPHERE>), smem_optin); SET((k_extend<true, false, true, RT_OBJ_SPHERE>), smem_optin);
+        SET((k_extend<false, false, false>), smem_optin); SET((k_extend<false, true, false>), smem_optin);
+        SET((k_extend<false, false, true>), smem_optin); SET((k_extend<false, true, true>), smem_optin);
+        SET((k_shade<false, false, false>), sizeof(ShadeSmem)); SET((k_shade<true, false, false>), sizeof(ShadeSmem));
+        SET((k_shade<false, true, false>), sizeof(ShadeSmem)); SET((k_shade<true, true, false>), sizeof(ShadeSmem));
+        SET((k_shade<false, false, true>), sizeof(ShadeSmem)); SET((k_shade<true, false, true>), sizeof(ShadeSmem));
+        SET((k_shade<false, true, true>), sizeof(ShadeSmem)); SET((k_shade<true, true, true>), sizeof(ShadeSmem));
 #undef SET
-    return e;
+        g_smem_err[dev] = e;
+    });
+    return g_smem_err[dev];
 }
 
 int extend_max_blocks_per_sm(size_t smem_bytes) {
@@ -775,20 +789,6 @@ int extend_max_blocks_per_sm(size_t smem_bytes) {
 
 void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
                   bool last_bounce, bool count, bool sort, bool nee) {
-    static bool configured_dev[64] = {};         // the attribute is per device
-    int dev = 0; cudaGetDevice(&dev);
-    bool &configured = configured_dev[dev & 63];
-    if (!configured) {
-        cudaFuncSetAttribute(k_shade<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        cudaFuncSetAttribute(k_shade<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ShadeSmem));
-        configured = true;
-    }
     const int grid = persistent_grid(c, RT_SH_CTAS_PER_SM);
 #define RT_SHADE_ARGS <<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort)
 #define RT_SHADE_CAM(C_, N_) { if (bounce == 0) k_shade<C_, N_, true> RT_SHADE_ARGS; else k_shade<C_, N_, false> RT_SHADE_ARGS; }

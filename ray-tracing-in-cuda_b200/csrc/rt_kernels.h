@@ -26,11 +26,13 @@ void launch_sum_ordered(const LaunchCfg &c, float *accum, const float *const *pa
 void launch_tonemap(const LaunchCfg &c, const float *accum, unsigned char *rgb8, int W, int H, int spp, int gamma);
 void launch_aov(const LaunchCfg &c, const DScene &sc, float *out);
 int extend_max_blocks_per_sm(size_t smem_bytes);
-cudaError_t extend_configure_smem(size_t smem_bytes);
+#define RT_MAX_DEVICES 64
+cudaError_t kernels_configure_device(int dev, size_t smem_optin);   // once per device: dynamic shared-memory limits of every kernel instance
 
 // ---- LBVH build (rt_lbvh.cu) ----
 struct DObject { int type, material, xform, pad; float p[12]; };   // = rt_object_desc
 
+#define RT_LBVH_INFO_WORDS (4 + RT_MAX_GIANTS)
 struct LbvhBuffers {                // all device pointers, sized for n objects
     int n;
     const DObject *objects;
@@ -43,6 +45,10 @@ struct LbvhBuffers {                // all device pointers, sized for n objects
     int *left, *right, *parent;     // Karras topology (n-1, n-1, 2n-1)
     int *flags;                     // refit arrival counters (n-1)
     float *node_aabb, *leaf_aabb;   // 6 floats per internal node / per sorted leaf
+    unsigned char *giant;           // per object: kept out of the tree (k_giants_mark)
+    int *info;                      // RT_LBVH_INFO_WORDS ints: [0] leaves of the tree, [1] giants, [2] tree depth, [3] giant candidates,
+                                    // [4 ..] leaf codes of the giants
+    float4 cam;                     // camera origin + lens radius (padding of a giant sphere's box, read by the tile lists only)
     // outputs consumed by traversal
     BvhNode *nodes;
     BvhNodeS *nodes_s;

@@ -63,27 +63,57 @@ __device__ void object_aabb(const DObject &ob, const float4 *xforms, float bmin[
     }
 }
 
-// step 1: boxes + scene / centroid bounds (warp-reduced, then one atomic per warp per word)
+// min/max of six values per thread over the warp, then one atomic per warp and word into bounds[base .. base + 5]
+__device__ __forceinline__ void warp_bounds(float v[6], unsigned *bounds, int base) {
+    for (int k = 0; k < 6; ++k) {
+        const bool is_min = k < 3;
+        float x = v[k];
+        for (int o = 16; o > 0; o >>= 1) { float y = __shfl_xor_sync(0xffffffffu, x, o); x = is_min ? fminf(x, y) : fmaxf(x, y); }
+        if ((threadIdx.x & 31) == 0) { if (is_min) atomicMin(&bounds[base + k], f2ord(x)); else atomicMax(&bounds[base + k], f2ord(x)); }
+    }
+}
+
+// step 1: object boxes + scene bounds
 __global__ void __launch_bounds__(256) k_obj_aabb(int n, const DObject *__restrict__ objects, const float4 *__restrict__ xforms,
                                                   float *__restrict__ obmin, float *__restrict__ obmax, unsigned *bounds) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    float v[12];
-    for (int k = 0; k < 12; ++k) v[k] = (k % 6) < 3 ? INFINITY : -INFINITY;
+    float v[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
     if (i < n) {
         float bmin[3], bmax[3];
         object_aabb(objects[i], xforms, bmin, bmax);
-        for (int k = 0; k < 3; ++k) {
-            obmin[3 * i + k] = bmin[k]; obmax[3 * i + k] = bmax[k];
-            const float c = 0.5f * (bmin[k] + bmax[k]);
-            v[k] = bmin[k]; v[3 + k] = bmax[k]; v[6 + k] = c; v[9 + k] = c;
-        }
+        for (int k = 0; k < 3; ++k) { obmin[3 * i + k] = bmin[k]; obmax[3 * i + k] = bmax[k]; v[k] = bmin[k]; v[3 + k] = bmax[k]; }
     }
-    for (int k = 0; k < 12; ++k) {
-        const bool is_min = (k % 6) < 3;
-        float x = v[k];
-        for (int o = 16; o > 0; o >>= 1) { float y = __shfl_xor_sync(0xffffffffu, x, o); x = is_min ? fminf(x, y) : fmaxf(x, y); }
-        if ((threadIdx.x & 31) == 0) { if (is_min) atomicMin(&bounds[k], f2ord(x)); else atomicMax(&bounds[k], f2ord(x)); }
-    }
+    warp_bounds(v, bounds, 0);
+}
+
+// step 1b: giants — objects whose largest extent exceeds a quarter of the scene's (the r = 1000 ground sphere of the RTIOW scene,
+// the 200 x 200 rects of blue2.json).  In the tree, every box on such an object's ancestor chain would cover the whole scene and
+// prune nothing; they stay out of it (key 2^63: the last leaf slots, in scene-file order) and the traversal tests them first.
+// info[3] counts the candidates; more than RT_MAX_GIANTS of them (a scene made of large pieces) and none is taken out.
+__device__ __forceinline__ float scene_extent(const unsigned *bounds) {
+    return fmaxf(ord2f(bounds[3]) - ord2f(bounds[0]), fmaxf(ord2f(bounds[4]) - ord2f(bounds[1]), ord2f(bounds[5]) - ord2f(bounds[2])));
+}
+__device__ __forceinline__ float object_extent(const float *obmin, const float *obmax, int i) {
+    return fmaxf(obmax[3 * i] - obmin[3 * i], fmaxf(obmax[3 * i + 1] - obmin[3 * i + 1], obmax[3 * i + 2] - obmin[3 * i + 2]));
+}
+__global__ void __launch_bounds__(256) k_giants_mark(int n, const float *__restrict__ obmin, const float *__restrict__ obmax,
+                                                     const unsigned *__restrict__ bounds, unsigned char *__restrict__ giant, int *info) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool g = false;
+    if (i < n) { g = object_extent(obmin, obmax, i) > 0.25f * scene_extent(bounds); giant[i] = g ? 1 : 0; }
+    const unsigned m = __ballot_sync(0xffffffffu, g);
+    if (m && (threadIdx.x & 31) == 0) atomicAdd(&info[3], __popc(m));
+}
+// step 1c: centroid bounds of the objects that go into the tree; thread 0 publishes n_tree / n_giants
+__global__ void __launch_bounds__(256) k_centroid_bounds(int n, const float *__restrict__ obmin, const float *__restrict__ obmax,
+                                                         const unsigned char *__restrict__ giant, unsigned *bounds, int *info) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ng = info[3] > RT_MAX_GIANTS ? 0 : info[3];
+    if (i == 0) { info[0] = n - ng; info[1] = ng; }
+    float v[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    if (i < n && !(ng && giant[i]))
+        for (int k = 0; k < 3; ++k) { const float c = 0.5f * (obmin[3 * i + k] + obmax[3 * i + k]); v[k] = c; v[3 + k] = c; }
+    warp_bounds(v, bounds, 6);
 }
 
 __device__ __forceinline__ unsigned long long expand21(unsigned v) {
@@ -102,11 +132,14 @@ __device__ __forceinline__ unsigned quant21(float c, float cmin, float ext) {
     return (unsigned)q;
 }
 
-// step 2: 63-bit Morton code of the box centroid, normalised to the centroid bounds
+// step 2: 63-bit Morton code of the box centroid, normalised to the centroid bounds; giants: 2^63
 __global__ void __launch_bounds__(256) k_morton(int n, const float *__restrict__ obmin, const float *__restrict__ obmax,
-                                                const unsigned *__restrict__ bounds, unsigned long long *keys, int *vals) {
+                                                const unsigned *__restrict__ bounds, const unsigned char *__restrict__ giant,
+                                                const int *__restrict__ info, unsigned long long *keys, int *vals) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    vals[i] = i;
+    if (info[1] && giant[i]) { keys[i] = 0x8000000000000000ull; return; }
     unsigned q[3];
     for (int k = 0; k < 3; ++k) {
         const float cmin = ord2f(bounds[6 + k]), cmax = ord2f(bounds[9 + k]);
@@ -114,7 +147,6 @@ __global__ void __launch_bounds__(256) k_morton(int n, const float *__restrict__
         q[k] = quant21(c, cmin, cmax - cmin);
     }
     keys[i] = expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
-    vals[i] = i;
 }
 
 // ---- step 3: stable LSD radix sort, 8-bit digits, (key, value) pairs ----
@@ -199,19 +231,28 @@ __global__ void __launch_bounds__(256) k_radix_scatter(int n, int n_tiles, const
 }
 
 // step 4: per sorted leaf slot: padded box + the geometry tables the traversal reads (Morton order = memory order)
+// A giant sphere's box is read by the camera-beam tile lists only (k_tile_lists): padded by the float error bound of sphere::hit
+// for rays that start within D of the centre — m^2 + 2 r m <= 2^-18 (D^2 + r^2), oracle/lbvh_host.c:giant_sphere_pad — instead of
+// 2^-10 of its extent (1.95 units for the RTIOW ground sphere, which kept every sky tile of that camera non-empty).
 __global__ void __launch_bounds__(256) k_leaf_setup(int n, const int *__restrict__ sorted, const DObject *__restrict__ objects,
                                                     const float *__restrict__ obmin, const float *__restrict__ obmax,
-                                                    const unsigned *__restrict__ bounds, float *__restrict__ leaf_aabb,
+                                                    const unsigned *__restrict__ bounds, const int *__restrict__ info, float4 cam,
+                                                    float *__restrict__ leaf_aabb,
                                                     float4 *primA, float4 *primB, float4 *primC, int *prim_obj, int *prim_mat) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     const int i = sorted[j];
-    const float sext = fmaxf(ord2f(bounds[3]) - ord2f(bounds[0]), fmaxf(ord2f(bounds[4]) - ord2f(bounds[1]), ord2f(bounds[5]) - ord2f(bounds[2])));
-    const float pad_abs = sext * 9.5367431640625e-07f;
-    const float e = fmaxf(obmax[3 * i] - obmin[3 * i], fmaxf(obmax[3 * i + 1] - obmin[3 * i + 1], obmax[3 * i + 2] - obmin[3 * i + 2]));
-    const float pad = __fmaf_rn(e, 9.765625e-04f, pad_abs);
-    for (int k = 0; k < 3; ++k) { leaf_aabb[6 * j + k] = obmin[3 * i + k] - pad; leaf_aabb[6 * j + 3 + k] = obmax[3 * i + k] + pad; }
+    const float pad_abs = scene_extent(bounds) * 9.5367431640625e-07f;
+    const float e = object_extent(obmin, obmax, i);
+    float pad = __fmaf_rn(e, 9.765625e-04f, pad_abs);
     const DObject ob = objects[i];
+    if (j >= info[0] && ob.type == RT_OBJ_SPHERE) {
+        const float dx = cam.x - ob.p[0], dy = cam.y - ob.p[1], dz = cam.z - ob.p[2];
+        const float D = sqrtf(dx * dx + dy * dy + dz * dz) + cam.w, r = fabsf(ob.p[3]);
+        const float x = 3.814697265625e-06f * (D * D + r * r);
+        pad = x / (sqrtf(r * r + x) + r) + pad_abs;
+    }
+    for (int k = 0; k < 3; ++k) { leaf_aabb[6 * j + k] = obmin[3 * i + k] - pad; leaf_aabb[6 * j + 3 + k] = obmax[3 * i + k] + pad; }
     const float *p = ob.p;
     float4 A = make_float4(0, 0, 0, 0), B = A, C = A;
     switch (ob.type) {
@@ -237,9 +278,10 @@ __device__ __forceinline__ int lb_delta(const unsigned long long *__restrict__ m
     return 64 + __clz(i ^ j);
 }
 
-__global__ void __launch_bounds__(256) k_karras(int n, const unsigned long long *__restrict__ keys, int *__restrict__ left,
+__global__ void __launch_bounds__(256) k_karras(const int *__restrict__ info, const unsigned long long *__restrict__ keys, int *__restrict__ left,
                                                 int *__restrict__ right, int *__restrict__ parent) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = info[0];                      // leaves of the tree (the giants sit behind them in the sorted order)
     if (i >= n - 1) return;
     if (i == 0) parent[0] = -1;
     const int d = lb_delta(keys, n, i, i + 1) - lb_delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
@@ -266,11 +308,18 @@ __global__ void __launch_bounds__(256) k_karras(int n, const unsigned long long 
 }
 
 // step 6: bottom-up refit; the second thread to arrive at a node computes its box (min/max are order-independent)
-__global__ void __launch_bounds__(256) k_refit(int n, const float *__restrict__ leaf_aabb, const int *__restrict__ left,
+__global__ void __launch_bounds__(256) k_refit(int *info, const float *__restrict__ leaf_aabb, const int *__restrict__ left,
                                                const int *__restrict__ right, const int *__restrict__ parent, int *flags,
                                                float *node_aabb) {
     const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
-    if (leaf >= n) return;
+    const int n = info[0];
+    const bool valid = leaf < n && n >= 2;
+    // depth of the tree = the largest number of internal nodes above a leaf: bounds the traversal stack (checked at upload)
+    int depth = 0;
+    if (valid) for (int c = parent[n - 1 + leaf]; c >= 0; c = parent[c]) ++depth;
+    depth = __reduce_max_sync(0xffffffffu, depth);
+    if ((threadIdx.x & 31) == 0 && depth) atomicMax(&info[2], depth);
+    if (!valid) return;
     int cur = parent[n - 1 + leaf];
     while (cur >= 0) {
         __threadfence();
@@ -287,11 +336,15 @@ __global__ void __launch_bounds__(256) k_refit(int n, const float *__restrict__ 
 }
 
 // step 7: pack into 64-byte traversal nodes (both child boxes inline)
-__global__ void __launch_bounds__(256) k_pack(int n, const int *__restrict__ left, const int *__restrict__ right,
+__global__ void __launch_bounds__(256) k_pack(int n_all, int *info, const int *__restrict__ left, const int *__restrict__ right,
                                               const float *__restrict__ node_aabb, const float *__restrict__ leaf_aabb,
                                               const int *__restrict__ sorted, const DObject *__restrict__ objects, BvhNode *nodes,
                                               BvhNodeS *nodes_s) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = info[0];
+    // leaf codes of the giants (slots n .. n_all - 1) for the traversal prologue; depth of a one-leaf tree
+    if (i < info[1]) info[4 + i] = (objects[sorted[n + i]].type << 28) | (n + i);
+    if (i == 0 && n == 1) info[2] = 1;
     const int n_nodes = n >= 2 ? n - 1 : 1;
     if (i >= n_nodes) return;
     int L, R;
@@ -332,9 +385,12 @@ void lbvh_build(const LaunchCfg &c, LbvhBuffers &b) {
     auto bump = [&](int k = 1) { if (c.launches) *c.launches += k; };
     const int g = n > 0 ? (n + 255) / 256 : 1;
     k_bounds_init<<<1, 32, 0, s>>>(b.bounds); bump();
+    cudaMemsetAsync(b.info, 0, sizeof(int) * RT_LBVH_INFO_WORDS, s);
     if (n > 0) {
         k_obj_aabb<<<g, 256, 0, s>>>(n, b.objects, b.xforms, b.obj_bmin, b.obj_bmax, b.bounds); bump();
-        k_morton<<<g, 256, 0, s>>>(n, b.obj_bmin, b.obj_bmax, b.bounds, b.keys[0], b.vals[0]); bump();
+        k_giants_mark<<<g, 256, 0, s>>>(n, b.obj_bmin, b.obj_bmax, b.bounds, b.giant, b.info); bump();
+        k_centroid_bounds<<<g, 256, 0, s>>>(n, b.obj_bmin, b.obj_bmax, b.giant, b.bounds, b.info); bump();
+        k_morton<<<g, 256, 0, s>>>(n, b.obj_bmin, b.obj_bmax, b.bounds, b.giant, b.info, b.keys[0], b.vals[0]); bump();
         const int n_tiles = (n + RS_TILE - 1) / RS_TILE;
         int cur = 0;
         for (int pass = 0; pass < 8; ++pass) {
@@ -345,13 +401,13 @@ void lbvh_build(const LaunchCfg &c, LbvhBuffers &b) {
             cur ^= 1;
         }
         // 8 passes: the sorted data is back in buffer 0
-        k_leaf_setup<<<g, 256, 0, s>>>(n, b.vals[0], b.objects, b.obj_bmin, b.obj_bmax, b.bounds, b.leaf_aabb, b.primA, b.primB,
+        k_leaf_setup<<<g, 256, 0, s>>>(n, b.vals[0], b.objects, b.obj_bmin, b.obj_bmax, b.bounds, b.info, b.cam, b.leaf_aabb, b.primA, b.primB,
                                        b.primC, b.prim_obj, b.prim_mat); bump();
-        if (n >= 2) {
+        if (n >= 2) {           // the tree has n_tree = info[0] <= n leaves: the kernels read it on the device
             cudaMemsetAsync(b.flags, 0, sizeof(int) * (size_t)(n - 1), s);
-            k_karras<<<g, 256, 0, s>>>(n, b.keys[0], b.left, b.right, b.parent); bump();
-            k_refit<<<g, 256, 0, s>>>(n, b.leaf_aabb, b.left, b.right, b.parent, b.flags, b.node_aabb); bump();
+            k_karras<<<g, 256, 0, s>>>(b.info, b.keys[0], b.left, b.right, b.parent); bump();
+            k_refit<<<g, 256, 0, s>>>(b.info, b.leaf_aabb, b.left, b.right, b.parent, b.flags, b.node_aabb); bump();
         }
     }
-    k_pack<<<g, 256, 0, s>>>(n, b.left, b.right, b.node_aabb, b.leaf_aabb, b.vals[0], b.objects, b.nodes, b.nodes_s); bump();
+    k_pack<<<g, 256, 0, s>>>(n, b.info, b.left, b.right, b.node_aabb, b.leaf_aabb, b.vals[0], b.objects, b.nodes, b.nodes_s); bump();
 }

@@ -31,10 +31,14 @@ struct DTexture { int type; int even; int odd; int image; float4 color; };      
 struct DImage { cudaTextureObject_t tex; int width, height; };
 
 #define RT_TILE_K 16
+#define RT_MAX_GIANTS 16        // objects kept out of the tree and tested first by every ray (rt_lbvh.cu:k_giants_mark)
 struct DCamera { float3 origin, llc, horizontal, vertical, u, v, w; float lens_radius; };
 
 struct DScene {
-    int n_prims, n_nodes;
+    int n_prims, n_nodes;                  // all leaf slots; inner nodes of the tree (1 when the tree has fewer than two leaves)
+    int n_tree, n_giants;                  // leaf slots [0, n_tree) form the tree, [n_tree, n_prims) hold the giants
+    int giant_code[RT_MAX_GIANTS];         // their leaf codes (type << 28 | slot)
+    const float *leaf_aabb;                // padded box per leaf slot (tile lists: boxes of the giants)
     int width, height, max_depth, sampling, bg_mode, defocus;
     float3 background;
     DCamera cam;

@@ -98,6 +98,11 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
     best_t = tmax; best_code = -1;
     if (sc.n_prims == 0) return;
     const float a = dot3(d, d), inv_a = 1.0f / a;
+    // giants first (rt_lbvh.cu:k_giants_mark): the few objects that span the scene are not in the tree; testing them up front also
+    // hands the walk a tight best_t from its first node.  The tie rule does not depend on the order of the tests.
+    for (int g = 0; g < sc.n_giants; ++g)
+        if (leaf_visit<COUNT, ONLY>(sc, sc.giant_code[g], o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
+    if (sc.n_tree == 0) return;
     float3 ood = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
     const bool px = !(fabsf(ood.x) <= RT_BOX_OOD_MAX), py = !(fabsf(ood.y) <= RT_BOX_OOD_MAX), pz = !(fabsf(ood.z) <= RT_BOX_OOD_MAX);
     if (px) ood.x = copysignf(RT_BOX_OOD_MAX, d.x);

@@ -152,7 +152,13 @@ class Renderer:
             r["left"].ctypes.data_as(P(C.c_int32)), r["right"].ctypes.data_as(P(C.c_int32)),
             r["parent"].ctypes.data_as(P(C.c_int32)), r["node_aabb"].ctypes.data_as(P(C.c_float)),
             r["leaf_aabb"].ctypes.data_as(P(C.c_float)), r["scene_aabb"].ctypes.data_as(P(C.c_float))), "rt_bvh_download")
-        r["n"] = n
+        nt, ng, depth = C.c_int32(), C.c_int32(), C.c_int32()
+        self._check(self.lib.rt_bvh_info(self.ctx, C.byref(nt), C.byref(ng), C.byref(depth)), "rt_bvh_info")
+        # the tree holds n_tree leaves (n_tree - 1 internal nodes); the giants occupy the last n_giants sorted slots
+        m = max(nt.value - 1, 0)
+        r.update(n=n, n_tree=nt.value, n_giants=ng.value, depth=depth.value, morton=r["morton"][:n], prim=r["prim"][:n],
+                 leaf_aabb=r["leaf_aabb"][:n], left=r["left"][:m], right=r["right"][:m], node_aabb=r["node_aabb"][:m],
+                 parent=r["parent"][:max(2 * nt.value - 1, 0)])
         return r
 
 

@@ -50,6 +50,9 @@ def lib():
         L.orc_atan2f.argtypes = [C.c_float, C.c_float]; L.orc_atan2f.restype = C.c_float
         L.orc_lbvh_build.argtypes = [P(capi.SceneDesc), P(C.c_uint64), P(C.c_int32), P(C.c_int32), P(C.c_int32),
                                      P(C.c_int32), fp, fp, fp]
+        L.orc_lbvh_build_ex.argtypes = [P(capi.SceneDesc), P(C.c_uint64), P(C.c_int32), P(C.c_int32), P(C.c_int32),
+                                        P(C.c_int32), fp, fp, fp, P(C.c_int32)]
+        L.orc_render_bvh.argtypes = [P(capi.SceneDesc), C.c_uint32, C.c_int, C.c_int, fp, C.c_int, C.c_int, P(C.c_int64), P(C.c_int64)]
         L.orc_radix_sort_pairs.argtypes = [P(C.c_uint64), P(C.c_int32), C.c_int]
         L.orc_radix_sort_pairs.restype = None
         _lib = L
@@ -227,6 +230,21 @@ def render_ex(sc, seed=0x2023, spp_begin=0, spp_count=0, threads=None, flags=0):
     return out, nr.value, ns.value
 
 
+COUNTER_NAMES = ("n_box_tests", "n_node_visits", "n_sphere_reject", "n_sphere_accept", "n_rect_tests", "n_cyl_reject", "n_cyl_accept",
+                 "n_tri_tests", "n_boxprim_tests", "max_stack")
+
+
+def render_bvh(sc, seed=0x2023, spp_begin=0, spp_count=0, threads=None, flags=0):
+    """orc_render through the host twin of the device traversal (oracle/orc_trav.c); returns (image, rays, counters dict)."""
+    W, H = sc.desc.width, sc.desc.height
+    out = np.zeros((H, W, 3), np.float32)
+    nr = C.c_int64(0)
+    cnt = (C.c_int64 * 10)()
+    rc = lib().orc_render_bvh(sc.ptr, seed, spp_begin, spp_count, fptr(out), threads or os.cpu_count() or 1, flags, C.byref(nr), cnt)
+    assert rc == 0, rc
+    return out, nr.value, dict(zip(COUNTER_NAMES, [int(x) for x in cnt]))
+
+
 def aov(sc):
     out = np.zeros((sc.desc.height, sc.desc.width, 24), np.float32)
     assert lib().orc_aov(sc.ptr, fptr(out)) == 0
@@ -248,10 +266,21 @@ def lbvh(sc):
              right=np.zeros(m, np.int32), parent=np.zeros(max(2 * n - 1, 1), np.int32), node_aabb=np.zeros((m, 6), np.float32),
              leaf_aabb=np.zeros((max(n, 1), 6), np.float32), scene_aabb=np.zeros(6, np.float32))
     P = C.POINTER
-    lib().orc_lbvh_build(sc.ptr, r["morton"].ctypes.data_as(P(C.c_uint64)), r["prim"].ctypes.data_as(P(C.c_int32)),
-                         r["left"].ctypes.data_as(P(C.c_int32)), r["right"].ctypes.data_as(P(C.c_int32)),
-                         r["parent"].ctypes.data_as(P(C.c_int32)), fptr(r["node_aabb"]), fptr(r["leaf_aabb"]),
-                         fptr(r["scene_aabb"]))
+    info = np.zeros(4, np.int32)
+    lib().orc_lbvh_build_ex(sc.ptr, r["morton"].ctypes.data_as(P(C.c_uint64)), r["prim"].ctypes.data_as(P(C.c_int32)),
+                            r["left"].ctypes.data_as(P(C.c_int32)), r["right"].ctypes.data_as(P(C.c_int32)),
+                            r["parent"].ctypes.data_as(P(C.c_int32)), fptr(r["node_aabb"]), fptr(r["leaf_aabb"]),
+                            fptr(r["scene_aabb"]), info.ctypes.data_as(P(C.c_int32)))
+    return trim_bvh(r, n, int(info[0]), int(info[1]), int(info[2]))
+
+
+def trim_bvh(r, n, n_tree, n_giants, depth):
+    """Keeps the valid part of the LBVH arrays: n_tree leaves form the tree (n_tree - 1 internal nodes), the giants sit in the
+    last n_giants leaf slots; parent = n_tree - 1 internal entries then n_tree leaf entries."""
+    m = max(n_tree - 1, 0)
+    r = dict(r)
+    r.update(n=n, n_tree=n_tree, n_giants=n_giants, depth=depth, morton=r["morton"][:n], prim=r["prim"][:n], leaf_aabb=r["leaf_aabb"][:n],
+             left=r["left"][:m], right=r["right"][:m], node_aabb=r["node_aabb"][:m], parent=r["parent"][:max(2 * n_tree - 1, 0)])
     return r
 
 

@@ -38,11 +38,13 @@ def test_lbvh_bit_exact(rt, name):
     n = got["n"]
     if n == 0:
         return
+    assert (got["n_tree"], got["n_giants"], got["depth"]) == (want["n_tree"], want["n_giants"], want["depth"])
+    assert got["n_giants"] == {"rtiow_486": 1, "sample_scene": 1, "sample_scene_ext": 1, "blue": 2, "blue2": 2}.get(name, 0)
     assert np.array_equal(got["morton"], want["morton"])
     assert np.array_equal(got["prim"], want["prim"])
     assert np.array_equal(got["scene_aabb"], want["scene_aabb"])
     assert np.array_equal(got["leaf_aabb"], want["leaf_aabb"])
-    if n >= 2:
+    if got["n_tree"] >= 2:
         for k in ("left", "right", "parent"):
             assert np.array_equal(got[k], want[k]), k
         assert np.array_equal(got["node_aabb"], want["node_aabb"])
@@ -94,9 +96,10 @@ def test_lbvh_bit_exact_random(rt, n, seed):
     got = rt.bvh()
     want = orc.lbvh(orc.load_scene(sc))
     assert got["n"] == len(sc["object"]["data"])
+    assert (got["n_tree"], got["n_giants"], got["depth"]) == (want["n_tree"], want["n_giants"], want["depth"])
     for k in ("morton", "prim", "leaf_aabb", "scene_aabb"):
         assert np.array_equal(got[k], want[k]), k
-    if got["n"] >= 2:
+    if got["n_tree"] >= 2:
         for k in ("left", "right", "parent", "node_aabb"):
             assert np.array_equal(got[k], want[k]), k
 
@@ -134,6 +137,24 @@ def test_render_matches_oracle_sample_for_sample(rt, name, spp):
     err = np.abs(got - want)
     bad = (err > 1e-5 * spp).any(-1).sum()
     assert bad == 0, f"{bad} pixels differ, max {err.max()}"
+
+
+@pytest.mark.parametrize("name,spp", [("rtiow_486", 3), ("blue2", 4), ("sample_scene_ext", 3), ("dna_000", 2)])
+def test_traversal_counters_match_the_host_twin(rt, name, spp):
+    """The device's event counters (inner-node visits, box tests, leaf tests per primitive type) against a serial count of the
+    same walk (oracle/orc_trav.c: giants first, ordered descent, far child pushed with its entry distance): integer work, exact.
+    Bounce 0 goes through the tree too (RT_RENDER_NO_TILE_LISTS), like every ray of the host twin."""
+    W, H = 96, 54
+    rt.upload_json(scene_path(name))
+    rt.override(width=W, height=H, spp=spp)
+    rt.stats_reset()
+    rt.render(seed=0x51, flags=capi.RT_RENDER_COUNT_EVENTS | capi.RT_RENDER_NO_TILE_LISTS)
+    got, _, st = rt.download()
+    want, nrays, cnt = orc.render_bvh(orc.load_scene(scene_path(name), width=W, height=H, spp=spp), seed=0x51)
+    assert st["rays"] == nrays and np.array_equal(got, want)
+    for k in ("n_node_visits", "n_box_tests", "n_sphere_reject", "n_sphere_accept", "n_rect_tests", "n_cyl_reject", "n_cyl_accept",
+              "n_tri_tests", "n_boxprim_tests"):
+        assert st[k] == cnt[k], (k, st[k], cnt[k])
 
 
 def test_render_options_do_not_change_the_image(rt):

@@ -196,12 +196,14 @@ def test_tonemap_matches_reference_formulas():
 
 
 def test_lbvh_host_invariants():
-    """Host LBVH twin: sorted keys, every leaf reachable exactly once, boxes enclose children."""
+    """Host LBVH twin: sorted keys, every leaf of the tree reachable exactly once, boxes enclose children; the giant (the
+    r = 1000 ground sphere) sits behind the tree's leaves with the key 2^63."""
     sc = orc.load_scene(orc.GOLDEN + "/rtiow_486.json")
     r = orc.lbvh(sc)
     n = sc.desc.n_objects
     assert np.all(np.diff(r["morton"].astype(np.float64)) >= 0) and sorted(r["prim"].tolist()) == list(range(n))
-    seen = np.zeros(n, int)
+    assert r["n_tree"] == n - 1 and r["n_giants"] == 1 and int(r["morton"][-1]) == 1 << 63 and int(r["morton"][-2]) < 1 << 63
+    seen = np.zeros(r["n_tree"], int)
     stack = [0]
     while stack:
         i = stack.pop()
@@ -285,3 +287,20 @@ def test_ball_sampler_bit_layout_against_an_independent_statement():
     assert clear.mean() > 0.99
     agree = np.all(got == want, axis=1)
     assert agree[clear].mean() > 0.999       # an edge trial earlier in a stream shifts that stream only
+
+
+@pytest.mark.parametrize("name", ["sample_scene", "blue", "blue2", "dna_000", "rtiow_486", "sample_scene_ext", "basic_scene"])
+def test_host_twin_of_the_traversal_equals_the_linear_walk(name):
+    """oracle/orc_trav.c walks the host-built LBVH with the device's conservative box arithmetic and visiting order (giants first);
+    it must find what the reference's linear walk (object.cuh:23-37, orc_hit.c) finds on every ray: bit-identical images, equal
+    ray counts.  The same check runs on the device in the -m gpu tests; this one needs no GPU."""
+    sc = orc.load_scene(f"{orc.GOLDEN}/{name}.json", width=64, height=36, spp=3)
+    a, na = orc.render(sc, seed=5)
+    b, nb, cnt = orc.render_bvh(sc, seed=5)
+    assert na == nb and np.array_equal(a, b)
+    tree = orc.lbvh(sc)
+    assert tree["n_tree"] + tree["n_giants"] == sc.desc.n_objects
+    assert cnt["max_stack"] <= max(tree["depth"], 0)
+    if name == "rtiow_486":          # the r = 1000 ground sphere stays out of the tree
+        assert tree["n_giants"] == 1 and sc.desc.objects[int(tree["prim"][-1])].p[3] == 1000.0
+        assert cnt["n_node_visits"] / nb < 10.5
