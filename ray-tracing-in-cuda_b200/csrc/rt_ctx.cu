@@ -307,7 +307,7 @@ static int upload_to_device(rt_ctx *ctx) {
     // device scene header
     DScene &ds = ctx->ds;
     ds.n_prims = n; ds.n_tree = info[0]; ds.n_giants = info[1]; ds.n_nodes = ds.n_tree >= 2 ? ds.n_tree - 1 : 1;
-    for (int g = 0; g < RT_MAX_GIANTS; ++g) ds.giant_code[g] = g < ds.n_giants ? info[4 + g] : 0;
+    ds.giant_code = ctx->d_lbvh_info.p + 4;
     ds.leaf_aabb = ctx->d_leaf_aabb.p;
     ds.width = d.width; ds.height = d.height; ds.max_depth = d.max_depth; ds.sampling = d.sampling; ds.bg_mode = d.background_mode;
     ds.defocus = (d.sampling == RT_SAMPLING_REFERENCE_CPU && d.camera.aperture > 0.0f) ? 1 : 0;

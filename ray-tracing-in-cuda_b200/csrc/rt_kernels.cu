@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(128) k_tile_lists(DScene sc, int *__restrict__
     int *out = list + (size_t)t * RT_TILE_K;
     for (int g = 0; g < sc.n_giants; ++g) {       // the giants are not in the tree: their padded boxes sit in the last leaf slots
         const float *bx = sc.leaf_aabb + 6 * (size_t)(sc.n_tree + g);
-        if (beam_box(ol, oh, dl, dh, v3(bx[0], bx[1], bx[2]), v3(bx[3], bx[4], bx[5]))) out[n++] = sc.giant_code[g];
+        if (beam_box(ol, oh, dl, dh, v3(bx[0], bx[1], bx[2]), v3(bx[3], bx[4], bx[5]))) out[n++] = __ldg(&sc.giant_code[g]);
     }
     if (sc.n_tree > 0) stack[sp++] = 0;
     while (sp > 0 && !bad) {
@@ -222,7 +222,7 @@ template <bool SMEM, bool COUNT, bool SHADOW, int ONLY = -1>
 __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf, int max_batch) {
     const bool fixup = max_batch < 0;
     if (fixup) max_batch = -max_batch;
-    extern __shared__ float4 s_raw[];
+    extern __shared__ float2 s_raw[];
     const int n = SHADOW ? q.shcount[bounce] : q.qcount[bounce];
     if (n == 0) return;
     const int total_warps = gridDim.x * (RT_EXT_BLOCK / 32);
@@ -231,8 +231,8 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
     if ((long long)blockIdx.x * (RT_EXT_BLOCK / 32) * batch >= n) return;
     const char *nodes = reinterpret_cast<const char *>(sc.nodes);
     if (SMEM) {
-        const float4 *src = reinterpret_cast<const float4 *>(sc.nodes_s);
-        for (int i = threadIdx.x; i < sc.n_nodes * (int)(sizeof(BvhNodeS) / 16); i += blockDim.x) s_raw[i] = __ldg(&src[i]);
+        const float2 *src = reinterpret_cast<const float2 *>(sc.nodes_s);
+        for (int i = threadIdx.x; i < sc.n_nodes * (int)(sizeof(BvhNodeS) / 8); i += blockDim.x) s_raw[i] = __ldg(&src[i]);
         __syncthreads();
         nodes = reinterpret_cast<const char *>(s_raw);
     }

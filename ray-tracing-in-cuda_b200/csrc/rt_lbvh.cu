@@ -370,10 +370,13 @@ __global__ void __launch_bounds__(256) k_pack(int n_all, int *info, const int *_
     nd.d = make_int4(lc, rc, 0, 0);
     nodes[i] = nd;
     BvhNodeS ns;
-    ns.lx = make_float4(lb[0], lb[3], lb[3], lb[0]); ns.ly = make_float4(lb[1], lb[4], lb[4], lb[1]); ns.lz = make_float4(lb[2], lb[5], lb[5], lb[2]);
-    ns.rx = make_float4(rb[0], rb[3], rb[3], rb[0]); ns.ry = make_float4(rb[1], rb[4], rb[4], rb[1]); ns.rz = make_float4(rb[2], rb[5], rb[5], rb[2]);
+    for (int k = 0; k < 3; ++k) {
+        float2 *l = k == 0 ? ns.lx : k == 1 ? ns.ly : ns.lz, *r = k == 0 ? ns.rx : k == 1 ? ns.ry : ns.rz;
+        l[0] = make_float2(lb[k], lb[3 + k]); l[1] = make_float2(lb[3 + k], lb[k]);
+        r[0] = make_float2(rb[k], rb[3 + k]); r[1] = make_float2(rb[3 + k], rb[k]);
+    }
     // inner children as byte offsets into the node array (the traversal adds them to a shared-memory address)
-    ns.link = make_int4(lc >= 0 ? lc << 7 : lc, rc >= 0 ? rc << 7 : rc, 0, 0); ns.pad = make_int4(0, 0, 0, 0);
+    ns.link = make_int2(lc >= 0 ? lc * (int)sizeof(BvhNodeS) : lc, rc >= 0 ? rc * (int)sizeof(BvhNodeS) : rc);
     nodes_s[i] = ns;
 }
 

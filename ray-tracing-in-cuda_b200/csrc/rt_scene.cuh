@@ -14,15 +14,19 @@ struct __align__(16) BvhNode {   // 64 B: both child boxes + child links; one no
     float4 c;   // r.min.z r.max.x r.max.y r.max.z
     int4 d;     // left, right, unused, unused.   child >= 0: internal node; child < 0: leaf, ~child = type<<28 | slot
 };
-// The same node laid out for the extend stage's sign-ordered slab test (128 B).  Per box and axis the two planes are stored
+// The same node laid out for the extend stage's sign-ordered slab test.  Per box and axis the two planes are stored
 // as (lo, hi, hi, lo): an 8-byte load at offset 0 yields (near, far) for a ray travelling in +axis, at offset 8 for -axis,
 // so the traversal needs no per-plane min/max or select — the ray's direction signs are folded into the load address.
-struct __align__(16) BvhNodeS {
-    float4 lx, ly, lz;   // left child box
-    float4 rx, ry, rz;   // right child box
-    int4 link;           // left, right (same encoding as BvhNode::d), unused, unused
-    int4 pad;
+// 104 bytes = 13 x 8: an ODD number of 8-byte bank pairs, so the same field of nodes i and j lies in the same shared-memory
+// bank pair only when i = j (mod 16).  With the 128-byte stride this struct had first, every node's field sat in the SAME bank
+// pair and the 8-byte loads of a warp whose lanes visit different nodes were fully serialised: ncu (r02a) had 51-61 % of the
+// shared-memory wavefronts of k_extend at bounces 2-3 as bank conflicts and the shared-memory pipe at 77-82 % of its peak.
+struct __align__(8) BvhNodeS {
+    float2 lx[2], ly[2], lz[2];   // left child box: per axis (lo, hi), (hi, lo)
+    float2 rx[2], ry[2], rz[2];   // right child box
+    int2 link;                    // left, right (leaf: ~code as BvhNode::d; inner: byte offset of the node = index * 104)
 };
+static_assert(sizeof(BvhNodeS) == 104, "BvhNodeS must be 13 x 8 bytes");
 #define RT_LEAF_SLOT_MASK 0x0fffffff
 #define RT_LEAF_NONE (~(7 << 28))   // a leaf code that is never hit (its box is empty)
 
@@ -37,7 +41,8 @@ struct DCamera { float3 origin, llc, horizontal, vertical, u, v, w; float lens_r
 struct DScene {
     int n_prims, n_nodes;                  // all leaf slots; inner nodes of the tree (1 when the tree has fewer than two leaves)
     int n_tree, n_giants;                  // leaf slots [0, n_tree) form the tree, [n_tree, n_prims) hold the giants
-    int giant_code[RT_MAX_GIANTS];         // their leaf codes (type << 28 | slot)
+    const int *giant_code;                 // their leaf codes (type << 28 | slot), device array (a by-value array indexed at run time
+                                           // would force a local-memory copy of this whole struct in every kernel)
     const float *leaf_aabb;                // padded box per leaf slot (tile lists: boxes of the giants)
     int width, height, max_depth, sampling, bg_mode, defocus;
     float3 background;

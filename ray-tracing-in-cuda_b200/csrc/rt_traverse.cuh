@@ -9,7 +9,7 @@
 // Leaf tests are the exact reference arithmetic (rt_scene.cuh).
 //
 // Two node layouts, one algorithm:
-//   SIGNED = true   BvhNodeS (128 B): plane pairs stored (lo, hi, hi, lo) per box and axis; the ray's direction signs pick
+//   SIGNED = true   BvhNodeS (104 B): plane pairs stored (lo, hi, hi, lo) per box and axis; the ray's direction signs pick
 //                   the 8-byte half that reads (near, far), so a box costs 6 FFMA + 2 three-input min/max + 2 min/max.
 //                   Used when the whole tree is staged in shared memory.
 //   SIGNED = false  BvhNode (64 B): both boxes in three float4; near/far planes picked by the sign predicates.  Half the bytes per visit —
@@ -37,7 +37,6 @@ __device__ __forceinline__ void count_leaf(TravCounters &c, int code, bool hit) 
 #define RT_BOX_OOD_MAX 1e18f                 // |1/d| clamp: beyond it the ray counts as parallel to the slab pair
 #define RT_BOX_PAR 1e10f                     // absolute margin of a parallel axis (t units; larger than any scene distance)
 #define RT_TRAV_DONE ((int)0x80000000)
-#define RT_NODE_S_SHIFT 7                    // BvhNodeS links of inner children are byte offsets (index << 7)
 
 // One exact leaf test with the closest-hit bookkeeping of the linear walk (object.cuh:23-37): a root equal to the current
 // best replaces it when the object comes later in the scene file.  Returns true when the hit was taken.
@@ -101,7 +100,7 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
     // giants first (rt_lbvh.cu:k_giants_mark): the few objects that span the scene are not in the tree; testing them up front also
     // hands the walk a tight best_t from its first node.  The tie rule does not depend on the order of the tests.
     for (int g = 0; g < sc.n_giants; ++g)
-        if (leaf_visit<COUNT, ONLY>(sc, sc.giant_code[g], o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
+        if (leaf_visit<COUNT, ONLY>(sc, __ldg(&sc.giant_code[g]), o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
     if (sc.n_tree == 0) return;
     float3 ood = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
     const bool px = !(fabsf(ood.x) <= RT_BOX_OOD_MAX), py = !(fabsf(ood.y) <= RT_BOX_OOD_MAX), pz = !(fabsf(ood.z) <= RT_BOX_OOD_MAX);
