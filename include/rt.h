@@ -47,7 +47,13 @@ enum { RT_BG_CONSTANT = 0, RT_BG_SKY_GRADIENT = 1 };
  *                 lambertian = n + random_in_unit_sphere (material.cuh:42); no lens jitter (camera.cuh:33-34)
  *  REFERENCE_CPU: uniforms in [0,1); ball sampled over [-1,1)^3 (cmake-cpu-version/vec3.h:121-129);
  *                 lambertian = n + random_unit_vector (material.h:27); thin-lens defocus (camera.h:32-39) */
-enum { RT_SAMPLING_REFERENCE_GPU = 0, RT_SAMPLING_REFERENCE_CPU = 1 };
+enum { RT_SAMPLING_REFERENCE_GPU = 0, RT_SAMPLING_REFERENCE_CPU = 1,
+       /* flag, OR-ed to the family: draw the same distributions (uniform ball / octant ball, unit sphere, lens disk) DIRECTLY from
+        * one Philox block instead of through the reference's rejection loops (vec3.cuh:133-141, vec3.h:121-129,157-165).  The
+        * reference is matched statistically only (its generators are XORWOW / mt19937), so both satisfy the converged-render
+        * tolerance; the loops diverge (acceptance pi/6 per trial) and were half the instructions of the shade stage.  The JSON
+        * reader sets it unless the scene says "sampler": "rejection". */
+       RT_SAMPLING_DIRECT = 2 };
 
 typedef struct rt_object_desc {
     int32_t type;       /* RT_OBJ_* */

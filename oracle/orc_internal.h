@@ -46,7 +46,8 @@ typedef struct {
     uint32_t ctr[4];
     uint32_t out[4];
     int idx;
-    int sampling;          /* RT_SAMPLING_* : [0,1) for CPU semantics, (0,1] for GPU semantics */
+    int sampling;          /* family, RT_SAMPLING_REFERENCE_GPU / _CPU : [0,1) for CPU semantics, (0,1] for GPU semantics */
+    int direct;            /* RT_SAMPLING_DIRECT: direct draws instead of the reference's rejection loops */
     const float *replay;   /* known-answer tests: replayed uniforms instead of Philox */
     int replay_n, replay_pos;
     int draws;
@@ -55,6 +56,9 @@ typedef struct {
 void orc_rng_init(orc_rng *r, uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t bounce, int sampling);
 float orc_rng_next(orc_rng *r);
 void orc_rng_block(orc_rng *r, uint32_t out[4]);
+/* direct draws (RT_SAMPLING_DIRECT; csrc/rt_shade.cuh:ball_direct): uniform unit vector + radius of a uniform ball point */
+void orc_sincos_turn24(uint32_t k, float *c, float *s);
+void orc_ball_direct(orc_rng *rng, v3 *unit, float *rad);
 
 /* ---- prepared scene ---- */
 typedef struct {

@@ -82,7 +82,7 @@ void orc_rng_init(orc_rng *r, uint32_t seed, uint32_t pixel, uint32_t sample, ui
     memset(r, 0, sizeof *r);
     r->key[0] = seed; r->key[1] = pixel;
     r->ctr[0] = sample; r->ctr[1] = bounce; r->ctr[2] = 0; r->ctr[3] = 0x5254u;
-    r->idx = 4; r->sampling = sampling;
+    r->idx = 4; r->sampling = sampling & 1; r->direct = (sampling & RT_SAMPLING_DIRECT) ? 1 : 0;
 }
 
 float orc_rng_next(orc_rng *r) {
@@ -184,9 +184,54 @@ void orc_camera_setup(const rt_camera_desc *c, orc_camera *cam) {
 }
 
 /* get_ray: camera.h:32-39 with defocus, camera.cuh:31-39 without */
+/* ---- direct draws: the distributions of the reference's rejection samplers without the loops (our definition of how the
+ * Philox words are cut; the reference draws from XORWOW / mt19937 and is matched statistically only) ---- */
+void orc_sincos_turn24(uint32_t k, float *c, float *s) {   /* angle 2 pi k / 2^24 - pi / 4 */
+    const float th = (float)((int)(k & 0x3fffffu) - 0x200000) * 3.74507398e-07f;
+    const float s2 = th * th;
+    float ps = fmaf(s2, 2.72425904768169858e-06f, -1.98400259250774980e-04f);
+    ps = fmaf(s2, ps, 8.33333190530538559e-03f);
+    ps = fmaf(s2, ps, -1.66666671633720398e-01f);
+    const float sn = fmaf(th * s2, ps, th);
+    float pc = fmaf(s2, -2.72958857294724998e-07f, 2.48005617322633043e-05f);
+    pc = fmaf(s2, pc, -1.38888880610466003e-03f);
+    pc = fmaf(s2, pc, 4.16666679084300995e-02f);
+    const float cs = fmaf(s2 * s2, pc, fmaf(-0.5f, s2, 1.0f));
+    const uint32_t q = k >> 22;
+    *c = (q & 1u) ? sn : cs; *s = (q & 1u) ? cs : sn;
+    if (q == 1u || q == 2u) *c = -*c;
+    if (q >= 2u) *s = -*s;
+}
+static uint32_t k24_of(float u) { uint32_t k = (uint32_t)(u * 16777216.0f); return k > 0xffffffu ? 0xffffffu : k; }
+static void ball_direct_k(uint32_t k1, uint32_t k2, uint32_t k3, uint32_t k4, uint32_t k5, v3 *unit, float *rad) {
+    const float z = fmaf(-2.0f, (float)k1 * 5.9604644775390625e-08f, 1.0f);
+    const float r = sqrtf(fmaxf(fmaf(-z, z, 1.0f), 0.0f));
+    float c, s;
+    orc_sincos_turn24(k2, &c, &s);
+    *unit = V(r * c, r * s, z);
+    uint32_t m = k3 > k4 ? k3 : k4; if (k5 > m) m = k5;
+    *rad = (float)(m + 1u) * 5.9604644775390625e-08f;
+}
+void orc_ball_direct(orc_rng *rng, v3 *unit, float *rad) {
+    if (rng->replay) {          /* replayed uniforms: five draws as they come */
+        float a = orc_rng_next(rng), b = orc_rng_next(rng), c = orc_rng_next(rng), d = orc_rng_next(rng), e = orc_rng_next(rng);
+        ball_direct_k(k24_of(a), k24_of(b), k24_of(c), k24_of(d), k24_of(e), unit, rad);
+        return;
+    }
+    uint32_t w[4];
+    orc_rng_block(rng, w);      /* one whole block; the next draw starts a new one */
+    rng->draws += 5;
+    ball_direct_k(w[0] >> 8, w[1] >> 8, w[2] >> 8, w[3] >> 8, (w[0] & 0xffu) | ((w[1] & 0xffu) << 8) | ((w[2] & 0xffu) << 16), unit, rad);
+}
+
 void orc_get_ray(const orc_camera *cam, float s, float t, int defocus, orc_rng *rng, v3 *o, v3 *d) {
     float rx = 0.0f, ry = 0.0f;
-    if (defocus) {
+    if (defocus && rng->direct) {   /* uniform disk: radius sqrt(u1), angle from u2 */
+        float u1 = orc_rng_next(rng), u2 = orc_rng_next(rng), c, sn;
+        orc_sincos_turn24(k24_of(u2), &c, &sn);
+        float rr = sqrtf(u1);
+        rx = cam->lens_radius * (rr * c); ry = cam->lens_radius * (rr * sn);
+    } else if (defocus) {
         for (;;) {   /* random_in_unit_disk, vec3.h:157-165 */
             float px = fmaf(2.0f, orc_rng_next(rng), -1.0f), py = fmaf(2.0f, orc_rng_next(rng), -1.0f);
             if (fmaf(py, py, px * px) >= 1.0f) continue;

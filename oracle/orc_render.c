@@ -73,7 +73,11 @@ static v3 random_in_unit_sphere(orc_rng *rng) {
 void orc_ball_samples(uint32_t seed, uint32_t first_pixel, uint32_t sample, uint32_t bounce, int sampling, int n, float *out) {
     for (int i = 0; i < n; ++i) {
         orc_rng r; orc_rng_init(&r, seed, first_pixel + (uint32_t)i, sample, bounce, sampling);
-        v3 p = random_in_unit_sphere(&r);
+        v3 p;
+        if (r.direct) {       /* the ball point of the direct sampler: radius * unit vector (componentwise |.| in the GPU family) */
+            float rad; orc_ball_direct(&r, &p, &rad);
+            p = r.sampling == RT_SAMPLING_REFERENCE_GPU ? vscale(rad, V(fabsf(p.x), fabsf(p.y), fabsf(p.z))) : vscale(rad, p);
+        } else p = random_in_unit_sphere(&r);
         out[3 * i] = p.x; out[3 * i + 1] = p.y; out[3 * i + 2] = p.z;
     }
 }
@@ -88,8 +92,14 @@ int orc_scatter(const rt_scene_desc *sc, int mat, v3 rd, const orc_hit *rec, orc
     *so = rec->p;
     switch (m->type) {
     case RT_MAT_LAMBERTIAN: {   /* material.cuh:37-52 (GPU) | material.h:25-35 (CPU) */
-        v3 r = random_in_unit_sphere(rng);
-        if (rng->sampling == RT_SAMPLING_REFERENCE_CPU) r = vunit(r);     /* random_unit_vector, vec3.h:131-134 */
+        v3 r;
+        if (rng->direct) {        /* same distributions, drawn directly: octant ball (GPU family) | unit vector (CPU family) */
+            float rad; orc_ball_direct(rng, &r, &rad);
+            if (rng->sampling == RT_SAMPLING_REFERENCE_GPU) r = vscale(rad, V(fabsf(r.x), fabsf(r.y), fabsf(r.z)));
+        } else {
+            r = random_in_unit_sphere(rng);
+            if (rng->sampling == RT_SAMPLING_REFERENCE_CPU) r = vunit(r);     /* random_unit_vector, vec3.h:131-134 */
+        }
         v3 dir = vadd(rec->n, r);
         if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = rec->n;   /* near_zero, vec3.cuh:66-68 */
         *sd = dir;
@@ -99,7 +109,11 @@ int orc_scatter(const rt_scene_desc *sc, int mat, v3 rd, const orc_hit *rec, orc
     case RT_MAT_METAL: {        /* material.cuh:63-70 */
         v3 refl = reflect(vunit(rd), rec->n);
         float fuzz = m->fuzz < 1.0f ? m->fuzz : 1.0f;
-        v3 r = random_in_unit_sphere(rng);
+        v3 r;
+        if (rng->direct) {
+            float rad; orc_ball_direct(rng, &r, &rad);
+            r = rng->sampling == RT_SAMPLING_REFERENCE_GPU ? vscale(rad, V(fabsf(r.x), fabsf(r.y), fabsf(r.z))) : vscale(rad, r);
+        } else r = random_in_unit_sphere(rng);
         *sd = vfma(fuzz, r, refl);
         *att = V(m->albedo[0], m->albedo[1], m->albedo[2]);
         return dot3(*sd, rec->n) > 0.0f;
@@ -200,7 +214,7 @@ static void *worker(void *arg) {
                 float u = ((float)x + orc_rng_next(&rng)) / (float)(W - 1);
                 float v = ((float)y + orc_rng_next(&rng)) / (float)(H - 1);
                 v3 o, d;
-                int defocus = sc->sampling == RT_SAMPLING_REFERENCE_CPU && sc->camera.aperture > 0.0f;
+                int defocus = (sc->sampling & 1) == RT_SAMPLING_REFERENCE_CPU && sc->camera.aperture > 0.0f;
                 orc_get_ray(&j->cam, u, v, defocus, &rng, &o, &d);
                 v3 c = ray_color(sc, o, d, j->seed, pixel, (uint32_t)s, &rays, &j->nee, &shadow, j->bvh, &cnt);
                 sum = vadd(sum, c);                                   /* fixed order: ascending sample index */
@@ -221,7 +235,7 @@ static void *worker(void *arg) {
 static int render_impl(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
                        int flags, int64_t *n_rays, int64_t *n_shadow_rays, int use_bvh, int64_t *counters) {
     if (!sc || !rgb_sum || sc->width < 1 || sc->height < 1) return RT_ERR_INVALID;
-    if ((flags & RT_RENDER_NEE) && sc->sampling != RT_SAMPLING_REFERENCE_CPU) return RT_ERR_INVALID;
+    if ((flags & RT_RENDER_NEE) && (sc->sampling & 1) != RT_SAMPLING_REFERENCE_CPU) return RT_ERR_INVALID;
     job_t j; memset(&j, 0, sizeof j);
     j.sc = sc; j.seed = seed; j.s0 = spp_begin; j.sn = spp_count > 0 ? spp_count : sc->samples_per_pixel; j.out = rgb_sum;
     orc_camera_setup(&sc->camera, &j.cam);
@@ -283,7 +297,7 @@ int orc_aov(const rt_scene_desc *sc, float *aov) {
             q[0] = 1.0f; q[1] = rec.t; q[2] = rec.p.x; q[3] = rec.p.y; q[4] = rec.p.z;
             q[5] = rec.n.x; q[6] = rec.n.y; q[7] = rec.n.z; q[8] = (float)rec.front; q[9] = rec.u; q[10] = rec.v;
             q[11] = (float)rec.prim; q[12] = (float)rec.mat;
-            orc_rng rng; memset(&rng, 0, sizeof rng); rng.replay = fixed_u; rng.replay_n = 8; rng.sampling = sc->sampling;
+            orc_rng rng; memset(&rng, 0, sizeof rng); rng.replay = fixed_u; rng.replay_n = 8; rng.sampling = sc->sampling & 1; rng.direct = (sc->sampling & RT_SAMPLING_DIRECT) ? 1 : 0;
             v3 att, so, sd;
             int ok = orc_scatter(sc, rec.mat, d, &rec, &rng, &att, &so, &sd);
             q[13] = att.x; q[14] = att.y; q[15] = att.z;

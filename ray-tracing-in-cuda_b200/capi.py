@@ -13,6 +13,7 @@ RT_MAT_LAMBERTIAN, RT_MAT_METAL, RT_MAT_DIELECTRIC, RT_MAT_DIFFUSE_LIGHT = range
 RT_TEX_SOLID, RT_TEX_CHECKER, RT_TEX_IMAGE = range(3)
 RT_BG_CONSTANT, RT_BG_SKY_GRADIENT = range(2)
 RT_SAMPLING_REFERENCE_GPU, RT_SAMPLING_REFERENCE_CPU = range(2)
+RT_SAMPLING_DIRECT = 2       # flag: direct draws instead of the reference's rejection loops
 RT_RENDER_KEEP_ACCUM, RT_RENDER_COUNT_EVENTS, RT_RENDER_NO_SORT, RT_RENDER_NEE, RT_RENDER_TIME_STAGES, RT_RENDER_SORT = 1, 2, 4, 8, 16, 32
 RT_RENDER_SERIAL = 64
 RT_RENDER_NO_TILE_LISTS = 256

@@ -309,8 +309,9 @@ static int upload_to_device(rt_ctx *ctx) {
     ds.n_prims = n; ds.n_tree = info[0]; ds.n_giants = info[1]; ds.n_nodes = ds.n_tree >= 2 ? ds.n_tree - 1 : 1;
     ds.giant_code = ctx->d_lbvh_info.p + 4;
     ds.leaf_aabb = ctx->d_leaf_aabb.p;
-    ds.width = d.width; ds.height = d.height; ds.max_depth = d.max_depth; ds.sampling = d.sampling; ds.bg_mode = d.background_mode;
-    ds.defocus = (d.sampling == RT_SAMPLING_REFERENCE_CPU && d.camera.aperture > 0.0f) ? 1 : 0;
+    ds.width = d.width; ds.height = d.height; ds.max_depth = d.max_depth; ds.sampling = d.sampling & 1; ds.direct = (d.sampling & RT_SAMPLING_DIRECT) ? 1 : 0;
+    ds.bg_mode = d.background_mode;
+    ds.defocus = (ds.sampling == RT_SAMPLING_REFERENCE_CPU && d.camera.aperture > 0.0f) ? 1 : 0;
     ds.background = make_float3(d.background[0], d.background[1], d.background[2]);
     camera_setup(d.camera, ds.cam);
     ds.nodes = ctx->d_nodes.p; ds.nodes_s = ctx->d_nodes_s.p; ds.primA = ctx->d_primA.p; ds.primB = ctx->d_primB.p; ds.primC = ctx->d_primC.p;

@@ -209,6 +209,8 @@ struct Loader {
         d.background_mode = (v && v->kind == JValue::Str && v->str == "sky_gradient") ? RT_BG_SKY_GRADIENT : RT_BG_CONSTANT;
         v = root.get("sampling");
         d.sampling = (v && v->kind == JValue::Str && v->str == "reference_cpu") ? RT_SAMPLING_REFERENCE_CPU : RT_SAMPLING_REFERENCE_GPU;
+        v = root.get("sampler");          // "rejection": the reference's loops; default: the same distributions drawn directly
+        if (!(v && v->kind == JValue::Str && v->str == "rejection")) d.sampling |= RT_SAMPLING_DIRECT;
         // camera, parser.hpp:113-126
         const JValue *cam = root.get("camera");
         if (!cam) return fail("scene: missing \"camera\"");

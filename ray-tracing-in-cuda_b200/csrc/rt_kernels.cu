@@ -58,7 +58,7 @@ __global__ void k_pass_init(Queues q, int max_depth, int n_queue0) {
 // to the ray: the bounce-0 extend launch disappears.  Paths it cannot cover (margin pixels outside the 8x4 tiling, tiles
 // with more than RT_TILE_K candidates) get the RT_HIT_TODO mark and are traversed by a fix-up extend launch.
 #define RT_HIT_TODO ((int)0x80000001)
-template <bool HITS, bool COUNT>
+template <bool HITS, bool COUNT, bool DIRECT>
 __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsigned seed, int spp_begin, int n_paths, int zero_radiance) {
     // one thread per (tile-ordered) pixel slot and group of samples: the pixel arithmetic is done once, the sample planes are
     // written with stride n_pixels (each plane coalesced across the warp).  The grid covers every pixel slot in x.
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
         const float u = ((float)x + rng.next()) / div_w;
         const float v = ((float)y + rng.next()) / div_h;
         float3 o, d;
-        camera_ray(sc.cam, u, v, sc.defocus != 0, rng, o, d);
+        camera_ray<DIRECT>(sc.cam, u, v, sc.defocus != 0, rng, o, d);
         if (empty_tile) {             // main.cu:61-63 with throughput 1
             const float3 bg = background(sc, d);
             q.radiance[i] = make_float4(bg.x, bg.y, bg.z, 0.0f);
@@ -377,7 +377,7 @@ __device__ __forceinline__ void shade_issue_loads(ShadeSmem &sm, const DScene &s
     tma_load_1d(sm.in_hit[stage], q.hits + first, b8, &sm.full[stage]);
 }
 
-template <bool COUNT, bool NEE, bool CAM>
+template <bool COUNT, bool NEE, bool CAM, bool DIRECT>
 __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene sc, Queues q, unsigned seed, int spp_begin, int bounce, int buf,
                                                          int last_bounce, int sort) {
     extern __shared__ __align__(128) unsigned char s_shade_raw[];
@@ -485,7 +485,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                 } else {
                     Rng rng; rng.init(seed, (unsigned)__float_as_int(d4.w), (unsigned)(spp_begin + __float_as_int(t4.w)), (unsigned)bounce + 1u, sc.sampling);
                     float3 att, sd;
-                    const bool ok = scatter(sc, m, d, rec, rng, att, sd);
+                    const bool ok = scatter<DIRECT>(sc, m, d, rec, rng, att, sd);
                     if (ok && !last_bounce) {
                         alive = true;
                         no = rec.p; nd = sd; nthr = thr * att;
@@ -653,7 +653,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_aov(DScene sc, float *__restrict__
                 // fixed uniforms 0.5,0.5,0.5,... as in the oracle/reference harness: only `att` and `ok` are recorded
                 FixedRng fr;
                 float3 sd;
-                ok = scatter(sc, m, d, rec, fr, att, sd);
+                ok = sc.direct ? scatter<true>(sc, m, d, rec, fr, att, sd) : scatter<false>(sc, m, d, rec, fr, att, sd);
             }
             q[13] = att.x; q[14] = att.y; q[15] = att.z; q[16] = E.x; q[17] = E.y; q[18] = E.z; q[22] = ok ? 1.0f : 0.0f;
         } else {
@@ -718,9 +718,15 @@ void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsi
     int gy = (c.num_sms * 16 + bx - 1) / bx;
     gy = gy < 1 ? 1 : (gy > n_s ? n_s : gy);
 #define RT_GEN_ARGS <<<dim3(bx, gy), RT_BLOCK, 0, c.stream>>>(sc, q, seed, spp_begin, n_paths, zero_radiance ? 1 : 0)
-    if (!hits) k_generate<false, false> RT_GEN_ARGS;
-    else if (count) k_generate<true, true> RT_GEN_ARGS;
-    else k_generate<true, false> RT_GEN_ARGS;
+    if (sc.direct) {
+        if (!hits) k_generate<false, false, true> RT_GEN_ARGS;
+        else if (count) k_generate<true, true, true> RT_GEN_ARGS;
+        else k_generate<true, false, true> RT_GEN_ARGS;
+    } else {
+        if (!hits) k_generate<false, false, false> RT_GEN_ARGS;
+        else if (count) k_generate<true, true, false> RT_GEN_ARGS;
+        else k_generate<true, false, false> RT_GEN_ARGS;
+    }
 #undef RT_GEN_ARGS
     bump(c);
 }
@@ -770,10 +776,13 @@ cudaError_t kernels_configure_device(int dev, size_t smem_optin) {
         SET((k_extend<true, false, false, RT_OBJ_SPHERE>), smem_optin); SET((k_extend<true, false, true, RT_OBJ_SPHERE>), smem_optin);
         SET((k_extend<false, false, false>), smem_optin); SET((k_extend<false, true, false>), smem_optin);
         SET((k_extend<false, false, true>), smem_optin); SET((k_extend<false, true, true>), smem_optin);
-        SET((k_shade<false, false, false>), sizeof(ShadeSmem)); SET((k_shade<true, false, false>), sizeof(ShadeSmem));
-        SET((k_shade<false, true, false>), sizeof(ShadeSmem)); SET((k_shade<true, true, false>), sizeof(ShadeSmem));
-        SET((k_shade<false, false, true>), sizeof(ShadeSmem)); SET((k_shade<true, false, true>), sizeof(ShadeSmem));
-        SET((k_shade<false, true, true>), sizeof(ShadeSmem)); SET((k_shade<true, true, true>), sizeof(ShadeSmem));
+#define SET_SH(D_) \
+        SET((k_shade<false, false, false, D_>), sizeof(ShadeSmem)); SET((k_shade<true, false, false, D_>), sizeof(ShadeSmem)); \
+        SET((k_shade<false, true, false, D_>), sizeof(ShadeSmem)); SET((k_shade<true, true, false, D_>), sizeof(ShadeSmem)); \
+        SET((k_shade<false, false, true, D_>), sizeof(ShadeSmem)); SET((k_shade<true, false, true, D_>), sizeof(ShadeSmem)); \
+        SET((k_shade<false, true, true, D_>), sizeof(ShadeSmem)); SET((k_shade<true, true, true, D_>), sizeof(ShadeSmem));
+        SET_SH(false) SET_SH(true)
+#undef SET_SH
 #undef SET
         g_smem_err[dev] = e;
     });
@@ -791,7 +800,8 @@ void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigne
                   bool last_bounce, bool count, bool sort, bool nee) {
     const int grid = persistent_grid(c, RT_SH_CTAS_PER_SM);
 #define RT_SHADE_ARGS <<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort)
-#define RT_SHADE_CAM(C_, N_) { if (bounce == 0) k_shade<C_, N_, true> RT_SHADE_ARGS; else k_shade<C_, N_, false> RT_SHADE_ARGS; }
+#define RT_SHADE_CAM(C_, N_) { if (sc.direct) { if (bounce == 0) k_shade<C_, N_, true, true> RT_SHADE_ARGS; else k_shade<C_, N_, false, true> RT_SHADE_ARGS; } \
+                              else { if (bounce == 0) k_shade<C_, N_, true, false> RT_SHADE_ARGS; else k_shade<C_, N_, false, false> RT_SHADE_ARGS; } }
     if (count) { if (nee) RT_SHADE_CAM(true, true) else RT_SHADE_CAM(true, false) }
     else { if (nee) RT_SHADE_CAM(false, true) else RT_SHADE_CAM(false, false) }
 #undef RT_SHADE_CAM

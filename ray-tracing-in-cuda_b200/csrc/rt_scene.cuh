@@ -44,7 +44,8 @@ struct DScene {
     const int *giant_code;                 // their leaf codes (type << 28 | slot), device array (a by-value array indexed at run time
                                            // would force a local-memory copy of this whole struct in every kernel)
     const float *leaf_aabb;                // padded box per leaf slot (tile lists: boxes of the giants)
-    int width, height, max_depth, sampling, bg_mode, defocus;
+    int width, height, max_depth, sampling, bg_mode, defocus;      // sampling: the family (RT_SAMPLING_REFERENCE_GPU / _CPU)
+    int direct;                            // RT_SAMPLING_DIRECT: direct draws instead of the reference's rejection loops
     float3 background;
     DCamera cam;
     const BvhNode *nodes;                  // AOV pass and build tests

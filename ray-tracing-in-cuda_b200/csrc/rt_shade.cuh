@@ -78,6 +78,55 @@ __device__ __forceinline__ float3 random_in_unit_sphere<Rng>(Rng &rng, int sampl
     return p;
 }
 
+// ---- direct draws (RT_SAMPLING_DIRECT): the same distributions without the rejection loops ----
+// The reference's samplers are rejection loops (vec3.cuh:133-141, vec3.h:121-129,157-165): acceptance pi/6 per trial for the ball,
+// so a warp waits for its unluckiest lane and the loop ran at ~10 of 32 lanes (half the instructions of k_shade, ncu r01f).
+// The reference is matched statistically only (its generators are XORWOW / mt19937, ours Philox), so the same distributions
+// may be drawn directly from five 24-bit integers k1..k5 of ONE Philox block:
+//   direction  z = 1 - 2 k1/2^24, angle 2 pi k2/2^24 (- pi/4: a constant turn keeps a uniform angle uniform, and the octant
+//              reduction below then needs no further shift), r = sqrt(1 - z^2)              -> uniform on the unit sphere
+//   radius     max(k3, k4, k5) has density 3 r^2: the radial law of the uniform ball         -> unit * radius uniform in the ball
+// GPU family (vec3.cuh:133-141 samples the positive octant only): componentwise |.| of the above.
+// cos / sin of the angle: quarter turns from the top two bits, the polynomial pair of rt_sinf on [-pi/4, pi/4) for the rest.
+__device__ __forceinline__ void rt_sincos_turn24(uint32_t k, float &c, float &s) {
+    const float th = (float)((int)(k & 0x3fffffu) - 0x200000) * 3.74507398e-07f;      // (pi/2) 2^-22 : theta in [-pi/4, pi/4)
+    const float s2 = th * th;
+    float ps = __fmaf_rn(s2, 2.72425904768169858e-06f, -1.98400259250774980e-04f);
+    ps = __fmaf_rn(s2, ps, 8.33333190530538559e-03f);
+    ps = __fmaf_rn(s2, ps, -1.66666671633720398e-01f);
+    const float sn = __fmaf_rn(th * s2, ps, th);
+    float pc = __fmaf_rn(s2, -2.72958857294724998e-07f, 2.48005617322633043e-05f);
+    pc = __fmaf_rn(s2, pc, -1.38888880610466003e-03f);
+    pc = __fmaf_rn(s2, pc, 4.16666679084300995e-02f);
+    const float cs = __fmaf_rn(s2 * s2, pc, __fmaf_rn(-0.5f, s2, 1.0f));
+    const uint32_t q = k >> 22;
+    c = (q & 1u) ? sn : cs; s = (q & 1u) ? cs : sn;
+    if (q == 1u || q == 2u) c = -c;
+    if (q >= 2u) s = -s;
+}
+// unit: uniform on the sphere; rad: radius of a uniform ball point (only metal fuzz and the GPU family's lambertian use it)
+__device__ __forceinline__ void ball_direct_k(uint32_t k1, uint32_t k2, uint32_t k3, uint32_t k4, uint32_t k5, float3 &unit, float &rad) {
+    const float z = __fmaf_rn(-2.0f, (float)k1 * 5.9604644775390625e-08f, 1.0f);
+    const float r = sqrtf(fmaxf(__fmaf_rn(-z, z, 1.0f), 0.0f));
+    float c, s;
+    rt_sincos_turn24(k2, c, s);
+    unit = v3(r * c, r * s, z);
+    const uint32_t m = max(k3, max(k4, k5));
+    rad = (float)(m + 1u) * 5.9604644775390625e-08f;
+}
+__device__ __forceinline__ uint32_t k24_of(float u) { const uint32_t k = (uint32_t)(u * 16777216.0f); return k > 0xffffffu ? 0xffffffu : k; }
+template <class R>
+__device__ __forceinline__ void ball_direct(R &rng, float3 &unit, float &rad) {      // replayed uniforms: five draws as they come
+    const float a = rng.next(), b = rng.next(), c = rng.next(), d = rng.next(), e = rng.next();
+    ball_direct_k(k24_of(a), k24_of(b), k24_of(c), k24_of(d), k24_of(e), unit, rad);
+}
+template <>
+__device__ __forceinline__ void ball_direct<Rng>(Rng &rng, float3 &unit, float &rad) {
+    const uint4 B = rng.next_block();
+    ball_direct_k(B.x >> 8, B.y >> 8, B.z >> 8, B.w >> 8, (B.x & 0xffu) | ((B.y & 0xffu) << 8) | ((B.z & 0xffu) << 16), unit, rad);
+    rng.idx = 4;
+}
+
 __device__ __forceinline__ float3 reflect3(float3 v, float3 n) {   // vec3.cuh:121-123
     float k = 2.0f * dot3(v, n);
     return v3(__fmaf_rn(-k, n.x, v.x), __fmaf_rn(-k, n.y, v.y), __fmaf_rn(-k, n.z, v.z));
@@ -85,16 +134,23 @@ __device__ __forceinline__ float3 reflect3(float3 v, float3 n) {   // vec3.cuh:1
 
 // material::scatter for the four material classes (material.cuh:37-52, 63-70, 130-158, 169-173).
 // Returns false when the path ends here.  att: attenuation; sd: scattered direction (origin is rec.p).
-template <class R>
+template <bool DIRECT, class R>
 __device__ __forceinline__ bool scatter(const DScene &sc, const DMaterial &m, float3 rd, const HitRec &rec, R &rng,
                                         float3 &att, float3 &sd) {
     // lambertian and metal draw the same random_in_unit_sphere(): one shared (convergent) rejection loop for both classes,
     // then the short class-specific tails — a warp holding a mix of the two pays for the expensive part once
     float3 r = v3(0, 0, 0);
-    if (m.type == RT_MAT_LAMBERTIAN || m.type == RT_MAT_METAL) r = random_in_unit_sphere(rng, sc.sampling);
+    if (m.type == RT_MAT_LAMBERTIAN || m.type == RT_MAT_METAL) {
+        if (DIRECT) {
+            float rad;
+            ball_direct(rng, r, rad);
+            if (sc.sampling == RT_SAMPLING_REFERENCE_GPU) r = rad * v3(fabsf(r.x), fabsf(r.y), fabsf(r.z));     // octant ball for both classes
+            else if (m.type == RT_MAT_METAL) r = rad * r;                                                        // ball | unit vector
+        } else r = random_in_unit_sphere(rng, sc.sampling);
+    }
     switch (m.type) {
     case RT_MAT_LAMBERTIAN: {
-        if (sc.sampling == RT_SAMPLING_REFERENCE_CPU) r = vunit(r);     // random_unit_vector (material.h:27)
+        if (!DIRECT && sc.sampling == RT_SAMPLING_REFERENCE_CPU) r = vunit(r);     // random_unit_vector (material.h:27)
         float3 dir = rec.n + r;
         if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = rec.n;
         sd = dir;
@@ -233,9 +289,16 @@ __device__ __forceinline__ float3 background(const DScene &sc, float3 d) {
 }
 
 // camera::get_ray, camera.cuh:31-39 (no lens) / cmake-cpu-version/camera.h:32-39 (thin lens)
+template <bool DIRECT = false>
 __device__ __forceinline__ void camera_ray(const DCamera &cam, float s, float t, bool defocus, Rng &rng, float3 &o, float3 &d) {
     float rx = 0.0f, ry = 0.0f;
-    if (defocus) {
+    if (defocus && DIRECT) {      // uniform disk without the loop: radius sqrt(u1), angle from u2
+        const float u1 = rng.next(), u2 = rng.next();
+        float c, sn;
+        rt_sincos_turn24(k24_of(u2), c, sn);
+        const float rr = sqrtf(u1);
+        rx = cam.lens_radius * (rr * c); ry = cam.lens_radius * (rr * sn);
+    } else if (defocus) {
         for (;;) {
             float px = __fmaf_rn(2.0f, rng.next(), -1.0f), py = __fmaf_rn(2.0f, rng.next(), -1.0f);
             if (__fmaf_rn(py, py, px * px) >= 1.0f) continue;

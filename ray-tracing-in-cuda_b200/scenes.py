@@ -38,7 +38,7 @@ class TableScene:
     """Owns the numpy / ctypes arrays behind a capi.SceneDesc (`.desc`), ready for Renderer.upload()."""
 
     def __init__(self, objects, materials, textures, camera, width, height, spp, max_depth=50, background=(0.5, 0.7, 1.0),
-                 sky_gradient=True, sampling=capi.RT_SAMPLING_REFERENCE_GPU):
+                 sky_gradient=True, sampling=capi.RT_SAMPLING_REFERENCE_GPU | capi.RT_SAMPLING_DIRECT):
         self.objects = np.ascontiguousarray(objects, dtype=OBJECT_DTYPE)
         D = self.desc = capi.SceneDesc()
         D.width, D.height, D.max_depth, D.samples_per_pixel = width, height, max_depth, spp

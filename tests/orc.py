@@ -131,6 +131,8 @@ def load_scene(src, width=None, height=None, spp=None, max_depth=None, base_dir=
         D.background[k] = d["background"][k]
     D.background_mode = capi.RT_BG_SKY_GRADIENT if d.get("background_mode") == "sky_gradient" else capi.RT_BG_CONSTANT
     D.sampling = capi.RT_SAMPLING_REFERENCE_CPU if d.get("sampling") == "reference_cpu" else capi.RT_SAMPLING_REFERENCE_GPU
+    if d.get("sampler") != "rejection":
+        D.sampling |= capi.RT_SAMPLING_DIRECT
     cam = d["camera"]
     for k in range(3):
         D.camera.lookfrom[k] = cam["lookfrom"][k]; D.camera.lookat[k] = cam["lookat"][k]; D.camera.vup[k] = cam["vup"][k]

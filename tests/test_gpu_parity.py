@@ -121,18 +121,28 @@ def test_aov_matches_oracle_and_reference(rt, name):
     assert np.abs(got[..., 13:22] - ref[..., 13:22])[same].max() <= 1e-5
 
 
-@pytest.mark.parametrize("name,spp", [("sample_scene", 8), ("blue", 4), ("blue2", 8), ("dna_000", 4), ("rtiow_486", 8), ("basic_scene", 3),
-                                      ("sample_scene_ext", 6)])
-def test_render_matches_oracle_sample_for_sample(rt, name, spp):
+def scene_dict(name, sampler=None):
+    with open(scene_path(name)) as f:
+        d = json.load(f)
+    if sampler:
+        d["sampler"] = sampler        # "rejection": the reference's loops instead of the direct draws (RT_SAMPLING_DIRECT)
+    return d
+
+
+@pytest.mark.parametrize("name,spp,sampler", [("sample_scene", 8, None), ("blue", 4, None), ("blue2", 8, None), ("dna_000", 4, None),
+                                              ("rtiow_486", 8, None), ("basic_scene", 3, None), ("sample_scene_ext", 6, None),
+                                              ("rtiow_486", 6, "rejection"), ("blue2", 6, "rejection"), ("sample_scene_ext", 4, "rejection")])
+def test_render_matches_oracle_sample_for_sample(rt, name, spp, sampler):
     """Full path tracing, same Philox streams: per-pixel radiance sums within 1e-5 per sample of the brute-force oracle,
-    and exactly the same number of path segments."""
+    and exactly the same number of path segments — with the direct samplers (default) and with the reference's rejection loops."""
     W, H = 96, 54
-    rt.upload_json(scene_path(name))
+    d = scene_dict(name, sampler)
+    rt.upload_json_text(json.dumps(d), base_dir=G)
     rt.override(width=W, height=H, spp=spp)
     rt.stats_reset()
     rt.render(seed=0x2023)
     got, _, st = rt.download()
-    want, nrays = orc.render(orc.load_scene(scene_path(name), width=W, height=H, spp=spp), seed=0x2023)
+    want, nrays = orc.render(orc.load_scene(d, width=W, height=H, spp=spp, base_dir=G), seed=0x2023)
     assert st["rays"] == nrays
     err = np.abs(got - want)
     bad = (err > 1e-5 * spp).any(-1).sum()

@@ -72,6 +72,51 @@ def test_ball_sampler_distribution():
     assert np.abs(q.mean(0) - 0.375).max() < 3e-3
 
 
+def test_direct_sampler_distribution_and_bit_layout():
+    """RT_SAMPLING_DIRECT: the ball / octant-ball / unit-sphere distributions of the reference's rejection samplers drawn from
+    one Philox block without a loop.  (1) same moments as the rejection sampler's ball (E[x]=0, E[x^2]=1/5, P(|p|<r)=r^3,
+    uncorrelated axes), directions uniform on the sphere (E[z]=0, E[z^2]=1/3, octants equally likely); (2) an independent numpy
+    statement of how the block is cut: z from word 0 >> 8, angle from word 1 >> 8 (- pi/4), radius = max of three 24-bit fields."""
+    L = orc.lib()
+    n = 200000
+    out = np.zeros(3 * n, np.float32)
+    mode = capi.RT_SAMPLING_REFERENCE_CPU | capi.RT_SAMPLING_DIRECT
+    L.orc_ball_samples(7, 0, 3, 1, mode, n, orc.fptr(out))
+    p = out.reshape(n, 3).astype(np.float64)
+    r2 = (p * p).sum(1)
+    assert r2.max() <= 1.0 + 1e-6
+    assert np.abs(p.mean(0)).max() < 5e-3 and np.abs((p * p).mean(0) - 0.2).max() < 3e-3 and abs(r2.mean() - 0.6) < 3e-3
+    for r in (0.25, 0.5, 0.75):
+        assert abs((r2 < r * r).mean() - r ** 3) < 4e-3
+    assert np.abs(np.corrcoef(p.T) - np.eye(3)).max() < 0.01
+    u = p / np.sqrt(r2)[:, None]
+    assert np.abs(u.mean(0)).max() < 5e-3 and np.abs((u * u).mean(0) - 1 / 3).max() < 3e-3
+    octant = (u[:, 0] > 0) * 4 + (u[:, 1] > 0) * 2 + (u[:, 2] > 0)
+    assert np.abs(np.bincount(octant.astype(int), minlength=8) / n - 0.125).max() < 4e-3
+    assert abs(np.corrcoef(np.sqrt(r2), u[:, 2])[0, 1]) < 0.01          # radius independent of direction
+    L.orc_ball_samples(7, 0, 3, 1, capi.RT_SAMPLING_REFERENCE_GPU | capi.RT_SAMPLING_DIRECT, n, orc.fptr(out))
+    q = out.reshape(n, 3).astype(np.float64)
+    assert q.min() >= 0.0 and np.abs(q.mean(0) - 0.375).max() < 3e-3 and np.array_equal(q, np.abs(p))
+    # the bit layout, stated independently in float64 (positions to 2e-6: the device polynomials are float32)
+    m = 512
+    got = np.zeros(3 * m, np.float32)
+    L.orc_ball_samples(9, 100, 5, 2, mode, m, orc.fptr(got))
+    got = got.reshape(m, 3).astype(np.float64)
+    w = np.zeros((m, 4), np.uint32)
+    for i in range(m):
+        ctr = (C.c_uint32 * 4)(5, 2, 0, 0x5254); key = (C.c_uint32 * 2)(9, 100 + i); o = (C.c_uint32 * 4)()
+        L.orc_philox4x32_10(ctr, key, o)
+        w[i] = list(o)
+    w = w.astype(np.int64)
+    z = 1.0 - 2.0 * (w[:, 0] >> 8) / 2.0 ** 24
+    ang = 2 * np.pi * (w[:, 1] >> 8) / 2.0 ** 24 - np.pi / 4
+    k5 = (w[:, 0] & 0xff) | ((w[:, 1] & 0xff) << 8) | ((w[:, 2] & 0xff) << 16)
+    rad = (np.maximum(np.maximum(w[:, 2] >> 8, w[:, 3] >> 8), k5) + 1) / 2.0 ** 24
+    rr = np.sqrt(np.maximum(1 - z * z, 0))
+    want = rad[:, None] * np.stack([rr * np.cos(ang), rr * np.sin(ang), z], 1)
+    assert np.abs(got - want).max() < 2e-6
+
+
 def test_transcendentals_against_libm():
     L = orc.lib()
     rng = np.random.default_rng(0)
