@@ -156,12 +156,14 @@ def make_upload(rt, workload):
         from rt_b200 import scenes
         n = int(scene.split(":")[1])
         ts = scenes.mesh_scene(n, n, W, H, spp)
-        desc = {"max_depth": ts.desc.max_depth, "objects": int(ts.desc.n_objects), "h2d": int(ts.objects.nbytes) + 32 * 8, "tables": ts}
+        desc = {"max_depth": ts.desc.max_depth, "objects": int(ts.desc.n_objects), "h2d": int(ts.objects.nbytes) + 32 * 8, "tables": ts,
+                "gradient": ts.desc.background_mode == 1}
         return (lambda r: r.upload(ts)), desc
     text = scene_text(scene, W, H, spp)
     d = json.loads(text)
     h2d = 64 * len(d["object"]["data"]) + 32 * (len(d["material"]["data"]) + len(d["texture"]["data"])) + len(text)
-    return (lambda r: r.upload_json_text(text, GOLDEN)), {"max_depth": d["max_depth"], "objects": len(d["object"]["data"]), "h2d": h2d, "text": text}
+    return (lambda r: r.upload_json_text(text, GOLDEN)), {"max_depth": d["max_depth"], "objects": len(d["object"]["data"]), "h2d": h2d, "text": text,
+                                                          "gradient": d.get("background_mode") == "sky_gradient"}
 
 
 def run_reference_binary(width, height, spp, procs):
@@ -212,7 +214,7 @@ def reference_sample(workload, procs):
     if scene.startswith("@mesh"):      # the reference has no C++ mesh path at all: the oracle port is the CPU statement
         return oracle_sample(workload, procs, 32, 18, 1)
     if scene == "rtiow_486.json" and os.path.exists(REF_BIN):
-        w, h, s = 960, 540, 1
+        w, h, s = 480, 270, 8          # 8 spp: the reference's per-pixel by-value copy of the world (main.cpp:45-55) is amortised
         dt = run_reference_binary(w, h, s, procs)
         return procs * w * h * s, dt, f"{procs} x cmake_cpu_mt -w {w} -h {h} -spp {s} -d 50 (unmodified reference binary, 1 thread each)", "reference"
     if not os.path.exists(REF_GPU_HARNESS):
@@ -350,17 +352,19 @@ def main():
     scene, W, H, spp = WORKLOADS[args.workload]
     upload, sdesc = make_upload(rt, args.workload)
     stream = torch.cuda.Stream()
-    s0, s1 = multi_gpu.spp_slice(spp, rank, world)                 # this rank's slice of the sample indices
+    s0, s1 = multi_gpu.spp_slice(spp, rank, world)        # this rank's whole sample chunks (rt_rank_chunks); the library deals them itself
     flags = capi.RT_RENDER_SORT if args.sort else 0       # timed region: the default schedule (two passes in flight)
 
     with torch.cuda.stream(stream):
         r = rt.Renderer(local, stream=stream.cuda_stream)
+        multi_gpu.init_comm(r)        # the LIBRARY's NCCL communicator (csrc/rt_multi.cu); torch.distributed only carries the unique id
         upload(r)
-        accum = multi_gpu.accum_view(r, local)      # zero-copy torch view of the library's accumulation buffer
 
         def step_resident():
-            r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=flags, max_paths_per_pass=args.max_paths)
-            multi_gpu.reduce_image(accum, dst=0)
+            # every rank renders its chunks into per-chunk buffers; the library gathers them on rank 0 over NCCL and adds them in
+            # chunk order (bit-identical image for any rank count)
+            r.render_shard(seed=0x2023, spp_count=spp, flags=flags, max_paths_per_pass=args.max_paths)
+            r.gather_image(0)
 
         def barrier():
             if world > 1:
@@ -398,7 +402,8 @@ def main():
         # per-stage times: one extra step right after the timed region with a CUDA-event pair around every launch, which
         # needs one pass at a time (RT_RENDER_TIME_STAGES serialises the two pass streams)
         r.stats_reset()
-        r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=flags | capi.RT_RENDER_TIME_STAGES, max_paths_per_pass=args.max_paths)
+        r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, total_spp=spp, flags=flags | capi.RT_RENDER_TIME_STAGES | capi.RT_RENDER_KEEP_CHUNKS,
+                 max_paths_per_pass=args.max_paths)
         _, _, sg = r.download(want_sum=False, want_rgb8=False)
         barrier()
 
@@ -408,8 +413,8 @@ def main():
 
         def step_e2e():
             upload(r)
-            r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, flags=0, max_paths_per_pass=args.max_paths)
-            multi_gpu.reduce_image(accum, dst=0)
+            r.render_shard(seed=0x2023, spp_count=spp, flags=0, max_paths_per_pass=args.max_paths)
+            r.gather_image(0)
             if rank == 0:
                 return r.download(gamma=0, out_sum=pin_sum, out_rgb8=pin_rgb8)
             r.synchronize()
@@ -429,6 +434,14 @@ def main():
         ms_e2e = float(ms2.item()) / max(2, args.steps // 2)
 
     if rank == 0:
+        # integrity: the render is bit-reproducible (counter-based RNG, fixed-order accumulation, chunk-ordered multi-GPU sum), so the
+        # float image of the last end-to-end step must hash to the committed value of this workload — on ANY number of GPUs
+        import hashlib
+        image_sha = hashlib.sha256(np.ascontiguousarray(out[0]).tobytes()).hexdigest()
+        hpath = os.path.join(GOLDEN, "image_hashes.json")
+        known = json.load(open(hpath)) if os.path.exists(hpath) else {}
+        want_sha = known.get(args.workload)
+        image_check = "no committed hash" if want_sha is None else ("ok" if want_sha == image_sha else "MISMATCH")
         total_samples = W * H * spp
         value = total_samples / (ms_step * 1e-3)
         rays = st["rays"] / args.steps * world            # rank 0 traced 1/world of them
@@ -455,8 +468,13 @@ def main():
         # no throughput record) + W8/sample when it also resolves the bounce-0 hits; shade R56/ray minus the 16-byte throughput
         # record at bounce 0, + W48 per survivor (rays - samples) + W16 per finished path; accumulate R16/sample (+12 B/pixel RMW
         # per pass, ignored).  Paths of empty camera tiles move fewer bytes than this (not subtracted: no such tile in RTIOW).
-        queue_bytes = ((32.0 + (8.0 if bounce0_in_generate else 0.0)) * samples_rank + 56.0 * rays_rank - 16.0 * samples_rank
-                       + 48.0 * (rays_rank - samples_rank) + 16.0 * samples_rank + 16.0 * samples_rank)
+        # Camera paths of empty tiles (their beam touches no leaf box) never enter the queues: under a constant background they move no
+        # bytes at all, under the sky gradient only their 16-byte radiance record (written by generate, read by accumulate).
+        skipped = float(sg.get("paths_skipped", 0))
+        gradient = sdesc.get("gradient", False)
+        queued = samples_rank - skipped
+        queue_bytes = ((32.0 + (8.0 if bounce0_in_generate else 0.0)) * queued + 56.0 * (rays_rank - skipped) - 16.0 * queued
+                       + 48.0 * (rays_rank - samples_rank) + 16.0 * queued + 16.0 * queued + (32.0 * skipped if gradient else 0.0))
         hbm_ach = queue_bytes / (ms_other * 1e-3) / 1e9 if ms_other > 0 else 0.0
         if args.workload == "rtiow_1080p_1024spp" and os.path.exists(tpath):
             tj = json.load(open(tpath))
@@ -466,7 +484,7 @@ def main():
             "metric": "samples_per_second", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "scene": scene, "width": W, "height": H, "spp": spp, "max_depth": sdesc["max_depth"],
-                       "objects": sdesc["objects"], "partition": f"spp split over {world} GPU(s), one NCCL reduce of the float accumulation buffer",
+                       "objects": sdesc["objects"], "partition": f"8 sample chunks dealt to {world} GPU(s); chunk sums gathered on rank 0 by the library (NCCL send/recv) and added in chunk order",
                        "l2": "wavefront queues (GBs) exceed the 126 MB L2 every pass; no explicit flush needed"},
             "mrays_per_s": rays / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays / total_samples,
             "stage_ms_per_step": {"generate": sg["ms_generate"], "extend": ms_extend, "shade": sg["ms_shade"], "accumulate": sg["ms_accumulate"],
@@ -481,6 +499,7 @@ def main():
             "e2e": {"value": total_samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": W * H * 3 * 4 + W * H * 3, "ms_per_step": ms_e2e},
             "gpu_launches": int(st["launches"] / args.steps), "clocks": clocks,
+            "image_sha256": image_sha, "image_check": image_check,
         }
         if world == 1 and not args.no_cpu_baseline:
             n, dt, desc, kind = reference_sample(args.workload, 1)
@@ -489,6 +508,9 @@ def main():
     r.close()
     if world > 1:
         dist.destroy_process_group()
+    if rank == 0 and image_check == "MISMATCH":
+        sys.stderr.write(f"bench.py: image hash {image_sha} differs from the committed {want_sha} for {args.workload}\n")
+        sys.exit(3)
 
 
 if __name__ == "__main__":

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 /* error codes */
 enum { RT_OK = 0, RT_ERR_INVALID = 1, RT_ERR_CUDA = 2, RT_ERR_IO = 3, RT_ERR_PARSE = 4, RT_ERR_NO_SCENE = 5, RT_ERR_NO_DEVICE = 6 };
@@ -123,7 +123,9 @@ enum { RT_RENDER_KEEP_ACCUM = 1,     /* add to the accumulation buffer instead o
                                         with an even material mix — measured slower on the reference's scenes) */
        RT_RENDER_SERIAL = 64,      /* one pass at a time on the context's stream (default: two passes in flight on two streams, so the
                                         short late-bounce launches of one overlap the other; same image either way) */
-       RT_RENDER_NO_TILE_LISTS = 256 }; /* traverse the tree for bounce 0 too (default: the generate stage resolves bounce-0 hits from the
+       RT_RENDER_NO_TILE_LISTS = 256,
+       RT_RENDER_KEEP_CHUNKS = 512 };  /* leave this call's chunk sums in their buffers instead of folding them into the accumulation
+                                        buffer: the root of a multi-GPU render gathers and folds them (rt_gather_image) */ /* traverse the tree for bounce 0 too (default: the generate stage resolves bounce-0 hits from the
                                         per-tile candidate lists of the camera beams; same image either way) */
 
 typedef struct rt_render_params {
@@ -132,7 +134,20 @@ typedef struct rt_render_params {
     int32_t spp_count;      /* number of samples; <= 0 means the scene's samples_per_pixel */
     int32_t flags;          /* RT_RENDER_* */
     int64_t max_paths_per_pass;   /* wavefront size cap; <= 0 picks a default from free device memory */
+    int32_t total_spp;      /* sample count of the whole image this call contributes to (sets the chunk boundaries of the
+                               fixed-order accumulation, rt_sample_chunk); <= 0: max(scene samples_per_pixel, spp_begin + spp_count) */
+    int32_t reserved;
 } rt_render_params;
+
+/* Fixed-order accumulation.  The samples [0, total_spp) of an image fall into RT_SAMPLE_CHUNKS chunks,
+ * chunk k = [k * total_spp / 8, (k + 1) * total_spp / 8).  A chunk's samples are summed one by one in ascending order into the
+ * chunk's own buffer; the image is (((c0 + c1) + c2) + ...) in ascending chunk order.  Because the boundaries depend on total_spp
+ * only, the float sums are bit-identical whether one GPU renders every chunk or several GPUs render disjoint sets of whole
+ * chunks (rt_comm_*, rt_group_*), and whether the chunks arrive in one rt_render call or in several ascending calls with
+ * RT_RENDER_KEEP_ACCUM.  (A call whose sample range cuts a chunk in two still renders every sample exactly once; only the
+ * rounding of that chunk's sum then differs from the one-call image.) */
+#define RT_SAMPLE_CHUNKS 8
+void rt_sample_chunk(int total_spp, int k, int *begin, int *end);
 
 typedef struct rt_stats {
     int64_t samples;            /* camera paths started */
@@ -145,6 +160,9 @@ typedef struct rt_stats {
     /* event counters for the algorithmic-flop model of SURVEY.md §8(d) (only with COUNT_EVENTS) */
     int64_t n_box_tests, n_sphere_reject, n_sphere_accept, n_rect_tests, n_cyl_reject, n_cyl_accept,
             n_tri_tests, n_boxprim_tests, n_shade, n_generate, n_node_visits;
+    int64_t n_generate_leaf_tests;  /* leaf tests the generate stage made on the tile candidate lists (COUNT_EVENTS; not in the n_*_tests above,
+                                       which are the extend stage's) */
+    int64_t paths_skipped;          /* camera paths of empty tiles that never entered the queues (their records move no bytes) */
 } rt_stats;
 
 typedef struct rt_scene_info {
@@ -184,6 +202,36 @@ int rt_accum_device_ptr(rt_ctx *ctx, void **dev_ptr, size_t *n_floats);
 /* Fixed-order sum of n_partials accumulation buffers (device pointers, e.g. gathered from the ranks) into this
  * ctx's accumulation buffer: acc = ((p0 + p1) + p2) + ...  — bit-reproducible for any GPU count. */
 int rt_accum_sum_ordered(rt_ctx *ctx, const void *const *partials, int n_partials);
+
+/* ---- several GPUs, one image (replaces the process-per-GPU scheme of gpu-version/blue.py:23-32) ----
+ * The sample chunks of the image (rt_sample_chunk) are dealt to the ranks, rank r renders chunks rt_rank_chunks(n, r) into per-chunk
+ * buffers, and the root gathers them over NVLink (NCCL send/receive on the render streams; NCCL is bound at run time with dlopen,
+ * RT_NCCL_LIB overrides the library name) and adds them in chunk order: the float image is bit-identical for any number of GPUs.
+ *
+ * (a) one process per GPU (torchrun / mpirun): every rank creates its own context; rank 0 calls rt_comm_unique_id and hands the 128
+ *     bytes to the others by any means (MPI, torch.distributed, a file); every rank calls rt_comm_init, then per image
+ *     rt_render_shard + rt_gather_image (both asynchronous on the context's stream), and the root rt_download. */
+void rt_rank_chunks(int n_ranks, int rank, int *chunk_begin, int *chunk_end);
+int rt_comm_unique_id(void *id, size_t bytes /* >= 128 */);
+int rt_comm_init(rt_ctx *ctx, const void *id, int n_ranks, int rank);
+int rt_comm_destroy(rt_ctx *ctx);           /* also done by rt_destroy */
+/* As rt_render for samples [0, spp_count) of which this rank renders its chunks (spp_begin must be 0; KEEP_ACCUM is ignored). */
+int rt_render_shard(rt_ctx *ctx, const rt_render_params *params);
+/* Moves every rank's chunk sums to `root` and folds them there into the accumulation buffer.  Collective: every rank calls it. */
+int rt_gather_image(rt_ctx *ctx, int root);
+/* (b) one process driving several devices: n contexts + ncclCommInitAll behind one handle; the image ends up on devices[0]. */
+typedef struct rt_group rt_group;
+int rt_group_create(rt_group **out, const int *devices, int n_devices);
+void rt_group_destroy(rt_group *g);
+const char *rt_group_last_error(const rt_group *g);    /* creation failures: rt_last_error(NULL) */
+int rt_group_size(const rt_group *g);
+rt_ctx *rt_group_ctx(rt_group *g, int i);              /* the i-th device's context (introspection; owned by the group) */
+int rt_group_scene_upload(rt_group *g, const rt_scene_desc *scene);
+int rt_group_scene_upload_json(rt_group *g, const char *path);
+int rt_group_scene_upload_json_text(rt_group *g, const char *json_text, const char *base_dir);
+int rt_group_scene_override(rt_group *g, int width, int height, int samples_per_pixel, int max_depth);
+int rt_group_render(rt_group *g, const rt_render_params *params);     /* asynchronous */
+int rt_group_download(rt_group *g, float *rgb_sum, size_t n_floats, unsigned char *rgb8, int total_spp, int gamma, rt_stats *stats);
 
 /* Synchronises.  rgb_sum (may be NULL): width*height*3 float sums, row 0 = bottom.  rgb8 (may be NULL):
  * width*height*3 bytes, tonemapped on the device by total_spp, rows flipped (row 0 = top), gamma != 0 applies the

@@ -190,9 +190,10 @@ static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t
 }
 
 typedef struct {
-    const rt_scene_desc *sc; orc_camera cam; uint32_t seed; int s0, sn; float *out;
+    const rt_scene_desc *sc; orc_camera cam; uint32_t seed; int s0, sn, total; float *out;
     int row_next; pthread_mutex_t mu; int64_t rays, shadow; nee_t nee;
     const orc_bvh *bvh; orc_trav_counters cnt;
+    int stride;            /* > 1: only pixels whose index is a multiple of stride are rendered (parity checks at full image sizes) */
 } job_t;
 
 static void *worker(void *arg) {
@@ -208,8 +209,18 @@ static void *worker(void *arg) {
         if (y >= H) break;
         for (int x = 0; x < W; ++x) {
             uint32_t pixel = (uint32_t)(y * W + x);
+            if (j->stride > 1 && pixel % (uint32_t)j->stride != 0) continue;
             v3 sum = V(0, 0, 0);
-            for (int s = j->s0; s < j->s0 + j->sn; ++s) {          /* main.cu:95-103 */
+            int first_chunk = 1;
+            /* fixed-order accumulation (rt.h: rt_sample_chunk): the samples fall into 8 chunks by the TOTAL sample count; a chunk is
+             * summed sample by sample (main.cu:95-103), the chunk sums are combined in chunk order */
+            for (int k = 0; k < RT_SAMPLE_CHUNKS; ++k) {
+            int cb = (int)((long long)k * j->total / RT_SAMPLE_CHUNKS), ce = (int)((long long)(k + 1) * j->total / RT_SAMPLE_CHUNKS);
+            if (k == RT_SAMPLE_CHUNKS - 1 && ce < j->s0 + j->sn) ce = j->s0 + j->sn;
+            const int pb = cb > j->s0 ? cb : j->s0, pe = ce < j->s0 + j->sn ? ce : j->s0 + j->sn;
+            if (pb >= pe) continue;
+            v3 csum = V(0, 0, 0);
+            for (int s = pb; s < pe; ++s) {
                 orc_rng rng; orc_rng_init(&rng, j->seed, pixel, (uint32_t)s, 0u, sc->sampling);
                 float u = ((float)x + orc_rng_next(&rng)) / (float)(W - 1);
                 float v = ((float)y + orc_rng_next(&rng)) / (float)(H - 1);
@@ -217,7 +228,10 @@ static void *worker(void *arg) {
                 int defocus = (sc->sampling & 1) == RT_SAMPLING_REFERENCE_CPU && sc->camera.aperture > 0.0f;
                 orc_get_ray(&j->cam, u, v, defocus, &rng, &o, &d);
                 v3 c = ray_color(sc, o, d, j->seed, pixel, (uint32_t)s, &rays, &j->nee, &shadow, j->bvh, &cnt);
-                sum = vadd(sum, c);                                   /* fixed order: ascending sample index */
+                csum = vadd(csum, c);                                 /* fixed order: ascending sample index */
+            }
+            sum = first_chunk ? csum : vadd(sum, csum);
+            first_chunk = 0;
             }
             float *q = j->out + 3 * (size_t)pixel;
             q[0] = sum.x; q[1] = sum.y; q[2] = sum.z;
@@ -232,12 +246,14 @@ static void *worker(void *arg) {
     return NULL;
 }
 
+static int g_stride = 1;      /* set by orc_render_bvh_strided around its render_impl call (test infrastructure: not re-entrant) */
 static int render_impl(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
-                       int flags, int64_t *n_rays, int64_t *n_shadow_rays, int use_bvh, int64_t *counters) {
+                       int flags, int64_t *n_rays, int64_t *n_shadow_rays, int use_bvh, int64_t *counters, int total_spp) {
     if (!sc || !rgb_sum || sc->width < 1 || sc->height < 1) return RT_ERR_INVALID;
     if ((flags & RT_RENDER_NEE) && (sc->sampling & 1) != RT_SAMPLING_REFERENCE_CPU) return RT_ERR_INVALID;
     job_t j; memset(&j, 0, sizeof j);
     j.sc = sc; j.seed = seed; j.s0 = spp_begin; j.sn = spp_count > 0 ? spp_count : sc->samples_per_pixel; j.out = rgb_sum;
+    j.total = total_spp > 0 ? total_spp : (sc->samples_per_pixel > j.s0 + j.sn ? sc->samples_per_pixel : j.s0 + j.sn);
     orc_camera_setup(&sc->camera, &j.cam);
     int *lights = (int *)malloc(sizeof(int) * (size_t)(sc->n_objects > 0 ? sc->n_objects : 1));
     unsigned char *is_light = (unsigned char *)calloc((size_t)(sc->n_objects > 0 ? sc->n_objects : 1), 1);
@@ -248,7 +264,7 @@ static int render_impl(const rt_scene_desc *sc, uint32_t seed, int spp_begin, in
     }
     j.nee.lights = lights; j.nee.is_light = is_light;
     orc_bvh *bvh = use_bvh ? orc_bvh_create(sc) : NULL;
-    j.bvh = bvh;
+    j.bvh = bvh; j.stride = g_stride;
     pthread_mutex_init(&j.mu, NULL);
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 256) n_threads = 256;
@@ -269,12 +285,26 @@ static int render_impl(const rt_scene_desc *sc, uint32_t seed, int spp_begin, in
 
 int orc_render_ex(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
                   int flags, int64_t *n_rays, int64_t *n_shadow_rays) {
-    return render_impl(sc, seed, spp_begin, spp_count, rgb_sum, n_threads, flags, n_rays, n_shadow_rays, 0, NULL);
+    return render_impl(sc, seed, spp_begin, spp_count, rgb_sum, n_threads, flags, n_rays, n_shadow_rays, 0, NULL, 0);
+}
+
+/* the samples [spp_begin, spp_begin + spp_count) of an image of total_spp samples: one rank's share of a multi-GPU render */
+int orc_render_range(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, int total_spp, float *rgb_sum, int n_threads,
+                     int64_t *n_rays) {
+    return render_impl(sc, seed, spp_begin, spp_count, rgb_sum, n_threads, 0, n_rays, NULL, 0, NULL, total_spp);
+}
+
+/* as orc_render_bvh for the pixels whose index is a multiple of `stride` only (the others stay untouched in rgb_sum) */
+int orc_render_bvh_strided(const rt_scene_desc *sc, uint32_t seed, float *rgb_sum, int n_threads, int stride, int64_t *n_rays) {
+    g_stride = stride > 1 ? stride : 1;
+    const int rc = render_impl(sc, seed, 0, 0, rgb_sum, n_threads, 0, n_rays, NULL, 1, NULL, 0);
+    g_stride = 1;
+    return rc;
 }
 
 int orc_render_bvh(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
                    int flags, int64_t *n_rays, int64_t *counters) {
-    return render_impl(sc, seed, spp_begin, spp_count, rgb_sum, n_threads, flags, n_rays, NULL, 1, counters);
+    return render_impl(sc, seed, spp_begin, spp_count, rgb_sum, n_threads, flags, n_rays, NULL, 1, counters, 0);
 }
 
 int orc_render(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,

@@ -36,6 +36,10 @@ int orc_render(const rt_scene_desc *scene, uint32_t seed, int spp_begin, int spp
 /* as orc_render, with rt_render flags (RT_RENDER_NEE: next-event estimation, reference_cpu sampling only) */
 int orc_render_ex(const rt_scene_desc *scene, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum,
                   int n_threads, int flags, int64_t *n_rays, int64_t *n_shadow_rays);
+/* samples [spp_begin, spp_begin + spp_count) of an image of total_spp samples (chunk boundaries of the fixed-order accumulation
+ * from total_spp, rt.h: rt_sample_chunk) */
+int orc_render_range(const rt_scene_desc *scene, uint32_t seed, int spp_begin, int spp_count, int total_spp, float *rgb_sum,
+                     int n_threads, int64_t *n_rays);
 /* first-hit record, 24 floats per pixel (same layout as oracle/ref_build/ref_gpu_harness.cpp `aov`) */
 int orc_aov(const rt_scene_desc *scene, float *aov);
 /* color.cuh:15-35 (gamma=0) / color.cuh:70-95 (gamma=1): rgb8 rows flipped so row 0 = top */
@@ -76,6 +80,8 @@ int orc_lbvh_build_ex(const rt_scene_desc *scene, uint64_t *morton_sorted, int32
  * box-primitive tests, deepest stack — the serial statement of the device's event counters (rt_stats). */
 int orc_render_bvh(const rt_scene_desc *scene, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
                    int flags, int64_t *n_rays, int64_t *counters);
+/* orc_render_bvh restricted to the pixels whose index is a multiple of `stride` (others untouched): full-size parity checks */
+int orc_render_bvh_strided(const rt_scene_desc *scene, uint32_t seed, float *rgb_sum, int n_threads, int stride, int64_t *n_rays);
 /* stable LSD radix sort of (key, value) pairs — the host statement of the device sort, exposed for tests */
 void orc_radix_sort_pairs(uint64_t *keys, int32_t *vals, int n);
 

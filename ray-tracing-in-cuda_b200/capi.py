@@ -17,6 +17,8 @@ RT_SAMPLING_DIRECT = 2       # flag: direct draws instead of the reference's rej
 RT_RENDER_KEEP_ACCUM, RT_RENDER_COUNT_EVENTS, RT_RENDER_NO_SORT, RT_RENDER_NEE, RT_RENDER_TIME_STAGES, RT_RENDER_SORT = 1, 2, 4, 8, 16, 32
 RT_RENDER_SERIAL = 64
 RT_RENDER_NO_TILE_LISTS = 256
+RT_RENDER_KEEP_CHUNKS = 512
+RT_SAMPLE_CHUNKS = 8
 
 
 class ObjectDesc(C.Structure):
@@ -60,7 +62,7 @@ class SceneDesc(C.Structure):
 
 class RenderParams(C.Structure):
     _fields_ = [("seed", C.c_uint32), ("spp_begin", C.c_int32), ("spp_count", C.c_int32), ("flags", C.c_int32),
-                ("max_paths_per_pass", C.c_int64)]
+                ("max_paths_per_pass", C.c_int64), ("total_spp", C.c_int32), ("reserved", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -70,7 +72,8 @@ class Stats(C.Structure):
                 ("n_box_tests", C.c_int64), ("n_sphere_reject", C.c_int64), ("n_sphere_accept", C.c_int64),
                 ("n_rect_tests", C.c_int64), ("n_cyl_reject", C.c_int64), ("n_cyl_accept", C.c_int64),
                 ("n_tri_tests", C.c_int64), ("n_boxprim_tests", C.c_int64), ("n_shade", C.c_int64),
-                ("n_generate", C.c_int64), ("n_node_visits", C.c_int64)]
+                ("n_generate", C.c_int64), ("n_node_visits", C.c_int64),
+                ("n_generate_leaf_tests", C.c_int64), ("paths_skipped", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -86,7 +89,10 @@ class SceneInfo(C.Structure):
 RT_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_scene_upload", "rt_scene_upload_json",
               "rt_scene_upload_json_text", "rt_scene_info_get", "rt_scene_override", "rt_render", "rt_render_aov",
               "rt_accum_device_ptr", "rt_accum_sum_ordered", "rt_download", "rt_synchronize", "rt_stats_reset",
-              "rt_bvh_download", "rt_bvh_info", "rt_write_ppm", "rt_write_png", "rt_read_png", "rt_free", "rt_probe_fp32_peak", "rt_host_alloc",
+              "rt_bvh_download", "rt_bvh_info", "rt_sample_chunk", "rt_rank_chunks", "rt_comm_unique_id", "rt_comm_init", "rt_comm_destroy",
+              "rt_render_shard", "rt_gather_image", "rt_group_create", "rt_group_destroy", "rt_group_last_error", "rt_group_size", "rt_group_ctx",
+              "rt_group_scene_upload", "rt_group_scene_upload_json", "rt_group_scene_upload_json_text", "rt_group_scene_override",
+              "rt_group_render", "rt_group_download", "rt_write_ppm", "rt_write_png", "rt_read_png", "rt_free", "rt_probe_fp32_peak", "rt_host_alloc",
               "rt_host_free"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -116,6 +122,24 @@ def load_library(path=None):
     lib.rt_scene_info_get.argtypes = [vp, P(SceneInfo)]
     lib.rt_scene_override.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
     lib.rt_render.argtypes = [vp, P(RenderParams)]
+    lib.rt_rank_chunks.argtypes = [C.c_int, C.c_int, P(C.c_int), P(C.c_int)]; lib.rt_rank_chunks.restype = None
+    lib.rt_comm_unique_id.argtypes = [vp, C.c_size_t]
+    lib.rt_comm_init.argtypes = [vp, vp, C.c_int, C.c_int]
+    lib.rt_comm_destroy.argtypes = [vp]
+    lib.rt_render_shard.argtypes = [vp, P(RenderParams)]
+    lib.rt_gather_image.argtypes = [vp, C.c_int]
+    lib.rt_group_create.argtypes = [P(vp), P(C.c_int), C.c_int]
+    lib.rt_group_destroy.argtypes = [vp]; lib.rt_group_destroy.restype = None
+    lib.rt_group_last_error.argtypes = [vp]; lib.rt_group_last_error.restype = C.c_char_p
+    lib.rt_group_size.argtypes = [vp]
+    lib.rt_group_ctx.argtypes = [vp, C.c_int]; lib.rt_group_ctx.restype = vp
+    lib.rt_group_scene_upload.argtypes = [vp, P(SceneDesc)]
+    lib.rt_group_scene_upload_json.argtypes = [vp, C.c_char_p]
+    lib.rt_group_scene_upload_json_text.argtypes = [vp, C.c_char_p, C.c_char_p]
+    lib.rt_group_scene_override.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.rt_group_render.argtypes = [vp, P(RenderParams)]
+    lib.rt_group_download.argtypes = [vp, P(C.c_float), C.c_size_t, P(C.c_ubyte), C.c_int, C.c_int, P(Stats)]
+    lib.rt_sample_chunk.argtypes = [C.c_int, C.c_int, P(C.c_int), P(C.c_int)]; lib.rt_sample_chunk.restype = None
     lib.rt_render_aov.argtypes = [vp, P(C.c_float), C.c_size_t]
     lib.rt_accum_device_ptr.argtypes = [vp, P(vp), P(C.c_size_t)]
     lib.rt_accum_sum_ordered.argtypes = [vp, P(vp), C.c_int]

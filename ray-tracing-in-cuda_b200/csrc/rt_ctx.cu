@@ -77,6 +77,7 @@ static void free_images(rt_ctx *c) {
 
 extern "C" void rt_destroy(rt_ctx *c) {
     if (!c) return;
+    rt_comm_destroy(c);
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     free_images(c);
@@ -91,6 +92,7 @@ extern "C" void rt_destroy(rt_ctx *c) {
     for (int k = 1; k < RT_MAX_SETS; ++k) if (c->extra_stream[k]) cudaStreamDestroy(c->extra_stream[k]);
     c->d_counters.release(); c->d_tile_list.release(); c->d_tile_cnt.release(); c->d_tile_bad.release(); c->d_accum.release(); c->d_rgb8.release(); c->d_aov.release();
     c->d_partials.release(); c->d_rays.release();
+    for (int k = 0; k < RT_ACC_CHUNKS; ++k) c->d_chunk[k].release();
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     for (int k = 0; k < 2; ++k) if (c->ev_count[k]) cudaEventDestroy(c->ev_count[k]);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -465,6 +467,7 @@ static int ensure_tile_lists(rt_ctx *ctx) {
     static const bool keep_empty = getenv("RT_NO_EMPTY_TILES") != nullptr;
     if (n_empty > 0 && !keep_empty) ds.tile_empty_prefix = ctx->d_tile_prefix.p;
     ctx->tiles_all_empty = ds.tile_empty_prefix && ds.tile_mode == 1 && n_empty == n_tiles;
+    ctx->tiles_n_empty = ds.tile_empty_prefix ? n_empty : 0;
     return RT_OK;
 }
 
@@ -492,6 +495,16 @@ static int ensure_accum(rt_ctx *ctx) {
     const size_t n = (size_t)ctx->ds.width * ctx->ds.height * 3;
     if (ctx->d_accum.n < n) { CU(ctx->d_accum.alloc(n)); ctx->accum_valid = false; }
     return RT_OK;
+}
+
+static_assert(RT_ACC_CHUNKS == RT_SAMPLE_CHUNKS, "chunk count of the kernels and of rt.h");
+extern "C" void rt_sample_chunk(int total_spp, int k, int *begin, int *end) {
+    if (total_spp < 0) total_spp = 0;
+    if (k < 0) k = 0;
+    if (k > RT_SAMPLE_CHUNKS) k = RT_SAMPLE_CHUNKS;
+    const long long b = (long long)k * total_spp / RT_SAMPLE_CHUNKS, e = k < RT_SAMPLE_CHUNKS ? (long long)(k + 1) * total_spp / RT_SAMPLE_CHUNKS : total_spp;
+    if (begin) *begin = (int)b;
+    if (end) *end = (int)e;
 }
 
 extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
@@ -529,11 +542,26 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         long long by_mem = (long long)((double)(free_b + held) * 0.5 / per_path) / n_sets;
         // big wavefronts amortise the ~100 short late-bounce launches of a pass: 2 x 256 M paths = 61 GB of the 180 GB
         // (RTIOW 1080p 1024 spp: 508.9 / 498.3 / 493.3 ms per step at 64 / 128 / 256 M paths per stream)
-        max_paths = std::min<long long>(by_mem, (512ll << 20) / n_sets);
+        // (576 M: one 128-sample chunk of a 1080p image — 265 M paths — stays one pass per stream)
+        max_paths = std::min<long long>(by_mem, (576ll << 20) / n_sets);
     }
     max_paths = std::min<long long>(max_paths, 1ll << 30);
-    int s_pass = (int)std::max<long long>(1, std::min<long long>(spp, max_paths / np));
-    if (n_sets > 1) s_pass = std::min(s_pass, (spp + n_sets - 1) / n_sets);        // at least one pass per stream
+    // Fixed-order accumulation (rt.h: rt_sample_chunk): the samples of the render fall into RT_ACC_CHUNKS chunks whose boundaries
+    // depend on the TOTAL sample count only; a chunk is summed sample by sample into its own buffer, the buffers are combined in
+    // chunk order.  A pass never straddles a chunk boundary.
+    const int total_spp = prm->total_spp > 0 ? prm->total_spp : std::max(ctx->hs.d.samples_per_pixel, prm->spp_begin + spp);
+    struct Piece { int chunk, begin, end; };
+    std::vector<Piece> pieces;
+    int largest_piece = 1;
+    for (int k = 0; k < RT_ACC_CHUNKS; ++k) {
+        int cb, ce;
+        rt_sample_chunk(total_spp, k, &cb, &ce);
+        if (k == RT_ACC_CHUNKS - 1) ce = std::max(ce, prm->spp_begin + spp);      // samples past the total count the last chunk
+        const int pb = std::max(cb, prm->spp_begin), pe = std::min(ce, prm->spp_begin + spp);
+        if (pb < pe) { pieces.push_back({k, pb, pe}); largest_piece = std::max(largest_piece, pe - pb); }
+    }
+    int s_pass = (int)std::max<long long>(1, std::min<long long>(largest_piece, max_paths / np));
+    if (n_sets > 1 && pieces.size() == 1) s_pass = std::min(s_pass, (largest_piece + n_sets - 1) / n_sets);        // at least one pass per stream
     const long long cap = (long long)s_pass * np;
     if (cap > (1ll << 30) - 64) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: image too large for one wavefront pass");
     int rc = ensure_accum(ctx); if (rc) return rc;
@@ -549,7 +577,8 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     float ms_stage[5] = {0, 0, 0, 0, 0};
     cudaEvent_t *evs = ctx->ev_count;       // COUNT_EVENTS: one synchronising event pair per stage launch (owned by the context)
     if (time_stages) {          // event pairs are recorded without synchronising and resolved in rt_download
-        const size_t n_passes = (size_t)((spp + s_pass - 1) / s_pass);
+        size_t n_passes = 0;
+        for (const Piece &pc : pieces) n_passes += (size_t)((pc.end - pc.begin + s_pass - 1) / s_pass);
         const size_t need = ctx->pending.size() + n_passes * (2 + 3 * (size_t)ds.max_depth);
         while (ctx->ev_pool.size() < 2 * need) { cudaEvent_t e; if (cudaEventCreate(&e) != cudaSuccess) return rt_fail(ctx, RT_ERR_CUDA, "cudaEventCreate"); ctx->ev_pool.push_back(e); }
     }
@@ -568,41 +597,59 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         for (int k = 1; k < n_sets; ++k) CU(cudaStreamWaitEvent(ctx->extra_stream[k], ctx->ev_fork, 0));
     }
     int last_set = 0;
-    for (int done = 0; done < spp; done += s_pass) {
-        const int sn = std::min(s_pass, spp - done);
-        const int n_paths = sn * np;
-        const int k = (int)(passes % n_sets);
-        QueueSet &S = ctx->qs[k];
-        const LaunchCfg &cfg = S.cfg;
-        launch_pass_init(cfg, S.q, ds.max_depth, n_paths);
-        // bounce 0: generate resolves the hits of every path whose tile has a candidate list (ds.tile_mode; k_generate)
-        const int tile_mode = (prm->flags & RT_RENDER_NO_TILE_LISTS) ? 0 : ds.tile_mode;
-        DScene dsp = ds;                 // this pass's view of the scene: no tile data when the candidate lists are switched off
-        if (tile_mode == 0) { dsp.tile_mode = 0; dsp.tile_list = nullptr; dsp.tile_cnt = nullptr; dsp.tile_empty_prefix = nullptr; }
-        timed(0, [&] { launch_generate(cfg, dsp, S.q, prm->seed, prm->spp_begin + done, n_paths, nee, tile_mode != 0, count); });
-        int buf = 0;
-        // every tile's beam misses everything (empty scene, camera looking away): no path enters the queues
-        const bool no_paths = tile_mode == 1 && ctx->tiles_all_empty;
-        const int depth_needed = ctx->scene_scatters ? ds.max_depth : 1;      // nothing survives the first vertex of an all-emitter scene
-        for (int b = 0; b < depth_needed && !no_paths; ++b) {
-            if (b > 0 || tile_mode != 1) timed(1, [&] { launch_extend(cfg, dsp, S.q, b, buf, count, b == 0 && tile_mode == 2); });
-            timed(2, [&] { launch_shade(cfg, dsp, S.q, prm->seed, prm->spp_begin + done, b, buf, b == ds.max_depth - 1, count, sort, nee); });
-            if (nee) timed(4, [&] { launch_shadow(cfg, dsp, S.q, b); });
-            buf ^= 1;
+    const size_t n_img = (size_t)np * 3;
+    ChunkPtrs cp{};
+    int n_cp = 0;
+    for (const Piece &pc : pieces) {
+        CU(ctx->d_chunk[pc.chunk].alloc(n_img));
+        cp.p[n_cp++] = ctx->d_chunk[pc.chunk].p;
+        // equal passes within the piece (a 128-sample chunk at a 123-sample cap: 64 + 64, not 123 + 5)
+        const int len = pc.end - pc.begin, n_pass = (len + s_pass - 1) / s_pass, step = (len + n_pass - 1) / n_pass;
+        bool clear_chunk = true;
+        for (int done = 0; done < len; done += step) {
+            const int sn = std::min(step, len - done);
+            const int n_paths = sn * np;
+            const int k = (int)(passes % n_sets);
+            QueueSet &S = ctx->qs[k];
+            const LaunchCfg &cfg = S.cfg;
+            const int first_sample = pc.begin + done;
+            launch_pass_init(cfg, S.q, ds.max_depth, n_paths);
+            // bounce 0: generate resolves the hits of every path whose tile has a candidate list (ds.tile_mode; k_generate)
+            const int tile_mode = (prm->flags & RT_RENDER_NO_TILE_LISTS) ? 0 : ds.tile_mode;
+            DScene dsp = ds;                 // this pass's view of the scene: no tile data when the candidate lists are switched off
+            if (tile_mode == 0) { dsp.tile_mode = 0; dsp.tile_list = nullptr; dsp.tile_cnt = nullptr; dsp.tile_empty_prefix = nullptr; }
+            timed(0, [&] { launch_generate(cfg, dsp, S.q, prm->seed, first_sample, n_paths, nee, tile_mode != 0, count); });
+            int buf = 0;
+            // every tile's beam misses everything (empty scene, camera looking away): no path enters the queues
+            const bool no_paths = tile_mode == 1 && ctx->tiles_all_empty;
+            if (dsp.tile_empty_prefix) ctx->stats.paths_skipped += (long long)ctx->tiles_n_empty * 32 * sn;
+            const int depth_needed = ctx->scene_scatters ? ds.max_depth : 1;      // nothing survives the first vertex of an all-emitter scene
+            for (int b = 0; b < depth_needed && !no_paths; ++b) {
+                if (b > 0 || tile_mode != 1) timed(1, [&] { launch_extend(cfg, dsp, S.q, b, buf, count, b == 0 && tile_mode == 2); });
+                timed(2, [&] { launch_shade(cfg, dsp, S.q, prm->seed, first_sample, b, buf, b == ds.max_depth - 1, count, sort, nee); });
+                if (nee) timed(4, [&] { launch_shadow(cfg, dsp, S.q, b); });
+                buf ^= 1;
+            }
+            // samples are added to a chunk buffer in ascending order whatever the stream: pass p's accumulate follows pass p-1's
+            if (n_sets > 1 && passes > 0) CU(cudaStreamWaitEvent(cfg.stream, ctx->qs[last_set].ev_acc, 0));
+            const int *const_tiles = (dsp.tile_empty_prefix && ds.bg_mode != RT_BG_SKY_GRADIENT) ? dsp.tile_cnt : nullptr;
+            timed(3, [&] { launch_accumulate(cfg, S.q, ctx->d_chunk[pc.chunk].p, ds.width, ds.height, sn, clear_chunk, ds.max_depth, ctx->d_rays.p,
+                                             const_tiles, ds.background); });
+            if (n_sets > 1) CU(cudaEventRecord(S.ev_acc, cfg.stream));
+            clear_chunk = false;
+            last_set = k;
+            ++passes;
         }
-        // samples are added to the image in ascending order whatever the stream: pass p's accumulate follows pass p-1's
-        if (n_sets > 1 && passes > 0) CU(cudaStreamWaitEvent(cfg.stream, ctx->qs[last_set].ev_acc, 0));
-        const int *const_tiles = (dsp.tile_empty_prefix && ds.bg_mode != RT_BG_SKY_GRADIENT) ? dsp.tile_cnt : nullptr;
-        timed(3, [&] { launch_accumulate(cfg, S.q, ctx->d_accum.p, ds.width, ds.height, sn, clear, ds.max_depth, ctx->d_rays.p, const_tiles,
-                                         ds.background); });
-        if (n_sets > 1) CU(cudaEventRecord(S.ev_acc, cfg.stream));
-        clear = false;
-        last_set = k;
-        ++passes;
     }
     if (n_sets > 1) {           // join: the caller's stream continues after both pass streams
         // (a last pass on the caller's stream has already waited for the other stream's final accumulate)
         if (last_set != 0) CU(cudaStreamWaitEvent(s, ctx->qs[last_set].ev_acc, 0));
+    }
+    for (int k = 0; k < RT_ACC_CHUNKS; ++k) ctx->chunk_live[k] = 0;
+    if (prm->flags & RT_RENDER_KEEP_CHUNKS) {      // multi-GPU: the chunk buffers travel to the root (rt_gather_image), which folds them
+        for (const Piece &pc : pieces) ctx->chunk_live[pc.chunk] = 1;
+    } else {
+        launch_fold_chunks(ctx->cfg, ctx->d_accum.p, cp, n_cp, !clear, (long long)n_img);
     }
     CU(cudaEventRecord(ctx->ev1, s));
     if (trace) {
@@ -612,7 +659,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
                 passes, s_pass, n_sets);
     }
     CU(cudaGetLastError());
-    ctx->accum_valid = true;
+    if (!(prm->flags & RT_RENDER_KEEP_CHUNKS)) ctx->accum_valid = true;
     rt_stats &st = ctx->stats;
     st.samples += (long long)spp * np; st.passes += passes;
     if (count) {
@@ -623,6 +670,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         st.n_rect_tests += c[CTR_RECT]; st.n_cyl_reject += c[CTR_CYL_REJECT]; st.n_cyl_accept += c[CTR_CYL_ACCEPT];
         st.n_tri_tests += c[CTR_TRI]; st.n_boxprim_tests += c[CTR_BOXPRIM]; st.n_shade += c[CTR_SHADE];
         st.n_generate += (long long)spp * np; st.n_node_visits += c[CTR_NODE_VISITS];
+        st.n_generate_leaf_tests += c[CTR_GEN_LEAF];
         st.ms_generate += ms_stage[0]; st.ms_extend += ms_stage[1]; st.ms_shade += ms_stage[2]; st.ms_accumulate += ms_stage[3]; st.ms_shadow += ms_stage[4];
         if (c[CTR_STACK_OVERFLOW]) return rt_fail(ctx, RT_ERR_INVALID, "traversal stack overflow (BVH deeper than RT_TRAV_STACK)");
     }

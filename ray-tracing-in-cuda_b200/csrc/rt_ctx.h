@@ -76,7 +76,9 @@ struct rt_ctx {
     cudaEvent_t ev_fork = nullptr;
     DevBuf<unsigned long long> d_counters, d_rays;
     // primary-ray candidate lists per 8x4 tile (rebuilt after an upload or a size override)
-    DevBuf<int> d_tile_list, d_tile_cnt, d_tile_bad, d_tile_prefix; bool tiles_dirty = true, tiles_all_empty = false;
+    DevBuf<int> d_tile_list, d_tile_cnt, d_tile_bad, d_tile_prefix; bool tiles_dirty = true, tiles_all_empty = false; int tiles_n_empty = 0;
+    DevBuf<float> d_chunk[RT_ACC_CHUNKS];   // per-sample-chunk sums of the current render (folded into d_accum in chunk order)
+    int chunk_live[RT_ACC_CHUNKS] = {};    // chunks rendered by the last rt_render with RT_RENDER_KEEP_CHUNKS (multi-GPU gather)
     DevBuf<float> d_accum; DevBuf<unsigned char> d_rgb8; DevBuf<float> d_aov; DevBuf<const float *> d_partials;
     // stats
     rt_stats stats{};
@@ -84,6 +86,9 @@ struct rt_ctx {
     std::vector<cudaEvent_t> ev_pool;   // RT_RENDER_TIME_STAGES: (start, stop) pairs, resolved in rt_download
     std::vector<int> pending;           // stage id per recorded pair
     bool accum_valid = false;
+    // multi-GPU (rt_multi.cu): NCCL communicator of this context's rank, bound at run time
+    void *comm = nullptr; int comm_ranks = 1, comm_rank = 0; bool comm_owned = false;
+    int shard_total = 0;               // total sample count of the last rt_render_shard
 };
 
 int rt_fail(rt_ctx *ctx, int code, const std::string &msg);

@@ -110,12 +110,8 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
             q.hits[i] = make_int2(__float_as_int(best_t), best_code);
         }
     }
-    if (HITS && COUNT) {
-        flush_counter<COUNT>(q.counters, CTR_SPH_REJECT, cnt.sph_rej); flush_counter<COUNT>(q.counters, CTR_SPH_ACCEPT, cnt.sph_acc);
-        flush_counter<COUNT>(q.counters, CTR_RECT, cnt.rect); flush_counter<COUNT>(q.counters, CTR_CYL_REJECT, cnt.cyl_rej);
-        flush_counter<COUNT>(q.counters, CTR_CYL_ACCEPT, cnt.cyl_acc); flush_counter<COUNT>(q.counters, CTR_TRI, cnt.tri);
-        flush_counter<COUNT>(q.counters, CTR_BOXPRIM, cnt.boxprim);
-    }
+    if (HITS && COUNT)       // this stage's own leaf tests (one counter: they are not extend-stage work)
+        flush_counter<COUNT>(q.counters, CTR_GEN_LEAF, cnt.sph_rej + cnt.sph_acc + cnt.rect + cnt.cyl_rej + cnt.cyl_acc + cnt.tri + cnt.boxprim);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -585,6 +581,19 @@ __global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restric
     }
 }
 
+// Fixed-order combination of the sample chunks of a render (rt_ctx.cu:rt_render): image = (((c0 + c1) + c2) + ...) in ascending
+// chunk order, each c_k a sequential sum over the samples of chunk k.  The chunk boundaries depend on the total sample count
+// only, so the image is bit-identical whether one GPU renders all chunks or eight GPUs render one each.
+__global__ void __launch_bounds__(RT_BLOCK) k_fold_chunks(float *__restrict__ accum, ChunkPtrs cp, int n_chunks, int keep, long long n) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float a = keep ? accum[i] : 0.0f;
+#pragma unroll
+        for (int k = 0; k < RT_ACC_CHUNKS; ++k)
+            if (k < n_chunks) a = (k == 0 && !keep) ? cp.p[0][i] : a + cp.p[k][i];
+        accum[i] = a;
+    }
+}
+
 // acc = ((p0 + p1) + p2) + ... : fixed-order combination of per-GPU partial sums
 __global__ void k_sum_ordered(float *__restrict__ accum, const float *const *__restrict__ partials, int n_partials, long long n) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -828,6 +837,12 @@ void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W,
     int blocks = (W * H + RT_BLOCK - 1) / RT_BLOCK;
     k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, accum, W, H, n_samples, clear ? 1 : 0, q.qcount, max_depth, total_rays, q.shcount,
                                                     const_tiles, bg);
+    bump(c);
+}
+
+void launch_fold_chunks(const LaunchCfg &c, float *accum, const ChunkPtrs &cp, int n_chunks, bool keep, long long n) {
+    if (n_chunks <= 0) return;
+    k_fold_chunks<<<persistent_grid(c, 8), RT_BLOCK, 0, c.stream>>>(accum, cp, n_chunks, keep ? 1 : 0, n);
     bump(c);
 }
 

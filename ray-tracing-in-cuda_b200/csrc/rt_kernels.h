@@ -22,6 +22,9 @@ void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const in
 void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce);
 void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W, int H, int n_samples, bool clear, int max_depth,
                        unsigned long long *total_rays, const int *const_tiles, float3 bg);
+#define RT_ACC_CHUNKS 8            // sample chunks of the fixed-order accumulation (rt.h: rt_sample_chunk)
+struct ChunkPtrs { const float *p[RT_ACC_CHUNKS]; };
+void launch_fold_chunks(const LaunchCfg &c, float *accum, const ChunkPtrs &cp, int n_chunks, bool keep, long long n);
 void launch_sum_ordered(const LaunchCfg &c, float *accum, const float *const *partials_dev, int n_partials, long long n);
 void launch_tonemap(const LaunchCfg &c, const float *accum, unsigned char *rgb8, int W, int H, int spp, int gamma);
 void launch_aov(const LaunchCfg &c, const DScene &sc, float *out);

@@ -14,7 +14,7 @@
 
 // event counters (rt_stats, SURVEY.md §8(d) flop model)
 enum { CTR_BOX = 0, CTR_SPH_REJECT, CTR_SPH_ACCEPT, CTR_RECT, CTR_CYL_REJECT, CTR_CYL_ACCEPT, CTR_TRI, CTR_BOXPRIM,
-       CTR_SHADE, CTR_GENERATE, CTR_NODE_VISITS, CTR_STACK_OVERFLOW, CTR_COUNT = 16 };
+       CTR_SHADE, CTR_GENERATE, CTR_NODE_VISITS, CTR_STACK_OVERFLOW, CTR_GEN_LEAF, CTR_COUNT = 16 };
 
 // SoA ray queues: every per-ray field is one float4 array, read and written with coalesced 16-byte accesses.
 struct Queues {

@@ -74,9 +74,33 @@ class Renderer:
         return i
 
     # ---- render ----
-    def render(self, seed=0x2023, spp_begin=0, spp_count=0, flags=0, max_paths_per_pass=0):
-        p = capi.RenderParams(seed, spp_begin, spp_count, flags, max_paths_per_pass)
+    def render(self, seed=0x2023, spp_begin=0, spp_count=0, flags=0, max_paths_per_pass=0, total_spp=0):
+        p = capi.RenderParams(seed, spp_begin, spp_count, flags, max_paths_per_pass, total_spp, 0)
         self._check(self.lib.rt_render(self.ctx, C.byref(p)), "rt_render")
+
+    # ---- several GPUs, one image: one context per rank (rt_comm_*, rt_render_shard, rt_gather_image) ----
+    @staticmethod
+    def comm_unique_id(lib_path=None):
+        """128 bytes from rank 0, to be handed to every rank (torch.distributed / MPI / a file) for comm_init."""
+        lib = capi.load_library(lib_path)
+        buf = C.create_string_buffer(128)
+        rc = lib.rt_comm_unique_id(buf, 128)
+        if rc != 0:
+            msg = lib.rt_last_error(None)
+            raise RtError(f"rt_comm_unique_id failed ({rc}): {msg.decode() if msg else ''}")
+        return buf.raw
+
+    def comm_init(self, unique_id, n_ranks, rank):
+        self._check(self.lib.rt_comm_init(self.ctx, C.c_char_p(bytes(unique_id)), int(n_ranks), int(rank)), "rt_comm_init")
+
+    def render_shard(self, seed=0x2023, spp_count=0, flags=0, max_paths_per_pass=0):
+        """This rank's whole sample chunks of an image of spp_count (default: the scene's) samples; asynchronous."""
+        p = capi.RenderParams(seed, 0, spp_count, flags, max_paths_per_pass, 0, 0)
+        self._check(self.lib.rt_render_shard(self.ctx, C.byref(p)), "rt_render_shard")
+
+    def gather_image(self, root=0):
+        """Collective: every rank's chunk sums travel to `root`, which adds them in chunk order (bit-identical for any rank count)."""
+        self._check(self.lib.rt_gather_image(self.ctx, int(root)), "rt_gather_image")
 
     def render_aov(self):
         i = self.info()
@@ -160,6 +184,72 @@ class Renderer:
                  leaf_aabb=r["leaf_aabb"][:n], left=r["left"][:m], right=r["right"][:m], node_aabb=r["node_aabb"][:m],
                  parent=r["parent"][:max(2 * nt.value - 1, 0)])
         return r
+
+
+class Group:
+    """One process driving several GPUs (rt_group_*): scene replicated, the sample chunks of an image dealt to the devices,
+    chunk sums gathered on devices[0] over NVLink and added in chunk order."""
+
+    def __init__(self, devices, lib_path=None):
+        self.lib = capi.load_library(lib_path)
+        self.g = C.c_void_p()
+        arr = (C.c_int * len(devices))(*devices)
+        rc = self.lib.rt_group_create(C.byref(self.g), arr, len(devices))
+        if rc != 0:
+            msg = self.lib.rt_last_error(None)
+            raise RtError(f"rt_group_create failed ({rc}): {msg.decode() if msg else ''}")
+        self.devices = list(devices)
+
+    def _check(self, rc, what):
+        if rc != 0:
+            msg = self.lib.rt_group_last_error(self.g)
+            raise RtError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    def close(self):
+        if getattr(self, "g", None):
+            self.lib.rt_group_destroy(self.g)
+            self.g = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload_json(self, path):
+        self._check(self.lib.rt_group_scene_upload_json(self.g, os.fsencode(path)), "rt_group_scene_upload_json")
+
+    def upload_json_text(self, text, base_dir=None):
+        self._check(self.lib.rt_group_scene_upload_json_text(self.g, text.encode(), os.fsencode(base_dir) if base_dir else None),
+                    "rt_group_scene_upload_json_text")
+
+    def upload(self, scene_desc):
+        d = getattr(scene_desc, "desc", scene_desc)
+        self._check(self.lib.rt_group_scene_upload(self.g, C.byref(d)), "rt_group_scene_upload")
+
+    def override(self, width=0, height=0, spp=0, max_depth=0):
+        self._check(self.lib.rt_group_scene_override(self.g, width or 0, height or 0, spp or 0, max_depth or 0), "rt_group_scene_override")
+
+    def info(self):
+        i = capi.SceneInfo()
+        if self.lib.rt_scene_info_get(self.lib.rt_group_ctx(self.g, 0), C.byref(i)) != 0:
+            raise RtError("rt_scene_info_get failed")
+        return i
+
+    def render(self, seed=0x2023, spp_count=0, flags=0, max_paths_per_pass=0):
+        p = capi.RenderParams(seed, 0, spp_count, flags, max_paths_per_pass, 0, 0)
+        self._check(self.lib.rt_group_render(self.g, C.byref(p)), "rt_group_render")
+
+    def download(self, total_spp=0, gamma=0, want_sum=True, want_rgb8=True):
+        i = self.info()
+        rgb_sum = np.zeros((i.height, i.width, 3), np.float32) if want_sum else None
+        rgb8 = np.zeros((i.height, i.width, 3), np.uint8) if want_rgb8 else None
+        st = capi.Stats()
+        self._check(self.lib.rt_group_download(self.g, rgb_sum.ctypes.data_as(C.POINTER(C.c_float)) if want_sum else None,
+                                               rgb_sum.size if want_sum else 0,
+                                               rgb8.ctypes.data_as(C.POINTER(C.c_ubyte)) if want_rgb8 else None, total_spp, gamma, C.byref(st)),
+                    "rt_group_download")
+        return rgb_sum, rgb8, st.as_dict()
 
 
 def write_ppm(path, rgb8):

@@ -52,6 +52,8 @@ def lib():
                                      P(C.c_int32), fp, fp, fp]
         L.orc_lbvh_build_ex.argtypes = [P(capi.SceneDesc), P(C.c_uint64), P(C.c_int32), P(C.c_int32), P(C.c_int32),
                                         P(C.c_int32), fp, fp, fp, P(C.c_int32)]
+        L.orc_render_bvh_strided.argtypes = [P(capi.SceneDesc), C.c_uint32, fp, C.c_int, C.c_int, P(C.c_int64)]
+        L.orc_render_range.argtypes = [P(capi.SceneDesc), C.c_uint32, C.c_int, C.c_int, C.c_int, fp, C.c_int, P(C.c_int64)]
         L.orc_render_bvh.argtypes = [P(capi.SceneDesc), C.c_uint32, C.c_int, C.c_int, fp, C.c_int, C.c_int, P(C.c_int64), P(C.c_int64)]
         L.orc_radix_sort_pairs.argtypes = [P(C.c_uint64), P(C.c_int32), C.c_int]
         L.orc_radix_sort_pairs.restype = None
@@ -218,6 +220,23 @@ def render(sc, seed=0x2023, spp_begin=0, spp_count=0, threads=None):
     out = np.zeros((H, W, 3), np.float32)
     nr = C.c_int64(0)
     rc = lib().orc_render(sc.ptr, seed, spp_begin, spp_count, fptr(out), threads or os.cpu_count() or 1, C.byref(nr))
+    assert rc == 0
+    return out, nr.value
+
+
+def render_bvh_strided(sc, seed, stride, threads=None):
+    """Host-twin render of the pixels whose index is a multiple of `stride` (the other pixels stay 0); returns (image, rays)."""
+    out = np.zeros((sc.desc.height, sc.desc.width, 3), np.float32)
+    nr = C.c_int64(0)
+    assert lib().orc_render_bvh_strided(sc.ptr, seed, fptr(out), threads or os.cpu_count() or 1, stride, C.byref(nr)) == 0
+    return out, nr.value
+
+
+def render_range(sc, seed, spp_begin, spp_count, total_spp, threads=None):
+    """One rank's share [spp_begin, spp_begin + spp_count) of an image of total_spp samples."""
+    out = np.zeros((sc.desc.height, sc.desc.width, 3), np.float32)
+    nr = C.c_int64(0)
+    rc = lib().orc_render_range(sc.ptr, seed, spp_begin, spp_count, total_spp, fptr(out), threads or os.cpu_count() or 1, C.byref(nr))
     assert rc == 0
     return out, nr.value
 

@@ -22,17 +22,17 @@ def lib():
 
 def test_header_and_library_export_the_same_symbols(lib):
     hdr = open(os.path.join(ROOT, "include", "rt.h")).read()
-    declared = set(re.findall(r"^(?:int|void|const char \*)\s*(rt_[a-z0-9_]+)\(", hdr, re.M))
+    declared = set(re.findall(r"^(?:int|void|const char \*|rt_ctx \*)\s*(rt_[a-z0-9_]+)\(", hdr, re.M))
     assert declared == set(capi.RT_SYMBOLS), declared ^ set(capi.RT_SYMBOLS)
     for name in declared:
         assert getattr(lib, name) is not None
-    assert lib.rt_abi_version() == 1
+    assert lib.rt_abi_version() == 2
 
 
 def test_struct_layouts_match_header():
     assert C.sizeof(capi.ObjectDesc) == 64 and C.sizeof(capi.XformDesc) == 96
     assert C.sizeof(capi.MaterialDesc) == 32 and C.sizeof(capi.TextureDesc) == 32
-    assert C.sizeof(capi.CameraDesc) == 52 and C.sizeof(capi.RenderParams) == 24
+    assert C.sizeof(capi.CameraDesc) == 52 and C.sizeof(capi.RenderParams) == 32
 
 
 def test_no_device_is_an_error_not_a_fallback(lib):

@@ -121,6 +121,22 @@ def test_aov_matches_oracle_and_reference(rt, name):
     assert np.abs(got[..., 13:22] - ref[..., 13:22])[same].max() <= 1e-5
 
 
+def constant_image_sum(bg, spp):
+    """spp x bg as the fixed-order accumulation adds it: sample by sample within each of the 8 sample chunks (main.cu:95-104),
+    chunk sums combined in chunk order (rt.h: rt_sample_chunk)."""
+    from rt_b200 import multi_gpu
+    total = None
+    for k in range(8):
+        b, e = multi_gpu.sample_chunk(spp, k)
+        if e <= b:
+            continue
+        c = np.zeros(3, np.float32)
+        for _ in range(e - b):
+            c = c + bg
+        total = c if total is None else total + c
+    return total
+
+
 def scene_dict(name, sampler=None):
     with open(scene_path(name)) as f:
         d = json.load(f)
@@ -253,9 +269,7 @@ def test_full_size_properties(rt):
     rt.stats_reset(); rt.render(seed=1)
     img, _, st = rt.download()
     bg = np.array([0.0005, 0.0007, 0.00099], np.float32)
-    want = np.zeros(3, np.float32)
-    for _ in range(16):
-        want = want + bg
+    want = constant_image_sum(bg, 16)
     assert np.array_equal(img, np.broadcast_to(want, img.shape)) and st["rays"] == 1920 * 1080 * 16
     rt.upload_json(scene_path("blue2")); rt.override(spp=4)
     rt.render(seed=2)
@@ -543,8 +557,87 @@ def test_empty_tiles_skip_the_queues(rt, name, W, H, spp):
         assert st["rays"] == st_full["rays"], kw
     if name == "basic_scene":       # no objects: every pixel is spp x background, added one sample at a time (main.cu:95-104)
         bg = np.array(json.load(open(scene_path(name)))["background"], np.float32)
-        acc = np.zeros(3, np.float32)
-        for _ in range(spp):
-            acc = acc + bg
-        assert np.array_equal(full, np.broadcast_to(acc, full.shape))
+        assert np.array_equal(full, np.broadcast_to(constant_image_sum(bg, spp), full.shape))
         assert st_full["rays"] == W * H * spp
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+# parity at the sizes that are timed (bench.py), fixed-order accumulation, several GPUs
+# ---------------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["rtiow_486", "blue2"])
+def test_full_hd_render_matches_the_oracle_pixel_for_pixel(rt, name):
+    """The configuration bench.py times — 1920 x 1080, tile_mode 1, passes alternating between the two pass streams — against
+    the multi-threaded oracle: every pixel within 1e-5 per sample (in practice bit-identical) and the same ray count.  3 spp = three
+    sample chunks = three passes.  rtiow_486 goes through the host twin of the traversal (orc_trav.c, itself checked against the
+    linear walk in the CPU tests: the brute-force walk over 486 spheres would take minutes here); blue2 through the linear walk."""
+    W, H, spp = 1920, 1080, 3
+    d = scene_dict(name)
+    d["camera"].setdefault("aspect_ratio", d["width"] / d["height"])
+    rt.upload_json_text(json.dumps(d), base_dir=G)
+    rt.override(width=W, height=H, spp=spp)
+    rt.stats_reset()
+    rt.render(seed=0x2023)
+    got, _, st = rt.download()
+    assert st["passes"] >= 3
+    sc = orc.load_scene(d, width=W, height=H, spp=spp, base_dir=G)
+    want, nrays = (orc.render_bvh(sc, seed=0x2023)[:2] if name == "rtiow_486" else orc.render(sc, seed=0x2023))
+    assert st["rays"] == nrays
+    err = np.abs(got - want)
+    assert (err > 1e-5 * spp).any(-1).sum() == 0, err.max()
+
+
+def test_4k_mesh_render_matches_the_host_twin_on_a_pixel_subset(rt):
+    """BASELINE config 4 at its image size: a displaced-grid triangle mesh at 3840 x 2160, every 97th pixel compared with the
+    host twin of the traversal (the tree is read from global memory here: 64-byte nodes, one pass stream)."""
+    from rt_b200 import scenes
+    ts = scenes.mesh_scene(96, 96, width=3840, height=2160, spp=2, seed=5, max_depth=6)
+    rt.upload(ts)
+    rt.render(seed=3)
+    got, _, _ = rt.download()
+    want, _ = orc.render_bvh_strided(ts, 3, 97)
+    sel = (np.arange(3840 * 2160) % 97 == 0).reshape(2160, 3840)
+    assert np.abs(got[sel] - want[sel]).max() <= 1e-5 * 2
+    assert np.abs(want[sel]).max() > 0
+
+
+@pytest.mark.parametrize("world", [2, 3, 4, 8])
+def test_rank_shards_rendered_one_after_the_other_give_the_one_call_image(rt, world):
+    """Fixed-order accumulation: the sample chunks depend on the total sample count only, so the shards of `world` ranks — here
+    rendered in turn on one GPU with RT_RENDER_KEEP_ACCUM — fold to exactly the image of one rt_render call."""
+    from rt_b200 import multi_gpu
+    W, H, spp = 64, 36, 21
+    rt.upload_json(scene_path("sample_scene_ext")); rt.override(width=W, height=H, spp=spp)
+    rt.render(seed=8)
+    full, _, _ = rt.download()
+    for r in range(world):
+        s0, s1 = multi_gpu.spp_slice(spp, r, world)
+        if s1 > s0:
+            rt.render(seed=8, spp_begin=s0, spp_count=s1 - s0, total_spp=spp, flags=capi.RT_RENDER_KEEP_ACCUM if r else 0)
+    assert np.array_equal(rt.download()[0], full)
+    want, _ = orc.render(orc.load_scene(scene_path("sample_scene_ext"), width=W, height=H, spp=spp, base_dir=G), seed=8)
+    assert np.array_equal(full, want)                       # the oracle states the same chunk order
+
+
+def test_device_group_image_is_bit_identical_for_any_gpu_count():
+    """rt_group_* (one process, n devices, NCCL behind the C ABI): the image and the ray count for 1, 2, 4, 8 devices (as many as
+    the box has) equal the single-context render bit for bit."""
+    import torch
+    from rt_b200 import renderer as rmod
+    W, H, spp = 160, 90, 24
+    one = Renderer(0)
+    one.upload_json(scene_path("rtiow_486")); one.override(width=W, height=H, spp=spp)
+    one.stats_reset(); one.render(seed=5)
+    want, _, st1 = one.download()
+    one.close()
+    for n in (1, 2, 4, 8):
+        if n > torch.cuda.device_count():
+            break
+        g = rmod.Group(list(range(n)))
+        g.upload_json(scene_path("rtiow_486")); g.override(width=W, height=H, spp=spp)
+        g.render(seed=5)
+        got, _, st = g.download()
+        assert np.array_equal(got, want), n
+        assert st["rays"] == st1["rays"], n
+        g.render(seed=6)                                    # the group is reusable
+        assert not np.array_equal(g.download()[0], want)
+        g.close()
