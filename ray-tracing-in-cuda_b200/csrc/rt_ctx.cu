@@ -85,7 +85,7 @@ extern "C" void rt_destroy(rt_ctx *c) {
     c->d_obmin.release(); c->d_obmax.release(); c->d_node_aabb.release(); c->d_leaf_aabb.release(); c->d_bounds.release();
     c->d_hist.release(); c->d_keys[0].release(); c->d_keys[1].release(); c->d_vals[0].release(); c->d_vals[1].release();
     c->d_left.release(); c->d_right.release(); c->d_parent.release(); c->d_flags.release(); c->d_prim_obj.release();
-    c->d_prim_mat.release(); c->d_giant.release(); c->d_lbvh_info.release(); c->d_tile_prefix.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_light_slot.release(); c->d_light_type.release(); c->d_obj_light.release(); c->d_light_area.release();
+    c->d_prim_mat.release(); c->d_giant.release(); c->d_lbvh_info.release(); c->d_tile_prefix.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_nodes4.release(); c->d_light_slot.release(); c->d_light_type.release(); c->d_obj_light.release(); c->d_light_area.release();
     c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
     for (int k = 0; k < RT_MAX_SETS; ++k) { c->qs[k].release(); if (c->qs[k].ev_acc) cudaEventDestroy(c->qs[k].ev_acc); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -328,6 +328,15 @@ static int upload_to_device(rt_ctx *ctx) {
     int per_sm = extend_max_blocks_per_sm(ctx->cfg.bvh_smem_bytes);
     if (per_sm < 1) { ctx->cfg.bvh_smem_bytes = 0; per_sm = extend_max_blocks_per_sm(0); }
     ctx->cfg.extend_blocks_per_sm = per_sm < 1 ? 1 : per_sm;
+    ds.nodes4 = nullptr;
+    static const bool no_bvh4 = getenv("RT_NO_BVH4") != nullptr;      // A/B: two-wide 64-byte nodes
+    if (!ctx->cfg.bvh_smem_bytes && ds.n_tree > 0 && !no_bvh4) {          // tree walked from global memory: four-wide nodes (rt_scene.cuh: BvhNode4)
+        CU(ctx->d_nodes4.alloc((size_t)ds.n_nodes));
+        lbvh_pack4(ctx->cfg, ctx->lb, ctx->d_nodes4.p);
+        CU(cudaGetLastError());
+        CU(cudaStreamSynchronize(s));
+        ds.nodes4 = ctx->d_nodes4.p;
+    }
     ds.only_type = d.n_objects > 0 ? hs.objects[0].type : -1;
     for (int i = 1; i < d.n_objects; ++i) if (hs.objects[i].type != ds.only_type) { ds.only_type = -1; break; }
     // a scene whose objects are all emitters (dna.py frames) ends every path at its first vertex: one bounce is the whole job
@@ -548,20 +557,21 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     max_paths = std::min<long long>(max_paths, 1ll << 30);
     // Fixed-order accumulation (rt.h: rt_sample_chunk): the samples of the render fall into RT_ACC_CHUNKS chunks whose boundaries
     // depend on the TOTAL sample count only; a chunk is summed sample by sample into its own buffer, the buffers are combined in
-    // chunk order.  A pass never straddles a chunk boundary.
+    // chunk order.  A pass may span several chunks: k_accumulate sums each chunk's planes into that chunk's buffer (AccumPlan).
     const int total_spp = prm->total_spp > 0 ? prm->total_spp : std::max(ctx->hs.d.samples_per_pixel, prm->spp_begin + spp);
     struct Piece { int chunk, begin, end; };
     std::vector<Piece> pieces;
-    int largest_piece = 1;
     for (int k = 0; k < RT_ACC_CHUNKS; ++k) {
         int cb, ce;
         rt_sample_chunk(total_spp, k, &cb, &ce);
         if (k == RT_ACC_CHUNKS - 1) ce = std::max(ce, prm->spp_begin + spp);      // samples past the total count the last chunk
         const int pb = std::max(cb, prm->spp_begin), pe = std::min(ce, prm->spp_begin + spp);
-        if (pb < pe) { pieces.push_back({k, pb, pe}); largest_piece = std::max(largest_piece, pe - pb); }
+        if (pb < pe) pieces.push_back({k, pb, pe});
     }
-    int s_pass = (int)std::max<long long>(1, std::min<long long>(largest_piece, max_paths / np));
-    if (n_sets > 1 && pieces.size() == 1) s_pass = std::min(s_pass, (largest_piece + n_sets - 1) / n_sets);        // at least one pass per stream
+    // equal passes (1024 samples at a 139-sample cap: 8 x 128, not 7 x 139 + 51), at least one per stream
+    const int s_cap = (int)std::max<long long>(1, std::min<long long>(spp, max_paths / np));
+    const int n_pass_total = std::max((spp + s_cap - 1) / s_cap, std::min(n_sets, spp));
+    const int s_pass = (spp + n_pass_total - 1) / n_pass_total;
     const long long cap = (long long)s_pass * np;
     if (cap > (1ll << 30) - 64) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: image too large for one wavefront pass");
     int rc = ensure_accum(ctx); if (rc) return rc;
@@ -577,8 +587,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     float ms_stage[5] = {0, 0, 0, 0, 0};
     cudaEvent_t *evs = ctx->ev_count;       // COUNT_EVENTS: one synchronising event pair per stage launch (owned by the context)
     if (time_stages) {          // event pairs are recorded without synchronising and resolved in rt_download
-        size_t n_passes = 0;
-        for (const Piece &pc : pieces) n_passes += (size_t)((pc.end - pc.begin + s_pass - 1) / s_pass);
+        const size_t n_passes = (size_t)n_pass_total;
         const size_t need = ctx->pending.size() + n_passes * (2 + 3 * (size_t)ds.max_depth);
         while (ctx->ev_pool.size() < 2 * need) { cudaEvent_t e; if (cudaEventCreate(&e) != cudaSuccess) return rt_fail(ctx, RT_ERR_CUDA, "cudaEventCreate"); ctx->ev_pool.push_back(e); }
     }
@@ -600,19 +609,30 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     const size_t n_img = (size_t)np * 3;
     ChunkPtrs cp{};
     int n_cp = 0;
+    bool chunk_clear[RT_ACC_CHUNKS];
     for (const Piece &pc : pieces) {
         CU(ctx->d_chunk[pc.chunk].alloc(n_img));
         cp.p[n_cp++] = ctx->d_chunk[pc.chunk].p;
-        // equal passes within the piece (a 128-sample chunk at a 123-sample cap: 64 + 64, not 123 + 5)
-        const int len = pc.end - pc.begin, n_pass = (len + s_pass - 1) / s_pass, step = (len + n_pass - 1) / n_pass;
-        bool clear_chunk = true;
-        for (int done = 0; done < len; done += step) {
-            const int sn = std::min(step, len - done);
+        chunk_clear[pc.chunk] = true;
+    }
+    {
+        for (int done = 0; done < spp; done += s_pass) {
+            const int sn = std::min(s_pass, spp - done);
             const int n_paths = sn * np;
             const int k = (int)(passes % n_sets);
             QueueSet &S = ctx->qs[k];
             const LaunchCfg &cfg = S.cfg;
-            const int first_sample = pc.begin + done;
+            const int first_sample = prm->spp_begin + done;
+            // this pass's sample planes by chunk
+            AccumPlan plan{};
+            for (const Piece &pc : pieces) {
+                const int lo = std::max(pc.begin, first_sample), hi = std::min(pc.end, first_sample + sn);
+                if (lo >= hi) continue;
+                plan.first[plan.n] = lo - first_sample; plan.first[plan.n + 1] = hi - first_sample;
+                plan.buf[plan.n] = ctx->d_chunk[pc.chunk].p; plan.clear[plan.n] = chunk_clear[pc.chunk] ? 1 : 0;
+                chunk_clear[pc.chunk] = false;
+                ++plan.n;
+            }
             launch_pass_init(cfg, S.q, ds.max_depth, n_paths);
             // bounce 0: generate resolves the hits of every path whose tile has a candidate list (ds.tile_mode; k_generate)
             const int tile_mode = (prm->flags & RT_RENDER_NO_TILE_LISTS) ? 0 : ds.tile_mode;
@@ -633,10 +653,8 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
             // samples are added to a chunk buffer in ascending order whatever the stream: pass p's accumulate follows pass p-1's
             if (n_sets > 1 && passes > 0) CU(cudaStreamWaitEvent(cfg.stream, ctx->qs[last_set].ev_acc, 0));
             const int *const_tiles = (dsp.tile_empty_prefix && ds.bg_mode != RT_BG_SKY_GRADIENT) ? dsp.tile_cnt : nullptr;
-            timed(3, [&] { launch_accumulate(cfg, S.q, ctx->d_chunk[pc.chunk].p, ds.width, ds.height, sn, clear_chunk, ds.max_depth, ctx->d_rays.p,
-                                             const_tiles, ds.background); });
+            timed(3, [&] { launch_accumulate(cfg, S.q, plan, ds.width, ds.height, sn, ds.max_depth, ctx->d_rays.p, const_tiles, ds.background); });
             if (n_sets > 1) CU(cudaEventRecord(S.ev_acc, cfg.stream));
-            clear_chunk = false;
             last_set = k;
             ++passes;
         }

@@ -66,7 +66,7 @@ struct rt_ctx {
     DevBuf<unsigned long long> d_keys[2]; DevBuf<int> d_vals[2], d_left, d_right, d_parent, d_flags, d_prim_obj, d_prim_mat, d_lbvh_info;
     DevBuf<unsigned char> d_giant;
     int bvh_depth = 0;
-    DevBuf<BvhNode> d_nodes; DevBuf<BvhNodeS> d_nodes_s; DevBuf<float4> d_primA, d_primB, d_primC;
+    DevBuf<BvhNode> d_nodes; DevBuf<BvhNodeS> d_nodes_s; DevBuf<BvhNode4> d_nodes4; DevBuf<float4> d_primA, d_primB, d_primC;
     // sampled lights (next-event estimation)
     DevBuf<int> d_light_slot, d_light_type, d_obj_light; DevBuf<float> d_light_area;
     // wavefront: two independent queue sets, one per stream, so that the short late-bounce launches of one pass overlap

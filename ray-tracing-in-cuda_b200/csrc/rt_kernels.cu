@@ -96,6 +96,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
             q.radiance[i] = make_float4(bg.x, bg.y, bg.z, 0.0f);
             continue;
         }
+        RT_CHECK(i >= 0 && (long long)i < q.cap);
         q.ray_o[0][i] = make_float4(o.x, o.y, o.z, __int_as_float(i));
         if (zero_radiance) q.radiance[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);      // NEE: several stages add to it
         q.ray_d[0][i] = make_float4(d.x, d.y, d.z, __int_as_float(pixel));        // the Philox key word travels with the path
@@ -188,6 +189,7 @@ __global__ void __launch_bounds__(128) k_tile_lists(DScene sc, int *__restrict__
             const float3 hi = side ? v3(nd.c.y, nd.c.z, nd.c.w) : v3(nd.a.w, nd.b.x, nd.b.y);
             const int child = side ? nd.d.y : nd.d.x;
             if (!beam_box(ol, oh, dl, dh, lo, hi)) continue;
+            RT_CHECK(n <= RT_TILE_K && sp <= 64);
             if (child < 0) { if (n < RT_TILE_K) out[n++] = ~child; else bad = true; }
             else if (sp < 64) stack[sp++] = child;
             else bad = true;
@@ -248,15 +250,21 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, in
             if (!SHADOW && fixup && q.hits[i].y != RT_HIT_TODO) continue;
             const float4 o4 = ray_o[i], d4 = ray_d[i];
             float t; int code;
+            RT_CHECK(i >= 0 && (long long)i < q.cap);
             if (SHADOW) {
-                traverse<SMEM, COUNT, true, RT_SSTACK, ONLY>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt, sstack);
+                if (SMEM) traverse<true, COUNT, true, RT_SSTACK, ONLY>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt, sstack);
+                else if (sc.nodes4) traverse4<COUNT, true, RT_SSTACK, ONLY>(sc, sc.nodes4, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt, sstack);
+                else traverse<false, COUNT, true, RT_SSTACK, ONLY>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, 0.999f, t, code, cnt, sstack);
                 if (code < 0) {
                     const int pid = __float_as_int(o4.w);
+                    RT_CHECK(pid >= 0 && (long long)pid < q.cap);
                     const float4 c = q.sh_c[i], r = q.radiance[pid];
                     q.radiance[pid] = make_float4(r.x + c.x, r.y + c.y, r.z + c.z, 0.0f);
                 }
             } else {
-                traverse<SMEM, COUNT, false, RT_SSTACK, ONLY>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt, sstack);
+                if (SMEM) traverse<true, COUNT, false, RT_SSTACK, ONLY>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt, sstack);
+                else if (sc.nodes4) traverse4<COUNT, false, RT_SSTACK, ONLY>(sc, sc.nodes4, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt, sstack);
+                else traverse<false, COUNT, false, RT_SSTACK, ONLY>(sc, nodes, f4xyz(o4), f4xyz(d4), 0.001f, FLT_MAX, t, code, cnt, sstack);
                 q.hits[i] = make_int2(__float_as_int(t), code);
             }
         }
@@ -495,6 +503,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                     }
                 }
             }
+            RT_CHECK(path_id >= 0 && (long long)path_id < q.cap);
             if (!alive) {
                 if (NEE) { const float4 r0 = q.radiance[path_id]; rad = v3(r0.x + rad.x, r0.y + rad.y, r0.z + rad.z); }
                 q.radiance[path_id] = make_float4(rad.x, rad.y, rad.z, 0.0f);
@@ -508,6 +517,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                 const int leader = __ffs(ms) - 1;
                 if (lane == leader) pos = atomicAdd(&q.shcount[bounce], __popc(ms));
                 pos = __shfl_sync(0xffffffffu, pos, leader) + __popc(ms & lanemask_lt());
+                RT_CHECK(pos >= 0 && (long long)pos < q.cap);
                 if (sh_on) {
                     q.sh_o[pos] = make_float4(sh_x.x, sh_x.y, sh_x.z, __int_as_float(path_id));
                     q.sh_d[pos] = make_float4(sh_w.x, sh_w.y, sh_w.z, 0.0f);
@@ -524,6 +534,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
             const int leader = __ffs(m) - 1;
             if (lane == leader) pos = atomicAdd(&sm.n_out, __popc(m));
             pos = __shfl_sync(0xffffffffu, pos, leader) + __popc(m & lanemask_lt());
+            RT_CHECK(pos >= 0 && pos + (alive ? 0 : 0) < RT_SH_CHUNK);
             if (alive) {
                 sm.out_o[pos] = make_float4(no.x, no.y, no.z, __int_as_float(path_id | sh_flag));
                 sm.out_d[pos] = make_float4(nd.x, nd.y, nd.z, key_pixel);
@@ -536,6 +547,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
             const int n_out = sm.n_out;
             if (n_out) {
                 const int base = atomicAdd(next_count, n_out);
+                RT_CHECK(n_out <= RT_SH_CHUNK && base >= 0 && (long long)base + n_out <= q.cap);
                 tma_store_1d(q.ray_o[buf ^ 1] + base, sm.out_o, (unsigned)n_out * 16u);
                 tma_store_1d(q.ray_d[buf ^ 1] + base, sm.out_d, (unsigned)n_out * 16u);
                 tma_store_1d(q.thr[buf ^ 1] + base, sm.out_thr, (unsigned)n_out * 16u);
@@ -554,8 +566,10 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
 // ------------------------------------------------------------------------------------------------
 // const_tiles: tile_cnt of a pass whose generate skipped the empty tiles under a constant background (else nullptr) — their
 // pixels get the constant added once per sample, in the same order as the sum over radiance records would.
-__global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restrict__ radiance, float *__restrict__ accum, int W, int H,
-                                                         int n_samples, int clear, const int *__restrict__ qcount, int max_depth,
+// plan: the pass's sample planes fall into up to RT_ACC_CHUNKS runs, one per sample chunk of the fixed-order accumulation
+// (rt.h: rt_sample_chunk); run j = planes [first[j], first[j+1]) is summed, in plane order, into chunk buffer buf[j].
+__global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restrict__ radiance, AccumPlan plan, int W, int H,
+                                                         int n_samples, const int *__restrict__ qcount, int max_depth,
                                                          unsigned long long *total_rays, const int *__restrict__ shcount,
                                                          const int *__restrict__ const_tiles, float3 bg) {
     const int np = W * H;
@@ -568,16 +582,23 @@ __global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restric
     }
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < np; k += gridDim.x * blockDim.x) {
         const int p = plane_to_pixel(W, H, k);
-        float r = 0.0f, g = 0.0f, b = 0.0f;
-        if (!clear) { r = accum[3 * p]; g = accum[3 * p + 1]; b = accum[3 * p + 2]; }
-        if (const_tiles && k < (W & ~7) * (H & ~3) && __ldg(&const_tiles[k >> 5]) == 0) {
-            for (int s = 0; s < n_samples; ++s) { r += bg.x; g += bg.y; b += bg.z; }
-        } else
-        for (int s = 0; s < n_samples; ++s) {
-            const float4 c = radiance[(long long)s * np + k];
-            r += c.x; g += c.y; b += c.z;
+        const bool constant = const_tiles && k < (W & ~7) * (H & ~3) && __ldg(&const_tiles[k >> 5]) == 0;
+#pragma unroll
+        for (int j = 0; j < RT_ACC_CHUNKS; ++j) {
+            if (j >= plan.n) break;
+            float *__restrict__ accum = plan.buf[j];
+            float r = 0.0f, g = 0.0f, b = 0.0f;
+            if (!plan.clear[j]) { r = accum[3 * p]; g = accum[3 * p + 1]; b = accum[3 * p + 2]; }
+            const int s0 = plan.first[j], s1 = plan.first[j + 1];
+            if (constant) {
+                for (int s = s0; s < s1; ++s) { r += bg.x; g += bg.y; b += bg.z; }
+            } else
+            for (int s = s0; s < s1; ++s) {
+                const float4 c = radiance[(long long)s * np + k];
+                r += c.x; g += c.y; b += c.z;
+            }
+            accum[3 * p] = r; accum[3 * p + 1] = g; accum[3 * p + 2] = b;
         }
-        accum[3 * p] = r; accum[3 * p + 1] = g; accum[3 * p + 2] = b;
     }
 }
 
@@ -832,10 +853,10 @@ void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const in
     bump(c);
 }
 
-void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W, int H, int n_samples, bool clear, int max_depth,
+void launch_accumulate(const LaunchCfg &c, const Queues &q, const AccumPlan &plan, int W, int H, int n_samples, int max_depth,
                        unsigned long long *total_rays, const int *const_tiles, float3 bg) {
     int blocks = (W * H + RT_BLOCK - 1) / RT_BLOCK;
-    k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, accum, W, H, n_samples, clear ? 1 : 0, q.qcount, max_depth, total_rays, q.shcount,
+    k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, plan, W, H, n_samples, q.qcount, max_depth, total_rays, q.shcount,
                                                     const_tiles, bg);
     bump(c);
 }

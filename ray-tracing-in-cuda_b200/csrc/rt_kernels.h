@@ -20,10 +20,12 @@ void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigne
                   bool last_bounce, bool count, bool sort, bool nee);
 void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const int *obj_light, int *light_slot);
 void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce);
-void launch_accumulate(const LaunchCfg &c, const Queues &q, float *accum, int W, int H, int n_samples, bool clear, int max_depth,
-                       unsigned long long *total_rays, const int *const_tiles, float3 bg);
 #define RT_ACC_CHUNKS 8            // sample chunks of the fixed-order accumulation (rt.h: rt_sample_chunk)
 struct ChunkPtrs { const float *p[RT_ACC_CHUNKS]; };
+// one pass's sample planes by chunk: run j = planes [first[j], first[j + 1]) goes to buf[j] (cleared first when clear[j])
+struct AccumPlan { int n; int first[RT_ACC_CHUNKS + 1]; int clear[RT_ACC_CHUNKS]; float *buf[RT_ACC_CHUNKS]; };
+void launch_accumulate(const LaunchCfg &c, const Queues &q, const AccumPlan &plan, int W, int H, int n_samples, int max_depth,
+                       unsigned long long *total_rays, const int *const_tiles, float3 bg);
 void launch_fold_chunks(const LaunchCfg &c, float *accum, const ChunkPtrs &cp, int n_chunks, bool keep, long long n);
 void launch_sum_ordered(const LaunchCfg &c, float *accum, const float *const *partials_dev, int n_partials, long long n);
 void launch_tonemap(const LaunchCfg &c, const float *accum, unsigned char *rgb8, int W, int H, int spp, int gamma);
@@ -59,4 +61,5 @@ struct LbvhBuffers {                // all device pointers, sized for n objects
     int *prim_obj, *prim_mat;
 };
 void lbvh_build(const LaunchCfg &c, LbvhBuffers &b);
+void lbvh_pack4(const LaunchCfg &c, const LbvhBuffers &b, BvhNode4 *nodes4);      // after lbvh_build: four-wide nodes for global-memory trees
 size_t lbvh_hist_words(int n);

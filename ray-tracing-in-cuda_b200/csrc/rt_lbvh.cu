@@ -380,6 +380,45 @@ __global__ void __launch_bounds__(256) k_pack(int n_all, int *info, const int *_
     nodes_s[i] = ns;
 }
 
+// step 8 (trees walked from global memory only): four-wide nodes = every even-depth binary node with its grandchildren
+__global__ void __launch_bounds__(256) k_pack4(const int *__restrict__ info, const int *__restrict__ left, const int *__restrict__ right,
+                                               const int *__restrict__ parent, const float *__restrict__ node_aabb,
+                                               const float *__restrict__ leaf_aabb, const int *__restrict__ sorted,
+                                               const DObject *__restrict__ objects, BvhNode4 *nodes4) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = info[0];
+    const int n_nodes = n >= 2 ? n - 1 : 1;
+    if (i >= n_nodes) return;
+    int ch[4] = {RT_LEAF_NONE, RT_LEAF_NONE, RT_LEAF_NONE, RT_LEAF_NONE};      // binary links: >= 0 inner, < 0 ~slot; RT_LEAF_NONE: empty
+    int m = 0;
+    if (n >= 2) {
+        int depth = 0;
+        for (int c = parent[i]; c >= 0; c = parent[c]) ++depth;
+        if (depth & 1) return;                                 // odd depth: folded into its parent's four-wide node
+        const int L = left[i], R = right[i];
+        if (L < 0) ch[m++] = L; else { ch[m++] = left[L]; ch[m++] = right[L]; }
+        if (R < 0) ch[m++] = R; else { ch[m++] = left[R]; ch[m++] = right[R]; }
+    } else if (n == 1) ch[m++] = ~0;
+    float pl[6][4]; int ln[4];
+    for (int k = 0; k < 4; ++k) {
+        const int c = ch[k];
+        if (c == RT_LEAF_NONE) { for (int a = 0; a < 3; ++a) { pl[a][k] = INFINITY; pl[3 + a][k] = -INFINITY; } ln[k] = RT_LEAF_NONE; continue; }
+        const float *src = c >= 0 ? node_aabb + 6 * c : leaf_aabb + 6 * (~c);
+        for (int a = 0; a < 6; ++a) pl[a][k] = src[a];
+        ln[k] = c >= 0 ? c : ~((objects[sorted[~c]].type << 28) | (~c));
+    }
+    BvhNode4 nd;
+    for (int a = 0; a < 6; ++a) nd.plane[a] = make_float4(pl[a][0], pl[a][1], pl[a][2], pl[a][3]);
+    nd.link = make_int4(ln[0], ln[1], ln[2], ln[3]); nd.pad = make_int4(0, 0, 0, 0);
+    nodes4[i] = nd;
+}
+
+void lbvh_pack4(const LaunchCfg &c, const LbvhBuffers &b, BvhNode4 *nodes4) {
+    const int g = b.n > 0 ? (b.n + 255) / 256 : 1;
+    k_pack4<<<g, 256, 0, c.stream>>>(b.info, b.left, b.right, b.parent, b.node_aabb, b.leaf_aabb, b.vals[0], b.objects, nodes4);
+    if (c.launches) ++*c.launches;
+}
+
 size_t lbvh_hist_words(int n) { return (size_t)256 * (size_t)((n + RS_TILE - 1) / RS_TILE > 0 ? (n + RS_TILE - 1) / RS_TILE : 1); }
 
 void lbvh_build(const LaunchCfg &c, LbvhBuffers &b) {

@@ -27,6 +27,16 @@ struct __align__(8) BvhNodeS {
     int2 link;                    // left, right (leaf: ~code as BvhNode::d; inner: byte offset of the node = index * 104)
 };
 static_assert(sizeof(BvhNodeS) == 104, "BvhNodeS must be 13 x 8 bytes");
+// Trees that do not fit into shared memory (the 1 M-triangle mesh: 64 MB of 64-byte nodes) are walked through L1/L2, where the
+// walk is bound by the latency of dependent node fetches.  BvhNode4 = a binary node at EVEN depth with its four grandchildren
+// (a leaf child keeps its own slot): one 128-byte line per visit, half as many dependent fetches per ray.  Child boxes are
+// stored per plane (lo.x of the four children, ...), so the ray's direction signs pick whole 16-byte loads as near / far planes.
+// Indexed by the binary node index (odd-depth entries stay unused: no compaction pass).
+struct __align__(16) BvhNode4 {
+    float4 plane[6];    // lo.x lo.y lo.z hi.x hi.y hi.z, one component per child; an empty slot holds (+inf, -inf): never hit
+    int4 link;          // >= 0: BvhNode4 index, < 0: leaf, ~link = type<<28 | slot
+    int4 pad;
+};
 #define RT_LEAF_SLOT_MASK 0x0fffffff
 #define RT_LEAF_NONE (~(7 << 28))   // a leaf code that is never hit (its box is empty)
 
@@ -49,7 +59,8 @@ struct DScene {
     float3 background;
     DCamera cam;
     const BvhNode *nodes;                  // AOV pass and build tests
-    const BvhNodeS *nodes_s;               // extend stage
+    const BvhNodeS *nodes_s;               // extend stage, tree staged in shared memory
+    const BvhNode4 *nodes4;                // extend stage, tree read from global memory (null when the tree fits shared memory)
     const float4 *primA, *primB, *primC;   // geometry by leaf slot
     const int *prim_obj;                   // slot -> object index in the scene file (closest-hit tie rule)
     const int *prim_mat;                   // slot -> material index

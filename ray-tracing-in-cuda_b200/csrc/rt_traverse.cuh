@@ -175,6 +175,7 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
             if (hl && hr) {
                 const bool lfirst = tnl <= tnr;
                 const int2 far_ = make_int2(lfirst ? nd.y : nd.x, __float_as_int(lfirst ? tnr : tnl));
+                RT_CHECK(sp >= 0 && sp - SD < RT_TRAV_STACK);
                 if (SD > 0 && sp < SD) { sts_i2(sstack + (unsigned)sp * RT_SSTACK_STRIDE, far_); ++sp; }
                 else if (sp - SD < RT_TRAV_STACK) { stack[sp - SD] = far_; ++sp; }
                 else if (COUNT) cnt.overflow++;
@@ -187,4 +188,94 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
         }
     }
 #undef RT_POP
+}
+
+// ---- four-wide traversal for trees read from global memory (rt_scene.cuh: BvhNode4) ----
+// Same result contract and the same conservative plane arithmetic as traverse(); a visit fetches one 128-byte node (the ray's
+// direction signs pick the near / far plane of every pair as a whole 16-byte load), tests four boxes, orders the children it
+// hits with a five-comparator network and pushes all but the nearest (farthest first).
+__device__ __forceinline__ void cswap(float &ta, int &la, float &tb, int &lb) {
+    const bool sw = tb < ta;
+    const float t0 = sw ? tb : ta, t1 = sw ? ta : tb;
+    const int l0 = sw ? lb : la, l1 = sw ? la : lb;
+    ta = t0; tb = t1; la = l0; lb = l1;
+}
+
+template <bool COUNT, bool ANY_HIT, int SD = 0, int ONLY = -1>
+__device__ __forceinline__ void traverse4(const DScene &sc, const BvhNode4 *__restrict__ nodes, float3 o, float3 d, float tmin, float tmax,
+                                          float &best_t, int &best_code, TravCounters &cnt, unsigned sstack = 0) {
+    best_t = tmax; best_code = -1;
+    if (sc.n_prims == 0) return;
+    const float a = dot3(d, d), inv_a = 1.0f / a;
+    for (int g = 0; g < sc.n_giants; ++g)
+        if (leaf_visit<COUNT, ONLY>(sc, __ldg(&sc.giant_code[g]), o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
+    if (sc.n_tree == 0) return;
+    float3 ood = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    const bool px = !(fabsf(ood.x) <= RT_BOX_OOD_MAX), py = !(fabsf(ood.y) <= RT_BOX_OOD_MAX), pz = !(fabsf(ood.z) <= RT_BOX_OOD_MAX);
+    if (px) ood.x = copysignf(RT_BOX_OOD_MAX, d.x);
+    if (py) ood.y = copysignf(RT_BOX_OOD_MAX, d.y);
+    if (pz) ood.z = copysignf(RT_BOX_OOD_MAX, d.z);
+    const float3 oo = v3(-(o.x * ood.x), -(o.y * ood.y), -(o.z * ood.z));
+    const float3 ca = v3(__fmaf_rn(RT_BOX_ABS, fabsf(oo.x), px ? RT_BOX_PAR : 0.0f), __fmaf_rn(RT_BOX_ABS, fabsf(oo.y), py ? RT_BOX_PAR : 0.0f),
+                         __fmaf_rn(RT_BOX_ABS, fabsf(oo.z), pz ? RT_BOX_PAR : 0.0f));
+    const float GN = 1.0f - RT_BOX_REL, GF = 1.0f + RT_BOX_REL;
+    const float3 oodn = v3(ood.x * GN, ood.y * GN, ood.z * GN), oodf = v3(ood.x * GF, ood.y * GF, ood.z * GF);
+    const float3 oon = v3(__fmaf_rn(oo.x, GN, -ca.x), __fmaf_rn(oo.y, GN, -ca.y), __fmaf_rn(oo.z, GN, -ca.z));
+    const float3 oof = v3(__fmaf_rn(oo.x, GF, ca.x), __fmaf_rn(oo.y, GF, ca.y), __fmaf_rn(oo.z, GF, ca.z));
+    // plane indices within the node: near = lo (0..2) for a ray travelling in +axis, hi (3..5) otherwise; far the other one
+    const int nx = __float_as_int(d.x) < 0 ? 3 : 0, ny = __float_as_int(d.y) < 0 ? 4 : 1, nz = __float_as_int(d.z) < 0 ? 5 : 2;
+    const int fx = 3 - nx, fy = 5 - ny, fz = 7 - nz;
+    int2 stack[RT_TRAV_STACK];
+    int sp = 0, cur = 0;
+#define RT_POP4()                                                                \
+    for (;;) {                                                                   \
+        if (sp == 0) { cur = RT_TRAV_DONE; break; }                              \
+        --sp;                                                                    \
+        int2 e_;                                                                 \
+        if (SD > 0 && sp < SD) e_ = lds_stack(sstack + (unsigned)sp * RT_SSTACK_STRIDE); \
+        else e_ = stack[sp - SD];                                                \
+        if (__int_as_float(e_.y) <= best_t) { cur = e_.x; break; }               \
+    }
+#define RT_PUSH4(L_, T_)                                                         \
+    {                                                                            \
+        const int2 e_ = make_int2(L_, __float_as_int(T_));                       \
+        RT_CHECK(sp >= 0 && sp - SD < RT_TRAV_STACK);                            \
+        if (SD > 0 && sp < SD) { sts_i2(sstack + (unsigned)sp * RT_SSTACK_STRIDE, e_); ++sp; } \
+        else if (sp - SD < RT_TRAV_STACK) { stack[sp - SD] = e_; ++sp; }         \
+        else if (COUNT) cnt.overflow++;                                          \
+    }
+    while (cur != RT_TRAV_DONE) {
+        if (cur < 0) {
+            if (leaf_visit<COUNT, ONLY>(sc, ~cur, o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
+            RT_POP4()
+        }
+        if (cur >= 0) {
+            const float4 *__restrict__ nd = reinterpret_cast<const float4 *>(nodes + cur);
+            const float4 pnx = nd[nx], pny = nd[ny], pnz = nd[nz], pfx = nd[fx], pfy = nd[fy], pfz = nd[fz];
+            const int4 lk = *reinterpret_cast<const int4 *>(nd + 6);
+            float t0, t1, t2, t3;
+#define RT_BOX4(C_, T_)                                                                                                             \
+            {                                                                                                                       \
+                const float tn_ = fmaxf(fmaxf(__fmaf_rn(pnx.C_, oodn.x, oon.x), __fmaf_rn(pny.C_, oodn.y, oon.y)),                   \
+                                        fmaxf(__fmaf_rn(pnz.C_, oodn.z, oon.z), tmin));                                              \
+                const float tf_ = fminf(fminf(__fmaf_rn(pfx.C_, oodf.x, oof.x), __fmaf_rn(pfy.C_, oodf.y, oof.y)),                   \
+                                        fminf(__fmaf_rn(pfz.C_, oodf.z, oof.z), best_t));                                            \
+                T_ = tn_ <= tf_ ? tn_ : INFINITY;                                                                                   \
+            }
+            RT_BOX4(x, t0) RT_BOX4(y, t1) RT_BOX4(z, t2) RT_BOX4(w, t3)
+#undef RT_BOX4
+            if (COUNT) { cnt.box += 4; cnt.nodes++; }
+            int l0 = lk.x, l1 = lk.y, l2 = lk.z, l3 = lk.w;
+            cswap(t0, l0, t1, l1); cswap(t2, l2, t3, l3); cswap(t0, l0, t2, l2); cswap(t1, l1, t3, l3); cswap(t1, l1, t2, l2);
+            if (t0 == INFINITY) { RT_POP4() }
+            else {
+                if (t3 != INFINITY) RT_PUSH4(l3, t3)
+                if (t2 != INFINITY) RT_PUSH4(l2, t2)
+                if (t1 != INFINITY) RT_PUSH4(l1, t1)
+                cur = l0;
+            }
+        }
+    }
+#undef RT_POP4
+#undef RT_PUSH4
 }

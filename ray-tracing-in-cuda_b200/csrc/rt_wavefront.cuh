@@ -2,6 +2,15 @@
 #pragma once
 #include "rt_shade.cuh"
 
+// Checked build (tools/build_variant.py checked -DRT_CHECKED=1): device-side asserts on every queue / staging / stack index the
+// kernels compute.  compute-sanitizer is closed on this GPU pool ("runs under it have left GPUs needing a reset"), so the small
+// renders of tools/sanitize_run.py run against this build instead; log under profiles/.
+#ifdef RT_CHECKED
+#include <cassert>
+#define RT_CHECK(cond) assert(cond)
+#else
+#define RT_CHECK(cond) ((void)0)
+#endif
 #define RT_NUM_BINS 5          // miss, lambertian, metal, dielectric, diffuse_light
 #define RT_TRAV_STACK 64
 #ifndef RT_SSTACK

@@ -576,7 +576,7 @@ def test_full_hd_render_matches_the_oracle_pixel_for_pixel(rt, name):
     rt.upload_json_text(json.dumps(d), base_dir=G)
     rt.override(width=W, height=H, spp=spp)
     rt.stats_reset()
-    rt.render(seed=0x2023)
+    rt.render(seed=0x2023, max_paths_per_pass=W * H)          # one sample plane per pass: three passes over the two pass streams
     got, _, st = rt.download()
     assert st["passes"] >= 3
     sc = orc.load_scene(d, width=W, height=H, spp=spp, base_dir=G)
