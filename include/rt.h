@@ -58,13 +58,16 @@ enum { RT_SAMPLING_REFERENCE_GPU = 0, RT_SAMPLING_REFERENCE_CPU = 1,
 typedef struct rt_object_desc {
     int32_t type;       /* RT_OBJ_* */
     int32_t material;   /* index into materials */
-    int32_t xform;      /* index into xforms (object-to-world) or -1; honoured for CYLINDER and BOX */
+    int32_t xform;      /* index into xforms (object-to-world, rigid) or -1; honoured for SPHERE, ??_RECT, CYLINDER (required) and BOX —
+                           the reference's instance machinery, vec3.cuh:303-427 / object.cuh:225-231; TRIANGLE vertices are world space
+                           (the JSON reader bakes "rotate" / "translate" of triangles and meshes into them) */
     int32_t reserved;
     /* SPHERE:   cx cy cz radius              (object.cuh:40-94; radius may be negative)
      * ??_RECT:  a0 a1 b0 b1 k                (object.cuh:96-197; xy: x0 x1 y0 y1 | xz: x0 x1 z0 z1 | yz: y0 y1 z0 z1)
      * CYLINDER: radius zmin zmax             (object.cuh:216-297; axis = object-space z, no caps)
      * BOX:      minx miny minz maxx maxy maxz (extension; object-space if xform >= 0)
-     * TRIANGLE: v0 v1 v2 (9 floats, world space; extension) */
+     * TRIANGLE: v0 v1 v2 (9 floats, world space; extension); p[9..11]: per-vertex texture coordinates, the BITS of each float =
+     *           u | v << 16 as 16-bit unorm (OBJ `vt`); all three zero = none (uv = the barycentrics) */
     float p[12];
 } rt_object_desc;
 

@@ -36,7 +36,10 @@ void orc_object_aabb(const rt_scene_desc *sc, int i, float bmin[3], float bmax[3
     case RT_OBJ_SPHERE: {
         float r = fabsf(p[3]);
         for (int k = 0; k < 3; ++k) { bmin[k] = p[k] - r; bmax[k] = p[k] + r; }
-        return;
+        if (!xf) return;
+        for (int k = 0; k < 3; ++k) { lo[k] = bmin[k]; hi[k] = bmax[k]; }      /* instance: world box of the object-space box's corners */
+        corners = 1;
+        break;
     }
     case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: {
         int a = ob->type == RT_OBJ_YZ_RECT ? 1 : 0, b = ob->type == RT_OBJ_XY_RECT ? 1 : 2;
@@ -44,7 +47,10 @@ void orc_object_aabb(const rt_scene_desc *sc, int i, float bmin[3], float bmax[3
         bmin[a] = fminf(p[0], p[1]); bmax[a] = fmaxf(p[0], p[1]);
         bmin[b] = fminf(p[2], p[3]); bmax[b] = fmaxf(p[2], p[3]);
         bmin[k] = p[4] - 1e-4f; bmax[k] = p[4] + 1e-4f;
-        return;
+        if (!xf) return;
+        for (int q = 0; q < 3; ++q) { lo[q] = bmin[q]; hi[q] = bmax[q]; }
+        corners = 1;
+        break;
     }
     case RT_OBJ_CYLINDER: {
         float r = fabsf(p[0]);

@@ -10,9 +10,14 @@ static void set_face_normal(orc_hit *rec, v3 d, v3 outward) {   /* hittable.cuh:
 
 /* sphere::hit, object.cuh:47-75.  inv_a = 1/dot(d,d) is hoisted per ray (one rounding differs from the
  * reference's division; covered by the 1e-5 tolerance against oracle/_ref). */
-static int hit_sphere(const float *p, v3 o, v3 d, float inv_a, float tmin, float tmax, orc_hit *rec) {
+static int hit_sphere(const float *p, const rt_xform_desc *xf, v3 o, v3 d, float inv_a, float tmin, float tmax, orc_hit *rec) {
     v3 c = V(p[0], p[1], p[2]);
     float r = p[3];
+    const v3 wd = d;
+    if (xf) {      /* rotate / translate instance (vec3.cuh:303-427, applied as object.cuh:225-231 does for the cylinder) */
+        o = orc_xform_point(xf->m_inv, o); d = orc_xform_vec(xf->m_inv, d);
+        inv_a = 1.0f / dot3(d, d);
+    }
     v3 oc = vsub(o, c);
     float a = dot3(d, d);
     float hb = dot3(oc, d);
@@ -28,7 +33,10 @@ static int hit_sphere(const float *p, v3 o, v3 d, float inv_a, float tmin, float
     rec->t = root;
     rec->p = vfma(root, d, o);
     v3 n = vscale(1.0f / r, vsub(rec->p, c));
-    set_face_normal(rec, d, n);
+    if (xf) {      /* the uv below follow the object-space normal: the texture turns with the sphere */
+        rec->p = orc_xform_point(xf->m, rec->p);
+        set_face_normal(rec, wd, orc_xform_normal(xf->m_inv, n));
+    } else set_face_normal(rec, d, n);
     /* get_sphere_uv(outward normal), object.cuh:87-93 */
     float theta = orc_acosf(-n.y);
     float phi = orc_atan2f(-n.z, n.x) + ORC_PI_F;
@@ -38,7 +46,9 @@ static int hit_sphere(const float *p, v3 o, v3 d, float inv_a, float tmin, float
 }
 
 /* xy_rect / xz_rect / yz_rect ::hit, object.cuh:105-122,142-159,175-192 */
-static int hit_rect(int type, const float *p, v3 o, v3 d, float tmin, float tmax, orc_hit *rec) {
+static int hit_rect(int type, const float *p, const rt_xform_desc *xf, v3 o, v3 d, float tmin, float tmax, orc_hit *rec) {
+    const v3 wd = d;
+    if (xf) { o = orc_xform_point(xf->m_inv, o); d = orc_xform_vec(xf->m_inv, d); }
     float oa, ob, ok, da, db, dk;
     if (type == RT_OBJ_XY_RECT) { oa = o.x; ob = o.y; ok = o.z; da = d.x; db = d.y; dk = d.z; }
     else if (type == RT_OBJ_XZ_RECT) { oa = o.x; ob = o.z; ok = o.y; da = d.x; db = d.z; dk = d.y; }
@@ -52,6 +62,11 @@ static int hit_rect(int type, const float *p, v3 o, v3 d, float tmin, float tmax
     rec->v = (b - b0) / (b1 - b0);
     rec->t = t;
     v3 n = type == RT_OBJ_XY_RECT ? V(0, 0, 1) : type == RT_OBJ_XZ_RECT ? V(0, 1, 0) : V(1, 0, 0);
+    if (xf) {
+        rec->p = orc_xform_point(xf->m, vfma(t, d, o));
+        set_face_normal(rec, wd, orc_xform_normal(xf->m_inv, n));
+        return 1;
+    }
     rec->front = dk < 0.0f;                 /* dot(d, axis) == d.axis */
     rec->n = rec->front ? n : vneg(n);
     rec->p = vfma(t, d, o);
@@ -142,7 +157,14 @@ static int hit_triangle(const float *p, v3 o, v3 d, float tmin, float tmax, orc_
     float t = dot3(e2, qv) * inv;
     if (t < tmin || tmax < t) return 0;
     v3 n = V(fmaf(e1.y, e2.z, -(e1.z * e2.y)), fmaf(e1.z, e2.x, -(e1.x * e2.z)), fmaf(e1.x, e2.y, -(e1.y * e2.x)));
-    rec->t = t; rec->u = u; rec->v = v;
+    /* per-vertex texture coordinates (OBJ `vt`): 16-bit unorm pairs in p[9..11]; none: (0,0), (1,0), (0,1) = the barycentrics */
+    uint32_t q[3];
+    memcpy(q, p + 9, sizeof q);
+    if ((q[0] | q[1] | q[2]) == 0u) { q[1] = 0x0000ffffu; q[2] = 0xffff0000u; }
+    const float w0 = (1.0f - u) - v;
+    rec->u = fmaf(v, (float)(q[2] & 0xffffu) / 65535.0f, fmaf(u, (float)(q[1] & 0xffffu) / 65535.0f, w0 * ((float)(q[0] & 0xffffu) / 65535.0f)));
+    rec->v = fmaf(v, (float)(q[2] >> 16) / 65535.0f, fmaf(u, (float)(q[1] >> 16) / 65535.0f, w0 * ((float)(q[0] >> 16) / 65535.0f)));
+    rec->t = t;
     rec->p = vfma(t, d, o);
     set_face_normal(rec, d, vunit(n));
     return 1;
@@ -154,8 +176,8 @@ int orc_hit_object(const rt_scene_desc *sc, int i, v3 o, v3 d, float inv_a, floa
     static const rt_xform_desc ident = {{1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0}, {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0}};
     int h = 0;
     switch (ob->type) {
-    case RT_OBJ_SPHERE: h = hit_sphere(ob->p, o, d, inv_a, tmin, tmax, rec); break;
-    case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: h = hit_rect(ob->type, ob->p, o, d, tmin, tmax, rec); break;
+    case RT_OBJ_SPHERE: h = hit_sphere(ob->p, xf, o, d, inv_a, tmin, tmax, rec); break;
+    case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: h = hit_rect(ob->type, ob->p, xf, o, d, tmin, tmax, rec); break;
     case RT_OBJ_CYLINDER: h = hit_cylinder(ob->p, xf ? xf : &ident, o, d, tmin, tmax, rec); break;
     case RT_OBJ_BOX: h = hit_box(ob->p, xf, o, d, tmin, tmax, rec); break;
     case RT_OBJ_TRIANGLE: h = hit_triangle(ob->p, o, d, tmin, tmax, rec); break;

@@ -19,6 +19,7 @@
 int orc_is_nee_light(const rt_scene_desc *sc, int i) {
     const rt_object_desc *o = &sc->objects[i];
     if (sc->materials[o->material].type != RT_MAT_DIFFUSE_LIGHT) return 0;
+    if (o->xform >= 0 && o->type != RT_OBJ_CYLINDER) return 0;      /* rotated / translated sphere and rect lights are not sampled */
     return o->type == RT_OBJ_SPHERE || o->type == RT_OBJ_XY_RECT || o->type == RT_OBJ_XZ_RECT || o->type == RT_OBJ_YZ_RECT ||
            o->type == RT_OBJ_CYLINDER || o->type == RT_OBJ_TRIANGLE;
 }

@@ -281,6 +281,7 @@ static int upload_to_device(rt_ctx *ctx) {
         for (int i = 0; i < n; ++i) {
             const rt_object_desc &o = hs.objects[i];
             if (hs.materials[o.material].type != RT_MAT_DIFFUSE_LIGHT) continue;
+            if (o.xform >= 0 && o.type != RT_OBJ_CYLINDER) continue;      // rotated / translated sphere and rect lights are not sampled (they emit when hit)
             const float *p = o.p; float area;
             if (o.type == RT_OBJ_SPHERE) area = 4.0f * 3.14159274101257324f * (p[3] * p[3]);
             else if (o.type == RT_OBJ_XY_RECT || o.type == RT_OBJ_XZ_RECT || o.type == RT_OBJ_YZ_RECT) area = fabsf((p[1] - p[0]) * (p[3] - p[2]));
@@ -338,7 +339,8 @@ static int upload_to_device(rt_ctx *ctx) {
         ds.nodes4 = ctx->d_nodes4.p;
     }
     ds.only_type = d.n_objects > 0 ? hs.objects[0].type : -1;
-    for (int i = 1; i < d.n_objects; ++i) if (hs.objects[i].type != ds.only_type) { ds.only_type = -1; break; }
+    for (int i = 0; i < d.n_objects; ++i)       // the specialised sphere loop carries no instance transforms
+        if (hs.objects[i].type != ds.only_type || (ds.only_type == RT_OBJ_SPHERE && hs.objects[i].xform >= 0)) { ds.only_type = -1; break; }
     // a scene whose objects are all emitters (dna.py frames) ends every path at its first vertex: one bounce is the whole job
     ctx->scene_scatters = false;
     for (int i = 0; i < d.n_objects; ++i)

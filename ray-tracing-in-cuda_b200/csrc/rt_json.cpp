@@ -169,23 +169,57 @@ struct Loader {
         hs.xforms.push_back(x);
         return true;
     }
+    // p <- m * p for a 3x4 row-major matrix, plain left-to-right float arithmetic (the Python loader of the tests states the same)
+    static void bake(const float *m, float *p) {
+        const float x = p[0], y = p[1], z = p[2];
+        for (int r = 0; r < 3; ++r) p[r] = ((m[4 * r] * x + m[4 * r + 1] * y) + m[4 * r + 2] * z) + m[4 * r + 3];
+    }
+    // (u, v) clamped to [0, 1] as two 16-bit unorm values in the bits of one float (rt.h: TRIANGLE p[9..11])
+    static float pack_uv(float u, float v) {
+        u = u < 0.0f ? 0.0f : (u > 1.0f ? 1.0f : u); v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+        const uint32_t q = (uint32_t)(u * 65535.0f + 0.5f) | ((uint32_t)(v * 65535.0f + 0.5f) << 16);
+        float f; memcpy(&f, &q, 4);
+        return f;
+    }
     std::string resolve(const std::string &f) const { return (!f.empty() && f[0] == '/') || base.empty() ? f : base + "/" + f; }
-    bool load_obj(const std::string &file, int material, float scale, const float tr[3], const std::string &where) {
+    // Wavefront OBJ: v, vt and f (v, v/vt, v/vt/vn, v//vn; negative indices; polygons fan-triangulated).  With `rot` (a 3x4 matrix whose
+    // translation column is the mesh's translate) a vertex is m * (scale * v), else scale * v + tr.  `vt` -> per-vertex uv of the triangles.
+    bool load_obj(const std::string &file, int material, float scale, const float tr[3], const float *rot, const std::string &where) {
         std::ifstream in(resolve(file));
         if (!in) return fail(where + ": cannot open mesh file " + file);
-        std::vector<float> v; std::string line;
+        std::vector<float> v, vt; std::string line;
         while (std::getline(in, line)) {
             std::istringstream ls(line); std::string tag; ls >> tag;
-            if (tag == "v") { float x, y, z; ls >> x >> y >> z; v.push_back(x * scale + tr[0]); v.push_back(y * scale + tr[1]); v.push_back(z * scale + tr[2]); }
+            if (tag == "v") {
+                float p[3]; ls >> p[0] >> p[1] >> p[2];
+                if (rot) { for (int a = 0; a < 3; ++a) p[a] = p[a] * scale; bake(rot, p); }
+                else for (int a = 0; a < 3; ++a) p[a] = p[a] * scale + tr[a];
+                v.insert(v.end(), p, p + 3);
+            } else if (tag == "vt") { float a = 0, b = 0; ls >> a >> b; vt.push_back(a); vt.push_back(b); }
             else if (tag == "f") {
-                std::vector<int> idx; std::string tok;
-                while (ls >> tok) { int i = atoi(tok.c_str()); idx.push_back(i < 0 ? (int)(v.size() / 3) + i : i - 1); }
+                std::vector<int> idx, tidx; std::string tok;
+                while (ls >> tok) {
+                    int i = atoi(tok.c_str());
+                    idx.push_back(i < 0 ? (int)(v.size() / 3) + i : i - 1);
+                    int ti = -1;
+                    const size_t sl = tok.find('/');
+                    if (sl != std::string::npos && sl + 1 < tok.size() && tok[sl + 1] != '/') {
+                        const int j = atoi(tok.c_str() + sl + 1);
+                        ti = j < 0 ? (int)(vt.size() / 2) + j : j - 1;
+                    }
+                    tidx.push_back(ti);
+                }
                 for (size_t k = 1; k + 1 < idx.size(); ++k) {     // fan triangulation
                     rt_object_desc o{}; o.type = RT_OBJ_TRIANGLE; o.material = material; o.xform = -1;
-                    const int tri[3] = {idx[0], idx[k], idx[k + 1]};
+                    const int tri[3] = {idx[0], idx[k], idx[k + 1]}, tt[3] = {tidx[0], tidx[k], tidx[k + 1]};
+                    const bool has_uv = tt[0] >= 0 && tt[1] >= 0 && tt[2] >= 0;
                     for (int c = 0; c < 3; ++c) {
                         if (tri[c] < 0 || (size_t)tri[c] * 3 + 2 >= v.size()) return fail(where + ": face index out of range in " + file);
                         for (int a = 0; a < 3; ++a) o.p[3 * c + a] = v[3 * tri[c] + a];
+                        if (has_uv) {
+                            if ((size_t)tt[c] * 2 + 1 >= vt.size()) return fail(where + ": texture index out of range in " + file);
+                            o.p[9 + c] = pack_uv(vt[2 * tt[c]], vt[2 * tt[c] + 1]);
+                        }
                     }
                     hs.objects.push_back(o);
                 }
@@ -283,10 +317,18 @@ struct Loader {
                 for (int k = 0; k < 5; ++k) { double vv; if (!num(o, keys[k], vv, where)) return false; q.p[k] = (float)vv; }
                 return true;
             };
-            if (t == "sphere") { q.type = RT_OBJ_SPHERE; if (!vec(o, "center", 3, q.p, where) || !num(o, "radius", x, where)) return false; q.p[3] = (float)x; }
-            else if (t == "xy_rect") { q.type = RT_OBJ_XY_RECT; if (!five("x0", "x1", "y0", "y1")) return false; }
-            else if (t == "xz_rect") { q.type = RT_OBJ_XZ_RECT; if (!five("x0", "x1", "z0", "z1")) return false; }
-            else if (t == "yz_rect") { q.type = RT_OBJ_YZ_RECT; if (!five("y0", "y1", "z0", "z1")) return false; }
+            // "rotate" / "translate" are honoured on EVERY object type (the reference's transform machinery is general,
+            // vec3.cuh:303-427, although its parser only feeds it for cylinders, parser.hpp:423-440): sphere / rect / box / cylinder
+            // as an instance transform, triangle / mesh baked into the vertices
+            if (t == "sphere") {
+                q.type = RT_OBJ_SPHERE;
+                if (!vec(o, "center", 3, q.p, where) || !num(o, "radius", x, where)) return false;
+                q.p[3] = (float)x;
+                if (!xform(o, where, q.xform, false)) return false;
+            }
+            else if (t == "xy_rect") { q.type = RT_OBJ_XY_RECT; if (!five("x0", "x1", "y0", "y1") || !xform(o, where, q.xform, false)) return false; }
+            else if (t == "xz_rect") { q.type = RT_OBJ_XZ_RECT; if (!five("x0", "x1", "z0", "z1") || !xform(o, where, q.xform, false)) return false; }
+            else if (t == "yz_rect") { q.type = RT_OBJ_YZ_RECT; if (!five("y0", "y1", "z0", "z1") || !xform(o, where, q.xform, false)) return false; }
             else if (t == "cylinder") {
                 q.type = RT_OBJ_CYLINDER;
                 const char *keys[3] = {"radius", "zmin", "zmax"};
@@ -298,13 +340,32 @@ struct Loader {
             } else if (t == "triangle") {
                 q.type = RT_OBJ_TRIANGLE;
                 if (!vec(o, "v0", 3, q.p, where) || !vec(o, "v1", 3, q.p + 3, where) || !vec(o, "v2", 3, q.p + 6, where)) return false;
+                int xi = -1;
+                if (!xform(o, where, xi, false)) return false;
+                if (xi >= 0) { for (int c = 0; c < 3; ++c) bake(hs.xforms[xi].m, q.p + 3 * c); hs.xforms.pop_back(); }
+                const JValue *uvs = o->get("uv");       // optional [[u0,v0],[u1,v1],[u2,v2]]
+                if (uvs && uvs->kind == JValue::Arr && uvs->arr.size() >= 3)
+                    for (int c = 0; c < 3; ++c) {
+                        const JValue *e = uvs->arr[c].get();
+                        if (e->kind != JValue::Arr || e->arr.size() < 2 || e->arr[0]->kind != JValue::Num || e->arr[1]->kind != JValue::Num) return fail(where + ": \"uv\" must hold three [u, v] pairs");
+                        q.p[9 + c] = pack_uv((float)e->arr[0]->num, (float)e->arr[1]->num);
+                    }
             } else if (t == "mesh") {
                 const JValue *f = o->get("file");
                 if (!f || f->kind != JValue::Str) return fail(where + ": missing \"file\"");
                 float scale = 1.0f, tr[3] = {0, 0, 0};
                 const JValue *sv = o->get("scale"); if (sv && sv->kind == JValue::Num) scale = (float)sv->num;
                 if (o->get("translate") && !vec(o, "translate", 3, tr, where)) return false;
-                if (!load_obj(f->str, q.material, scale, tr, where)) return false;
+                // "rotate" on a mesh: vertices are scaled, rotated about the origin, then translated (translate(t) * rotate, as for every object)
+                int xi = -1;
+                const float *rot = nullptr;
+                if (o->get("rotate")) {
+                    if (!xform(o, where, xi, false)) return false;
+                    rot = hs.xforms[xi].m;
+                }
+                const bool ok = load_obj(f->str, q.material, scale, tr, rot, where);
+                if (xi >= 0) hs.xforms.pop_back();
+                if (!ok) return false;
                 continue;
             } else return fail(where + ": unknown object type \"" + t + "\"");
             hs.objects.push_back(q);

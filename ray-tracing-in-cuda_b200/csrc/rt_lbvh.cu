@@ -25,7 +25,9 @@ __device__ void object_aabb(const DObject &ob, const float4 *xforms, float bmin[
     case RT_OBJ_SPHERE: {
         float r = fabsf(p[3]);
         for (int k = 0; k < 3; ++k) { bmin[k] = p[k] - r; bmax[k] = p[k] + r; }
-        return;
+        if (ob.xform < 0) return;
+        for (int k = 0; k < 3; ++k) { lo[k] = bmin[k]; hi[k] = bmax[k]; }      // instance: world box of the object-space box's corners
+        break;
     }
     case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: {
         int a = ob.type == RT_OBJ_YZ_RECT ? 1 : 0, b = ob.type == RT_OBJ_XY_RECT ? 1 : 2;
@@ -33,7 +35,9 @@ __device__ void object_aabb(const DObject &ob, const float4 *xforms, float bmin[
         bmin[a] = fminf(p[0], p[1]); bmax[a] = fmaxf(p[0], p[1]);
         bmin[b] = fminf(p[2], p[3]); bmax[b] = fmaxf(p[2], p[3]);
         bmin[k] = p[4] - 1e-4f; bmax[k] = p[4] + 1e-4f;
-        return;
+        if (ob.xform < 0) return;
+        for (int q = 0; q < 3; ++q) { lo[q] = bmin[q]; hi[q] = bmax[q]; }
+        break;
     }
     case RT_OBJ_CYLINDER: {
         float r = fabsf(p[0]);
@@ -256,15 +260,20 @@ __global__ void __launch_bounds__(256) k_leaf_setup(int n, const int *__restrict
     const float *p = ob.p;
     float4 A = make_float4(0, 0, 0, 0), B = A, C = A;
     switch (ob.type) {
-    case RT_OBJ_SPHERE: A = make_float4(p[0], p[1], p[2], p[3]); break;
-    case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: A = make_float4(p[0], p[1], p[2], p[3]); B.x = p[4]; break;
+    case RT_OBJ_SPHERE: A = make_float4(p[0], p[1], p[2], p[3]); B.w = __int_as_float(ob.xform); break;
+    case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: A = make_float4(p[0], p[1], p[2], p[3]); B.x = p[4]; B.w = __int_as_float(ob.xform); break;
     case RT_OBJ_CYLINDER: A = make_float4(p[0], p[1], p[2], __int_as_float(ob.xform)); break;
     case RT_OBJ_BOX: A = make_float4(p[0], p[1], p[2], __int_as_float(ob.xform)); B = make_float4(p[3], p[4], p[5], 0.0f); break;
-    case RT_OBJ_TRIANGLE:
-        A = make_float4(p[0], p[1], p[2], 0.0f);
-        B = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], 0.0f);
-        C = make_float4(p[6] - p[0], p[7] - p[1], p[8] - p[2], 0.0f);
+    case RT_OBJ_TRIANGLE: {
+        // per-vertex texture coordinates: p[9..11] hold (u, v) as 16-bit unorm pairs; all zero = none: (0,0), (1,0), (0,1), which
+        // makes the interpolated uv the barycentrics
+        unsigned q0 = __float_as_uint(p[9]), q1 = __float_as_uint(p[10]), q2 = __float_as_uint(p[11]);
+        if ((q0 | q1 | q2) == 0u) { q1 = 0x0000ffffu; q2 = 0xffff0000u; }
+        A = make_float4(p[0], p[1], p[2], __uint_as_float(q0));
+        B = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], __uint_as_float(q1));
+        C = make_float4(p[6] - p[0], p[7] - p[1], p[8] - p[2], __uint_as_float(q2));
         break;
+    }
     }
     primA[j] = A; primB[j] = B; primC[j] = C;
     prim_obj[j] = i; prim_mat[j] = ob.material;

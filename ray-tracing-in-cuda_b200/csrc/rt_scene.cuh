@@ -214,11 +214,25 @@ template <int ONLY = -1>
 __device__ __forceinline__ bool leaf_t(const DScene &sc, int code, float3 o, float3 d, float a, float inv_a, float tmin, float tmax, float &t) {
     const int type = (unsigned)code >> 28, slot = code & RT_LEAF_SLOT_MASK;
     const float4 A = __ldg(&sc.primA[slot]);
-    if (ONLY == RT_OBJ_SPHERE) return sphere_t(A, o, d, a, inv_a, tmin, tmax, t);
+    if (ONLY == RT_OBJ_SPHERE) return sphere_t(A, o, d, a, inv_a, tmin, tmax, t);     // (ONLY: no sphere carries a transform)
     switch (type) {
-    case RT_OBJ_SPHERE: return sphere_t(A, o, d, a, inv_a, tmin, tmax, t);
-    case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT:
-        return rect_t(type, A, __ldg(&sc.primB[slot]).x, o, d, tmin, tmax, t);
+    case RT_OBJ_SPHERE: {
+        // rotate / translate instance (vec3.cuh:303-427 applied as object.cuh:225-231 does for the cylinder): the ray goes to
+        // object space, t is unchanged (rigid transform, direction not normalised)
+        const int xi = __float_as_int(__ldg(&sc.primB[slot]).w);
+        if (xi < 0) return sphere_t(A, o, d, a, inv_a, tmin, tmax, t);
+        const float4 *xf = sc.xforms + 6 * xi;
+        const float3 od = xf_vec(xf + 3, d);
+        const float a2 = dot3(od, od);
+        return sphere_t(A, xf_point(xf + 3, o), od, a2, 1.0f / a2, tmin, tmax, t);
+    }
+    case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: {
+        const float4 B = __ldg(&sc.primB[slot]);
+        const int xi = __float_as_int(B.w);
+        if (xi < 0) return rect_t(type, A, B.x, o, d, tmin, tmax, t);
+        const float4 *xf = sc.xforms + 6 * xi;
+        return rect_t(type, A, B.x, xf_point(xf + 3, o), xf_vec(xf + 3, d), tmin, tmax, t);
+    }
     case RT_OBJ_CYLINDER: {
         const float4 *xf = sc.xforms + 6 * __float_as_int(A.w);
         return cylinder_t(A.x, A.y, A.z, xf_point(xf + 3, o), xf_vec(xf + 3, d), tmin, tmax, t);
@@ -251,9 +265,19 @@ __device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot,
     r.t = t; r.u = 0.0f; r.v = 0.0f;
     switch (type) {
     case RT_OBJ_SPHERE: {   // object.cuh:68-72,87-93
-        r.p = vfma(t, d, o);
-        float3 n = (1.0f / A.w) * (r.p - f4xyz(A));
-        set_face_normal(r, d, n);
+        const int xi = __float_as_int(__ldg(&sc.primB[slot]).w);
+        float3 n;
+        if (xi < 0) {
+            r.p = vfma(t, d, o);
+            n = (1.0f / A.w) * (r.p - f4xyz(A));
+            set_face_normal(r, d, n);
+        } else {            // instance: hit point and normal in object space (the uv follow the rotated sphere), then to world space
+            const float4 *xf = sc.xforms + 6 * xi;
+            const float3 op = vfma(t, xf_vec(xf + 3, d), xf_point(xf + 3, o));
+            n = (1.0f / A.w) * (op - f4xyz(A));
+            r.p = xf_point(xf, op);
+            set_face_normal(r, d, xf_normal(xf + 3, n));
+        }
         if (want_uv) {
             float theta = rt_acosf(-n.y);
             float phi = rt_atan2f(-n.z, n.x) + RT_PI_F;
@@ -262,14 +286,23 @@ __device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot,
         break;
     }
     case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: {   // object.cuh:113-121
+        const int xi = __float_as_int(__ldg(&sc.primB[slot]).w);
+        const float4 *xf = sc.xforms + 6 * (xi >= 0 ? xi : 0);
+        float3 oo = o, od = d;
+        if (xi >= 0) { oo = xf_point(xf + 3, o); od = xf_vec(xf + 3, d); }
         float oa, ob, ok, da, db, dk;
-        rect_axes(type, o, oa, ob, ok); rect_axes(type, d, da, db, dk);
+        rect_axes(type, oo, oa, ob, ok); rect_axes(type, od, da, db, dk);
         float a = __fmaf_rn(t, da, oa), b = __fmaf_rn(t, db, ob);
         r.u = (a - A.x) / (A.y - A.x); r.v = (b - A.z) / (A.w - A.z);
         float3 n = type == RT_OBJ_XY_RECT ? v3(0, 0, 1) : type == RT_OBJ_XZ_RECT ? v3(0, 1, 0) : v3(1, 0, 0);
-        r.front = dk < 0.0f;
-        r.n = r.front ? n : -n;
-        r.p = vfma(t, d, o);
+        if (xi < 0) {
+            r.front = dk < 0.0f;
+            r.n = r.front ? n : -n;
+            r.p = vfma(t, d, o);
+        } else {
+            r.p = xf_point(xf, vfma(t, od, oo));
+            set_face_normal(r, d, xf_normal(xf + 3, n));
+        }
         break;
     }
     case RT_OBJ_CYLINDER: {   // object.cuh:270-289
@@ -310,7 +343,13 @@ __device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot,
         float tt, bu = 0.0f, bv = 0.0f;
         triangle_t(v0, e1, e2, o, d, t, t, tt, bu, bv);
         float3 n = v3(__fmaf_rn(e1.y, e2.z, -(e1.z * e2.y)), __fmaf_rn(e1.z, e2.x, -(e1.x * e2.z)), __fmaf_rn(e1.x, e2.y, -(e1.y * e2.x)));
-        r.u = bu; r.v = bv;
+        if (want_uv) {      // per-vertex texture coordinates (OBJ `vt`), 16-bit unorm pairs in the w components; without `vt` the
+                            // vertices carry (0,0), (1,0), (0,1) and the sums below give (bu, bv)
+            const unsigned q0 = __float_as_uint(A.w), q1 = __float_as_uint(__ldg(&sc.primB[slot]).w), q2 = __float_as_uint(__ldg(&sc.primC[slot]).w);
+            const float w0 = (1.0f - bu) - bv;
+            r.u = __fmaf_rn(bv, (float)(q2 & 0xffffu) / 65535.0f, __fmaf_rn(bu, (float)(q1 & 0xffffu) / 65535.0f, w0 * ((float)(q0 & 0xffffu) / 65535.0f)));
+            r.v = __fmaf_rn(bv, (float)(q2 >> 16) / 65535.0f, __fmaf_rn(bu, (float)(q1 >> 16) / 65535.0f, w0 * ((float)(q0 >> 16) / 65535.0f)));
+        }
         r.p = vfma(t, d, o);
         set_face_normal(r, d, vunit(n));
         break;

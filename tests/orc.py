@@ -91,28 +91,65 @@ def read_image_rgb8(path):
     return np.ascontiguousarray(im)
 
 
+def make_xform(o):
+    """translate(t) * rotate(axis, angle) of an object's "rotate" / "translate" keys, through the oracle's orc_make_xform."""
+    xf = capi.XformDesc()
+    ax = np.array(o.get("rotate", {}).get("axis", [0, 0, 1]), np.float32)
+    tr = np.array(o.get("translate", [0, 0, 0]), np.float32)
+    lib().orc_make_xform(fptr(ax), float(o.get("rotate", {}).get("angle", 0.0)), int("rotate" in o), fptr(tr), int("translate" in o), C.byref(xf))
+    return xf
+
+
+def bake(m, p):
+    """m * p for a 3x4 row-major matrix in float32, left to right (csrc/rt_json.cpp: Loader::bake)."""
+    f = np.float32
+    x, y, z = f(p[0]), f(p[1]), f(p[2])
+    return [float(f(f(f(f(m[4 * r]) * x) + f(f(m[4 * r + 1]) * y)) + f(f(m[4 * r + 2]) * z)) + f(m[4 * r + 3])) for r in range(3)]
+
+
+def pack_uv(u, v):
+    """(u, v) clamped to [0, 1] as two 16-bit unorm values in one 32-bit word (rt.h: TRIANGLE p[9..11])."""
+    f = np.float32
+    u = min(max(f(u), f(0)), f(1)); v = min(max(f(v), f(0)), f(1))
+    return int(f(f(u * f(65535.0)) + f(0.5))) | (int(f(f(v * f(65535.0)) + f(0.5))) << 16)
+
+
 def expand_meshes(objs, base_dir):
     """`mesh` objects -> triangles, in place in the object order (same rules as csrc/rt_json.cpp load_obj: v' = v*scale + t
-    in float32, 1-based / negative indices, v/vt/vn tokens, fan triangulation)."""
+    in float32 — with "rotate": v' = M (v*scale), M = translate * rotate —, 1-based / negative indices, v/vt/vn tokens, `vt` ->
+    per-vertex uv, fan triangulation)."""
     out = []
     for o in objs:
         if o["type"] != "mesh":
             out.append(o)
             continue
         sc_, tr = np.float32(o.get("scale", 1.0)), np.array(o.get("translate", [0, 0, 0]), np.float32)
+        rot = make_xform(o).m if "rotate" in o else None
         path = o["file"] if os.path.isabs(o["file"]) else os.path.join(base_dir or ".", o["file"])
-        v = []
+        v, vt = [], []
         for line in open(path):
             t = line.split()
             if not t:
                 continue
             if t[0] == "v":
-                v.append([float(np.float32(np.float32(float(t[1 + k])) * sc_) + tr[k]) for k in range(3)])
+                if rot is not None:
+                    v.append(bake(rot, [np.float32(np.float32(float(t[1 + k])) * sc_) for k in range(3)]))
+                else:
+                    v.append([float(np.float32(np.float32(float(t[1 + k])) * sc_) + tr[k]) for k in range(3)])
+            elif t[0] == "vt":
+                vt.append((float(t[1]), float(t[2]) if len(t) > 2 else 0.0))
             elif t[0] == "f":
-                idx = [int(tok.split("/")[0]) for tok in t[1:]]
+                toks = [tok.split("/") for tok in t[1:]]
+                idx = [int(tk[0]) for tk in toks]
                 idx = [len(v) + i if i < 0 else i - 1 for i in idx]
+                tidx = [(int(tk[1]) if len(tk) > 1 and tk[1] else None) for tk in toks]
+                tidx = [None if j is None else (len(vt) + j if j < 0 else j - 1) for j in tidx]
                 for k in range(1, len(idx) - 1):
-                    out.append({"type": "triangle", "v0": v[idx[0]], "v1": v[idx[k]], "v2": v[idx[k + 1]], "material": o.get("material", 0)})
+                    tri = {"type": "triangle", "v0": v[idx[0]], "v1": v[idx[k]], "v2": v[idx[k + 1]], "material": o.get("material", 0)}
+                    tt = [tidx[0], tidx[k], tidx[k + 1]]
+                    if all(j is not None for j in tt):
+                        tri["uv"] = [list(vt[j]) for j in tt]
+                    out.append(tri)
     return out
 
 
@@ -167,16 +204,19 @@ def load_scene(src, width=None, height=None, spp=None, max_depth=None, base_dir=
         elif t == "box":
             vals = list(o["min"]) + list(o["max"])
         elif t == "triangle":
-            vals = list(o["v0"]) + list(o["v1"]) + list(o["v2"])
+            vs = [list(o["v0"]), list(o["v1"]), list(o["v2"])]
+            if "rotate" in o or "translate" in o:          # baked into the vertices (csrc/rt_json.cpp)
+                m = make_xform(o).m
+                vs = [bake(m, [np.float32(c) for c in vv]) for vv in vs]
+            vals = vs[0] + vs[1] + vs[2]
         for k, v in enumerate(vals):
             q.p[k] = v
-        if t in ("cylinder", "box") and (t == "cylinder" or "rotate" in o or "translate" in o):
-            xf = capi.XformDesc()
-            ax = np.array(o.get("rotate", {}).get("axis", [0, 0, 1]), np.float32)
-            tr = np.array(o.get("translate", [0, 0, 0]), np.float32)
-            L.orc_make_xform(fptr(ax), float(o.get("rotate", {}).get("angle", 0.0)), int("rotate" in o), fptr(tr),
-                             int("translate" in o), C.byref(xf))
-            q.xform = len(xforms); xforms.append(xf)
+        if t == "triangle" and "uv" in o:
+            bits = C.cast(q.p, C.POINTER(C.c_uint32))        # raw bits: a float round trip could alter NaN patterns
+            for c in range(3):
+                bits[9 + c] = pack_uv(*o["uv"][c])
+        if t != "triangle" and (t == "cylinder" or "rotate" in o or "translate" in o):
+            q.xform = len(xforms); xforms.append(make_xform(o))
     XA = (capi.XformDesc * max(1, len(xforms)))(*xforms)
     MA = (capi.MaterialDesc * max(1, len(mats)))()
     for i, m in enumerate(mats):
