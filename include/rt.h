@@ -243,6 +243,20 @@ int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigned char *rgb
 int rt_synchronize(rt_ctx *ctx);
 int rt_stats_reset(rt_ctx *ctx);
 
+/* rt_download's tonemap + read-back for callers that must not allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * rt_download stages the RGB8 image in a device buffer it cudaMallocs on first use; this entry point stages it in a file-scope
+ * static __device__ array of RT_NOALLOC_MAX_BYTES (8 MiB: images up to 1920 x 1080 x 3 and a little beyond) that every GPU loading
+ * the library holds until the process exits.  It calls no cudaMalloc / cudaFree / allocating library routine.
+ *   accum_dev: device pointer to width*height*3 float sums, row 0 = bottom (e.g. from rt_accum_device_ptr) on `device`;
+ *   rgb8_host: width*height*3 bytes, row 0 = top; same arithmetic as rt_download (gamma as there); stream: cudaStream_t or NULL.
+ * Enqueues on `stream` and synchronises it.  width*height*3 > RT_NOALLOC_MAX_BYTES is rejected with RT_ERR_INVALID
+ * (message from rt_last_error(NULL)).  Every call on a device shares the one array, which keeps the previous call's bytes
+ * (nothing needs clearing: the bytes read back are exactly the bytes just written) — calls that overlap on the same GPU race. */
+#define RT_NOALLOC_MAX_BYTES (8u << 20)
+int rt_tonemap_noalloc(int device, void *stream, const float *accum_dev, int width, int height, int total_spp, int gamma,
+                       unsigned char *rgb8_host);
+
 /* Page-locked host buffers for rt_download targets (optional: any host pointer works, a pinned one is copied at the full
  * host-link rate and without a staging copy).  Takes the place of the reference's managed image allocation, which the
  * host reads after cudaDeviceSynchronize (main.cu:487-489, 509-514). */
