@@ -127,6 +127,8 @@ enum { RT_RENDER_KEEP_ACCUM = 1,     /* add to the accumulation buffer instead o
        RT_RENDER_SERIAL = 64,      /* one pass at a time on the context's stream (default: two passes in flight on two streams, so the
                                         short late-bounce launches of one overlap the other; same image either way) */
        RT_RENDER_NO_TILE_LISTS = 256,
+       RT_RENDER_NO_TAIL = 1024,     /* keep the queue schedule to the last bounce (default: from bounce 8 on one launch finishes every
+                                        surviving path — same image either way) */
        RT_RENDER_KEEP_CHUNKS = 512 };  /* leave this call's chunk sums in their buffers instead of folding them into the accumulation
                                         buffer: the root of a multi-GPU render gathers and folds them (rt_gather_image) */ /* traverse the tree for bounce 0 too (default: the generate stage resolves bounce-0 hits from the
                                         per-tile candidate lists of the camera beams; same image either way) */
@@ -166,6 +168,8 @@ typedef struct rt_stats {
     int64_t n_generate_leaf_tests;  /* leaf tests the generate stage made on the tile candidate lists (COUNT_EVENTS; not in the n_*_tests above,
                                        which are the extend stage's) */
     int64_t paths_skipped;          /* camera paths of empty tiles that never entered the queues (their records move no bytes) */
+    float ms_tail;                  /* tail stage (one launch finishes the paths alive at the tail bounce), TIME_STAGES */
+    float reserved;
 } rt_stats;
 
 typedef struct rt_scene_info {

@@ -19,6 +19,7 @@ RT_RENDER_KEEP_ACCUM, RT_RENDER_COUNT_EVENTS, RT_RENDER_NO_SORT, RT_RENDER_NEE, 
 RT_RENDER_SERIAL = 64
 RT_RENDER_NO_TILE_LISTS = 256
 RT_RENDER_KEEP_CHUNKS = 512
+RT_RENDER_NO_TAIL = 1024
 RT_SAMPLE_CHUNKS = 8
 RT_NOALLOC_MAX_BYTES = 8 << 20      # static scratch of rt_tonemap_noalloc
 
@@ -75,7 +76,7 @@ class Stats(C.Structure):
                 ("n_rect_tests", C.c_int64), ("n_cyl_reject", C.c_int64), ("n_cyl_accept", C.c_int64),
                 ("n_tri_tests", C.c_int64), ("n_boxprim_tests", C.c_int64), ("n_shade", C.c_int64),
                 ("n_generate", C.c_int64), ("n_node_visits", C.c_int64),
-                ("n_generate_leaf_tests", C.c_int64), ("paths_skipped", C.c_int64)]
+                ("n_generate_leaf_tests", C.c_int64), ("paths_skipped", C.c_int64), ("ms_tail", C.c_float), ("reserved", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -586,7 +586,13 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     bool clear = !((prm->flags & RT_RENDER_KEEP_ACCUM) && ctx->accum_valid);
     if (count) CU(cudaMemsetAsync(ctx->d_counters.p, 0, sizeof(unsigned long long) * CTR_COUNT, s));
     long long passes = 0;
-    float ms_stage[5] = {0, 0, 0, 0, 0};
+    float ms_stage[6] = {0, 0, 0, 0, 0, 0};
+    // Tail stage (k_tail): the bounce from which the surviving paths are finished by one launch.  Trees staged in shared memory: bounce
+    // 8 (RTIOW: 3.5 % of the paths are still alive there); RT_TAIL_BOUNCE overrides, 0 or RT_RENDER_NO_TAIL switches it off.  Not with
+    // NEE (the shadow stage needs the queues) or COUNT_EVENTS (the counters belong to the extend stage).
+    static const int env_tail = getenv("RT_TAIL_BOUNCE") ? atoi(getenv("RT_TAIL_BOUNCE")) : -1;
+    int tail_b0 = env_tail >= 0 ? env_tail : 8;
+    if (nee || count || (prm->flags & RT_RENDER_NO_TAIL) || tail_b0 <= 0 || tail_b0 >= ds.max_depth) tail_b0 = -1;
     cudaEvent_t *evs = ctx->ev_count;       // COUNT_EVENTS: one synchronising event pair per stage launch (owned by the context)
     if (time_stages) {          // event pairs are recorded without synchronising and resolved in rt_download
         const size_t n_passes = (size_t)n_pass_total;
@@ -647,6 +653,8 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
             if (dsp.tile_empty_prefix) ctx->stats.paths_skipped += (long long)ctx->tiles_n_empty * 32 * sn;
             const int depth_needed = ctx->scene_scatters ? ds.max_depth : 1;      // nothing survives the first vertex of an all-emitter scene
             for (int b = 0; b < depth_needed && !no_paths; ++b) {
+                // from bounce tail_b0 on, one launch finishes every surviving path (k_tail) instead of 2 x (depth - b) queue launches
+                if (b == tail_b0 && b > 0) { timed(5, [&] { launch_tail(cfg, dsp, S.q, prm->seed, first_sample, b, buf); }); break; }
                 if (b > 0 || tile_mode != 1) timed(1, [&] { launch_extend(cfg, dsp, S.q, b, buf, count, b == 0 && tile_mode == 2); });
                 timed(2, [&] { launch_shade(cfg, dsp, S.q, prm->seed, first_sample, b, buf, b == ds.max_depth - 1, count, sort, nee); });
                 if (nee) timed(4, [&] { launch_shadow(cfg, dsp, S.q, b); });
@@ -691,7 +699,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
         st.n_tri_tests += c[CTR_TRI]; st.n_boxprim_tests += c[CTR_BOXPRIM]; st.n_shade += c[CTR_SHADE];
         st.n_generate += (long long)spp * np; st.n_node_visits += c[CTR_NODE_VISITS];
         st.n_generate_leaf_tests += c[CTR_GEN_LEAF];
-        st.ms_generate += ms_stage[0]; st.ms_extend += ms_stage[1]; st.ms_shade += ms_stage[2]; st.ms_accumulate += ms_stage[3]; st.ms_shadow += ms_stage[4];
+        st.ms_generate += ms_stage[0]; st.ms_extend += ms_stage[1]; st.ms_shade += ms_stage[2]; st.ms_accumulate += ms_stage[3]; st.ms_shadow += ms_stage[4]; st.ms_tail += ms_stage[5];
         if (c[CTR_STACK_OVERFLOW]) return rt_fail(ctx, RT_ERR_INVALID, "traversal stack overflow (BVH deeper than RT_TRAV_STACK)");
     }
     return RT_OK;
@@ -773,7 +781,8 @@ extern "C" int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigne
     if (stats && ctx->d_rays.p) { unsigned long long r[2] = {0, 0}; CU(cudaMemcpyAsync(r, ctx->d_rays.p, sizeof r, cudaMemcpyDeviceToHost, s)); CU(cudaStreamSynchronize(s)); ctx->stats.rays = (long long)r[0]; ctx->stats.shadow_rays = (long long)r[1]; }
     CU(cudaStreamSynchronize(s));
     if (!ctx->pending.empty()) {
-        float *acc[5] = {&ctx->stats.ms_generate, &ctx->stats.ms_extend, &ctx->stats.ms_shade, &ctx->stats.ms_accumulate, &ctx->stats.ms_shadow};
+        float *acc[6] = {&ctx->stats.ms_generate, &ctx->stats.ms_extend, &ctx->stats.ms_shade, &ctx->stats.ms_accumulate, &ctx->stats.ms_shadow,
+                         &ctx->stats.ms_tail};
         for (size_t k = 0; k < ctx->pending.size(); ++k) {
             float ms = 0;
             if (cudaEventElapsedTime(&ms, ctx->ev_pool[2 * k], ctx->ev_pool[2 * k + 1]) == cudaSuccess) *acc[ctx->pending[k]] += ms; else cudaGetLastError();

@@ -561,6 +561,103 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
 }
 
 // ------------------------------------------------------------------------------------------------
+// tail: finishes every path that is still alive at bounce b0 in ONE launch (extend + shade in a per-lane loop, no queues).
+//
+// The wavefront ends in dozens of launches over queues that have shrunk to a few per cent of the pass (RTIOW: 3.5 % of the paths
+// are alive at bounce 8, the queues stay non-empty to bounce ~45): each of those 2 x 40 launches is a few tens of microseconds of a
+// mostly empty GPU.  From bounce b0 on (rt_ctx.cu chooses it), a lane owns one path and runs  closest hit -> emitted / scatter  until
+// the path ends, then writes its radiance record; a finished lane takes the next entry of the bounce-b0 queue (warp-aggregated
+// atomic on the work cursor) once at least RT_TAIL_REFILL lanes of its warp are idle, so that the loop does not run at one or two
+// live lanes while 45-bounce stragglers finish.  Same Philox keys (pixel, sample, bounce + 1) and the same functions as k_extend /
+// k_shade: the image is bit-identical to the queue schedule (tests: RT_RENDER_NO_TAIL).  Also the "queue-free" schedule for scenes
+// of a dozen objects when b0 = 1.  Not used with NEE (the shadow stage needs its queue) or COUNT_EVENTS.
+// Segments traced beyond bounce b0 are added to qcount[b0 + 1] (ray statistics; the shade stage of bounce b0 never runs).
+// ------------------------------------------------------------------------------------------------
+#ifndef RT_TAIL_REFILL
+#define RT_TAIL_REFILL 4         // (1 / 4 / 12 / 24: tail 6.51 / 6.53 / 9.06 / 12.55 ms per 128-spp RTIOW pass)
+#endif
+template <bool SMEM, bool DIRECT, int ONLY = -1>
+#ifndef RT_TAIL_CTAS
+#define RT_TAIL_CTAS 2          // 64 registers with a few spills; 1 CTA (91 registers, 16 warps per SM): 9.06 vs 7.21 ms
+#endif
+__global__ void __launch_bounds__(RT_EXT_BLOCK, RT_TAIL_CTAS) k_tail(DScene sc, Queues q, unsigned seed, int spp_begin, int b0, int buf) {
+    extern __shared__ float2 s_raw[];
+    const int n = q.qcount[b0];
+    if (n == 0) return;
+    const char *nodes = reinterpret_cast<const char *>(sc.nodes);
+    if (SMEM) {
+        const float2 *src = reinterpret_cast<const float2 *>(sc.nodes_s);
+        for (int i = threadIdx.x; i < sc.n_nodes * (int)(sizeof(BvhNodeS) / 8); i += blockDim.x) s_raw[i] = __ldg(&src[i]);
+        __syncthreads();
+        nodes = reinterpret_cast<const char *>(s_raw);
+    }
+    const unsigned sstack = (unsigned)__cvta_generic_to_shared(s_raw) + (SMEM ? (unsigned)sc.n_nodes * (unsigned)sizeof(BvhNodeS) : 0u) +
+                            threadIdx.x * 8u;
+    int *cursor = &q.workctr[b0 * 2];
+    const float4 *__restrict__ in_o = q.ray_o[buf], *__restrict__ in_d = q.ray_d[buf], *__restrict__ in_t = q.thr[buf];
+    const int lane = lane_id();
+    TravCounters cnt = {};
+    // per-lane path state
+    int state = -1;                  // >= 0: path in flight (value = bounce); -1: idle, wants work; -2: the queue is exhausted
+    float3 o = v3(0, 0, 0), d = v3(0, 0, 0), thr = v3(0, 0, 0);
+    float key_pixel = 0.0f, key_sample = 0.0f;
+    int path_id = 0;
+    unsigned extra = 0;              // segments traced beyond bounce b0
+    for (;;) {
+        const unsigned idle = __ballot_sync(0xffffffffu, state == -1), live = __ballot_sync(0xffffffffu, state >= 0);
+        if (idle && (live == 0u || __popc(idle) >= RT_TAIL_REFILL)) {
+            int base = 0;
+            const int leader = __ffs(idle) - 1;
+            if (lane == leader) base = atomicAdd(cursor, __popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (state == -1) {
+                const int i = base + __popc(idle & lanemask_lt());
+                if (i < n) {
+                    const float4 o4 = in_o[i], d4 = in_d[i], t4 = in_t[i];
+                    o = f4xyz(o4); d = f4xyz(d4); thr = f4xyz(t4);
+                    path_id = __float_as_int(o4.w); key_pixel = d4.w; key_sample = t4.w;
+                    state = b0;
+                } else state = -2;
+            }
+        }
+        if (__ballot_sync(0xffffffffu, state >= 0) == 0u) {
+            if (__ballot_sync(0xffffffffu, state == -1) == 0u) break;      // every lane has seen the end of the queue
+            continue;
+        }
+        if (state >= 0) {
+            float t; int code;
+            if (SMEM) traverse<true, false, false, RT_SSTACK, ONLY>(sc, nodes, o, d, 0.001f, FLT_MAX, t, code, cnt, sstack);
+            else if (sc.nodes4) traverse4<false, false, RT_SSTACK, ONLY>(sc, sc.nodes4, o, d, 0.001f, FLT_MAX, t, code, cnt, sstack);
+            else traverse<false, false, false, RT_SSTACK, ONLY>(sc, nodes, o, d, 0.001f, FLT_MAX, t, code, cnt, sstack);
+            if (state > b0) ++extra;
+            float3 rad = v3(0, 0, 0);
+            bool alive = false;
+            if (code < 0) {
+                rad = thr * background(sc, d);
+            } else {
+                const int type = (unsigned)code >> 28, slot = code & RT_LEAF_SLOT_MASK;
+                const DMaterial m = sc.mats[__ldg(&sc.prim_mat[slot])];
+                HitRec rec;
+                hit_record(sc, type, slot, o, d, t, m.albedo.w != 0.0f, rec);
+                if (m.type == RT_MAT_DIFFUSE_LIGHT) {
+                    rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
+                } else {
+                    Rng rng; rng.init(seed, (unsigned)__float_as_int(key_pixel), (unsigned)(spp_begin + __float_as_int(key_sample)), (unsigned)state + 1u, sc.sampling);
+                    float3 att, sd;
+                    const bool ok = scatter<DIRECT>(sc, m, d, rec, rng, att, sd);
+                    if (ok && state != sc.max_depth - 1) { alive = true; o = rec.p; d = sd; thr = thr * att; }
+                }
+            }
+            if (alive) ++state;
+            else { q.radiance[path_id] = make_float4(rad.x, rad.y, rad.z, 0.0f); state = -1; }
+        }
+    }
+#pragma unroll
+    for (int k = 16; k > 0; k >>= 1) extra += __shfl_xor_sync(0xffffffffu, extra, k);
+    if (lane == 0 && extra) atomicAdd(&q.qcount[b0 + 1], (int)extra);
+}
+
+// ------------------------------------------------------------------------------------------------
 // accumulate: accum[pixel] += sum over this pass's samples, in ascending sample order (fixed order => the image is
 // bit-reproducible; replaces the register sum of main.cu:95-104).  One thread per pixel, S coalesced plane reads.
 // ------------------------------------------------------------------------------------------------
@@ -791,6 +888,25 @@ void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bo
     bump(c);
 }
 
+// tail stage: every path alive at bounce b0 is finished by one launch (k_tail)
+void launch_tail(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int b0, int buf) {
+    const int grid = persistent_grid(c, RT_TAIL_CTAS);
+    const size_t sm = c.bvh_smem_bytes + RT_SSTACK_BYTES;
+    const bool spheres = c.bvh_smem_bytes && sc.only_type == RT_OBJ_SPHERE;
+#define RT_TAIL_ARGS <<<grid, RT_EXT_BLOCK, sm, c.stream>>>(sc, q, seed, spp_begin, b0, buf)
+    if (sc.direct) {
+        if (spheres) k_tail<true, true, RT_OBJ_SPHERE> RT_TAIL_ARGS;
+        else if (c.bvh_smem_bytes) k_tail<true, true> RT_TAIL_ARGS;
+        else k_tail<false, true> RT_TAIL_ARGS;
+    } else {
+        if (spheres) k_tail<true, false, RT_OBJ_SPHERE> RT_TAIL_ARGS;
+        else if (c.bvh_smem_bytes) k_tail<true, false> RT_TAIL_ARGS;
+        else k_tail<false, false> RT_TAIL_ARGS;
+    }
+#undef RT_TAIL_ARGS
+    bump(c);
+}
+
 // The dynamic shared-memory limit is a property of the kernel on a device, shared by every context (and host thread) that uses
 // the device: it is raised ONCE per device to the opt-in maximum for every k_extend / k_shade instance, never to one scene's tree
 // size (a second context uploading a smaller tree must not lower the limit under the first one's launches).
@@ -806,6 +922,8 @@ cudaError_t kernels_configure_device(int dev, size_t smem_optin) {
         SET((k_extend<true, false, false, RT_OBJ_SPHERE>), smem_optin); SET((k_extend<true, false, true, RT_OBJ_SPHERE>), smem_optin);
         SET((k_extend<false, false, false>), smem_optin); SET((k_extend<false, true, false>), smem_optin);
         SET((k_extend<false, false, true>), smem_optin); SET((k_extend<false, true, true>), smem_optin);
+        SET((k_tail<true, true, RT_OBJ_SPHERE>), smem_optin); SET((k_tail<true, true>), smem_optin); SET((k_tail<false, true>), smem_optin);
+        SET((k_tail<true, false, RT_OBJ_SPHERE>), smem_optin); SET((k_tail<true, false>), smem_optin); SET((k_tail<false, false>), smem_optin);
 #define SET_SH(D_) \
         SET((k_shade<false, false, false, D_>), sizeof(ShadeSmem)); SET((k_shade<true, false, false, D_>), sizeof(ShadeSmem)); \
         SET((k_shade<false, true, false, D_>), sizeof(ShadeSmem)); SET((k_shade<true, true, false, D_>), sizeof(ShadeSmem)); \

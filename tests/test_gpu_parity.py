@@ -196,6 +196,11 @@ def test_render_options_do_not_change_the_image(rt):
     assert np.array_equal(rt.download()[0], base)
     rt.render(seed=5, flags=capi.RT_RENDER_SERIAL)                       # one stream instead of two passes in flight
     assert np.array_equal(rt.download()[0], base)
+    rt.stats_reset(); rt.render(seed=5, flags=capi.RT_RENDER_NO_TAIL)     # queue schedule to the last bounce instead of the tail launch
+    img, _, st_q = rt.download()
+    rt.stats_reset(); rt.render(seed=5)
+    _, _, st_t = rt.download()
+    assert np.array_equal(img, base) and st_q["rays"] == st_t["rays"] and st_q["launches"] > st_t["launches"]
     rt.render(seed=5, flags=capi.RT_RENDER_NO_TILE_LISTS)                # bounce 0 through the tree instead of the beam lists
     assert np.array_equal(rt.download()[0], base)
     rt.render(seed=5, flags=capi.RT_RENDER_SERIAL, max_paths_per_pass=W * H)

@@ -35,9 +35,9 @@ r.stats_reset()
 for _ in range(reps):
     r.render(seed=0x2023, flags=capi.RT_RENDER_TIME_STAGES | extra)
 _, _, st = r.download(want_sum=False, want_rgb8=False)
-tot = st["ms_generate"] + st["ms_extend"] + st["ms_shade"] + st["ms_accumulate"]
+tot = st["ms_generate"] + st["ms_extend"] + st["ms_shade"] + st["ms_accumulate"] + st["ms_tail"]
 out.update({"ms_generate": st["ms_generate"] / reps, "ms_extend": st["ms_extend"] / reps, "ms_shade": st["ms_shade"] / reps,
-            "ms_accumulate": st["ms_accumulate"] / reps, "ms_sum": tot / reps, "launches": st["launches"] / reps,
+            "ms_accumulate": st["ms_accumulate"] / reps, "ms_tail": st["ms_tail"] / reps, "ms_sum": tot / reps, "launches": st["launches"] / reps,
             "Msamples_per_s": W * H * spp / (tot / reps * 1e-3) / 1e6, "Grays_per_s_extend": st["rays"] / reps / (max(st["ms_extend"], 1e-9) / reps * 1e-3) / 1e9,
             "Grays_per_s_shade": st["rays"] / reps / (max(st["ms_shade"], 1e-9) / reps * 1e-3) / 1e9})
 # whole render, one launch of rt_render per repetition: two passes in flight (default) vs one at a time
