@@ -4,7 +4,7 @@
  * The reference has no BVH in its C++/CUDA trees (hittable_list is a linear walk, object.cuh:23-37;
  * aabb.hpp is dead code), so there is nothing to pin this against upstream: the contract is that the
  * GPU build is BIT-EXACT with this serial statement of the same algorithm (north star, kernel group 1).
- *   Morton:   63-bit, 21 bits per axis, centroid normalised to the centroid bounds
+ *   Morton:   63-bit, 21 bits per axis, centroid normalised to the centroid bounds (per axis; one scale for all axes in trees of more than 4096 leaves)
  *   sort:     stable LSD radix, 8 passes x 8-bit digits, on (morton, object index) pairs
  *   topology: Karras 2012, delta(i,j) = clz(m_i ^ m_j), ties broken by 64 + clz(i ^ j)
  *   boxes:    leaf = object box padded by 2^-10 * (largest object extent) + 2^-20 * (largest scene extent);
@@ -25,6 +25,7 @@
 #define ORC_MAX_GIANTS 16
 #endif
 #define ORC_GIANT_KEY 0x8000000000000000ULL
+#define ORC_MORTON_CUBE_MIN 4096
 
 void orc_object_aabb(const rt_scene_desc *sc, int i, float bmin[3], float bmax[3]) {
     const rt_object_desc *ob = &sc->objects[i];
@@ -160,13 +161,16 @@ int orc_lbvh_build_ex(const rt_scene_desc *sc, uint64_t *morton_sorted, int32_t 
     }
     uint64_t *keys = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)n);
     int32_t *vals = (int32_t *)malloc(sizeof(int32_t) * (size_t)n);
+    /* trees of more than ORC_MORTON_CUBE_MIN leaves (meshes): one scale for the three axes, a cubical Morton grid (the cells of a flat
+     * surface are not thin slabs); smaller scenes: every axis normalised to its own extent (rt_lbvh.cu:k_morton has the measurements) */
+    const float cext = fmaxf(cmax[0] - cmin[0], fmaxf(cmax[1] - cmin[1], cmax[2] - cmin[2]));
     for (int i = 0; i < n; ++i) {
         vals[i] = i;
         if (giant[i]) { keys[i] = ORC_GIANT_KEY; continue; }
         uint32_t q[3];
         for (int k = 0; k < 3; ++k) {
             float c = 0.5f * (bmin[3 * i + k] + bmax[3 * i + k]);
-            q[k] = quant21(c, cmin[k], cmax[k] - cmin[k]);
+            q[k] = quant21(c, cmin[k], nt > ORC_MORTON_CUBE_MIN ? cext : cmax[k] - cmin[k]);
         }
         keys[i] = expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
     }

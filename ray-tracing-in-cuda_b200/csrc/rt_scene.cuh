@@ -45,6 +45,7 @@ struct DTexture { int type; int even; int odd; int image; float4 color; };      
 struct DImage { cudaTextureObject_t tex; int width, height; };
 
 #define RT_TILE_K 16
+#define RT_MORTON_CUBE_MIN 4096 // trees with more leaves quantise their Morton codes on a cubical grid (rt_lbvh.cu:k_morton)
 #define RT_MAX_GIANTS 16        // objects kept out of the tree and tested first by every ray (rt_lbvh.cu:k_giants_mark)
 struct DCamera { float3 origin, llc, horizontal, vertical, u, v, w; float lens_radius; };
 
