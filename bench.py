@@ -405,6 +405,12 @@ def main():
         r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, total_spp=spp, flags=flags | capi.RT_RENDER_TIME_STAGES | capi.RT_RENDER_KEEP_CHUNKS,
                  max_paths_per_pass=args.max_paths)
         _, _, sg = r.download(want_sum=False, want_rgb8=False)
+        # the same with the queue schedule kept to the last bounce (no tail stage): every ray passes through k_extend / k_shade, which is
+        # what the event counters of the counted run describe — the roofline fractions are taken on THIS step
+        r.stats_reset()
+        r.render(seed=0x2023, spp_begin=s0, spp_count=s1 - s0, total_spp=spp, max_paths_per_pass=args.max_paths,
+                 flags=flags | capi.RT_RENDER_TIME_STAGES | capi.RT_RENDER_KEEP_CHUNKS | capi.RT_RENDER_NO_TAIL)
+        _, _, sq = r.download(want_sum=False, want_rgb8=False)
         barrier()
 
         # ---- e2e: host JSON text -> upload (+BVH build) -> render -> reduce -> download to host, every step ----
@@ -447,8 +453,9 @@ def main():
         rays = st["rays"] / args.steps * world            # rank 0 traced 1/world of them
         ext_flops, shade_flops = flop_model(counts)
         ext_flops *= scale; shade_flops *= scale
-        ms_extend = sg["ms_extend"]
-        ms_other = sg["ms_generate"] + sg["ms_shade"] + sg["ms_accumulate"]
+        ms_extend = sq["ms_extend"]
+        ms_other = sq["ms_generate"] + sq["ms_shade"] + sq["ms_accumulate"]
+        ms_tail = sg.get("ms_tail", 0.0)
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         ach = ext_flops / (ms_extend * 1e-3) / 1e12 if ms_extend > 0 else 0.0
@@ -458,19 +465,18 @@ def main():
         traffic, traffic_note = None, ""
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         depth = int(sdesc["max_depth"])
-        passes_sg = max(1, int(sg.get("passes", 1)))
-        # per pass: pass_init + generate + accumulate + `depth` shade launches + the extend launches
-        ext_per_pass = int(sg["launches"]) // passes_sg - 3 - depth
-        bounce0_in_generate = ext_per_pass == depth - 1       # primary hits resolved from the tile candidate lists
+        bounce0_in_generate = counts.get("n_generate_leaf_tests", 0) > 0       # primary hits resolved from the tile candidate lists
+        n_ext_launches = max(1, int(sq.get("launches_extend", 1)))
+        # rays of the extend launches: the counted run (no tail stage there) saw every ray; the timed schedule hands the paths alive at
+        # the tail bounce to k_tail, whose rays and time are reported separately (stage "tail") and are NOT in this roofline
         ext_rays = rays_rank - (samples_rank if bounce0_in_generate else 0.0)
-        n_ext_launches = passes_sg * max(1, ext_per_pass)
         # algorithmic bytes of the queue stages on this rank: generate W32/sample (ray_o, ray_d; camera paths carry
         # no throughput record) + W8/sample when it also resolves the bounce-0 hits; shade R56/ray minus the 16-byte throughput
         # record at bounce 0, + W48 per survivor (rays - samples) + W16 per finished path; accumulate R16/sample (+12 B/pixel RMW
         # per pass, ignored).  Paths of empty camera tiles move fewer bytes than this (not subtracted: no such tile in RTIOW).
         # Camera paths of empty tiles (their beam touches no leaf box) never enter the queues: under a constant background they move no
         # bytes at all, under the sky gradient only their 16-byte radiance record (written by generate, read by accumulate).
-        skipped = float(sg.get("paths_skipped", 0))
+        skipped = float(sq.get("paths_skipped", 0))
         gradient = sdesc.get("gradient", False)
         queued = samples_rank - skipped
         queue_bytes = ((32.0 + (8.0 if bounce0_in_generate else 0.0)) * queued + 56.0 * (rays_rank - skipped) - 16.0 * queued
@@ -487,13 +493,16 @@ def main():
                        "objects": sdesc["objects"], "partition": f"8 sample chunks dealt to {world} GPU(s); chunk sums gathered on rank 0 by the library (NCCL send/recv) and added in chunk order",
                        "l2": "wavefront queues (GBs) exceed the 126 MB L2 every pass; no explicit flush needed"},
             "mrays_per_s": rays / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays / total_samples,
-            "stage_ms_per_step": {"generate": sg["ms_generate"], "extend": ms_extend, "shade": sg["ms_shade"], "accumulate": sg["ms_accumulate"],
-                                  "serial_total": sg["ms_total"],
-                                  "note": "one extra step with per-launch CUDA events, one pass at a time; the timed steps keep two passes in flight"},
+            "stage_ms_per_step": {"generate": sg["ms_generate"], "extend": sg["ms_extend"], "shade": sg["ms_shade"], "accumulate": sg["ms_accumulate"],
+                                  "tail": ms_tail, "serial_total": sg["ms_total"],
+                                  "note": "one extra step with per-launch CUDA events, one pass at a time; the timed steps keep two passes in flight",
+                                  "queue_schedule": {"generate": sq["ms_generate"], "extend": sq["ms_extend"], "shade": sq["ms_shade"],
+                                                     "accumulate": sq["ms_accumulate"], "serial_total": sq["ms_total"],
+                                                     "note": "RT_RENDER_NO_TAIL: every bounce through the queues; the rooflines are taken on this step"}},
             "roofline": {"bound": "fp32", "kernel": "k_extend", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": ach / fp32_peak if fp32_peak else None, "traffic": traffic,
-                         "note": "algorithmic FLOPs (SURVEY §8(d) model, device event counters) / CUDA-event time of the extend launches "
-                                 "of one step run right after the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)" + traffic_note},
+                         "note": "algorithmic FLOPs (SURVEY §8(d) model, device event counters of the extend stage only) / CUDA-event time of the extend launches "
+                                 "of one queue-schedule step (RT_RENDER_NO_TAIL) run right after the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)" + traffic_note},
             "roofline_hbm": {"bound": "hbm", "kernel": "generate+shade+accumulate", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s",
                              "frac": hbm_ach / hbm_peak, "note": ("104 B/ray (+ 8 B/sample when generate writes the bounce-0 hit records; DESIGN.md §6) / CUDA-event time of those stages; peak from MEASURED_PEAKS.json (of measured)" if peaks else "of fallback")},
             "e2e": {"value": total_samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,

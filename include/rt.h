@@ -170,6 +170,8 @@ typedef struct rt_stats {
     int64_t paths_skipped;          /* camera paths of empty tiles that never entered the queues (their records move no bytes) */
     float ms_tail;                  /* tail stage (one launch finishes the paths alive at the tail bounce), TIME_STAGES */
     float reserved;
+    int64_t launches_extend;        /* extend-stage launches among `launches` (mean rays per extend launch for the roofline's traffic figure) */
+    int64_t rays_extend;            /* reserved (0) */
 } rt_stats;
 
 typedef struct rt_scene_info {

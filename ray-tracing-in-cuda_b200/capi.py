@@ -76,7 +76,8 @@ class Stats(C.Structure):
                 ("n_rect_tests", C.c_int64), ("n_cyl_reject", C.c_int64), ("n_cyl_accept", C.c_int64),
                 ("n_tri_tests", C.c_int64), ("n_boxprim_tests", C.c_int64), ("n_shade", C.c_int64),
                 ("n_generate", C.c_int64), ("n_node_visits", C.c_int64),
-                ("n_generate_leaf_tests", C.c_int64), ("paths_skipped", C.c_int64), ("ms_tail", C.c_float), ("reserved", C.c_float)]
+                ("n_generate_leaf_tests", C.c_int64), ("paths_skipped", C.c_int64), ("ms_tail", C.c_float), ("reserved", C.c_float),
+                ("launches_extend", C.c_int64), ("rays_extend", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

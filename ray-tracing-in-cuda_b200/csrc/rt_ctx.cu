@@ -655,7 +655,7 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
             for (int b = 0; b < depth_needed && !no_paths; ++b) {
                 // from bounce tail_b0 on, one launch finishes every surviving path (k_tail) instead of 2 x (depth - b) queue launches
                 if (b == tail_b0 && b > 0) { timed(5, [&] { launch_tail(cfg, dsp, S.q, prm->seed, first_sample, b, buf); }); break; }
-                if (b > 0 || tile_mode != 1) timed(1, [&] { launch_extend(cfg, dsp, S.q, b, buf, count, b == 0 && tile_mode == 2); });
+                if (b > 0 || tile_mode != 1) { ++ctx->stats.launches_extend; timed(1, [&] { launch_extend(cfg, dsp, S.q, b, buf, count, b == 0 && tile_mode == 2); }); }
                 timed(2, [&] { launch_shade(cfg, dsp, S.q, prm->seed, first_sample, b, buf, b == ds.max_depth - 1, count, sort, nee); });
                 if (nee) timed(4, [&] { launch_shadow(cfg, dsp, S.q, b); });
                 buf ^= 1;
@@ -682,6 +682,15 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     CU(cudaEventRecord(ctx->ev1, s));
     if (trace) {
         const auto t_done = std::chrono::steady_clock::now();
+        {       // queue lengths of the last pass of stream 0 (synchronises: a development aid for reading ncu launch lists)
+            std::vector<int> qc((size_t)ds.max_depth + 1);
+            cudaDeviceSynchronize();
+            if (ctx->qs[0].qcount.p && cudaMemcpy(qc.data(), ctx->qs[0].qcount.p, qc.size() * sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess) {
+                fprintf(stderr, "[rt_render] queue lengths by bounce:");
+                for (size_t b = 0; b < qc.size() && b < 14; ++b) fprintf(stderr, " %d", qc[b]);
+                fprintf(stderr, "\n");
+            }
+        }
         fprintf(stderr, "[rt_render] prep %.2f ms, enqueue %.2f ms, %lld passes of %d spp on %d stream(s)\n",
                 std::chrono::duration<double, std::milli>(t_prep - t_enter).count(), std::chrono::duration<double, std::milli>(t_done - t_prep).count(),
                 passes, s_pass, n_sets);

@@ -141,7 +141,14 @@ __device__ __forceinline__ void traverse(const DScene &sc, const char *__restric
             if (leaf_visit<COUNT, ONLY>(sc, ~cur, o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
             RT_POP()
         }
+        // "while-while": after the leaf step every lane descends to its NEXT leaf (or to the end of its walk) before any lane tests a
+        // leaf again, so the leaf step above runs with more lanes (RT_TRAV_DONE is negative: it ends this loop too).  Against the
+        // one-step "if-if" form (RT_IF_IF tuning builds): RTIOW extend 21.7 -> 20.7 ms per 128 spp, blue2 16.8 -> 16.0, sample_scene equal.
+#ifdef RT_IF_IF
         if (cur >= 0) {
+#else
+        while (cur >= 0) {
+#endif
             float tnl, tfl, tnr, tfr;
             int2 nd;
             if (SIGNED) {
@@ -249,7 +256,8 @@ __device__ __forceinline__ void traverse4(const DScene &sc, const BvhNode4 *__re
             if (leaf_visit<COUNT, ONLY>(sc, ~cur, o, d, a, inv_a, tmin, best_t, best_code, cnt) && ANY_HIT) return;
             RT_POP4()
         }
-        if (cur >= 0) {
+        if (cur >= 0) {     // one step per iteration: the while-while form of traverse() measured 37 % SLOWER here (latency-bound node fetches:
+                            // lanes waiting at a leaf keep no loads in flight)
             const float4 *__restrict__ nd = reinterpret_cast<const float4 *>(nodes + cur);
             const float4 pnx = nd[nx], pny = nd[ny], pnz = nd[nz], pfx = nd[fx], pfy = nd[fy], pfz = nd[fz];
             const int4 lk = *reinterpret_cast<const int4 *>(nd + 6);
