@@ -351,13 +351,16 @@ static int upload_to_device(rt_ctx *ctx) {
     return RT_OK;
 }
 
-extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *sc) {
+static int rt_scene_upload_impl(rt_ctx *ctx, const rt_scene_desc *sc) {
     if (!ctx) return RT_ERR_INVALID;
     if (!sc) return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload: scene is NULL");
     HostScene hs;
     hs.d = *sc;
     if (sc->n_objects < 0 || sc->n_xforms < 0 || sc->n_materials < 0 || sc->n_textures < 0 || sc->n_images < 0)
         return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload: negative table size");
+    if ((sc->n_objects > 0 && !sc->objects) || (sc->n_xforms > 0 && !sc->xforms) || (sc->n_materials > 0 && !sc->materials) ||
+        (sc->n_textures > 0 && !sc->textures) || (sc->n_images > 0 && !sc->images))
+        return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload: a table pointer is NULL although its count is > 0");
     hs.objects.assign(sc->objects, sc->objects + sc->n_objects);
     hs.xforms.assign(sc->xforms, sc->xforms + sc->n_xforms);
     hs.materials.assign(sc->materials, sc->materials + sc->n_materials);
@@ -375,8 +378,11 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *sc) {
     ctx->hs.fix_pointers();
     return upload_to_device(ctx);
 }
+extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *sc) {
+    return rt_guard(ctx, "rt_scene_upload", [&] { return rt_scene_upload_impl(ctx, sc); });
+}
 
-extern "C" int rt_scene_upload_json_text(rt_ctx *ctx, const char *text, const char *base_dir) {
+static int rt_scene_upload_json_text_impl(rt_ctx *ctx, const char *text, const char *base_dir) {
     if (!ctx) return RT_ERR_INVALID;
     if (!text) return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload_json_text: text is NULL");
     HostScene hs; std::string err;
@@ -389,8 +395,11 @@ extern "C" int rt_scene_upload_json_text(rt_ctx *ctx, const char *text, const ch
     ctx->hs.fix_pointers();
     return upload_to_device(ctx);
 }
+extern "C" int rt_scene_upload_json_text(rt_ctx *ctx, const char *text, const char *base_dir) {
+    return rt_guard(ctx, "rt_scene_upload_json_text", [&] { return rt_scene_upload_json_text_impl(ctx, text, base_dir); });
+}
 
-extern "C" int rt_scene_upload_json(rt_ctx *ctx, const char *path) {
+static int rt_scene_upload_json_impl(rt_ctx *ctx, const char *path) {
     if (!ctx) return RT_ERR_INVALID;
     if (!path) return rt_fail(ctx, RT_ERR_INVALID, "rt_scene_upload_json: path is NULL");
     std::ifstream f(path, std::ios::binary);
@@ -400,6 +409,9 @@ extern "C" int rt_scene_upload_json(rt_ctx *ctx, const char *path) {
     size_t k = p.find_last_of('/');
     if (k != std::string::npos) dir = p.substr(0, k);
     return rt_scene_upload_json_text(ctx, ss.str().c_str(), dir.c_str());
+}
+extern "C" int rt_scene_upload_json(rt_ctx *ctx, const char *path) {
+    return rt_guard(ctx, "rt_scene_upload_json", [&] { return rt_scene_upload_json_impl(ctx, path); });
 }
 
 extern "C" int rt_scene_info_get(rt_ctx *ctx, rt_scene_info *out) {
@@ -518,7 +530,7 @@ extern "C" void rt_sample_chunk(int total_spp, int k, int *begin, int *end) {
     if (end) *end = (int)e;
 }
 
-extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
+static int rt_render_impl(rt_ctx *ctx, const rt_render_params *prm) {
     if (!ctx) return RT_ERR_INVALID;
     if (!prm) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: params is NULL");
     if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "rt_render: no scene uploaded");
@@ -713,8 +725,11 @@ extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
     }
     return RT_OK;
 }
+extern "C" int rt_render(rt_ctx *ctx, const rt_render_params *prm) {
+    return rt_guard(ctx, "rt_render", [&] { return rt_render_impl(ctx, prm); });
+}
 
-extern "C" int rt_render_aov(rt_ctx *ctx, float *out, size_t n_floats) {
+static int rt_render_aov_impl(rt_ctx *ctx, float *out, size_t n_floats) {
     if (!ctx) return RT_ERR_INVALID;
     if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "rt_render_aov: no scene uploaded");
     CU(cudaSetDevice(ctx->device));
@@ -726,6 +741,9 @@ extern "C" int rt_render_aov(rt_ctx *ctx, float *out, size_t n_floats) {
     CU(cudaMemcpyAsync(out, ctx->d_aov.p, sizeof(float) * need, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return RT_OK;
+}
+extern "C" int rt_render_aov(rt_ctx *ctx, float *out, size_t n_floats) {
+    return rt_guard(ctx, "rt_render_aov", [&] { return rt_render_aov_impl(ctx, out, n_floats); });
 }
 
 extern "C" int rt_accum_device_ptr(rt_ctx *ctx, void **dev_ptr, size_t *n_floats) {
@@ -771,7 +789,7 @@ extern "C" int rt_stats_reset(rt_ctx *ctx) {
     return RT_OK;
 }
 
-extern "C" int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigned char *rgb8, int total_spp, int gamma, rt_stats *stats) {
+static int rt_download_impl(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigned char *rgb8, int total_spp, int gamma, rt_stats *stats) {
     if (!ctx) return RT_ERR_INVALID;
     if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "rt_download: no scene uploaded");
     CU(cudaSetDevice(ctx->device));
@@ -806,8 +824,11 @@ extern "C" int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigne
     }
     return RT_OK;
 }
+extern "C" int rt_download(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsigned char *rgb8, int total_spp, int gamma, rt_stats *stats) {
+    return rt_guard(ctx, "rt_download", [&] { return rt_download_impl(ctx, rgb_sum, n_floats, rgb8, total_spp, gamma, stats); });
+}
 
-extern "C" int rt_bvh_download(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left,
+static int rt_bvh_download_impl(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left,
                                int32_t *right, int32_t *parent, float *node_aabb, float *leaf_aabb, float *scene_aabb) {
     if (!ctx) return RT_ERR_INVALID;
     if (!ctx->have_scene) return rt_fail(ctx, RT_ERR_NO_SCENE, "rt_bvh_download: no scene uploaded");
@@ -832,6 +853,10 @@ extern "C" int rt_bvh_download(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_s
         if (node_aabb) CU(cudaMemcpy(node_aabb, ctx->d_node_aabb.p, sizeof(float) * 6 * (nt - 1), cudaMemcpyDeviceToHost));
     } else if (parent) parent[0] = -1;
     return RT_OK;
+}
+extern "C" int rt_bvh_download(rt_ctx *ctx, int32_t *n_prims, uint64_t *morton_sorted, int32_t *prim_sorted, int32_t *left,
+                               int32_t *right, int32_t *parent, float *node_aabb, float *leaf_aabb, float *scene_aabb) {
+    return rt_guard(ctx, "rt_bvh_download", [&] { return rt_bvh_download_impl(ctx, n_prims, morton_sorted, prim_sorted, left, right, parent, node_aabb, leaf_aabb, scene_aabb); });
 }
 
 extern "C" int rt_bvh_info(rt_ctx *ctx, int32_t *n_tree, int32_t *n_giants, int32_t *depth) {

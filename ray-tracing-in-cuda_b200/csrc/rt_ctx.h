@@ -1,5 +1,7 @@
 // rt_ctx.h — the host-side context behind the opaque rt_ctx of include/rt.h.
 #pragma once
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <vector>
 #include "rt_kernels.h"
@@ -92,5 +94,13 @@ struct rt_ctx {
 };
 
 int rt_fail(rt_ctx *ctx, int code, const std::string &msg);
+// No C++ exception may cross the extern "C" boundary (through ctypes that would be std::terminate in the host process): entry points
+// that allocate host memory run their body through this guard, which maps an exception to an RT_ERR_* code + message.
+template <class F> int rt_guard(rt_ctx *ctx, const char *what, F &&f) {
+    try { return f(); }
+    catch (const std::bad_alloc &) { return rt_fail(ctx, RT_ERR_INVALID, std::string(what) + ": out of host memory (size fields too large?)"); }
+    catch (const std::exception &e) { return rt_fail(ctx, RT_ERR_INVALID, std::string(what) + ": " + e.what()); }
+    catch (...) { return rt_fail(ctx, RT_ERR_INVALID, std::string(what) + ": unknown C++ exception"); }
+}
 int rt_json_to_scene(const char *text, const char *base_dir, HostScene &out, std::string &err);
 int rt_png_decode_file(const char *path, std::vector<uint8_t> &rgb, int &w, int &h, std::string &err);

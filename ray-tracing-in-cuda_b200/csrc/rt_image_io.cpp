@@ -8,11 +8,11 @@
 #include <cstring>
 #include <string>
 #include <vector>
-#include "../../include/rt.h"
+#include "rt_ctx.h"
 
 int rt_png_decode_file(const char *path, std::vector<uint8_t> &rgb, int &w, int &h, std::string &err);
 
-extern "C" int rt_write_ppm(const char *path, const unsigned char *rgb8, int width, int height) {
+static int rt_write_ppm_impl(const char *path, const unsigned char *rgb8, int width, int height) {
     if (!path || !rgb8 || width < 1 || height < 1) return RT_ERR_INVALID;
     FILE *f = fopen(path, "w");
     if (!f) return RT_ERR_IO;
@@ -31,6 +31,9 @@ extern "C" int rt_write_ppm(const char *path, const unsigned char *rgb8, int wid
     }
     return fclose(f) == 0 ? RT_OK : RT_ERR_IO;
 }
+extern "C" int rt_write_ppm(const char *path, const unsigned char *rgb8, int width, int height) {
+    return rt_guard(nullptr, "rt_write_ppm", [&] { return rt_write_ppm_impl(path, rgb8, width, height); });
+}
 
 static void put32(std::vector<uint8_t> &v, uint32_t x) { v.push_back(x >> 24); v.push_back(x >> 16); v.push_back(x >> 8); v.push_back(x); }
 static void chunk(std::vector<uint8_t> &out, const char *tag, const uint8_t *data, size_t n) {
@@ -41,7 +44,7 @@ static void chunk(std::vector<uint8_t> &out, const char *tag, const uint8_t *dat
     put32(out, (uint32_t)crc32(0, out.data() + start, (uInt)(n + 4)));
 }
 
-extern "C" int rt_write_png(const char *path, const unsigned char *rgb8, int width, int height) {
+static int rt_write_png_impl(const char *path, const unsigned char *rgb8, int width, int height) {
     if (!path || !rgb8 || width < 1 || height < 1) return RT_ERR_INVALID;
     const size_t stride = (size_t)width * 3;
     std::vector<uint8_t> raw((stride + 1) * height);
@@ -60,6 +63,9 @@ extern "C" int rt_write_png(const char *path, const unsigned char *rgb8, int wid
     if (!f) return RT_ERR_IO;
     bool ok = fwrite(out.data(), 1, out.size(), f) == out.size();
     return (fclose(f) == 0 && ok) ? RT_OK : RT_ERR_IO;
+}
+extern "C" int rt_write_png(const char *path, const unsigned char *rgb8, int width, int height) {
+    return rt_guard(nullptr, "rt_write_png", [&] { return rt_write_png_impl(path, rgb8, width, height); });
 }
 
 static inline int paeth(int a, int b, int c) {
@@ -98,6 +104,9 @@ int rt_png_decode_file(const char *path, std::vector<uint8_t> &rgb, int &w, int 
     int ch = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
     if (!ch) { err = "unsupported PNG colour type"; return RT_ERR_PARSE; }
     const size_t stride = (size_t)w * ch;
+    // the declared size must be plausible for the compressed data before anything is allocated for it (deflate expands at most
+    // ~1032 : 1): a header that claims 2^31 x 2^31 pixels over a few bytes of IDAT is rejected here, not by bad_alloc
+    if ((w > (1 << 20)) || (h > (1 << 20)) || (stride + 1) * (size_t)h > (idat.size() + 64) * 1100) { err = "PNG header declares more pixels than its data can hold"; return RT_ERR_PARSE; }
     std::vector<uint8_t> raw((stride + 1) * h);
     uLongf rlen = (uLongf)raw.size();
     if (uncompress(raw.data(), &rlen, idat.data(), (uLong)idat.size()) != Z_OK || rlen != raw.size()) { err = "PNG inflate failed"; return RT_ERR_PARSE; }
@@ -131,7 +140,7 @@ int rt_png_decode_file(const char *path, std::vector<uint8_t> &rgb, int &w, int 
     return RT_OK;
 }
 
-extern "C" int rt_read_png(const char *path, unsigned char **rgb8, int *width, int *height) {
+static int rt_read_png_impl(const char *path, unsigned char **rgb8, int *width, int *height) {
     if (!path || !rgb8 || !width || !height) return RT_ERR_INVALID;
     std::vector<uint8_t> rgb; int w, h; std::string err;
     int rc = rt_png_decode_file(path, rgb, w, h, err);
@@ -141,4 +150,7 @@ extern "C" int rt_read_png(const char *path, unsigned char **rgb8, int *width, i
     memcpy(out, rgb.data(), rgb.size());
     *rgb8 = out; *width = w; *height = h;
     return RT_OK;
+}
+extern "C" int rt_read_png(const char *path, unsigned char **rgb8, int *width, int *height) {
+    return rt_guard(nullptr, "rt_read_png", [&] { return rt_read_png_impl(path, rgb8, width, height); });
 }

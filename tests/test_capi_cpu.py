@@ -77,6 +77,20 @@ def test_png_and_ppm_writers(lib, tmp_path):
         renderer.read_png(str(tmp_path / "missing.png"))
 
 
+def test_crafted_png_is_an_error_not_a_crash(lib, tmp_path):
+    """No C++ exception crosses the C ABI: a PNG whose header declares 2^31 x 2^31 pixels over four bytes of data is rejected."""
+    import struct
+    import zlib
+
+    def chunk(t, d):
+        return struct.pack(">I", len(d)) + t + d + struct.pack(">I", zlib.crc32(t + d) & 0xffffffff)
+    png = (b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", 0x7fffffff, 0x7fffffff, 8, 2, 0, 0, 0)) +
+           chunk(b"IDAT", zlib.compress(b"\0\0\0\0")) + chunk(b"IEND", b""))
+    (tmp_path / "huge.png").write_bytes(png)
+    with pytest.raises(RtError):
+        renderer.read_png(str(tmp_path / "huge.png"))
+
+
 def test_animation_rules_follow_the_reference_scripts():
     import json
     basic = json.load(open(os.path.join(ROOT, "tests", "golden", "basic_scene.json")))
