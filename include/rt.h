@@ -129,6 +129,8 @@ enum { RT_RENDER_KEEP_ACCUM = 1,     /* add to the accumulation buffer instead o
        RT_RENDER_NO_TILE_LISTS = 256,
        RT_RENDER_NO_TAIL = 1024,     /* keep the queue schedule to the last bounce (default: from bounce 8 on one launch finishes every
                                         surviving path — same image either way) */
+       RT_RENDER_NEE_MIS = 2048,     /* RT_RENDER_NEE with multiple importance sampling: light samples and the emission a scattered ray finds on
+                                        a sampled light are combined with the balance heuristic (implies RT_RENDER_NEE) */
        RT_RENDER_KEEP_CHUNKS = 512 };  /* leave this call's chunk sums in their buffers instead of folding them into the accumulation
                                         buffer: the root of a multi-GPU render gathers and folds them (rt_gather_image) */ /* traverse the tree for bounce 0 too (default: the generate stage resolves bounce-0 hits from the
                                         per-tile candidate lists of the camera beams; same image either way) */
@@ -195,6 +197,15 @@ int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *scene);
 int rt_scene_upload_json(rt_ctx *ctx, const char *path);
 /* As above from an in-memory JSON text; base_dir resolves relative texture/mesh paths (may be NULL). */
 int rt_scene_upload_json_text(rt_ctx *ctx, const char *json_text, const char *base_dir);
+/* Animation without scene text (replaces "write one JSON per frame", gpu-version/blue.py:16-22, blue2.py:16-22): replaces objects
+ * [first_object, first_object + n_objects) and transforms [first_xform, first_xform + n_xforms) of the uploaded scene (either run may
+ * be empty) and rebuilds the device tables and the LBVH (a full device rebuild: it is cheaper than a refit pass would save).
+ * Object types / counts may change within the run; the tables keep their sizes.  On an invalid update the scene stays as it was. */
+int rt_scene_update(rt_ctx *ctx, const rt_object_desc *objects, int first_object, int n_objects, const rt_xform_desc *xforms,
+                    int first_xform, int n_xforms);
+/* translate(t) * rotate(axis, angle_deg) and its inverse exactly as the JSON reader builds them for "rotate" / "translate"
+ * (vec3.cuh:382-416, parser.hpp:423-440): matrices made here are bit-identical to those of rt_scene_upload_json. */
+void rt_make_xform(const float axis[3], double angle_deg, int has_rotate, const float translate[3], int has_translate, rt_xform_desc *out);
 int rt_scene_info_get(rt_ctx *ctx, rt_scene_info *out);
 /* Overrides applied to the uploaded scene before rendering (<= 0 leaves a field unchanged). */
 int rt_scene_override(rt_ctx *ctx, int width, int height, int samples_per_pixel, int max_depth);

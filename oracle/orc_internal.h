@@ -96,7 +96,8 @@ int orc_is_nee_light(const rt_scene_desc *sc, int i);
 float orc_light_area(const rt_scene_desc *sc, int i);
 int orc_light_list(const rt_scene_desc *sc, int *lights);
 int orc_nee_sample(const rt_scene_desc *sc, const int *lights, int n_lights, v3 x, v3 n, uint32_t seed, uint32_t pixel,
-                   uint32_t sample, uint32_t bounce, v3 *f, int64_t *shadow_rays);
+                   uint32_t sample, uint32_t bounce, int mis, v3 *f, int64_t *shadow_rays);
+float orc_mis_hit_weight(const rt_scene_desc *sc, int obj, int n_lights, v3 d, float t, v3 ny);
 
 v3 orc_xform_point(const float m[12], v3 p);
 v3 orc_xform_vec(const float m[12], v3 p);

@@ -110,8 +110,11 @@ static int occluded(const rt_scene_desc *sc, v3 o, v3 d, float tmin, float tmax)
 
 /* Returns 1 and the radiance factor f (to be multiplied by thr * albedo) when the sampled light is visible from x.
  * *shadow_rays is incremented when an occlusion ray was traced. */
+/* mis: the light sample is weighted with the balance heuristic against the cosine-weighted scatter direction that could have found
+ * the same point, w = p_l / (p_l + p_b) in solid-angle measure: p_l = |w|^2 / (cos_y * area * n_lights), p_b = cos_x / pi; the
+ * emission a scattered ray finds on a sampled light then carries the complementary weight (orc_mis_hit_weight). */
 int orc_nee_sample(const rt_scene_desc *sc, const int *lights, int n_lights, v3 x, v3 n, uint32_t seed, uint32_t pixel,
-                   uint32_t sample, uint32_t bounce, v3 *f, int64_t *shadow_rays) {
+                   uint32_t sample, uint32_t bounce, int mis, v3 *f, int64_t *shadow_rays) {
     orc_rng rng; orc_rng_init(&rng, seed, pixel, sample, (bounce + 1u) | 0x10000u, sc->sampling);
     float u0 = orc_rng_next(&rng), u1 = orc_rng_next(&rng), u2 = orc_rng_next(&rng);
     int k = (int)(u0 * (float)n_lights);
@@ -128,7 +131,21 @@ int orc_nee_sample(const rt_scene_desc *sc, const int *lights, int n_lights, v3 
     ++*shadow_rays;
     if (occluded(sc, x, w, 0.001f, 0.999f)) return 0;
     float g = ((cs * cl) / d2) * (orc_light_area(sc, obj) * ((float)n_lights * ORC_INV_PI_F));
+    if (mis) {
+        float pl = d2 / (cl * (orc_light_area(sc, obj) * (float)n_lights)), pb = cs * ORC_INV_PI_F;
+        g = g * (pl / (pl + pb));
+    }
     v3 Le = orc_emitted(sc, sc->objects[obj].material, tu, tv, y);
     *f = vscale(g, Le);
     return 1;
+}
+
+/* Balance-heuristic weight of the emission found by a ray scattered at a lambertian vertex (direction d = n + unit vector, NOT
+ * normalised: cos_x = |d| / 2, so p_b = |d| / (2 pi)) that hits sampled light `obj` at parameter t with unit normal ny. */
+float orc_mis_hit_weight(const rt_scene_desc *sc, int obj, int n_lights, v3 d, float t, v3 ny) {
+    float dd = dot3(d, d), len = sqrtf(dd);
+    float dist2 = (t * t) * dd;
+    float cy = fabsf(dot3(ny, d)) / len;
+    float pl = dist2 / (cy * (orc_light_area(sc, obj) * (float)n_lights)), pb = (len * 0.5f) * ORC_INV_PI_F;
+    return pb / (pb + pl);
 }

@@ -158,7 +158,7 @@ v3 orc_background(const rt_scene_desc *sc, v3 d) {
 
 /* ray_color, main.cu:17-70 / main.cpp:13-43.  Emission is non-zero only on diffuse_light, which never
  * scatters, so the radiance of a path is throughput * (E | background | 0) at its last vertex. */
-typedef struct { int on, n_lights; const int *lights; const unsigned char *is_light; } nee_t;
+typedef struct { int on, mis, n_lights; const int *lights; const unsigned char *is_light; } nee_t;
 
 static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t pixel, uint32_t sample, int64_t *nrays,
                     const nee_t *nee, int64_t *nshadow, const orc_bvh *bvh, orc_trav_counters *cnt) {
@@ -170,7 +170,8 @@ static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t
         const int hit = bvh ? orc_bvh_hit(bvh, o, d, 0.001f, FLT_MAX, 0, &rec, cnt) : orc_hit_world(sc, o, d, 0.001f, FLT_MAX, &rec);
         if (!hit) { L = vadd(L, vmul(thr, orc_background(sc, d))); break; }
         v3 E = orc_emitted(sc, rec.mat, rec.u, rec.v, rec.p);
-        if (prev_nee && nee->is_light[rec.prim]) E = V(0, 0, 0);
+        if (prev_nee && nee->is_light[rec.prim])       /* a sampled light found by the scattered ray: dropped, or MIS-weighted */
+            E = nee->mis ? vscale(orc_mis_hit_weight(sc, rec.prim, nee->n_lights, d, rec.t, rec.n), E) : V(0, 0, 0);
         orc_rng rng; orc_rng_init(&rng, seed, pixel, sample, (uint32_t)bounce + 1u, sc->sampling);
         v3 att, so, sd;
         int ok = orc_scatter(sc, rec.mat, d, &rec, &rng, &att, &so, &sd);
@@ -178,7 +179,7 @@ static v3 ray_color(const rt_scene_desc *sc, v3 o, v3 d, uint32_t seed, uint32_t
         prev_nee = 0;
         if (nee->on && nee->n_lights > 0 && sc->materials[rec.mat].type == RT_MAT_LAMBERTIAN) {
             v3 f;
-            if (orc_nee_sample(sc, nee->lights, nee->n_lights, rec.p, rec.n, seed, pixel, sample, (uint32_t)bounce, &f, nshadow))
+            if (orc_nee_sample(sc, nee->lights, nee->n_lights, rec.p, rec.n, seed, pixel, sample, (uint32_t)bounce, nee->mis, &f, nshadow))
                 L = vadd(L, vmul(vmul(thr, att), f));
             prev_nee = 1;
         }
@@ -250,14 +251,14 @@ static int g_stride = 1;      /* set by orc_render_bvh_strided around its render
 static int render_impl(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
                        int flags, int64_t *n_rays, int64_t *n_shadow_rays, int use_bvh, int64_t *counters, int total_spp) {
     if (!sc || !rgb_sum || sc->width < 1 || sc->height < 1) return RT_ERR_INVALID;
-    if ((flags & RT_RENDER_NEE) && (sc->sampling & 1) != RT_SAMPLING_REFERENCE_CPU) return RT_ERR_INVALID;
+    if ((flags & (RT_RENDER_NEE | RT_RENDER_NEE_MIS)) && (sc->sampling & 1) != RT_SAMPLING_REFERENCE_CPU) return RT_ERR_INVALID;
     job_t j; memset(&j, 0, sizeof j);
     j.sc = sc; j.seed = seed; j.s0 = spp_begin; j.sn = spp_count > 0 ? spp_count : sc->samples_per_pixel; j.out = rgb_sum;
     j.total = total_spp > 0 ? total_spp : (sc->samples_per_pixel > j.s0 + j.sn ? sc->samples_per_pixel : j.s0 + j.sn);
     orc_camera_setup(&sc->camera, &j.cam);
     int *lights = (int *)malloc(sizeof(int) * (size_t)(sc->n_objects > 0 ? sc->n_objects : 1));
     unsigned char *is_light = (unsigned char *)calloc((size_t)(sc->n_objects > 0 ? sc->n_objects : 1), 1);
-    j.nee.on = (flags & RT_RENDER_NEE) != 0;
+    j.nee.on = (flags & (RT_RENDER_NEE | RT_RENDER_NEE_MIS)) != 0; j.nee.mis = (flags & RT_RENDER_NEE_MIS) != 0;
     if (j.nee.on) {
         j.nee.n_lights = orc_light_list(sc, lights);
         for (int k = 0; k < j.nee.n_lights; ++k) is_light[lights[k]] = 1;

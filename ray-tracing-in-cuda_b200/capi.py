@@ -20,6 +20,7 @@ RT_RENDER_SERIAL = 64
 RT_RENDER_NO_TILE_LISTS = 256
 RT_RENDER_KEEP_CHUNKS = 512
 RT_RENDER_NO_TAIL = 1024
+RT_RENDER_NEE_MIS = 2048
 RT_SAMPLE_CHUNKS = 8
 RT_NOALLOC_MAX_BYTES = 8 << 20      # static scratch of rt_tonemap_noalloc
 
@@ -93,7 +94,7 @@ class SceneInfo(C.Structure):
 RT_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_scene_upload", "rt_scene_upload_json",
               "rt_scene_upload_json_text", "rt_scene_info_get", "rt_scene_override", "rt_render", "rt_render_aov",
               "rt_accum_device_ptr", "rt_accum_sum_ordered", "rt_download", "rt_synchronize", "rt_stats_reset",
-              "rt_bvh_download", "rt_bvh_info", "rt_sample_chunk", "rt_tonemap_noalloc", "rt_rank_chunks", "rt_comm_unique_id", "rt_comm_init", "rt_comm_destroy",
+              "rt_bvh_download", "rt_bvh_info", "rt_sample_chunk", "rt_tonemap_noalloc", "rt_scene_update", "rt_make_xform", "rt_rank_chunks", "rt_comm_unique_id", "rt_comm_init", "rt_comm_destroy",
               "rt_render_shard", "rt_gather_image", "rt_group_create", "rt_group_destroy", "rt_group_last_error", "rt_group_size", "rt_group_ctx",
               "rt_group_scene_upload", "rt_group_scene_upload_json", "rt_group_scene_upload_json_text", "rt_group_scene_override",
               "rt_group_render", "rt_group_download", "rt_write_ppm", "rt_write_png", "rt_read_png", "rt_free", "rt_probe_fp32_peak", "rt_host_alloc",
@@ -143,6 +144,8 @@ def load_library(path=None):
     lib.rt_group_scene_override.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
     lib.rt_group_render.argtypes = [vp, P(RenderParams)]
     lib.rt_group_download.argtypes = [vp, P(C.c_float), C.c_size_t, P(C.c_ubyte), C.c_int, C.c_int, P(Stats)]
+    lib.rt_scene_update.argtypes = [vp, P(ObjectDesc), C.c_int, C.c_int, P(XformDesc), C.c_int, C.c_int]
+    lib.rt_make_xform.argtypes = [P(C.c_float), C.c_double, C.c_int, P(C.c_float), C.c_int, P(XformDesc)]; lib.rt_make_xform.restype = None
     lib.rt_tonemap_noalloc.argtypes = [C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, P(C.c_ubyte)]
     lib.rt_sample_chunk.argtypes = [C.c_int, C.c_int, P(C.c_int), P(C.c_int)]; lib.rt_sample_chunk.restype = None
     lib.rt_render_aov.argtypes = [vp, P(C.c_float), C.c_size_t]

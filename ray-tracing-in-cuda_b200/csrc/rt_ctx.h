@@ -102,5 +102,6 @@ template <class F> int rt_guard(rt_ctx *ctx, const char *what, F &&f) {
     catch (const std::exception &e) { return rt_fail(ctx, RT_ERR_INVALID, std::string(what) + ": " + e.what()); }
     catch (...) { return rt_fail(ctx, RT_ERR_INVALID, std::string(what) + ": unknown C++ exception"); }
 }
+void rt_build_xform(const float axis[3], double angle_deg, bool has_rotate, const float t3[3], bool has_translate, rt_xform_desc *out);
 int rt_json_to_scene(const char *text, const char *base_dir, HostScene &out, std::string &err);
 int rt_png_decode_file(const char *path, std::vector<uint8_t> &rgb, int &w, int &h, std::string &err);

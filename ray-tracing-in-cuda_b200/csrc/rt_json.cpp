@@ -114,6 +114,42 @@ struct Parser {
     }
 };
 
+}  // namespace
+
+// translate(t) * rotate(axis, angle) and its inverse: vec3.cuh:382-416 + object.cuh:225-231 + parser.hpp:423-440.  One function for the JSON
+// reader and for rt_make_xform (callers that update transforms between frames get bit-identical matrices).
+static void mul4(const float a[16], const float b[16], float r[16]) {
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j)
+        r[i * 4 + j] = a[i * 4 + 0] * b[0 * 4 + j] + a[i * 4 + 1] * b[1 * 4 + j] + a[i * 4 + 2] * b[2 * 4 + j] + a[i * 4 + 3] * b[3 * 4 + j];
+}
+void rt_build_xform(const float axis[3], double angle_deg, bool has_rotate, const float t3[3], bool has_translate, rt_xform_desc *out) {
+    float m[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}, mi[16];
+    memcpy(mi, m, sizeof m);
+    if (has_rotate) {
+        float theta = (float)(angle_deg / 180.0 * M_PI);
+        float len = sqrtf(axis[0] * axis[0] + axis[1] * axis[1] + axis[2] * axis[2]);
+        float ax = axis[0] / len, ay = axis[1] / len, az = axis[2] / len;
+        float s = sinf(theta), c = cosf(theta);
+        float r[16] = {ax * ax + (1 - ax * ax) * c, ax * ay * (1 - c) - az * s, ax * az * (1 - c) + ay * s, 0,
+                       ax * ay * (1 - c) + az * s, ay * ay + (1 - ay * ay) * c, ay * az * (1 - c) - ax * s, 0,
+                       ax * az * (1 - c) - ay * s, ay * az * (1 - c) + ax * s, az * az + (1 - az * az) * c, 0,
+                       0, 0, 0, 1};
+        float rt[16], nm[16], nmi[16];
+        for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) rt[i * 4 + j] = r[j * 4 + i];
+        mul4(r, m, nm); mul4(mi, rt, nmi);
+        memcpy(m, nm, sizeof m); memcpy(mi, nmi, sizeof mi);
+    }
+    if (has_translate) {
+        float t[16] = {1, 0, 0, t3[0], 0, 1, 0, t3[1], 0, 0, 1, t3[2], 0, 0, 0, 1};
+        float ti[16] = {1, 0, 0, -t3[0], 0, 1, 0, -t3[1], 0, 0, 1, -t3[2], 0, 0, 0, 1};
+        float nm[16], nmi[16];
+        mul4(t, m, nm); mul4(mi, ti, nmi);
+        memcpy(m, nm, sizeof m); memcpy(mi, nmi, sizeof mi);
+    }
+    memcpy(out->m, m, sizeof out->m); memcpy(out->m_inv, mi, sizeof out->m_inv);
+}
+
+namespace {
 struct Loader {
     HostScene &hs; std::string base; std::string err;
     bool fail(const std::string &m) { if (err.empty()) err = m; return false; }
@@ -128,43 +164,14 @@ struct Loader {
         for (int i = 0; i < n; ++i) { if (v->arr[i]->kind != JValue::Num) return fail(where + ": \"" + key + "\" must hold numbers"); out[i] = (float)v->arr[i]->num; }
         return true;
     }
-    // translate(t) * rotate(axis, angle): vec3.cuh:382-416 + object.cuh:225-231 + parser.hpp:423-440
-    static void mul4(const float a[16], const float b[16], float r[16]) {
-        for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j)
-            r[i * 4 + j] = a[i * 4 + 0] * b[0 * 4 + j] + a[i * 4 + 1] * b[1 * 4 + j] + a[i * 4 + 2] * b[2 * 4 + j] + a[i * 4 + 3] * b[3 * 4 + j];
-    }
     bool xform(const JValue *o, const std::string &where, int &index, bool always) {
         const JValue *rot = o->get("rotate"), *tr = o->get("translate");
         if (!rot && !tr && !always) { index = -1; return true; }
-        float m[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}, mi[16];
-        memcpy(mi, m, sizeof m);
-        if (rot) {
-            float axis[3]; double angle;
-            if (!vec(rot, "axis", 3, axis, where + ".rotate") || !num(rot, "angle", angle, where + ".rotate")) return false;
-            float theta = (float)(angle / 180.0 * M_PI);
-            float len = sqrtf(axis[0] * axis[0] + axis[1] * axis[1] + axis[2] * axis[2]);
-            float ax = axis[0] / len, ay = axis[1] / len, az = axis[2] / len;
-            float s = sinf(theta), c = cosf(theta);
-            float r[16] = {ax * ax + (1 - ax * ax) * c, ax * ay * (1 - c) - az * s, ax * az * (1 - c) + ay * s, 0,
-                           ax * ay * (1 - c) + az * s, ay * ay + (1 - ay * ay) * c, ay * az * (1 - c) - ax * s, 0,
-                           ax * az * (1 - c) - ay * s, ay * az * (1 - c) + ax * s, az * az + (1 - az * az) * c, 0,
-                           0, 0, 0, 1};
-            float rt[16], nm[16], nmi[16];
-            for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) rt[i * 4 + j] = r[j * 4 + i];
-            mul4(r, m, nm); mul4(mi, rt, nmi);
-            memcpy(m, nm, sizeof m); memcpy(mi, nmi, sizeof mi);
-        }
-        if (tr) {
-            float t3[3];
-            if (!vec(o, "translate", 3, t3, where)) return false;
-            float t[16] = {1, 0, 0, t3[0], 0, 1, 0, t3[1], 0, 0, 1, t3[2], 0, 0, 0, 1};
-            float ti[16] = {1, 0, 0, -t3[0], 0, 1, 0, -t3[1], 0, 0, 1, -t3[2], 0, 0, 0, 1};
-            float nm[16], nmi[16];
-            mul4(t, m, nm); mul4(mi, ti, nmi);
-            memcpy(m, nm, sizeof m); memcpy(mi, nmi, sizeof mi);
-        }
+        float axis[3] = {0, 0, 1}, t3[3] = {0, 0, 0}; double angle = 0.0;
+        if (rot && (!vec(rot, "axis", 3, axis, where + ".rotate") || !num(rot, "angle", angle, where + ".rotate"))) return false;
+        if (tr && !vec(o, "translate", 3, t3, where)) return false;
         rt_xform_desc x;
-        memcpy(x.m, m, sizeof x.m); memcpy(x.m_inv, mi, sizeof x.m_inv);
+        rt_build_xform(axis, angle, rot != nullptr, t3, tr != nullptr, &x);
         index = (int)hs.xforms.size();
         hs.xforms.push_back(x);
         return true;

@@ -484,8 +484,9 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                 HitRec rec;
                 hit_record(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
-                    if (!(prev_nee && sc.obj_light[__ldg(&sc.prim_obj[slot])] >= 0))
-                        rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
+                    const int lk = prev_nee ? sc.obj_light[__ldg(&sc.prim_obj[slot])] : -1;
+                    if (lk < 0) rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
+                    else if (sc.nee_mis) rad = thr * (mis_hit_weight(sc, lk, d, __int_as_float(h.x), rec.n) * material_color(sc, m, rec.u, rec.v, rec.p));
                 } else {
                     Rng rng; rng.init(seed, (unsigned)__float_as_int(d4.w), (unsigned)(spp_begin + __float_as_int(t4.w)), (unsigned)bounce + 1u, sc.sampling);
                     float3 att, sd;

@@ -69,6 +69,7 @@ struct DScene {
     const DMaterial *mats;
     // next-event estimation (RT_RENDER_NEE): sampled lights in scene-file order
     int n_lights;
+    int nee_mis;                           // RT_RENDER_NEE_MIS: balance-heuristic weights on light samples and on emission found by scattered rays
     const int *light_slot;                 // light -> leaf slot
     const int *light_type;                 // light -> RT_OBJ_*
     const float *light_area;               // light -> surface area

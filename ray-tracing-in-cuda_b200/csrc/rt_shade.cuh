@@ -272,10 +272,24 @@ __device__ __forceinline__ bool light_sample(const DScene &sc, float3 x, float3 
     const float inv_d = 1.0f / sqrtf(d2);
     const float cs = dot3(n, w) * inv_d, cl = fabsf(dot3(ny, w)) * inv_d;
     if (!(cs > 0.0f) || !(cl > 0.0f)) return false;
-    const float g = ((cs * cl) / d2) * (sc.light_area[k] * ((float)sc.n_lights * RT_INV_PI_F));
+    float g = ((cs * cl) / d2) * (sc.light_area[k] * ((float)sc.n_lights * RT_INV_PI_F));
+    if (sc.nee_mis) {       // balance heuristic against the cosine-weighted scatter (oracle/orc_nee.c)
+        const float pl = d2 / (cl * (sc.light_area[k] * (float)sc.n_lights)), pb = cs * RT_INV_PI_F;
+        g = g * (pl / (pl + pb));
+    }
     const DMaterial m = sc.mats[sc.prim_mat[slot]];
     f = g * material_color(sc, m, tu, tv, y);
     return true;
+}
+
+// RT_RENDER_NEE_MIS: weight of the emission a ray scattered at a lambertian vertex (d = n + unit vector, not normalised: cos_x = |d| / 2)
+// finds on sampled light k at parameter t, unit normal ny (oracle/orc_nee.c:orc_mis_hit_weight)
+__device__ __forceinline__ float mis_hit_weight(const DScene &sc, int k, float3 d, float t, float3 ny) {
+    const float dd = dot3(d, d), len = sqrtf(dd);
+    const float dist2 = (t * t) * dd;
+    const float cy = fabsf(dot3(ny, d)) / len;
+    const float pl = dist2 / (cy * (sc.light_area[k] * (float)sc.n_lights)), pb = (len * 0.5f) * RT_INV_PI_F;
+    return pb / (pb + pl);
 }
 
 // miss colour: constant background (main.cu:61-63) or the RTIOW sky gradient (cmake-cpu-version/main.cpp:36-38)

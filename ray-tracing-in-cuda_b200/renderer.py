@@ -64,6 +64,21 @@ class Renderer:
         self._check(self.lib.rt_scene_upload(self.ctx, C.byref(d)), "rt_scene_upload")
         return self.info()
 
+    def scene_update(self, objects=None, first_object=0, xforms=None, first_xform=0):
+        """rt_scene_update: replace a run of objects (capi.ObjectDesc) and / or transforms (capi.XformDesc), rebuild on the device."""
+        objects, xforms = list(objects or []), list(xforms or [])
+        OA = (capi.ObjectDesc * max(1, len(objects)))(*objects)
+        XA = (capi.XformDesc * max(1, len(xforms)))(*xforms)
+        self._check(self.lib.rt_scene_update(self.ctx, OA, int(first_object), len(objects), XA, int(first_xform), len(xforms)), "rt_scene_update")
+
+    def make_xform(self, rotate=None, translate=None):
+        """translate * rotate exactly as the JSON reader builds it (rt_make_xform)."""
+        x = capi.XformDesc()
+        ax = (C.c_float * 3)(*(rotate["axis"] if rotate else (0, 0, 1)))
+        tr = (C.c_float * 3)(*(translate if translate is not None else (0, 0, 0)))
+        self.lib.rt_make_xform(ax, float(rotate["angle"]) if rotate else 0.0, int(rotate is not None), tr, int(translate is not None), C.byref(x))
+        return x
+
     def override(self, width=0, height=0, spp=0, max_depth=0):
         self._check(self.lib.rt_scene_override(self.ctx, width or 0, height or 0, spp or 0, max_depth or 0), "rt_scene_override")
         return self.info()
@@ -226,6 +241,21 @@ class Group:
     def upload(self, scene_desc):
         d = getattr(scene_desc, "desc", scene_desc)
         self._check(self.lib.rt_group_scene_upload(self.g, C.byref(d)), "rt_group_scene_upload")
+
+    def scene_update(self, objects=None, first_object=0, xforms=None, first_xform=0):
+        """rt_scene_update: replace a run of objects (capi.ObjectDesc) and / or transforms (capi.XformDesc), rebuild on the device."""
+        objects, xforms = list(objects or []), list(xforms or [])
+        OA = (capi.ObjectDesc * max(1, len(objects)))(*objects)
+        XA = (capi.XformDesc * max(1, len(xforms)))(*xforms)
+        self._check(self.lib.rt_scene_update(self.ctx, OA, int(first_object), len(objects), XA, int(first_xform), len(xforms)), "rt_scene_update")
+
+    def make_xform(self, rotate=None, translate=None):
+        """translate * rotate exactly as the JSON reader builds it (rt_make_xform)."""
+        x = capi.XformDesc()
+        ax = (C.c_float * 3)(*(rotate["axis"] if rotate else (0, 0, 1)))
+        tr = (C.c_float * 3)(*(translate if translate is not None else (0, 0, 0)))
+        self.lib.rt_make_xform(ax, float(rotate["angle"]) if rotate else 0.0, int(rotate is not None), tr, int(translate is not None), C.byref(x))
+        return x
 
     def override(self, width=0, height=0, spp=0, max_depth=0):
         self._check(self.lib.rt_group_scene_override(self.g, width or 0, height or 0, spp or 0, max_depth or 0), "rt_group_scene_override")

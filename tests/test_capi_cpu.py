@@ -135,3 +135,43 @@ def test_bench_clock_sampler_degrades_without_a_gpu():
     time.sleep(0.1)
     out = s.stop()
     assert "reasons" in out and "sm_mhz" in out
+
+
+def test_moving_light_rule_frame_deltas_and_frame_sequence_assembly(lib, tmp_path):
+    """README.md:14-17 of the reference (to-do: moving light, video from frames): the moving-light rule turns the emissive spheres
+    about the look-at axis and touches nothing else; scene_delta finds the table ranges rt_scene_update needs; write_apng assembles
+    frames in order into one animated PNG that an independent reader (PIL) plays back."""
+    import json
+    import math
+    from PIL import Image
+    ext = json.load(open(os.path.join(ROOT, "tests", "golden", "sample_scene_ext.json")))
+    f0, f30 = animation.moving_light_frame(ext, 0, 120), animation.moving_light_frame(ext, 30, 120)
+    mats = ext["material"]["data"]
+    moved = 0
+    for a, b, c in zip(ext["object"]["data"], f0["object"]["data"], f30["object"]["data"]):
+        if a["type"] == "sphere" and mats[a["material"]]["type"] == "diffuse_light":
+            cx, _, cz = ext["camera"]["lookat"]
+            r = lambda o: math.hypot(o["center"][0] - cx, o["center"][2] - cz)
+            assert a["center"] == pytest.approx(b["center"]) and r(c) == pytest.approx(r(a)) and c["center"][1] == a["center"][1]
+            assert c["center"] != pytest.approx(a["center"])       # a quarter turn
+            moved += 1
+        else:
+            assert a == b == c
+    assert moved == 1 and animation.scene_delta(f0, f30) is None      # triangles / meshes in the scene: full upload
+    blue2 = json.load(open(os.path.join(ROOT, "tests", "golden", "blue2.json")))
+    a, b = animation.blue2_frame(blue2, 0), animation.blue2_frame(blue2, 1)
+    assert animation.scene_delta(a, b) == (2, 6, 0, 4) and animation.scene_delta(a, a) == (0, 0, 0, 0)
+    b2 = json.loads(json.dumps(b)); b2["max_depth"] = 7
+    assert animation.scene_delta(a, b2) is None
+    paths = []
+    for k in range(4):
+        img = np.zeros((12, 16, 3), np.uint8); img[..., 0] = 60 * k; img[k, k] = 255
+        renderer.write_png(str(tmp_path / f"{k:03d}.png"), img); paths.append(str(tmp_path / f"{k:03d}.png"))
+    assert animation.write_apng(paths, str(tmp_path / "anim.png"), fps=12) == 4
+    im = Image.open(tmp_path / "anim.png")
+    assert im.n_frames == 4
+    for k in range(4):
+        im.seek(k)
+        assert np.array_equal(np.asarray(im.convert("RGB")), np.asarray(Image.open(paths[k])))
+    assert animation.write_frame_list(paths, str(tmp_path / "frames.txt"), fps=12) == 4
+    assert open(tmp_path / "frames.txt").read().count("duration 0.083333") == 4

@@ -415,25 +415,26 @@ def _nee_scene(extra_lights=True):
     return d
 
 
-@pytest.mark.parametrize("extra,depth", [(False, 0), (True, 0), (True, 3)])
-def test_nee_matches_oracle_sample_for_sample(rt, extra, depth):
+@pytest.mark.parametrize("extra,depth,mis", [(False, 0, False), (True, 0, False), (True, 3, False), (True, 0, True), (True, 3, True)])
+def test_nee_matches_oracle_sample_for_sample(rt, extra, depth, mis):
     """RT_RENDER_NEE (the shadow stage): light sampling at every lambertian vertex + any-hit occlusion rays, same
     Philox streams as oracle/orc_nee.c: radiance within 1e-5 per sample, equal path-segment and shadow-ray counts."""
     W, H, spp = 96, 54, 5
+    nee_flag = capi.RT_RENDER_NEE_MIS if mis else capi.RT_RENDER_NEE        # MIS: balance-heuristic weights (oracle/orc_nee.c)
     d = _nee_scene(extra)
     rt.upload_json_text(json.dumps(d), base_dir=G)
     rt.override(width=W, height=H, spp=spp, max_depth=depth)
     rt.stats_reset()
-    rt.render(seed=0x77, flags=capi.RT_RENDER_NEE)
+    rt.render(seed=0x77, flags=nee_flag)
     got, _, st = rt.download()
     want, nrays, nshadow = orc.render_ex(orc.load_scene(d, width=W, height=H, spp=spp, max_depth=depth or None, base_dir=G), seed=0x77,
-                                         flags=capi.RT_RENDER_NEE)
+                                         flags=nee_flag)
     assert nshadow > 0 and st["shadow_rays"] == nshadow and st["rays"] == nrays
     err = np.abs(got - want)
     bad = (err > 1e-5 * spp * max(1.0, want.max() / spp)).any(-1).sum()
     assert bad == 0, f"{bad} pixels differ, max {err.max()}"
     # scheduling options leave the NEE image unchanged too
-    rt.render(seed=0x77, flags=capi.RT_RENDER_NEE | capi.RT_RENDER_SORT, max_paths_per_pass=W * H * 2)
+    rt.render(seed=0x77, flags=nee_flag | capi.RT_RENDER_SORT, max_paths_per_pass=W * H * 2)
     assert np.array_equal(rt.download()[0], got)
 
 
@@ -646,3 +647,35 @@ def test_device_group_image_is_bit_identical_for_any_gpu_count():
         g.render(seed=6)                                    # the group is reusable
         assert not np.array_equal(g.download()[0], want)
         g.close()
+
+
+def test_incremental_animation_frames_equal_full_uploads(rt, tmp_path):
+    """rt_scene_update (table entries + device rebuild, transforms from rt_make_xform) instead of JSON text per frame: blue2.py's
+    rule and a moving emissive sphere give the same PNG bytes as the per-frame JSON path; an invalid update leaves the scene intact."""
+    from PIL import Image
+    from rt_b200 import animation
+    base = json.load(open(scene_path("blue2")))
+    full, inc = tmp_path / "full", tmp_path / "inc"
+    full.mkdir(); inc.mkdir()
+    r1 = animation.render_animation(rt, base, animation.blue2_frame, [0, 1, 2, 5], str(full), width=64, height=36, spp=2)
+    r2 = animation.render_animation(rt, base, animation.blue2_frame, [0, 1, 2, 5], str(inc), width=64, height=36, spp=2, incremental=True)
+    assert r1["incremental_updates"] == 0 and r2["incremental_updates"] == 3 and r1["rays"] == r2["rays"]
+    for f in (0, 1, 2, 5):
+        assert np.array_equal(np.asarray(Image.open(full / f"{f:03d}.png")), np.asarray(Image.open(inc / f"{f:03d}.png")))
+    lit = json.loads(json.dumps(base))
+    lit["texture"]["data"].append({"type": "solid_color", "color": [5, 5, 4]})
+    lit["material"]["data"].append({"type": "diffuse_light", "texture": len(lit["texture"]["data"]) - 1})
+    lit["object"]["data"].append({"type": "sphere", "center": [6, 4, 6], "radius": 1.0, "material": len(lit["material"]["data"]) - 1})
+    rule = lambda b, f: animation.moving_light_frame(b, f, 24, "{:03d}.png")
+    (tmp_path / "lf").mkdir(); (tmp_path / "li").mkdir()
+    animation.render_animation(rt, lit, rule, [0, 3, 6], str(tmp_path / "lf"), width=64, height=36, spp=2)
+    r = animation.render_animation(rt, lit, rule, [0, 3, 6], str(tmp_path / "li"), width=64, height=36, spp=2, incremental=True)
+    assert r["incremental_updates"] == 2
+    for f in (0, 3, 6):
+        a, b = np.asarray(Image.open(tmp_path / "lf" / f"{f:03d}.png")), np.asarray(Image.open(tmp_path / "li" / f"{f:03d}.png"))
+        assert np.array_equal(a, b)
+    assert not np.array_equal(np.asarray(Image.open(tmp_path / "lf" / "000.png")), np.asarray(Image.open(tmp_path / "lf" / "006.png")))
+    bad = capi.ObjectDesc(); bad.type = 0; bad.material = 99; bad.xform = -1
+    with pytest.raises(RtError, match="missing material"):
+        rt.scene_update([bad], 0)
+    rt.render(seed=1); rt.download()            # the context and its scene are still usable

@@ -283,6 +283,13 @@ def test_oracle_nee_same_expectation_as_plain_estimator():
     plain2, _, _ = orc.render_ex(sc, seed=4)
     nee2, _, _ = orc.render_ex(sc, seed=4, flags=capi.RT_RENDER_NEE)
     assert np.mean((nee - nee2) ** 2) < np.mean((plain - plain2) ** 2)
+    # multiple importance sampling (balance heuristic between the light sample and the scattered ray): same expectation again, and
+    # no noisier than light sampling alone on this scene (large rect light close to the floor: the scattered ray finds it often)
+    mis, _, nsm = orc.render_ex(sc, seed=3, flags=capi.RT_RENDER_NEE_MIS)
+    mis2, _, _ = orc.render_ex(sc, seed=4, flags=capi.RT_RENDER_NEE_MIS)
+    assert nsm == ns
+    assert abs(mis.mean() - plain.mean()) <= 0.05 * plain.mean()
+    assert np.mean((mis - mis2) ** 2) < 1.05 * np.mean((nee - nee2) ** 2)
 
 
 def _philox4x32_10(ctr, key):
