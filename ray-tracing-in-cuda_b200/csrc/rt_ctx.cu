@@ -7,6 +7,7 @@
 #include <cstring>
 #include <fstream>
 #include <sstream>
+#include <nvtx3/nvToolsExt.h>      // header-only NVTX v3: a no-op unless a profiler injects itself (ranges per stage)
 
 static thread_local std::string g_create_err;
 
@@ -645,13 +646,18 @@ static int rt_render_impl(rt_ctx *ctx, const rt_render_params *prm) {
         const size_t need = ctx->pending.size() + n_passes * (2 + 3 * (size_t)ds.max_depth);
         while (ctx->ev_pool.size() < 2 * need) { cudaEvent_t e; if (cudaEventCreate(&e) != cudaSuccess) return rt_fail(ctx, RT_ERR_CUDA, "cudaEventCreate"); ctx->ev_pool.push_back(e); }
     }
+    static const char *stage_name[6] = {"rt:generate", "rt:extend", "rt:shade", "rt:accumulate", "rt:shadow", "rt:tail"};
+    static const bool nvtx = getenv("RT_NVTX") != nullptr;       // one NVTX range per stage launch (host-side enqueue) + one per rt_render
+    if (nvtx) nvtxRangePushA("rt_render");
     auto timed = [&](int stage, auto &&fn) {
+        if (nvtx) nvtxRangePushA(stage_name[stage]);
         if (count) cudaEventRecord(evs[0], s);
         size_t slot = 0;
         if (time_stages) { slot = ctx->pending.size(); ctx->pending.push_back(stage); cudaEventRecord(ctx->ev_pool[2 * slot], s); }
         fn();
         if (time_stages) cudaEventRecord(ctx->ev_pool[2 * slot + 1], s);
         if (count) { cudaEventRecord(evs[1], s); cudaEventSynchronize(evs[1]); float ms = 0; cudaEventElapsedTime(&ms, evs[0], evs[1]); ms_stage[stage] += ms; }
+        if (nvtx) nvtxRangePop();
     };
     const auto t_prep = std::chrono::steady_clock::now();
     CU(cudaEventRecord(ctx->ev0, s));
@@ -727,6 +733,7 @@ static int rt_render_impl(rt_ctx *ctx, const rt_render_params *prm) {
         launch_fold_chunks(ctx->cfg, ctx->d_accum.p, cp, n_cp, !clear, (long long)n_img);
     }
     CU(cudaEventRecord(ctx->ev1, s));
+    if (nvtx) nvtxRangePop();
     if (trace) {
         const auto t_done = std::chrono::steady_clock::now();
         {       // queue lengths of the last pass of stream 0 (synchronises: a development aid for reading ncu launch lists)
