@@ -274,6 +274,8 @@ __device__ __forceinline__ void traverse4(const DScene &sc, const BvhNode4 *__re
 #undef RT_BOX4
             if (COUNT) { cnt.box += 4; cnt.nodes++; }
             int l0 = lk.x, l1 = lk.y, l2 = lk.z, l3 = lk.w;
+            // full order of the four entry distances (singling out only the nearest and pushing the rest in slot order measured equal:
+            // 65.6 vs 65.5 ms — the walk is not bound by this network)
             cswap(t0, l0, t1, l1); cswap(t2, l2, t3, l3); cswap(t0, l0, t2, l2); cswap(t1, l1, t3, l3); cswap(t1, l1, t2, l2);
             if (t0 == INFINITY) { RT_POP4() }
             else {
