@@ -330,6 +330,8 @@ static int upload_to_device(rt_ctx *ctx) {
     int per_sm = extend_max_blocks_per_sm(ctx->cfg.bvh_smem_bytes);
     if (per_sm < 1) { ctx->cfg.bvh_smem_bytes = 0; per_sm = extend_max_blocks_per_sm(0); }
     ctx->cfg.extend_blocks_per_sm = per_sm < 1 ? 1 : per_sm;
+    static const int env_ext_ctas = getenv("RT_EXT_CTAS") ? atoi(getenv("RT_EXT_CTAS")) : 0;       // tuning: persistent CTAs per SM
+    if (env_ext_ctas > 0) ctx->cfg.extend_blocks_per_sm = std::min(env_ext_ctas, ctx->cfg.extend_blocks_per_sm);
     ds.nodes4 = nullptr;
     static const bool no_bvh4 = getenv("RT_NO_BVH4") != nullptr;      // A/B: two-wide 64-byte nodes
     if (!ctx->cfg.bvh_smem_bytes && ds.n_tree > 0 && !no_bvh4) {          // tree walked from global memory: four-wide nodes (rt_scene.cuh: BvhNode4)

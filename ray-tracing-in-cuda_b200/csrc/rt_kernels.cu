@@ -947,7 +947,8 @@ int extend_max_blocks_per_sm(size_t smem_bytes) {
 
 void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int bounce, int buf,
                   bool last_bounce, bool count, bool sort, bool nee) {
-    const int grid = persistent_grid(c, RT_SH_CTAS_PER_SM);
+    static const int env_sh_ctas = getenv("RT_SH_CTAS") ? atoi(getenv("RT_SH_CTAS")) : 0;          // tuning: persistent CTAs per SM
+    const int grid = persistent_grid(c, env_sh_ctas > 0 && env_sh_ctas < RT_SH_CTAS_PER_SM ? env_sh_ctas : RT_SH_CTAS_PER_SM);
 #define RT_SHADE_ARGS <<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort)
 #define RT_SHADE_CAM(C_, N_) { if (sc.direct) { if (bounce == 0) k_shade<C_, N_, true, true> RT_SHADE_ARGS; else k_shade<C_, N_, false, true> RT_SHADE_ARGS; } \
                               else { if (bounce == 0) k_shade<C_, N_, true, false> RT_SHADE_ARGS; else k_shade<C_, N_, false, false> RT_SHADE_ARGS; } }
