@@ -1,6 +1,7 @@
 // rt_kernels.cu — the wavefront path-tracing kernels for sm_100a:
 //   tile_lists (once per scene) ; generate (+ bounce-0 hits) -> [ extend (LBVH traversal) -> shade (+ stream compaction)
-//   (-> shadow) ] x max_depth -> accumulate ; tonemap
+//   (-> shadow) ] x max_depth (from bounce 8: one tail launch finishes the surviving paths) -> accumulate (per sample chunk)
+//   -> fold chunks ; tonemap
 // They replace the reference's megakernel (gpu-version/main.cu:72-105 `render` + 17-70 `ray_color`), which runs one
 // thread per pixel, serial over samples, with virtual dispatch through device-heap pointers.
 //
@@ -8,8 +9,8 @@
 //   * persistent grids (SM count x resident CTAs); extend warps pull batches from a device-side cursor, shade CTAs own
 //     256-entry chunks — queue lengths never travel to the host, nearly-empty late bounces cost one tiny launch each;
 //   * SoA float4 ray queues (coalesced 16-byte accesses / TMA bulk copies), hit records of 8 bytes, 256 M paths per pass and stream;
-//   * the whole BVH is staged in shared memory in a sign-ordered 128-byte layout when it fits (RTIOW: 485 nodes = 62 KB),
-//     else 64-byte nodes are read via L1/L2; the first traversal-stack levels live in shared memory too; primary rays skip
+//   * the whole BVH is staged in shared memory in a sign-ordered 104-byte layout when tree + stack fit 112 KB (RTIOW: 484 nodes = 50 KB),
+//     else four-wide 128-byte nodes are read via L1/L2; objects that span the scene ("giants") stay out of the tree and are tested first; the first traversal-stack levels live in shared memory too; primary rays skip
 //     the tree through per-tile camera-beam candidate lists, and tiles whose beam touches nothing skip the queues altogether;
 //   * shade: TMA bulk loads/stores through shared staging, ballot/popc compaction, one global atomic per chunk, optional
 //     in-CTA sort by material class (RT_RENDER_SORT);
