@@ -481,6 +481,8 @@ def main():
         queued = samples_rank - skipped
         queue_bytes = ((32.0 + (8.0 if bounce0_in_generate else 0.0)) * queued + 56.0 * (rays_rank - skipped) - 16.0 * queued
                        + 48.0 * (rays_rank - samples_rank) + 16.0 * queued + 16.0 * queued + (32.0 * skipped if gradient else 0.0))
+        if sq["ms_shade"] == 0 and sq["ms_extend"] == 0:      # no queue stage ran (empty scene, or the one-kernel path of all-emitter scenes):
+            queue_bytes = 2.0 * 12.0 * W * H * 8              # only the chunk buffers are written and folded
         hbm_ach = queue_bytes / (ms_other * 1e-3) / 1e9 if ms_other > 0 else 0.0
         if args.workload == "rtiow_1080p_1024spp" and os.path.exists(tpath):
             tj = json.load(open(tpath))

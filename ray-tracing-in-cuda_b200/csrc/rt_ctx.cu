@@ -627,7 +627,11 @@ static int rt_render_impl(rt_ctx *ctx, const rt_render_params *prm) {
     if (cap > (1ll << 30) - 64) return rt_fail(ctx, RT_ERR_INVALID, "rt_render: image too large for one wavefront pass");
     int rc = ensure_accum(ctx); if (rc) return rc;
     rc = ensure_tile_lists(ctx); if (rc) return rc;
-    for (int k = 0; k < n_sets; ++k) {
+    // All-emitter scenes with complete tile candidate lists need no queues at all: one kernel per render (k_primary_only)
+    static const bool no_primary_only = getenv("RT_NO_PRIMARY_ONLY") != nullptr;
+    const bool primary_only = !ctx->scene_scatters && ds.tile_mode == 1 && !(prm->flags & RT_RENDER_NO_TILE_LISTS) && !nee && !count &&
+                              !no_primary_only && ds.n_prims > 0;
+    for (int k = 0; k < n_sets && !primary_only; ++k) {
         rc = ensure_queues(ctx, ctx->qs[k], cap, ds.max_depth, nee); if (rc) return rc;
         ctx->qs[k].cfg = ctx->cfg; ctx->qs[k].cfg.stream = k == 0 ? ctx->stream : ctx->extra_stream[k];
     }
@@ -677,7 +681,18 @@ static int rt_render_impl(rt_ctx *ctx, const rt_render_params *prm) {
         cp.p[n_cp++] = ctx->d_chunk[pc.chunk].p;
         chunk_clear[pc.chunk] = true;
     }
-    {
+    if (primary_only) {
+        AccumPlan plan{};
+        for (const Piece &pc : pieces) {
+            plan.first[plan.n] = pc.begin - prm->spp_begin; plan.first[plan.n + 1] = pc.end - prm->spp_begin;
+            plan.buf[plan.n] = ctx->d_chunk[pc.chunk].p; plan.clear[plan.n] = 1;
+            ++plan.n;
+        }
+        if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(2)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 2 * sizeof(unsigned long long), s)); }
+        timed(0, [&] { launch_primary_only(ctx->cfg, ds, plan, prm->seed, prm->spp_begin, spp, ctx->d_rays.p); });
+        if (ds.tile_empty_prefix) ctx->stats.paths_skipped += (long long)ctx->tiles_n_empty * 32 * spp;
+        ++passes;
+    } else {
         for (int done = 0; done < spp; done += s_pass) {
             const int sn = std::min(s_pass, spp - done);
             const int n_paths = sn * np;

@@ -701,6 +701,60 @@ __global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restric
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// primary_only: scenes whose objects are ALL emitters (the frames of gpu-version/dna.py: 60 emissive spheres + 30 emissive
+// cylinders) end every path at its first vertex, and with complete tile candidate lists (tile_mode 1) the first hit needs no tree.
+// Then generate -> shade<CAM> -> accumulate is one kernel with no queue at all: a thread owns a pixel, loops over the samples in
+// order, and adds each sample's radiance (emitter colour | background) to the running sum of the sample chunk it belongs to.  Same
+// functions, same Philox keys and the same order of float additions as the three-kernel path: bit-identical image
+// (test_empty_tiles_skip_the_queues compares with RT_RENDER_NO_TILE_LISTS), 112 B of queue traffic per sample gone.
+// ------------------------------------------------------------------------------------------------
+template <bool DIRECT>
+__global__ void __launch_bounds__(RT_BLOCK) k_primary_only(DScene sc, AccumPlan plan, unsigned seed, int spp_begin, int n_samples,
+                                                          unsigned long long *total_rays) {
+    const int np = sc.width * sc.height;
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k == 0) total_rays[0] += (unsigned long long)np * (unsigned long long)n_samples;       // one ray per camera path
+    if (k >= np) return;
+    const int pixel = plane_to_pixel(sc.width, sc.height, k);
+    const int y = pixel / sc.width, x = pixel - y * sc.width;
+    const float div_w = (float)(sc.width - 1), div_h = (float)(sc.height - 1);
+    const int n_cand = __ldg(&sc.tile_cnt[k >> 5]);                   // tile_mode 1: every pixel belongs to a tile with a complete list
+    const int *cand = sc.tile_list + (size_t)(k >> 5) * RT_TILE_K;
+    const bool gradient = sc.bg_mode == RT_BG_SKY_GRADIENT;
+    TravCounters cnt = {};
+#pragma unroll 1
+    for (int j = 0; j < plan.n; ++j) {
+        float *__restrict__ accum = plan.buf[j];
+        float r = 0.0f, g = 0.0f, b = 0.0f;
+        if (!plan.clear[j]) { r = accum[3 * pixel]; g = accum[3 * pixel + 1]; b = accum[3 * pixel + 2]; }
+#pragma unroll 1
+        for (int s = plan.first[j]; s < plan.first[j + 1]; ++s) {
+            float3 rad = sc.background;
+            if (n_cand != 0 || gradient) {
+                Rng rng; rng.init(seed, (unsigned)pixel, (unsigned)(spp_begin + s), 0u, sc.sampling);
+                const float u = ((float)x + rng.next()) / div_w;
+                const float v = ((float)y + rng.next()) / div_h;
+                float3 o, d;
+                camera_ray<DIRECT>(sc.cam, u, v, sc.defocus != 0, rng, o, d);
+                float best_t = FLT_MAX; int best_code = -1;
+                const float a = dot3(d, d), inv_a = 1.0f / a;
+                for (int c = 0; c < n_cand; ++c) leaf_visit<false>(sc, __ldg(&cand[c]), o, d, a, inv_a, 0.001f, best_t, best_code, cnt);
+                if (best_code < 0) rad = background(sc, d);
+                else {
+                    const int type = (unsigned)best_code >> 28, slot = best_code & RT_LEAF_SLOT_MASK;
+                    const DMaterial m = sc.mats[__ldg(&sc.prim_mat[slot])];
+                    HitRec rec;
+                    hit_record(sc, type, slot, o, d, best_t, m.albedo.w != 0.0f, rec);
+                    rad = m.type == RT_MAT_DIFFUSE_LIGHT ? material_color(sc, m, rec.u, rec.v, rec.p) : v3(0, 0, 0);
+                }
+            }
+            r += rad.x; g += rad.y; b += rad.z;
+        }
+        accum[3 * pixel] = r; accum[3 * pixel + 1] = g; accum[3 * pixel + 2] = b;
+    }
+}
+
 // Fixed-order combination of the sample chunks of a render (rt_ctx.cu:rt_render): image = (((c0 + c1) + c2) + ...) in ascending
 // chunk order, each c_k a sequential sum over the samples of chunk k.  The chunk boundaries depend on the total sample count
 // only, so the image is bit-identical whether one GPU renders all chunks or eight GPUs render one each.
@@ -979,6 +1033,14 @@ void launch_accumulate(const LaunchCfg &c, const Queues &q, const AccumPlan &pla
     int blocks = (W * H + RT_BLOCK - 1) / RT_BLOCK;
     k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, plan, W, H, n_samples, q.qcount, max_depth, total_rays, q.shcount,
                                                     const_tiles, bg);
+    bump(c);
+}
+
+void launch_primary_only(const LaunchCfg &c, const DScene &sc, const AccumPlan &plan, unsigned seed, int spp_begin, int n_samples,
+                         unsigned long long *total_rays) {
+    const int np = sc.width * sc.height;
+    if (sc.direct) k_primary_only<true><<<(np + RT_BLOCK - 1) / RT_BLOCK, RT_BLOCK, 0, c.stream>>>(sc, plan, seed, spp_begin, n_samples, total_rays);
+    else k_primary_only<false><<<(np + RT_BLOCK - 1) / RT_BLOCK, RT_BLOCK, 0, c.stream>>>(sc, plan, seed, spp_begin, n_samples, total_rays);
     bump(c);
 }
 

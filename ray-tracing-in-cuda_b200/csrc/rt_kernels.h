@@ -27,6 +27,8 @@ struct ChunkPtrs { const float *p[RT_ACC_CHUNKS]; };
 struct AccumPlan { int n; int first[RT_ACC_CHUNKS + 1]; int clear[RT_ACC_CHUNKS]; float *buf[RT_ACC_CHUNKS]; };
 void launch_accumulate(const LaunchCfg &c, const Queues &q, const AccumPlan &plan, int W, int H, int n_samples, int max_depth,
                        unsigned long long *total_rays, const int *const_tiles, float3 bg);
+void launch_primary_only(const LaunchCfg &c, const DScene &sc, const AccumPlan &plan, unsigned seed, int spp_begin, int n_samples,
+                         unsigned long long *total_rays);
 void launch_fold_chunks(const LaunchCfg &c, float *accum, const ChunkPtrs &cp, int n_chunks, bool keep, long long n);
 void launch_sum_ordered(const LaunchCfg &c, float *accum, const float *const *partials_dev, int n_partials, long long n);
 void launch_tonemap(const LaunchCfg &c, const float *accum, unsigned char *rgb8, int W, int H, int spp, int gamma);
