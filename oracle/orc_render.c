@@ -195,6 +195,7 @@ typedef struct {
     int row_next; pthread_mutex_t mu; int64_t rays, shadow; nee_t nee;
     const orc_bvh *bvh; orc_trav_counters cnt;
     int stride;            /* > 1: only pixels whose index is a multiple of stride are rendered (parity checks at full image sizes) */
+    const int32_t *only; int n_only;   /* when set: only these pixel indices (ascending) are rendered */
 } job_t;
 
 static void *worker(void *arg) {
@@ -211,6 +212,11 @@ static void *worker(void *arg) {
         for (int x = 0; x < W; ++x) {
             uint32_t pixel = (uint32_t)(y * W + x);
             if (j->stride > 1 && pixel % (uint32_t)j->stride != 0) continue;
+            if (j->only) {
+                int found = 0;
+                for (int q = 0; q < j->n_only && !found; ++q) found = j->only[q] == (int32_t)pixel;
+                if (!found) continue;
+            }
             v3 sum = V(0, 0, 0);
             int first_chunk = 1;
             /* fixed-order accumulation (rt.h: rt_sample_chunk): the samples fall into 8 chunks by the TOTAL sample count; a chunk is
@@ -247,6 +253,7 @@ static void *worker(void *arg) {
     return NULL;
 }
 
+static const int32_t *g_only = NULL; static int g_n_only = 0;     /* orc_render_pixels (same caveat as g_stride) */
 static int g_stride = 1;      /* set by orc_render_bvh_strided around its render_impl call (test infrastructure: not re-entrant) */
 static int render_impl(const rt_scene_desc *sc, uint32_t seed, int spp_begin, int spp_count, float *rgb_sum, int n_threads,
                        int flags, int64_t *n_rays, int64_t *n_shadow_rays, int use_bvh, int64_t *counters, int total_spp) {
@@ -265,7 +272,7 @@ static int render_impl(const rt_scene_desc *sc, uint32_t seed, int spp_begin, in
     }
     j.nee.lights = lights; j.nee.is_light = is_light;
     orc_bvh *bvh = use_bvh ? orc_bvh_create(sc) : NULL;
-    j.bvh = bvh; j.stride = g_stride;
+    j.bvh = bvh; j.stride = g_stride; j.only = g_only; j.n_only = g_n_only;
     pthread_mutex_init(&j.mu, NULL);
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 256) n_threads = 256;
@@ -300,6 +307,14 @@ int orc_render_bvh_strided(const rt_scene_desc *sc, uint32_t seed, float *rgb_su
     g_stride = stride > 1 ? stride : 1;
     const int rc = render_impl(sc, seed, 0, 0, rgb_sum, n_threads, 0, n_rays, NULL, 1, NULL, 0);
     g_stride = 1;
+    return rc;
+}
+
+/* only the listed pixels (the others stay untouched in rgb_sum); use_bvh = 0: the reference's linear walk (brute force) */
+int orc_render_pixels(const rt_scene_desc *sc, uint32_t seed, float *rgb_sum, int n_threads, const int32_t *pixels, int n_pixels, int use_bvh) {
+    g_only = pixels; g_n_only = n_pixels;
+    const int rc = render_impl(sc, seed, 0, 0, rgb_sum, n_threads, 0, NULL, NULL, use_bvh, NULL, 0);
+    g_only = NULL; g_n_only = 0;
     return rc;
 }
 
@@ -353,4 +368,39 @@ void orc_tonemap(const float *rgb_sum, int W, int H, int spp, int gamma, unsigne
                 x = x < 0.0f ? 0.0f : (x > 0.999f ? 0.999f : x);   /* clamp(x,0,0.999); NaN falls through as in the reference */
                 rgb8[3 * ((size_t)row * W + i) + c] = (unsigned char)(int)(256.0f * x);
             }
+}
+
+/* debug aid (tests / tools only): follows the paths of one pixel with the linear walk and reports the first ray on which the host
+ * twin of the traversal disagrees with it: out[0..2] = origin, [3..5] = direction, [6] = t linear, [7] = prim linear, [8] = t twin,
+ * [9] = prim twin, [10] = sample, [11] = bounce.  Returns 1 when a disagreement was found. */
+int orc_debug_first_mismatch(const rt_scene_desc *sc, uint32_t seed, int pixel, int n_samples, float *out) {
+    orc_camera cam; orc_camera_setup(&sc->camera, &cam);
+    orc_bvh *bvh = orc_bvh_create(sc);
+    const int W = sc->width, H = sc->height, x = pixel % W, y = pixel / W;
+    int found = 0;
+    for (int s = 0; s < n_samples && !found; ++s) {
+        orc_rng rng; orc_rng_init(&rng, seed, (uint32_t)pixel, (uint32_t)s, 0u, sc->sampling);
+        float u = ((float)x + orc_rng_next(&rng)) / (float)(W - 1), v = ((float)y + orc_rng_next(&rng)) / (float)(H - 1);
+        v3 o, d;
+        int defocus = (sc->sampling & 1) == RT_SAMPLING_REFERENCE_CPU && sc->camera.aperture > 0.0f;
+        orc_get_ray(&cam, u, v, defocus, &rng, &o, &d);
+        for (int bounce = 0; bounce < sc->max_depth; ++bounce) {
+            orc_hit a, b;
+            int ha = orc_hit_world(sc, o, d, 0.001f, FLT_MAX, &a), hb = orc_bvh_hit(bvh, o, d, 0.001f, FLT_MAX, 0, &b, NULL);
+            if (ha != hb || (ha && (a.prim != b.prim || a.t != b.t))) {
+                out[0] = o.x; out[1] = o.y; out[2] = o.z; out[3] = d.x; out[4] = d.y; out[5] = d.z;
+                out[6] = ha ? a.t : -1.0f; out[7] = ha ? (float)a.prim : -1.0f; out[8] = hb ? b.t : -1.0f; out[9] = hb ? (float)b.prim : -1.0f;
+                out[10] = (float)s; out[11] = (float)bounce;
+                found = 1; break;
+            }
+            if (!ha) break;
+            orc_rng r2; orc_rng_init(&r2, seed, (uint32_t)pixel, (uint32_t)s, (uint32_t)bounce + 1u, sc->sampling);
+            v3 att, so, sd;
+            if (!orc_scatter(sc, a.mat, d, &a, &r2, &att, &so, &sd)) break;
+            o = so; d = sd;
+        }
+    }
+    orc_bvh_destroy(bvh);
+    (void)H;
+    return found;
 }

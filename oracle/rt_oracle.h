@@ -82,6 +82,8 @@ int orc_render_bvh(const rt_scene_desc *scene, uint32_t seed, int spp_begin, int
                    int flags, int64_t *n_rays, int64_t *counters);
 /* orc_render_bvh restricted to the pixels whose index is a multiple of `stride` (others untouched): full-size parity checks */
 int orc_render_bvh_strided(const rt_scene_desc *scene, uint32_t seed, float *rgb_sum, int n_threads, int stride, int64_t *n_rays);
+/* only the listed pixel indices; use_bvh = 0: brute-force linear walk, 1: host twin of the traversal */
+int orc_render_pixels(const rt_scene_desc *scene, uint32_t seed, float *rgb_sum, int n_threads, const int32_t *pixels, int n_pixels, int use_bvh);
 /* stable LSD radix sort of (key, value) pairs — the host statement of the device sort, exposed for tests */
 void orc_radix_sort_pairs(uint64_t *keys, int32_t *vals, int n);
 

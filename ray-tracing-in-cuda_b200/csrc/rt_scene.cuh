@@ -44,7 +44,9 @@ struct DMaterial { int type; int texture; float fuzz; float ior; float4 albedo; 
 struct DTexture { int type; int even; int odd; int image; float4 color; };            // 32 B
 struct DImage { cudaTextureObject_t tex; int width, height; };
 
-#define RT_TILE_K 16
+#ifndef RT_TILE_K
+#define RT_TILE_K 64        // candidates per 8x4 tile; 16 covered every RTIOW tile but left 40 % of the mesh tiles to full traversal (64: 9 %)
+#endif
 #define RT_MORTON_CUBE_MIN 4096 // trees with more leaves quantise their Morton codes on a cubical grid (rt_lbvh.cu:k_morton)
 #define RT_MAX_GIANTS 16        // objects kept out of the tree and tested first by every ray (rt_lbvh.cu:k_giants_mark)
 struct DCamera { float3 origin, llc, horizontal, vertical, u, v, w; float lens_radius; };
@@ -206,6 +208,19 @@ __device__ __forceinline__ bool triangle_t(float3 v0, float3 e1, float3 e2, floa
     if (v < 0.0f || u + v > 1.0f) return false;
     float tt = dot3(e2, qv) * inv;
     if (tt < tmin || tmax < tt) return false;
+    // A grazing ray (|det| tiny) carries a barycentric error of ~1e-7 |o - v0| |d x e2| / |det|: the float test above can accept a point
+    // well outside the triangle — and outside its leaf box, where the tree (rightly) never looks: the 1 M-triangle terrain showed one
+    // such ray in ~1e9, found by the tile candidate lists and missed by the traversal.  A hit counts only if its point lies in the
+    // triangle's own box widened by 2^-11 of its largest extent, which is inside the leaf box (2^-10 of the extent + 2^-20 of the
+    // scene) whatever the rounding: linear walk, tile lists and tree then agree by construction (oracle/orc_hit.c states the same).
+    {
+        const float lx = v0.x + fminf(0.0f, fminf(e1.x, e2.x)), hx = v0.x + fmaxf(0.0f, fmaxf(e1.x, e2.x));
+        const float ly = v0.y + fminf(0.0f, fminf(e1.y, e2.y)), hy = v0.y + fmaxf(0.0f, fmaxf(e1.y, e2.y));
+        const float lz = v0.z + fminf(0.0f, fminf(e1.z, e2.z)), hz = v0.z + fmaxf(0.0f, fmaxf(e1.z, e2.z));
+        const float s = 4.8828125e-04f * fmaxf(hx - lx, fmaxf(hy - ly, hz - lz));
+        const float3 q = vfma(tt, d, o);
+        if (!(q.x >= lx - s && q.x <= hx + s && q.y >= ly - s && q.y <= hy + s && q.z >= lz - s && q.z <= hz + s)) return false;
+    }
     t = tt; bu = u; bv = v;
     return true;
 }

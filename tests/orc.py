@@ -53,6 +53,7 @@ def lib():
         L.orc_lbvh_build_ex.argtypes = [P(capi.SceneDesc), P(C.c_uint64), P(C.c_int32), P(C.c_int32), P(C.c_int32),
                                         P(C.c_int32), fp, fp, fp, P(C.c_int32)]
         L.orc_render_bvh_strided.argtypes = [P(capi.SceneDesc), C.c_uint32, fp, C.c_int, C.c_int, P(C.c_int64)]
+        L.orc_render_pixels.argtypes = [P(capi.SceneDesc), C.c_uint32, fp, C.c_int, P(C.c_int32), C.c_int, C.c_int]
         L.orc_render_range.argtypes = [P(capi.SceneDesc), C.c_uint32, C.c_int, C.c_int, C.c_int, fp, C.c_int, P(C.c_int64)]
         L.orc_render_bvh.argtypes = [P(capi.SceneDesc), C.c_uint32, C.c_int, C.c_int, fp, C.c_int, C.c_int, P(C.c_int64), P(C.c_int64)]
         L.orc_radix_sort_pairs.argtypes = [P(C.c_uint64), P(C.c_int32), C.c_int]
@@ -270,6 +271,14 @@ def render_bvh_strided(sc, seed, stride, threads=None):
     nr = C.c_int64(0)
     assert lib().orc_render_bvh_strided(sc.ptr, seed, fptr(out), threads or os.cpu_count() or 1, stride, C.byref(nr)) == 0
     return out, nr.value
+
+
+def render_pixels(sc, seed, pixels, use_bvh=False, threads=None):
+    """Oracle render of the listed pixel indices only (brute-force walk unless use_bvh); returns the (H, W, 3) image, zero elsewhere."""
+    out = np.zeros((sc.desc.height, sc.desc.width, 3), np.float32)
+    px = np.ascontiguousarray(sorted(int(p) for p in pixels), np.int32)
+    assert lib().orc_render_pixels(sc.ptr, seed, fptr(out), threads or os.cpu_count() or 1, px.ctypes.data_as(C.POINTER(C.c_int32)), len(px), int(use_bvh)) == 0
+    return out
 
 
 def render_range(sc, seed, spp_begin, spp_count, total_spp, threads=None):

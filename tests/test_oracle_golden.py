@@ -452,3 +452,18 @@ def test_extension_primitives_against_an_independent_float64_statement():
     want_rgb = tex[j, i]
     assert safe.sum() > 0.3 * W * H
     assert np.abs(aov[..., 13:16][safe] - want_rgb[safe]).max() <= 1e-6
+
+
+def test_grazing_triangle_hits_stay_inside_their_leaf_box():
+    """Found on the 1 M-triangle terrain at 4K (3 pixels in 2.1 G paths): a grazing camera ray whose float Moeller-Trumbore test accepted
+    a point 6e-5 outside a 0.03-wide triangle — outside its leaf box, so the tree never looked there while the linear walk and the tile
+    candidate lists took the hit.  The triangle test now rejects points outside the triangle's own box (+ 2^-11 of its extent); on the
+    rays that exposed it (pixel, sample from the failing run) the host twin of the traversal and the linear walk agree again."""
+    import ctypes as C
+    from rt_b200 import scenes
+    ts = scenes.mesh_scene(708, 708, 3840, 2160, 256)
+    L = orc.lib()
+    L.orc_debug_first_mismatch.argtypes = [C.POINTER(capi.SceneDesc), C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_float)]
+    out = np.zeros(12, np.float32)
+    for x, y, n_samples in ((840, 1008, 16), (3770, 967, 70)):         # mismatches were at samples 15 and 69
+        assert L.orc_debug_first_mismatch(ts.ptr, 0x2023, y * 3840 + x, n_samples, orc.fptr(out)) == 0, out
