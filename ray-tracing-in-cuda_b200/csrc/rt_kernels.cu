@@ -217,8 +217,13 @@ __global__ void __launch_bounds__(128) k_tile_lists(DScene sc, int *__restrict__
 // path and bounce, so the add needs no atomic).
 // max_batch < 0 (bounce 0 after a generate launch that resolved most hits itself): only entries carrying RT_HIT_TODO.
 // ONLY: RT_OBJ_SPHERE when every primitive of the scene is a sphere (no leaf dispatch in the loop), else -1.
+#ifdef RT_EXT_MINCTAS          // tuning builds: resident CTAs per SM the register allocation aims at
+#define RT_EXT_BOUNDS __launch_bounds__(RT_EXT_BLOCK, RT_EXT_MINCTAS)
+#else
+#define RT_EXT_BOUNDS __launch_bounds__(RT_EXT_BLOCK)
+#endif
 template <bool SMEM, bool COUNT, bool SHADOW, int ONLY = -1>
-__global__ void __launch_bounds__(RT_EXT_BLOCK) k_extend(DScene sc, Queues q, int bounce, int buf, int max_batch) {
+__global__ void RT_EXT_BOUNDS k_extend(DScene sc, Queues q, int bounce, int buf, int max_batch) {
     const bool fixup = max_batch < 0;
     if (fixup) max_batch = -max_batch;
     extern __shared__ float2 s_raw[];

@@ -16,7 +16,9 @@
 #ifndef RT_SSTACK
 #define RT_SSTACK 8            // traversal stack levels kept in shared memory by k_extend (rt_traverse.cuh); deeper ones: local memory
 #endif
+#ifndef RT_EXT_BLOCK
 #define RT_EXT_BLOCK 512       // k_extend CTA size
+#endif
 #define RT_SSTACK_STRIDE (RT_EXT_BLOCK * 8)     // bytes between two levels of the shared-memory stack (one int2 per thread and level)
 #define RT_SSTACK_BYTES (RT_SSTACK * RT_SSTACK_STRIDE)
 #define RT_BLOCK 256
