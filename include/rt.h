@@ -120,20 +120,21 @@ typedef struct rt_scene_desc {
 enum { RT_RENDER_KEEP_ACCUM = 1,     /* add to the accumulation buffer instead of clearing it first */
        RT_RENDER_COUNT_EVENTS = 2,   /* fill the event counters of rt_stats (slower; counts are deterministic) */
        RT_RENDER_NO_SORT = 4,        /* accepted and ignored (sorting is opt-in, see RT_RENDER_SORT) */
-       RT_RENDER_NEE = 8,            /* next-event estimation through the shadow stage (changes the estimator; default off) */
+       RT_RENDER_NEE = 8,            /* next-event estimation through the shadow stage (changes the estimator; default off): emissive
+                                        spheres, rects, cylinders, boxes and triangles are sampled, transformed instances included */
        RT_RENDER_TIME_STAGES = 16,   /* record CUDA events around every stage launch (no synchronisation); per-stage ms in rt_stats */
        RT_RENDER_SORT = 32,          /* sort every shade chunk by material class in shared memory (same image; pays off only for scenes
                                         with an even material mix — measured slower on the reference's scenes) */
        RT_RENDER_SERIAL = 64,      /* one pass at a time on the context's stream (default: two passes in flight on two streams, so the
                                         short late-bounce launches of one overlap the other; same image either way) */
-       RT_RENDER_NO_TILE_LISTS = 256,
+       RT_RENDER_NO_TILE_LISTS = 256, /* traverse the tree for bounce 0 too (default: the generate stage resolves bounce-0 hits from the
+                                        per-tile candidate lists of the camera beams; same image either way) */
        RT_RENDER_NO_TAIL = 1024,     /* keep the queue schedule to the last bounce (default: from bounce 8 on one launch finishes every
                                         surviving path — same image either way) */
        RT_RENDER_NEE_MIS = 2048,     /* RT_RENDER_NEE with multiple importance sampling: light samples and the emission a scattered ray finds on
                                         a sampled light are combined with the balance heuristic (implies RT_RENDER_NEE) */
        RT_RENDER_KEEP_CHUNKS = 512 };  /* leave this call's chunk sums in their buffers instead of folding them into the accumulation
-                                        buffer: the root of a multi-GPU render gathers and folds them (rt_gather_image) */ /* traverse the tree for bounce 0 too (default: the generate stage resolves bounce-0 hits from the
-                                        per-tile candidate lists of the camera beams; same image either way) */
+                                        buffer: the root of a multi-GPU render gathers and folds them (rt_gather_image) */
 
 typedef struct rt_render_params {
     uint32_t seed;          /* Philox key word 0 */

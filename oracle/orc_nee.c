@@ -9,8 +9,8 @@
  *   at every lambertian hit x: pick one light uniformly, one point y uniformly on its surface, and if the segment
  *   x->y is unoccluded add  thr * albedo * Le(y) * cos_x * cos_y / |y-x|^2 * (area * n_lights / pi);
  *   the scattered ray that leaves x then does NOT collect the emission of a sampled light it happens to hit.
- * Lights = objects with a diffuse_light material of type sphere / rect / cylinder / triangle, in scene-file order
- * (emissive boxes are not sampled; they keep contributing when hit).  Emitters emit on both faces (material.cuh:175-178).
+ * Lights = objects with a diffuse_light material of type sphere / rect / cylinder / box / triangle, in scene-file order;
+ * sphere, rect and box lights may carry a rotate / translate instance (sampled in object space, taken to world space).  Emitters emit on both faces (material.cuh:175-178).
  * Draws: a separate Philox stream per vertex (bounce word | 0x10000): light index, then two surface coordinates.
  */
 #include "orc_internal.h"
@@ -19,9 +19,8 @@
 int orc_is_nee_light(const rt_scene_desc *sc, int i) {
     const rt_object_desc *o = &sc->objects[i];
     if (sc->materials[o->material].type != RT_MAT_DIFFUSE_LIGHT) return 0;
-    if (o->xform >= 0 && o->type != RT_OBJ_CYLINDER) return 0;      /* rotated / translated sphere and rect lights are not sampled */
     return o->type == RT_OBJ_SPHERE || o->type == RT_OBJ_XY_RECT || o->type == RT_OBJ_XZ_RECT || o->type == RT_OBJ_YZ_RECT ||
-           o->type == RT_OBJ_CYLINDER || o->type == RT_OBJ_TRIANGLE;
+           o->type == RT_OBJ_CYLINDER || o->type == RT_OBJ_TRIANGLE || o->type == RT_OBJ_BOX;
 }
 
 float orc_light_area(const rt_scene_desc *sc, int i) {
@@ -35,6 +34,10 @@ float orc_light_area(const rt_scene_desc *sc, int i) {
         v3 e1 = V(p[3] - p[0], p[4] - p[1], p[5] - p[2]), e2 = V(p[6] - p[0], p[7] - p[1], p[8] - p[2]);
         v3 c = V(fmaf(e1.y, e2.z, -(e1.z * e2.y)), fmaf(e1.z, e2.x, -(e1.x * e2.z)), fmaf(e1.x, e2.y, -(e1.y * e2.x)));
         return 0.5f * sqrtf(dot3(c, c));
+    }
+    case RT_OBJ_BOX: {
+        float ex = fabsf(p[3] - p[0]), ey = fabsf(p[4] - p[1]), ez = fabsf(p[5] - p[2]);
+        return 2.0f * ((ey * ez + ez * ex) + ex * ey);
     }
     }
     return 0.0f;
@@ -65,6 +68,10 @@ static void light_point(const rt_scene_desc *sc, int i, float u1, float u2, v3 *
         float theta = orc_acosf(-dir.y);                       /* get_sphere_uv, object.cuh:87-93 */
         float ph = orc_atan2f(-dir.z, dir.x) + ORC_PI_F;
         *tu = ph * ORC_INV_2PI_F; *tv = theta * ORC_INV_PI_F;
+        if (o->xform >= 0) {       /* rotate / translate instance: the point and the normal go to world space (rigid: the area is unchanged) */
+            const rt_xform_desc *xf = &sc->xforms[o->xform];
+            *y = orc_xform_point(xf->m, *y); *ny = vunit(orc_xform_normal(xf->m_inv, *ny));
+        }
         return;
     }
     case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: {
@@ -73,6 +80,10 @@ static void light_point(const rt_scene_desc *sc, int i, float u1, float u2, v3 *
         else if (o->type == RT_OBJ_XZ_RECT) { *y = V(a, k, b); *ny = V(0, 1, 0); }
         else { *y = V(k, a, b); *ny = V(1, 0, 0); }
         *tu = (a - p[0]) / (p[1] - p[0]); *tv = (b - p[2]) / (p[3] - p[2]);    /* object.cuh:113-114 */
+        if (o->xform >= 0) {
+            const rt_xform_desc *xf = &sc->xforms[o->xform];
+            *y = orc_xform_point(xf->m, *y); *ny = vunit(orc_xform_normal(xf->m_inv, *ny));
+        }
         return;
     }
     case RT_OBJ_CYLINDER: {
@@ -83,6 +94,26 @@ static void light_point(const rt_scene_desc *sc, int i, float u1, float u2, v3 *
         *y = orc_xform_point(xf->m, op);
         *ny = vunit(orc_xform_normal(xf->m_inv, V(c, s, 0.0f)));
         *tu = (orc_atan2f(op.y, op.x) + ORC_2PI_F) * ORC_INV_4PI_F; *tv = (z - p[1]) / (p[2] - p[1]);   /* object.cuh:286-287 */
+        return;
+    }
+    case RT_OBJ_BOX: {      /* u1 picks the face in proportion to its area and is re-used inside it; uv as orc_hit.c gives them for a box */
+        const float *L = p, *H = p + 3;
+        float e[3] = {fabsf(p[3] - p[0]), fabsf(p[4] - p[1]), fabsf(p[5] - p[2])};
+        float wf[3] = {e[1] * e[2], e[2] * e[0], e[0] * e[1]};
+        float v = u1 * (2.0f * ((wf[0] + wf[1]) + wf[2]));
+        int fc = 0; float c = 0.0f;
+        while (fc < 5 && !(v < c + wf[fc >> 1])) { c += wf[fc >> 1]; ++fc; }
+        float s1 = fminf(fmaxf((v - c) / wf[fc >> 1], 0.0f), 0.99999994f);
+        int ax = fc >> 1, ua = (ax + 1) % 3, va = (ax + 2) % 3;
+        float P[3], nn[3] = {0.0f, 0.0f, 0.0f};
+        P[ax] = (fc & 1) ? H[ax] : L[ax]; nn[ax] = (fc & 1) ? 1.0f : -1.0f;
+        P[ua] = fmaf(s1, H[ua] - L[ua], L[ua]); P[va] = fmaf(u2, H[va] - L[va], L[va]);
+        *tu = (P[ua] - L[ua]) / (H[ua] - L[ua]); *tv = (P[va] - L[va]) / (H[va] - L[va]);
+        *y = V(P[0], P[1], P[2]); *ny = V(nn[0], nn[1], nn[2]);
+        if (o->xform >= 0) {
+            const rt_xform_desc *xf = &sc->xforms[o->xform];
+            *y = orc_xform_point(xf->m, *y); *ny = vunit(orc_xform_normal(xf->m_inv, *ny));
+        }
         return;
     }
     default: {   /* RT_OBJ_TRIANGLE */

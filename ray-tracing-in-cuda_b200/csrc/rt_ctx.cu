@@ -276,13 +276,12 @@ static int upload_to_device(rt_ctx *ctx) {
                                             " levels): too many objects share one Morton cell");
     }
 
-    // sampled lights for RT_RENDER_NEE: emissive spheres / rects / cylinders / triangles in scene-file order (oracle/orc_nee.c)
+    // sampled lights for RT_RENDER_NEE: emissive spheres / rects / cylinders / boxes / triangles in scene-file order (oracle/orc_nee.c)
     {
         std::vector<int> obj_light((size_t)std::max(1, n), -1), ltype; std::vector<float> larea;
         for (int i = 0; i < n; ++i) {
             const rt_object_desc &o = hs.objects[i];
             if (hs.materials[o.material].type != RT_MAT_DIFFUSE_LIGHT) continue;
-            if (o.xform >= 0 && o.type != RT_OBJ_CYLINDER) continue;      // rotated / translated sphere and rect lights are not sampled (they emit when hit)
             const float *p = o.p; float area;
             if (o.type == RT_OBJ_SPHERE) area = 4.0f * 3.14159274101257324f * (p[3] * p[3]);
             else if (o.type == RT_OBJ_XY_RECT || o.type == RT_OBJ_XZ_RECT || o.type == RT_OBJ_YZ_RECT) area = fabsf((p[1] - p[0]) * (p[3] - p[2]));
@@ -291,7 +290,10 @@ static int upload_to_device(rt_ctx *ctx) {
                 const float e1[3] = {p[3] - p[0], p[4] - p[1], p[5] - p[2]}, e2[3] = {p[6] - p[0], p[7] - p[1], p[8] - p[2]};
                 const float c[3] = {fmaf(e1[1], e2[2], -(e1[2] * e2[1])), fmaf(e1[2], e2[0], -(e1[0] * e2[2])), fmaf(e1[0], e2[1], -(e1[1] * e2[0]))};
                 area = 0.5f * sqrtf(fmaf(c[2], c[2], fmaf(c[1], c[1], c[0] * c[0])));
-            } else continue;                                   // emissive boxes are not sampled; they still emit when hit
+            } else if (o.type == RT_OBJ_BOX) {
+                const float ex = fabsf(p[3] - p[0]), ey = fabsf(p[4] - p[1]), ez = fabsf(p[5] - p[2]);
+                area = 2.0f * ((ey * ez + ez * ex) + ex * ey);
+            } else continue;
             obj_light[i] = (int)ltype.size(); ltype.push_back(o.type); larea.push_back(area);
         }
         const int nl = (int)ltype.size();

@@ -235,14 +235,19 @@ __device__ __forceinline__ bool light_sample(const DScene &sc, float3 x, float3 
         y = vfma(fabsf(A.w), dir, f4xyz(A));
         const float theta = rt_acosf(-dir.y), ph = rt_atan2f(-dir.z, dir.x) + RT_PI_F;
         tu = ph * RT_INV_2PI_F; tv = theta * RT_INV_PI_F;
+        const int xi = __float_as_int(sc.primB[slot].w);      // rotate / translate instance: the point and the normal go to world space
+        if (xi >= 0) { const float4 *xf = sc.xforms + 6 * xi; y = xf_point(xf, y); ny = vunit(xf_normal(xf + 3, ny)); }
         break;
     }
     case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: {
-        const float a = __fmaf_rn(u1, A.y - A.x, A.x), b = __fmaf_rn(u2, A.w - A.z, A.z), kk = sc.primB[slot].x;
+        const float4 B = sc.primB[slot];
+        const float a = __fmaf_rn(u1, A.y - A.x, A.x), b = __fmaf_rn(u2, A.w - A.z, A.z), kk = B.x;
         if (type == RT_OBJ_XY_RECT) { y = v3(a, b, kk); ny = v3(0, 0, 1); }
         else if (type == RT_OBJ_XZ_RECT) { y = v3(a, kk, b); ny = v3(0, 1, 0); }
         else { y = v3(kk, a, b); ny = v3(1, 0, 0); }
         tu = (a - A.x) / (A.y - A.x); tv = (b - A.z) / (A.w - A.z);
+        const int xi = __float_as_int(B.w);
+        if (xi >= 0) { const float4 *xf = sc.xforms + 6 * xi; y = xf_point(xf, y); ny = vunit(xf_normal(xf + 3, ny)); }
         break;
     }
     case RT_OBJ_CYLINDER: {
@@ -253,6 +258,25 @@ __device__ __forceinline__ bool light_sample(const DScene &sc, float3 x, float3 
         y = xf_point(xf, op);
         ny = vunit(xf_normal(xf + 3, v3(c, s, 0.0f)));
         tu = (rt_atan2f(op.y, op.x) + RT_2PI_F) * RT_INV_4PI_F; tv = (z - A.y) / (A.z - A.y);
+        break;
+    }
+    case RT_OBJ_BOX: {      // A = lo (w: instance transform), B = hi; u1 picks the face in proportion to its area and is re-used inside it
+        const float4 B = sc.primB[slot];
+        const float L[3] = {A.x, A.y, A.z}, H[3] = {B.x, B.y, B.z};
+        const float e[3] = {fabsf(B.x - A.x), fabsf(B.y - A.y), fabsf(B.z - A.z)};
+        const float wf[3] = {e[1] * e[2], e[2] * e[0], e[0] * e[1]};
+        const float v = u1 * (2.0f * ((wf[0] + wf[1]) + wf[2]));
+        int fc = 0; float c = 0.0f;
+        while (fc < 5 && !(v < c + wf[fc >> 1])) { c += wf[fc >> 1]; ++fc; }
+        const float s1 = fminf(fmaxf((v - c) / wf[fc >> 1], 0.0f), 0.99999994f);
+        const int ax = fc >> 1, ua = (ax + 1) % 3, va = (ax + 2) % 3;
+        float P[3], nn[3] = {0.0f, 0.0f, 0.0f};
+        P[ax] = (fc & 1) ? H[ax] : L[ax]; nn[ax] = (fc & 1) ? 1.0f : -1.0f;
+        P[ua] = __fmaf_rn(s1, H[ua] - L[ua], L[ua]); P[va] = __fmaf_rn(u2, H[va] - L[va], L[va]);
+        tu = (P[ua] - L[ua]) / (H[ua] - L[ua]); tv = (P[va] - L[va]) / (H[va] - L[va]);      // hit_record's box uv
+        y = v3(P[0], P[1], P[2]); ny = v3(nn[0], nn[1], nn[2]);
+        const int xi = __float_as_int(A.w);
+        if (xi >= 0) { const float4 *xf = sc.xforms + 6 * xi; y = xf_point(xf, y); ny = vunit(xf_normal(xf + 3, ny)); }
         break;
     }
     default: {   // RT_OBJ_TRIANGLE: A = v0, B = e1, C = e2

@@ -408,10 +408,15 @@ def _nee_scene(extra_lights=True):
     with open(scene_path("sample_scene_ext")) as f:
         d = json.load(f)
     d["sampling"] = "reference_cpu"
-    if extra_lights:     # a triangle light (sampled) and an emissive box (not sampled, still emits when hit)
+    if extra_lights:     # a triangle light and an emissive box (a face is picked by area)
         light = next(i for i, m in enumerate(d["material"]["data"]) if m["type"] == "diffuse_light")
         d["object"]["data"].append({"type": "triangle", "v0": [-3.0, 2.5, -2.0], "v1": [-2.0, 2.5, -2.0], "v2": [-2.5, 2.9, -1.2], "material": light})
         d["object"]["data"].append({"type": "box", "min": [2.6, -0.4, 1.0], "max": [2.9, -0.1, 1.3], "material": light})
+        # sphere and rect lights that carry a rotate / translate instance are sampled in world space
+        d["object"]["data"].append({"type": "sphere", "center": [0.1, 0.0, 0.05], "radius": 0.25, "material": light,
+                                    "rotate": {"axis": [0.2, 1, 0.1], "angle": 33}, "translate": [-1.2, 1.6, 0.8]})
+        d["object"]["data"].append({"type": "xy_rect", "x0": -0.3, "x1": 0.3, "y0": -0.2, "y1": 0.2, "k": 0.1, "material": light,
+                                    "rotate": {"axis": [1, 0.3, 0], "angle": -50}, "translate": [1.4, 1.9, 0.2]})
     return d
 
 
@@ -439,7 +444,10 @@ def test_nee_matches_oracle_sample_for_sample(rt, extra, depth, mis):
 
 
 def test_nee_same_expectation_lower_variance(rt):
-    """NEE and the plain estimator converge to the same image; on a scene lit by small lights NEE is the less noisy one."""
+    """Light sampling (eight lights of six kinds, three of them rotated instances) and light sampling + MIS converge to the plain
+    estimator's image, and with MIS the image is the less noisy one.  Light sampling ALONE is not on this scene: the emissive box stands
+    0.1 above the floor, and the 1/d^2 of a point sampled next to the shaded point is exactly what the balance heuristic is there for
+    (oracle, same seeds: plain 0.0068, light sampling 0.0110, MIS 0.0042 mean squared difference of two renders)."""
     W, H, spp = 64, 36, 256
     d = _nee_scene(True)
     d["background"] = [0.02, 0.02, 0.03]
@@ -448,9 +456,11 @@ def test_nee_same_expectation_lower_variance(rt):
     rt.render(seed=1); plain = rt.download()[0] / spp
     rt.render(seed=1, flags=capi.RT_RENDER_NEE); nee = rt.download()[0] / spp
     assert abs(nee.mean() - plain.mean()) <= 0.03 * plain.mean()
-    rt.render(seed=2, flags=capi.RT_RENDER_NEE); nee2 = rt.download()[0] / spp
+    rt.render(seed=1, flags=capi.RT_RENDER_NEE_MIS); mis = rt.download()[0] / spp
+    assert abs(mis.mean() - plain.mean()) <= 0.03 * plain.mean()
+    rt.render(seed=2, flags=capi.RT_RENDER_NEE_MIS); mis2 = rt.download()[0] / spp
     rt.render(seed=2); plain2 = rt.download()[0] / spp
-    assert np.mean((nee - nee2) ** 2) < np.mean((plain - plain2) ** 2)
+    assert np.mean((mis - mis2) ** 2) < 0.8 * np.mean((plain - plain2) ** 2)
 
 
 def test_nee_needs_cpu_sampling_convention(rt):

@@ -271,6 +271,12 @@ def test_oracle_nee_same_expectation_as_plain_estimator():
     with open(f"{orc.GOLDEN}/sample_scene_ext.json") as f:
         d = json.load(f)
     d["background"] = [0.02, 0.02, 0.03]
+    light = next(i for i, m in enumerate(d["material"]["data"]) if m["type"] == "diffuse_light")
+    # sphere and rect lights with a rotate / translate instance are sampled too (in world space)
+    d["object"]["data"].append({"type": "sphere", "center": [0.1, 0.0, 0.05], "radius": 0.25, "material": light,
+                                "rotate": {"axis": [0.2, 1, 0.1], "angle": 33}, "translate": [-1.2, 1.6, 0.8]})
+    d["object"]["data"].append({"type": "xy_rect", "x0": -0.3, "x1": 0.3, "y0": -0.2, "y1": 0.2, "k": 0.1, "material": light,
+                                "rotate": {"axis": [1, 0.3, 0], "angle": -50}, "translate": [1.4, 1.9, 0.2]})
     W, H, spp = 48, 27, 96
     with pytest.raises(AssertionError):
         orc.render_ex(orc.load_scene(d, width=W, height=H, spp=1, base_dir=orc.GOLDEN), flags=capi.RT_RENDER_NEE)
@@ -290,6 +296,32 @@ def test_oracle_nee_same_expectation_as_plain_estimator():
     assert nsm == ns
     assert abs(mis.mean() - plain.mean()) <= 0.05 * plain.mean()
     assert np.mean((mis - mis2) ** 2) < 1.05 * np.mean((nee - nee2) ** 2)
+
+
+def test_oracle_nee_transformed_and_box_lights_are_unbiased():
+    """Light sampling of a rotated box, a rotated sphere and a rotated rect (each alone over a diffuse floor, black background):
+    NEE and NEE+MIS converge to the plain estimator's mean.  A wrong area, normal or world-space point would bias the light sample."""
+    from rt_b200 import capi
+    lights = {
+        "box": {"type": "box", "min": [-0.3, -0.2, -0.25], "max": [0.3, 0.2, 0.25], "rotate": {"axis": [0.3, 1, 0.2], "angle": 35}, "translate": [0.2, 0.9, -1.0]},
+        "sphere": {"type": "sphere", "center": [0.05, 0.0, 0.1], "radius": 0.3, "rotate": {"axis": [1, 0.2, 0], "angle": 60}, "translate": [0.1, 0.9, -1.0]},
+        "rect": {"type": "xz_rect", "x0": -0.4, "x1": 0.4, "z0": -0.3, "z1": 0.3, "k": 0.0, "rotate": {"axis": [0, 0.2, 1], "angle": 25}, "translate": [0.0, 1.0, -1.0]},
+    }
+    W, H, spp = 48, 27, 192
+    for name, light in lights.items():
+        d = {"width": W, "height": H, "samples_per_pixel": spp, "max_depth": 6, "background": [0, 0, 0], "sampling": "reference_cpu",
+             "camera": {"lookfrom": [0, 1.2, 2.5], "lookat": [0, 0.3, -1], "vup": [0, 1, 0], "vfov": 50, "aspect_ratio": W / H, "aperture": 0.0, "focus_dist": 3.0},
+             "texture": {"data": [{"type": "solid_color", "color": [0.7, 0.7, 0.7]}, {"type": "solid_color", "color": [6, 5, 4]}]},
+             "material": {"data": [{"type": "lambertian", "texture": 0}, {"type": "diffuse_light", "texture": 1}]},
+             "object": {"data": [{"type": "sphere", "center": [0, -100, -1], "radius": 100, "material": 0},
+                                 {"type": "sphere", "center": [-0.9, 0.3, -1.2], "radius": 0.3, "material": 0}, dict(light, material=1)]}}
+        sc = orc.load_scene(d, width=W, height=H, spp=spp, base_dir=orc.GOLDEN)
+        plain, _, _ = orc.render_ex(sc, seed=11)
+        nee, _, ns = orc.render_ex(sc, seed=12, flags=capi.RT_RENDER_NEE)
+        mis, _, _ = orc.render_ex(sc, seed=13, flags=capi.RT_RENDER_NEE_MIS)
+        assert ns > 0
+        assert abs(nee.mean() - plain.mean()) <= 0.03 * plain.mean(), (name, nee.mean(), plain.mean())
+        assert abs(mis.mean() - plain.mean()) <= 0.03 * plain.mean(), (name, mis.mean(), plain.mean())
 
 
 def _philox4x32_10(ctr, key):
