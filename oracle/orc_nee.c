@@ -19,8 +19,9 @@
 int orc_is_nee_light(const rt_scene_desc *sc, int i) {
     const rt_object_desc *o = &sc->objects[i];
     if (sc->materials[o->material].type != RT_MAT_DIFFUSE_LIGHT) return 0;
-    return o->type == RT_OBJ_SPHERE || o->type == RT_OBJ_XY_RECT || o->type == RT_OBJ_XZ_RECT || o->type == RT_OBJ_YZ_RECT ||
-           o->type == RT_OBJ_CYLINDER || o->type == RT_OBJ_TRIANGLE || o->type == RT_OBJ_BOX;
+    if (!(o->type == RT_OBJ_SPHERE || o->type == RT_OBJ_XY_RECT || o->type == RT_OBJ_XZ_RECT || o->type == RT_OBJ_YZ_RECT ||
+          o->type == RT_OBJ_CYLINDER || o->type == RT_OBJ_TRIANGLE || o->type == RT_OBJ_BOX)) return 0;
+    return orc_light_area(sc, i) > 0.0f;       /* a degenerate emitter has no surface to sample */
 }
 
 float orc_light_area(const rt_scene_desc *sc, int i) {

@@ -294,6 +294,7 @@ static int upload_to_device(rt_ctx *ctx) {
                 const float ex = fabsf(p[3] - p[0]), ey = fabsf(p[4] - p[1]), ez = fabsf(p[5] - p[2]);
                 area = 2.0f * ((ey * ez + ez * ex) + ex * ey);
             } else continue;
+            if (!(area > 0.0f)) continue;                      // a degenerate emitter has no surface to sample (and 1/area in the MIS weight)
             obj_light[i] = (int)ltype.size(); ltype.push_back(o.type); larea.push_back(area);
         }
         const int nl = (int)ltype.size();

@@ -417,6 +417,8 @@ def _nee_scene(extra_lights=True):
                                     "rotate": {"axis": [0.2, 1, 0.1], "angle": 33}, "translate": [-1.2, 1.6, 0.8]})
         d["object"]["data"].append({"type": "xy_rect", "x0": -0.3, "x1": 0.3, "y0": -0.2, "y1": 0.2, "k": 0.1, "material": light,
                                     "rotate": {"axis": [1, 0.3, 0], "angle": -50}, "translate": [1.4, 1.9, 0.2]})
+        # a degenerate emitter (zero area) is left out of the light list: nothing to sample, no 1/area in the MIS weight
+        d["object"]["data"].append({"type": "triangle", "v0": [0.5, 2.0, 0.5], "v1": [0.6, 2.0, 0.5], "v2": [0.7, 2.0, 0.5], "material": light})
     return d
 
 
