@@ -44,7 +44,11 @@ NcclApi &nccl() {
             api.h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
             if (api.h) break;
         }
-        if (!api.h) { api.err = std::string("cannot load libnccl.so.2 (set RT_NCCL_LIB): ") + (dlerror() ? dlerror() : ""); return; }
+        if (!api.h) {
+            const char *why = dlerror();             // (the call clears the message: read it once)
+            api.err = std::string("cannot load libnccl.so.2 (set RT_NCCL_LIB): ") + (why ? why : "");
+            return;
+        }
 #define SYM(field, name) *(void **)(&api.field) = dlsym(api.h, name); if (!api.field) api.err = std::string("libnccl: missing symbol ") + name
         SYM(GetUniqueId, "ncclGetUniqueId"); SYM(CommInitRank, "ncclCommInitRank"); SYM(CommInitAll, "ncclCommInitAll");
         SYM(CommDestroy, "ncclCommDestroy"); SYM(Send, "ncclSend"); SYM(Recv, "ncclRecv"); SYM(GroupStart, "ncclGroupStart");
@@ -207,9 +211,13 @@ extern "C" void rt_group_destroy(rt_group *g) {
     delete g;
 }
 
+static int rt_group_create_impl(rt_group **out, const int *devices, int n_devices);
 extern "C" int rt_group_create(rt_group **out, const int *devices, int n_devices) {
     if (!out) return RT_ERR_INVALID;
     *out = nullptr;
+    return rt_guard(nullptr, "rt_group_create", [&] { return rt_group_create_impl(out, devices, n_devices); });
+}
+static int rt_group_create_impl(rt_group **out, const int *devices, int n_devices) {
     if (!devices || n_devices < 1 || n_devices > 64) return rt_fail(nullptr, RT_ERR_INVALID, "rt_group_create: bad device list");
     rt_group *g = new rt_group();
     for (int i = 0; i < n_devices; ++i) {
@@ -239,9 +247,12 @@ template <class F>
 static int group_each(rt_group *g, const char *what, F &&fn) {
     std::vector<int> rc(g->ctx.size(), 0);
     std::vector<std::thread> th;
-    for (size_t i = 1; i < g->ctx.size(); ++i) th.emplace_back([&, i] { rc[i] = fn(g->ctx[i]); });
-    rc[0] = fn(g->ctx[0]);
+    bool spawned = true;
+    try { for (size_t i = 1; i < g->ctx.size(); ++i) th.emplace_back([&, i] { rc[i] = fn(g->ctx[i]); }); }
+    catch (...) { spawned = false; }              // (std::system_error: no more threads) the ones that started still get joined
+    if (spawned) rc[0] = fn(g->ctx[0]);
     for (auto &t : th) t.join();
+    if (!spawned) return group_fail(g, RT_ERR_INVALID, std::string(what) + ": cannot start a host thread per device");
     for (size_t i = 0; i < rc.size(); ++i)
         if (rc[i]) return group_fail(g, rc[i], std::string(what) + " on device " + std::to_string(g->ctx[i]->device) + ": " + rt_last_error(g->ctx[i]));
     return RT_OK;
