@@ -86,7 +86,7 @@ extern "C" void rt_destroy(rt_ctx *c) {
     c->d_obmin.release(); c->d_obmax.release(); c->d_node_aabb.release(); c->d_leaf_aabb.release(); c->d_bounds.release();
     c->d_hist.release(); c->d_keys[0].release(); c->d_keys[1].release(); c->d_vals[0].release(); c->d_vals[1].release();
     c->d_left.release(); c->d_right.release(); c->d_parent.release(); c->d_flags.release(); c->d_prim_obj.release();
-    c->d_prim_mat.release(); c->d_giant.release(); c->d_lbvh_info.release(); c->d_tile_prefix.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_nodes4.release(); c->d_light_slot.release(); c->d_light_type.release(); c->d_obj_light.release(); c->d_light_area.release();
+    c->d_prim_mat.release(); c->d_slot_mat.release(); c->d_giant.release(); c->d_lbvh_info.release(); c->d_tile_prefix.release(); c->d_nodes.release(); c->d_nodes_s.release(); c->d_nodes4.release(); c->d_light_slot.release(); c->d_light_type.release(); c->d_obj_light.release(); c->d_light_area.release();
     c->d_primA.release(); c->d_primB.release(); c->d_primC.release();
     for (int k = 0; k < RT_MAX_SETS; ++k) { c->qs[k].release(); if (c->qs[k].ev_acc) cudaEventDestroy(c->qs[k].ev_acc); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -261,6 +261,12 @@ static int upload_to_device(rt_ctx *ctx) {
     lb.prim_obj = ctx->d_prim_obj.p; lb.prim_mat = ctx->d_prim_mat.p;
     CU(cudaEventRecord(ctx->ev0, s));
     lbvh_build(ctx->cfg, lb);
+    static const bool no_slot_mat = getenv("RT_NO_SLOT_MAT") != nullptr;
+    if (n > 0 && n <= (1 << 16) && !no_slot_mat) {       // per-slot material records (rt_scene.cuh: DScene::slot_mat)
+        CU(ctx->d_slot_mat.alloc(nn));
+        launch_slot_mats(ctx->cfg, n, ctx->d_prim_mat.p, ctx->d_mats.p, ctx->d_slot_mat.p);
+        ctx->ds.slot_mat = ctx->d_slot_mat.p;
+    } else ctx->ds.slot_mat = nullptr;
     CU(cudaEventRecord(ctx->ev1, s));
     CU(cudaGetLastError());
     int info[RT_LBVH_INFO_WORDS] = {};

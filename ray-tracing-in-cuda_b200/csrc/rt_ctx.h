@@ -65,7 +65,7 @@ struct rt_ctx {
     // LBVH
     LbvhBuffers lb{};
     DevBuf<float> d_obmin, d_obmax, d_node_aabb, d_leaf_aabb; DevBuf<unsigned> d_bounds, d_hist;
-    DevBuf<unsigned long long> d_keys[2]; DevBuf<int> d_vals[2], d_left, d_right, d_parent, d_flags, d_prim_obj, d_prim_mat, d_lbvh_info;
+    DevBuf<unsigned long long> d_keys[2]; DevBuf<int> d_vals[2], d_left, d_right, d_parent, d_flags, d_prim_obj, d_prim_mat, d_lbvh_info; DevBuf<DMaterial> d_slot_mat;
     DevBuf<unsigned char> d_giant;
     int bvh_depth = 0;
     DevBuf<BvhNode> d_nodes; DevBuf<BvhNodeS> d_nodes_s; DevBuf<BvhNode4> d_nodes4; DevBuf<float4> d_primA, d_primB, d_primC;

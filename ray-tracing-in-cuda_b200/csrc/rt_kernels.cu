@@ -486,7 +486,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
             } else {
                 if (COUNT) n_shaded++;
                 const int type = (unsigned)h.y >> 28, slot = h.y & RT_LEAF_SLOT_MASK;
-                const DMaterial m = sc.mats[__ldg(&sc.prim_mat[slot])];
+                const DMaterial m = sc.slot_mat ? sc.slot_mat[slot] : sc.mats[__ldg(&sc.prim_mat[slot])];
                 HitRec rec;
                 hit_record(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
@@ -643,7 +643,7 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK, RT_TAIL_CTAS) k_tail(DScene sc, 
                 rad = thr * background(sc, d);
             } else {
                 const int type = (unsigned)code >> 28, slot = code & RT_LEAF_SLOT_MASK;
-                const DMaterial m = sc.mats[__ldg(&sc.prim_mat[slot])];
+                const DMaterial m = sc.slot_mat ? sc.slot_mat[slot] : sc.mats[__ldg(&sc.prim_mat[slot])];
                 HitRec rec;
                 hit_record(sc, type, slot, o, d, t, m.albedo.w != 0.0f, rec);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {
@@ -748,7 +748,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_primary_only(DScene sc, AccumPlan 
                 if (best_code < 0) rad = background(sc, d);
                 else {
                     const int type = (unsigned)best_code >> 28, slot = best_code & RT_LEAF_SLOT_MASK;
-                    const DMaterial m = sc.mats[__ldg(&sc.prim_mat[slot])];
+                    const DMaterial m = sc.slot_mat ? sc.slot_mat[slot] : sc.mats[__ldg(&sc.prim_mat[slot])];
                     HitRec rec;
                     hit_record(sc, type, slot, o, d, best_t, m.albedo.w != 0.0f, rec);
                     rad = m.type == RT_MAT_DIFFUSE_LIGHT ? material_color(sc, m, rec.u, rec.v, rec.p) : v3(0, 0, 0);
@@ -1025,6 +1025,17 @@ __global__ void k_light_slots(int n, const int *__restrict__ prim_obj, const int
     if (j >= n) return;
     const int k = obj_light[prim_obj[j]];
     if (k >= 0) light_slot[k] = j;
+}
+
+// material record per leaf slot (small scenes): shade reads it with one load instead of prim_mat[slot] -> mats[...]
+__global__ void k_slot_mats(int n, const int *__restrict__ prim_mat, const DMaterial *__restrict__ mats, DMaterial *slot_mat) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) slot_mat[j] = mats[prim_mat[j]];
+}
+void launch_slot_mats(const LaunchCfg &c, int n, const int *prim_mat, const DMaterial *mats, DMaterial *slot_mat) {
+    if (n <= 0) return;
+    k_slot_mats<<<(n + 255) / 256, 256, 0, c.stream>>>(n, prim_mat, mats, slot_mat);
+    bump(c);
 }
 
 void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const int *obj_light, int *light_slot) {

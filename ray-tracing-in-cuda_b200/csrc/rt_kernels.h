@@ -20,6 +20,7 @@ void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigne
                   bool last_bounce, bool count, bool sort, bool nee);
 void launch_tail(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigned seed, int spp_begin, int b0, int buf);
 void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const int *obj_light, int *light_slot);
+void launch_slot_mats(const LaunchCfg &c, int n, const int *prim_mat, const DMaterial *mats, DMaterial *slot_mat);
 void launch_shadow(const LaunchCfg &c, const DScene &sc, const Queues &q, int bounce);
 #define RT_ACC_CHUNKS 8            // sample chunks of the fixed-order accumulation (rt.h: rt_sample_chunk)
 struct ChunkPtrs { const float *p[RT_ACC_CHUNKS]; };

@@ -78,6 +78,7 @@ struct DScene {
     const int *obj_light;                  // object index -> light index or -1
     // primary-ray candidate lists (rt_kernels.cu:k_tile_lists): per 8x4 pixel tile the leaves its camera beam can touch
     int only_type;                         // RT_OBJ_* when every primitive has that type (k_extend specialisation), else -1
+    const DMaterial *slot_mat;             // material record per leaf slot (scenes of <= 65 536 leaves; else nullptr): one load instead of prim_mat -> mats
     int tile_mode;                         // 0: none, 1: every path of a pass is covered, 2: covered where tile_cnt >= 0
     const int *tile_list, *tile_cnt;       // [n_tiles * RT_TILE_K] leaf codes, [n_tiles] count or -1 (too many: fix-up pass)
     const int *tile_empty_prefix;          // [n_tiles + 1] number of tiles with count 0 before tile t (their paths skip the queues), or null
