@@ -487,6 +487,10 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                 if (COUNT) n_shaded++;
                 const int type = (unsigned)h.y >> 28, slot = h.y & RT_LEAF_SLOT_MASK;
                 const DMaterial m = sc.slot_mat ? sc.slot_mat[slot] : sc.mats[__ldg(&sc.prim_mat[slot])];
+                // the scatter draw does not depend on the material: Philox and the direct sampler run while the record above is in flight
+                Rng rng; rng.init(seed, (unsigned)__float_as_int(d4.w), (unsigned)(spp_begin + __float_as_int(t4.w)), (unsigned)bounce + 1u, sc.sampling);
+                BallDraw ahead;
+                if (DIRECT) { rng.prime(); ahead = ball_direct_ahead(rng); }
                 HitRec rec;
                 hit_record(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
@@ -494,9 +498,8 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                     if (lk < 0) rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
                     else if (sc.nee_mis) rad = thr * (mis_hit_weight(sc, lk, d, __int_as_float(h.x), rec.n) * material_color(sc, m, rec.u, rec.v, rec.p));
                 } else {
-                    Rng rng; rng.init(seed, (unsigned)__float_as_int(d4.w), (unsigned)(spp_begin + __float_as_int(t4.w)), (unsigned)bounce + 1u, sc.sampling);
                     float3 att, sd;
-                    const bool ok = scatter<DIRECT>(sc, m, d, rec, rng, att, sd);
+                    const bool ok = scatter<DIRECT>(sc, m, d, rec, rng, att, sd, DIRECT ? &ahead : nullptr);
                     if (ok && !last_bounce) {
                         alive = true;
                         no = rec.p; nd = sd; nthr = thr * att;
@@ -644,14 +647,16 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK, RT_TAIL_CTAS) k_tail(DScene sc, 
             } else {
                 const int type = (unsigned)code >> 28, slot = code & RT_LEAF_SLOT_MASK;
                 const DMaterial m = sc.slot_mat ? sc.slot_mat[slot] : sc.mats[__ldg(&sc.prim_mat[slot])];
+                Rng rng; rng.init(seed, (unsigned)__float_as_int(key_pixel), (unsigned)(spp_begin + __float_as_int(key_sample)), (unsigned)state + 1u, sc.sampling);
+                BallDraw ahead;
+                if (DIRECT) { rng.prime(); ahead = ball_direct_ahead(rng); }      // (as in k_shade: under the latency of the material record)
                 HitRec rec;
                 hit_record(sc, type, slot, o, d, t, m.albedo.w != 0.0f, rec);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {
                     rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
                 } else {
-                    Rng rng; rng.init(seed, (unsigned)__float_as_int(key_pixel), (unsigned)(spp_begin + __float_as_int(key_sample)), (unsigned)state + 1u, sc.sampling);
                     float3 att, sd;
-                    const bool ok = scatter<DIRECT>(sc, m, d, rec, rng, att, sd);
+                    const bool ok = scatter<DIRECT>(sc, m, d, rec, rng, att, sd, DIRECT ? &ahead : nullptr);
                     if (ok && state != sc.max_depth - 1) { alive = true; o = rec.p; d = sd; thr = thr * att; }
                 }
             }

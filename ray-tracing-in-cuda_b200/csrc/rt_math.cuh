@@ -124,5 +124,11 @@ struct Rng {
         return (float)((x >> 8) + inc) * 5.9604644775390625e-08f;
     }
     // block-wise access for samplers that consume whole blocks (rt_shade.cuh:random_in_unit_sphere)
-    __device__ __forceinline__ uint4 next_block() { uint4 r = philox4x32_10(make_uint4(sample, bounce, block, 0x5254u), key); ++block; return r; }
+    __device__ __forceinline__ uint4 next_block() {
+        if (idx == 0) { idx = 4; return out; }            // the block prime() drew ahead of its use (idx == 0 occurs in no other state)
+        uint4 r = philox4x32_10(make_uint4(sample, bounce, block, 0x5254u), key); ++block; return r;
+    }
+    // Draws block 0 NOW (same values, same order of use): the shade stage calls it before the material record has arrived, so the ten
+    // Philox rounds run under the latency of that load instead of after it.
+    __device__ __forceinline__ void prime() { out = philox4x32_10(make_uint4(sample, bounce, 0u, 0x5254u), key); block = 1; idx = 0; }
 };

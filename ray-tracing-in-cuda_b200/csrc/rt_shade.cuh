@@ -134,16 +134,27 @@ __device__ __forceinline__ float3 reflect3(float3 v, float3 n) {   // vec3.cuh:1
 
 // material::scatter for the four material classes (material.cuh:37-52, 63-70, 130-158, 169-173).
 // Returns false when the path ends here.  att: attenuation; sd: scattered direction (origin is rec.p).
+// The direct sampler's unit vector and radius of a primed generator (Rng::prime), computed AHEAD of the material record: scatter() takes
+// them instead of drawing (the block is the one ball_direct would have consumed, so the values are the same).
+struct BallDraw { float3 unit; float rad; };
+__device__ __forceinline__ BallDraw ball_direct_ahead(const Rng &rng) {
+    const uint4 B = rng.out;
+    BallDraw b;
+    ball_direct_k(B.x >> 8, B.y >> 8, B.z >> 8, B.w >> 8, (B.x & 0xffu) | ((B.y & 0xffu) << 8) | ((B.z & 0xffu) << 16), b.unit, b.rad);
+    return b;
+}
+
 template <bool DIRECT, class R>
 __device__ __forceinline__ bool scatter(const DScene &sc, const DMaterial &m, float3 rd, const HitRec &rec, R &rng,
-                                        float3 &att, float3 &sd) {
+                                        float3 &att, float3 &sd, const BallDraw *ahead = nullptr) {
     // lambertian and metal draw the same random_in_unit_sphere(): one shared (convergent) rejection loop for both classes,
     // then the short class-specific tails — a warp holding a mix of the two pays for the expensive part once
     float3 r = v3(0, 0, 0);
     if (m.type == RT_MAT_LAMBERTIAN || m.type == RT_MAT_METAL) {
         if (DIRECT) {
             float rad;
-            ball_direct(rng, r, rad);
+            if (ahead) { r = ahead->unit; rad = ahead->rad; }
+            else ball_direct(rng, r, rad);
             if (sc.sampling == RT_SAMPLING_REFERENCE_GPU) r = rad * v3(fabsf(r.x), fabsf(r.y), fabsf(r.z));     // octant ball for both classes
             else if (m.type == RT_MAT_METAL) r = rad * r;                                                        // ball | unit vector
         } else r = random_in_unit_sphere(rng, sc.sampling);
