@@ -481,18 +481,22 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
             const bool prev_nee = NEE && (path_id & 0x40000000) != 0;
             if (NEE) path_id &= 0x3fffffff;
             float3 rad = v3(0, 0, 0);
-            if (h.y < 0) {
+            // The chunk is bound by the latency of its own dependent chain, so everything that does not need the
+            // slot's records runs UNDER their loads: the three loads go out first (a miss reads slot 0: one cached line, no branch in
+            // front of the loads), then the miss lanes' background, then Philox + the direct sampler of the hit lanes.
+            const bool hit = h.y >= 0;
+            const int type = hit ? (int)((unsigned)h.y >> 28) : 0, slot = hit ? (h.y & RT_LEAF_SLOT_MASK) : 0;
+            const float4 pA = __ldg(&sc.primA[slot]), pB = __ldg(&sc.primB[slot]);
+            const DMaterial m = sc.slot_mat ? sc.slot_mat[slot] : sc.mats[hit ? __ldg(&sc.prim_mat[slot]) : 0];     // (an empty scene has no slot 0 material index)
+            if (!hit) {
                 rad = thr * background(sc, d);
             } else {
                 if (COUNT) n_shaded++;
-                const int type = (unsigned)h.y >> 28, slot = h.y & RT_LEAF_SLOT_MASK;
-                const DMaterial m = sc.slot_mat ? sc.slot_mat[slot] : sc.mats[__ldg(&sc.prim_mat[slot])];
-                // the scatter draw does not depend on the material: Philox and the direct sampler run while the record above is in flight
                 Rng rng; rng.init(seed, (unsigned)__float_as_int(d4.w), (unsigned)(spp_begin + __float_as_int(t4.w)), (unsigned)bounce + 1u, sc.sampling);
                 BallDraw ahead;
                 if (DIRECT) { rng.prime(); ahead = ball_direct_ahead(rng); }
                 HitRec rec;
-                hit_record(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec);
+                hit_record(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec, pA, pB);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
                     const int lk = prev_nee ? sc.obj_light[__ldg(&sc.prim_obj[slot])] : -1;
                     if (lk < 0) rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
@@ -646,12 +650,13 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK, RT_TAIL_CTAS) k_tail(DScene sc, 
                 rad = thr * background(sc, d);
             } else {
                 const int type = (unsigned)code >> 28, slot = code & RT_LEAF_SLOT_MASK;
+                const float4 pA = __ldg(&sc.primA[slot]), pB = __ldg(&sc.primB[slot]);
                 const DMaterial m = sc.slot_mat ? sc.slot_mat[slot] : sc.mats[__ldg(&sc.prim_mat[slot])];
                 Rng rng; rng.init(seed, (unsigned)__float_as_int(key_pixel), (unsigned)(spp_begin + __float_as_int(key_sample)), (unsigned)state + 1u, sc.sampling);
                 BallDraw ahead;
-                if (DIRECT) { rng.prime(); ahead = ball_direct_ahead(rng); }      // (as in k_shade: under the latency of the material record)
+                if (DIRECT) { rng.prime(); ahead = ball_direct_ahead(rng); }      // (as in k_shade: under the latency of the slot's records)
                 HitRec rec;
-                hit_record(sc, type, slot, o, d, t, m.albedo.w != 0.0f, rec);
+                hit_record(sc, type, slot, o, d, t, m.albedo.w != 0.0f, rec, pA, pB);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {
                     rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
                 } else {

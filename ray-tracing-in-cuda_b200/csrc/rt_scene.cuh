@@ -278,12 +278,13 @@ __device__ __forceinline__ void set_face_normal(HitRec &r, float3 d, float3 outw
 
 // Rebuild the full hit record of the reference (p, normal, front_face, u, v) from (t, slot) — shade stage.
 // want_uv: sphere/cylinder uv cost an acos/atan2; only image textures read them.
-__device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot, float3 o, float3 d, float t, bool want_uv, HitRec &r) {
-    const float4 A = __ldg(&sc.primA[slot]);
+// A, B: the slot's primA / primB records, loaded by the caller (the shade stage issues these loads before anything else it does)
+__device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot, float3 o, float3 d, float t, bool want_uv, HitRec &r,
+                                           const float4 A, const float4 B) {
     r.t = t; r.u = 0.0f; r.v = 0.0f;
     switch (type) {
     case RT_OBJ_SPHERE: {   // object.cuh:68-72,87-93
-        const int xi = __float_as_int(__ldg(&sc.primB[slot]).w);
+        const int xi = __float_as_int(B.w);
         float3 n;
         if (xi < 0) {
             r.p = vfma(t, d, o);
@@ -304,7 +305,7 @@ __device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot,
         break;
     }
     case RT_OBJ_XY_RECT: case RT_OBJ_XZ_RECT: case RT_OBJ_YZ_RECT: {   // object.cuh:113-121
-        const int xi = __float_as_int(__ldg(&sc.primB[slot]).w);
+        const int xi = __float_as_int(B.w);
         const float4 *xf = sc.xforms + 6 * (xi >= 0 ? xi : 0);
         float3 oo = o, od = d;
         if (xi >= 0) { oo = xf_point(xf + 3, o); od = xf_vec(xf + 3, d); }
@@ -338,7 +339,6 @@ __device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot,
         break;
     }
     case RT_OBJ_BOX: {
-        const float4 B = __ldg(&sc.primB[slot]);
         const int xi = __float_as_int(A.w);
         const float4 *xf = sc.xforms + 6 * (xi >= 0 ? xi : 0);
         float3 oo = o, od = d;
@@ -357,13 +357,13 @@ __device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot,
         break;
     }
     default: {   // RT_OBJ_TRIANGLE
-        float3 v0 = f4xyz(A), e1 = f4xyz(__ldg(&sc.primB[slot])), e2 = f4xyz(__ldg(&sc.primC[slot]));
+        float3 v0 = f4xyz(A), e1 = f4xyz(B), e2 = f4xyz(__ldg(&sc.primC[slot]));
         float tt, bu = 0.0f, bv = 0.0f;
         triangle_t(v0, e1, e2, o, d, t, t, tt, bu, bv);
         float3 n = v3(__fmaf_rn(e1.y, e2.z, -(e1.z * e2.y)), __fmaf_rn(e1.z, e2.x, -(e1.x * e2.z)), __fmaf_rn(e1.x, e2.y, -(e1.y * e2.x)));
         if (want_uv) {      // per-vertex texture coordinates (OBJ `vt`), 16-bit unorm pairs in the w components; without `vt` the
                             // vertices carry (0,0), (1,0), (0,1) and the sums below give (bu, bv)
-            const unsigned q0 = __float_as_uint(A.w), q1 = __float_as_uint(__ldg(&sc.primB[slot]).w), q2 = __float_as_uint(__ldg(&sc.primC[slot]).w);
+            const unsigned q0 = __float_as_uint(A.w), q1 = __float_as_uint(B.w), q2 = __float_as_uint(__ldg(&sc.primC[slot]).w);
             const float w0 = (1.0f - bu) - bv;
             r.u = __fmaf_rn(bv, (float)(q2 & 0xffffu) / 65535.0f, __fmaf_rn(bu, (float)(q1 & 0xffffu) / 65535.0f, w0 * ((float)(q0 & 0xffffu) / 65535.0f)));
             r.v = __fmaf_rn(bv, (float)(q2 >> 16) / 65535.0f, __fmaf_rn(bu, (float)(q1 >> 16) / 65535.0f, w0 * ((float)(q0 >> 16) / 65535.0f)));
@@ -373,4 +373,7 @@ __device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot,
         break;
     }
     }
+}
+__device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot, float3 o, float3 d, float t, bool want_uv, HitRec &r) {
+    hit_record(sc, type, slot, o, d, t, want_uv, r, __ldg(&sc.primA[slot]), __ldg(&sc.primB[slot]));
 }
