@@ -387,7 +387,7 @@ __device__ __forceinline__ void shade_issue_loads(ShadeSmem &sm, const DScene &s
     tma_load_1d(sm.in_hit[stage], q.hits + first, b8, &sm.full[stage]);
 }
 
-template <bool COUNT, bool NEE, bool CAM, bool DIRECT>
+template <bool COUNT, bool NEE, bool CAM, bool DIRECT, int ONLY = -1>
 __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene sc, Queues q, unsigned seed, int spp_begin, int bounce, int buf,
                                                          int last_bounce, int sort) {
     extern __shared__ __align__(128) unsigned char s_shade_raw[];
@@ -496,7 +496,7 @@ __global__ void __launch_bounds__(RT_SH_CHUNK, RT_SH_CTAS_PER_SM) k_shade(DScene
                 BallDraw ahead;
                 if (DIRECT) { rng.prime(); ahead = ball_direct_ahead(rng); }
                 HitRec rec;
-                hit_record(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec, pA, pB);
+                hit_record<ONLY>(sc, type, slot, o, d, __int_as_float(h.x), m.albedo.w != 0.0f, rec, pA, pB);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {     // emitted(), material.cuh:175-178; scatter() == false
                     const int lk = prev_nee ? sc.obj_light[__ldg(&sc.prim_obj[slot])] : -1;
                     if (lk < 0) rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
@@ -656,7 +656,7 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK, RT_TAIL_CTAS) k_tail(DScene sc, 
                 BallDraw ahead;
                 if (DIRECT) { rng.prime(); ahead = ball_direct_ahead(rng); }      // (as in k_shade: under the latency of the slot's records)
                 HitRec rec;
-                hit_record(sc, type, slot, o, d, t, m.albedo.w != 0.0f, rec, pA, pB);
+                hit_record<ONLY>(sc, type, slot, o, d, t, m.albedo.w != 0.0f, rec, pA, pB);
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {
                     rad = thr * material_color(sc, m, rec.u, rec.v, rec.p);
                 } else {
@@ -1001,6 +1001,8 @@ cudaError_t kernels_configure_device(int dev, size_t smem_optin) {
         SET((k_shade<false, false, true, D_>), sizeof(ShadeSmem)); SET((k_shade<true, false, true, D_>), sizeof(ShadeSmem)); \
         SET((k_shade<false, true, true, D_>), sizeof(ShadeSmem)); SET((k_shade<true, true, true, D_>), sizeof(ShadeSmem));
         SET_SH(false) SET_SH(true)
+        SET((k_shade<false, false, false, false, RT_OBJ_SPHERE>), sizeof(ShadeSmem)); SET((k_shade<false, false, true, false, RT_OBJ_SPHERE>), sizeof(ShadeSmem));
+        SET((k_shade<false, false, false, true, RT_OBJ_SPHERE>), sizeof(ShadeSmem)); SET((k_shade<false, false, true, true, RT_OBJ_SPHERE>), sizeof(ShadeSmem));
 #undef SET_SH
 #undef SET
         g_smem_err[dev] = e;
@@ -1022,7 +1024,12 @@ void launch_shade(const LaunchCfg &c, const DScene &sc, const Queues &q, unsigne
 #define RT_SHADE_ARGS <<<grid, RT_SH_CHUNK, sizeof(ShadeSmem), c.stream>>>(sc, q, seed, spp_begin, bounce, buf, last_bounce, sort)
 #define RT_SHADE_CAM(C_, N_) { if (sc.direct) { if (bounce == 0) k_shade<C_, N_, true, true> RT_SHADE_ARGS; else k_shade<C_, N_, false, true> RT_SHADE_ARGS; } \
                               else { if (bounce == 0) k_shade<C_, N_, true, false> RT_SHADE_ARGS; else k_shade<C_, N_, false, false> RT_SHADE_ARGS; } }
-    if (count) { if (nee) RT_SHADE_CAM(true, true) else RT_SHADE_CAM(true, false) }
+    // all-sphere scenes (no instance transforms): the instance without the other primitives' hit-record code (fewer registers live)
+    if (!count && !nee && sc.only_type == RT_OBJ_SPHERE) {
+        if (sc.direct) { if (bounce == 0) k_shade<false, false, true, true, RT_OBJ_SPHERE> RT_SHADE_ARGS; else k_shade<false, false, false, true, RT_OBJ_SPHERE> RT_SHADE_ARGS; }
+        else { if (bounce == 0) k_shade<false, false, true, false, RT_OBJ_SPHERE> RT_SHADE_ARGS; else k_shade<false, false, false, false, RT_OBJ_SPHERE> RT_SHADE_ARGS; }
+    }
+    else if (count) { if (nee) RT_SHADE_CAM(true, true) else RT_SHADE_CAM(true, false) }
     else { if (nee) RT_SHADE_CAM(false, true) else RT_SHADE_CAM(false, false) }
 #undef RT_SHADE_CAM
 #undef RT_SHADE_ARGS

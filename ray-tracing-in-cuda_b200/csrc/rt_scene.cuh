@@ -279,12 +279,16 @@ __device__ __forceinline__ void set_face_normal(HitRec &r, float3 d, float3 outw
 // Rebuild the full hit record of the reference (p, normal, front_face, u, v) from (t, slot) — shade stage.
 // want_uv: sphere/cylinder uv cost an acos/atan2; only image textures read them.
 // A, B: the slot's primA / primB records, loaded by the caller (the shade stage issues these loads before anything else it does)
+// ONLY = RT_OBJ_SPHERE: every primitive of the scene is a sphere without an instance transform (DScene::only_type) — the other cases are
+// not compiled into the caller, which is what lets the shade kernel of such scenes live in fewer registers.
+template <int ONLY = -1>
 __device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot, float3 o, float3 d, float t, bool want_uv, HitRec &r,
                                            const float4 A, const float4 B) {
     r.t = t; r.u = 0.0f; r.v = 0.0f;
+    if (ONLY == RT_OBJ_SPHERE) type = RT_OBJ_SPHERE;
     switch (type) {
     case RT_OBJ_SPHERE: {   // object.cuh:68-72,87-93
-        const int xi = __float_as_int(B.w);
+        const int xi = ONLY == RT_OBJ_SPHERE ? -1 : __float_as_int(B.w);
         float3 n;
         if (xi < 0) {
             r.p = vfma(t, d, o);
