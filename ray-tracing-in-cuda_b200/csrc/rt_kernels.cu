@@ -59,7 +59,7 @@ __global__ void k_pass_init(Queues q, int max_depth, int n_queue0) {
 // to the ray: the bounce-0 extend launch disappears.  Paths it cannot cover (margin pixels outside the 8x4 tiling, tiles
 // with more than RT_TILE_K candidates) get the RT_HIT_TODO mark and are traversed by a fix-up extend launch.
 #define RT_HIT_TODO ((int)0x80000001)
-template <bool HITS, bool COUNT, bool DIRECT>
+template <bool HITS, bool COUNT, bool DIRECT, int ONLY = -1>      // ONLY = RT_OBJ_SPHERE: all-sphere scene, candidate tests without the type dispatch
 __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsigned seed, int spp_begin, int n_paths, int zero_radiance) {
     // one thread per (tile-ordered) pixel slot and group of samples: the pixel arithmetic is done once, the sample planes are
     // written with stride n_pixels (each plane coalesced across the warp).  The grid covers every pixel slot in x.
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(RT_BLOCK) k_generate(DScene sc, Queues q, unsi
             if (n_cand >= 0) {
                 best_code = -1;
                 const float a = dot3(d, d), inv_a = 1.0f / a;
-                for (int c = 0; c < n_cand; ++c) leaf_visit<COUNT>(sc, __ldg(&cand[c]), o, d, a, inv_a, 0.001f, best_t, best_code, cnt);
+                for (int c = 0; c < n_cand; ++c) leaf_visit<COUNT, ONLY>(sc, __ldg(&cand[c]), o, d, a, inv_a, 0.001f, best_t, best_code, cnt);
             }
             q.hits[i] = make_int2(__float_as_int(best_t), best_code);
         }
@@ -919,10 +919,12 @@ void launch_generate(const LaunchCfg &c, const DScene &sc, const Queues &q, unsi
     if (sc.direct) {
         if (!hits) k_generate<false, false, true> RT_GEN_ARGS;
         else if (count) k_generate<true, true, true> RT_GEN_ARGS;
+        else if (sc.only_type == RT_OBJ_SPHERE) k_generate<true, false, true, RT_OBJ_SPHERE> RT_GEN_ARGS;
         else k_generate<true, false, true> RT_GEN_ARGS;
     } else {
         if (!hits) k_generate<false, false, false> RT_GEN_ARGS;
         else if (count) k_generate<true, true, false> RT_GEN_ARGS;
+        else if (sc.only_type == RT_OBJ_SPHERE) k_generate<true, false, false, RT_OBJ_SPHERE> RT_GEN_ARGS;
         else k_generate<true, false, false> RT_GEN_ARGS;
     }
 #undef RT_GEN_ARGS
