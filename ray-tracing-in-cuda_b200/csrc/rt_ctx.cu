@@ -350,6 +350,8 @@ static int upload_to_device(rt_ctx *ctx) {
         CU(cudaStreamSynchronize(s));
         ds.nodes4 = ctx->d_nodes4.p;
     }
+    ds.sphere_xf = 0;
+    for (int i = 0; i < d.n_objects; ++i) if (hs.objects[i].type == RT_OBJ_SPHERE && hs.objects[i].xform >= 0) { ds.sphere_xf = 1; break; }
     ds.only_type = d.n_objects > 0 ? hs.objects[0].type : -1;
     for (int i = 0; i < d.n_objects; ++i)       // the specialised sphere loop carries no instance transforms
         if (hs.objects[i].type != ds.only_type || (ds.only_type == RT_OBJ_SPHERE && hs.objects[i].xform >= 0)) { ds.only_type = -1; break; }

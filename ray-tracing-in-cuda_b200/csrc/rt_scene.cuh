@@ -77,6 +77,7 @@ struct DScene {
     const float *light_area;               // light -> surface area
     const int *obj_light;                  // object index -> light index or -1
     // primary-ray candidate lists (rt_kernels.cu:k_tile_lists): per 8x4 pixel tile the leaves its camera beam can touch
+    int sphere_xf;                         // 1: some sphere carries an instance transform (else the sphere tests skip the primB.w flag load: a uniform branch)
     int only_type;                         // RT_OBJ_* when every primitive has that type (k_extend specialisation), else -1
     const DMaterial *slot_mat;             // material record per leaf slot (scenes of <= 65 536 leaves; else nullptr): one load instead of prim_mat -> mats
     int tile_mode;                         // 0: none, 1: every path of a pass is covered, 2: covered where tile_cnt >= 0
@@ -237,7 +238,7 @@ __device__ __forceinline__ bool leaf_t(const DScene &sc, int code, float3 o, flo
     case RT_OBJ_SPHERE: {
         // rotate / translate instance (vec3.cuh:303-427 applied as object.cuh:225-231 does for the cylinder): the ray goes to
         // object space, t is unchanged (rigid transform, direction not normalised)
-        const int xi = __float_as_int(__ldg(&sc.primB[slot]).w);
+        const int xi = sc.sphere_xf ? __float_as_int(__ldg(&sc.primB[slot]).w) : -1;
         if (xi < 0) return sphere_t(A, o, d, a, inv_a, tmin, tmax, t);
         const float4 *xf = sc.xforms + 6 * xi;
         const float3 od = xf_vec(xf + 3, d);
@@ -288,7 +289,7 @@ __device__ __forceinline__ void hit_record(const DScene &sc, int type, int slot,
     if (ONLY == RT_OBJ_SPHERE) type = RT_OBJ_SPHERE;
     switch (type) {
     case RT_OBJ_SPHERE: {   // object.cuh:68-72,87-93
-        const int xi = ONLY == RT_OBJ_SPHERE ? -1 : __float_as_int(B.w);
+        const int xi = (ONLY == RT_OBJ_SPHERE || !sc.sphere_xf) ? -1 : __float_as_int(B.w);
         float3 n;
         if (xi < 0) {
             r.p = vfma(t, d, o);
