@@ -655,7 +655,9 @@ static int rt_render_impl(rt_ctx *ctx, const rt_render_params *prm) {
     // 8 (RTIOW: 3.5 % of the paths are still alive there); RT_TAIL_BOUNCE overrides, 0 or RT_RENDER_NO_TAIL switches it off.  Not with
     // NEE (the shadow stage needs the queues) or COUNT_EVENTS (the counters belong to the extend stage).
     static const int env_tail = getenv("RT_TAIL_BOUNCE") ? atoi(getenv("RT_TAIL_BOUNCE")) : -1;
-    int tail_b0 = env_tail >= 0 ? env_tail : 8;
+    // all-sphere scenes run the lean instances of k_tail (rt_kernels.cu), for which an early hand-over pays: RTIOW 128-spp pass 43.28 /
+    // 43.42 / 43.62 / 43.99 ms from bounce 2 / 3 / 4 / 8; with the generic instances 8 is best (blue2 47.5 / 44.3 / 42.1 / 40.6)
+    int tail_b0 = env_tail >= 0 ? env_tail : ((ds.only_type == RT_OBJ_SPHERE && ctx->cfg.bvh_smem_bytes) ? 2 : 8);
     if (nee || count || (prm->flags & RT_RENDER_NO_TAIL) || tail_b0 <= 0 || tail_b0 >= ds.max_depth) tail_b0 = -1;
     cudaEvent_t *evs = ctx->ev_count;       // COUNT_EVENTS: one synchronising event pair per stage launch (owned by the context)
     if (time_stages) {          // event pairs are recorded without synchronising and resolved in rt_download
