@@ -489,6 +489,13 @@ def main():
             tj = json.load(open(tpath))
             traffic = tj["k_extend_dram_bytes_per_ray"] * ext_rays / n_ext_launches
             traffic_note = "; traffic = %.1f B/ray (ncu, profiles/traffic.json) x mean rays per extend launch, bytes" % tj["k_extend_dram_bytes_per_ray"]
+        # the tail stage (closest hit + shade of every bounce from the hand-over bounce on, one launch per pass): its rays are the ones
+        # neither generate nor an extend launch of the default schedule traced; numerator = their share of the counted run's
+        # algorithmic FLOPs (a per-ray average over all bounces: late bounces walk longer, so this understates the tail slightly)
+        tail_rays = max(0.0, rays_rank - (samples_rank if bounce0_in_generate else 0.0) - float(sg.get("rays_extend", 0)))
+        tail_flops = ext_flops * (tail_rays / ext_rays if ext_rays > 0 else 0.0) + shade_flops * (tail_rays / rays_rank if rays_rank > 0 else 0.0)
+        tail_ach = tail_flops / (ms_tail * 1e-3) / 1e12 if ms_tail > 0 else 0.0
+        stages = {"generate": sg["ms_generate"], "extend": sg["ms_extend"], "shade": sg["ms_shade"], "tail": ms_tail, "accumulate": sg["ms_accumulate"]}
         line = {
             "metric": "samples_per_second", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -506,6 +513,11 @@ def main():
                          "frac": ach / fp32_peak if fp32_peak else None, "traffic": traffic,
                          "note": "algorithmic FLOPs (SURVEY §8(d) model, device event counters of the extend stage only) / CUDA-event time of the extend launches "
                                  "of one queue-schedule step (RT_RENDER_NO_TAIL) run right after the timed region; peak = FP32 FMA-chain microbenchmark measured in this run (of measured)" + traffic_note},
+            "roofline_tail": {"bound": "fp32", "kernel": "k_tail", "achieved": tail_ach, "peak": fp32_peak, "unit": "TFLOP/s",
+                              "frac": tail_ach / fp32_peak if fp32_peak else None, "rays_share": tail_rays / rays_rank if rays_rank > 0 else 0.0,
+                              "note": "closest hit + shade of every bounce from the hand-over bounce on, one launch per pass: the share of the counted run's extend + shade "
+                                      "FLOPs that belongs to the rays this stage traced / its CUDA-event time in the default schedule"},
+            "largest_stage": max(stages, key=stages.get),
             "roofline_hbm": {"bound": "hbm", "kernel": "generate+shade+accumulate", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s",
                              "frac": hbm_ach / hbm_peak, "note": ("104 B/ray (+ 8 B/sample when generate writes the bounce-0 hit records; DESIGN.md §6) / CUDA-event time of those stages; peak from MEASURED_PEAKS.json (of measured)" if peaks else "of fallback")},
             "e2e": {"value": total_samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,

@@ -174,7 +174,7 @@ typedef struct rt_stats {
     float ms_tail;                  /* tail stage (one launch finishes the paths alive at the tail bounce), TIME_STAGES */
     float reserved;
     int64_t launches_extend;        /* extend-stage launches among `launches` (mean rays per extend launch for the roofline's traffic figure) */
-    int64_t rays_extend;            /* reserved (0) */
+    int64_t rays_extend;            /* rays that went through an extend launch (bounce 0 from the tile lists and the tail stage's rays are not among them) */
 } rt_stats;
 
 typedef struct rt_scene_info {

@@ -548,7 +548,7 @@ static int ensure_queues(rt_ctx *ctx, QueueSet &S, long long cap, int max_depth,
     CU(S.radiance.alloc(cap)); CU(S.hits.alloc(cap + 2));   // +2: the TMA copy of an odd-sized tail rounds up to 16 B
     CU(S.qcount.alloc(max_depth + 2)); CU(S.workctr.alloc((size_t)max_depth * 2));
     CU(ctx->d_counters.alloc(CTR_COUNT));
-    if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(2)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 2 * sizeof(unsigned long long), ctx->stream)); }
+    if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(3)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 3 * sizeof(unsigned long long), ctx->stream)); }
     S.cap = std::max(S.cap, cap);
     Queues &q = S.q;
     for (int k = 0; k < 2; ++k) { q.ray_o[k] = S.ray_o[k].p; q.ray_d[k] = S.ray_d[k].p; q.thr[k] = S.thr[k].p; }
@@ -701,7 +701,7 @@ static int rt_render_impl(rt_ctx *ctx, const rt_render_params *prm) {
             plan.buf[plan.n] = ctx->d_chunk[pc.chunk].p; plan.clear[plan.n] = 1;
             ++plan.n;
         }
-        if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(2)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 2 * sizeof(unsigned long long), s)); }
+        if (!ctx->d_rays.p) { CU(ctx->d_rays.alloc(3)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 3 * sizeof(unsigned long long), s)); }
         timed(0, [&] { launch_primary_only(ctx->cfg, ds, plan, prm->seed, prm->spp_begin, spp, ctx->d_rays.p); });
         if (ds.tile_empty_prefix) ctx->stats.paths_skipped += (long long)ctx->tiles_n_empty * 32 * spp;
         ++passes;
@@ -746,7 +746,8 @@ static int rt_render_impl(rt_ctx *ctx, const rt_render_params *prm) {
             // samples are added to a chunk buffer in ascending order whatever the stream: pass p's accumulate follows pass p-1's
             if (n_sets > 1 && passes > 0) CU(cudaStreamWaitEvent(cfg.stream, ctx->qs[last_set].ev_acc, 0));
             const int *const_tiles = (dsp.tile_empty_prefix && ds.bg_mode != RT_BG_SKY_GRADIENT) ? dsp.tile_cnt : nullptr;
-            timed(3, [&] { launch_accumulate(cfg, S.q, plan, ds.width, ds.height, sn, ds.max_depth, ctx->d_rays.p, const_tiles, ds.background); });
+            timed(3, [&] { launch_accumulate(cfg, S.q, plan, ds.width, ds.height, sn, ds.max_depth, ctx->d_rays.p, const_tiles, ds.background,
+                                             (tile_mode == 0 ? 0 : 1), (tail_b0 > 0 && !no_paths) ? tail_b0 : ds.max_depth); });
             if (n_sets > 1) CU(cudaEventRecord(S.ev_acc, cfg.stream));
             last_set = k;
             ++passes;
@@ -857,7 +858,7 @@ extern "C" int rt_stats_reset(rt_ctx *ctx) {
     ctx->stats.ms_build = ms_build;
     ctx->launches = 0;
     ctx->pending.clear();
-    if (ctx->d_rays.p) { CU(cudaSetDevice(ctx->device)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 2 * sizeof(unsigned long long), ctx->stream)); }
+    if (ctx->d_rays.p) { CU(cudaSetDevice(ctx->device)); CU(cudaMemsetAsync(ctx->d_rays.p, 0, 3 * sizeof(unsigned long long), ctx->stream)); }
     return RT_OK;
 }
 
@@ -877,7 +878,7 @@ static int rt_download_impl(rt_ctx *ctx, float *rgb_sum, size_t n_floats, unsign
         CU(cudaMemcpyAsync(rgb8, ctx->d_rgb8.p, need, cudaMemcpyDeviceToHost, s));
     }
     if (rgb_sum) CU(cudaMemcpyAsync(rgb_sum, ctx->d_accum.p, sizeof(float) * need, cudaMemcpyDeviceToHost, s));
-    if (stats && ctx->d_rays.p) { unsigned long long r[2] = {0, 0}; CU(cudaMemcpyAsync(r, ctx->d_rays.p, sizeof r, cudaMemcpyDeviceToHost, s)); CU(cudaStreamSynchronize(s)); ctx->stats.rays = (long long)r[0]; ctx->stats.shadow_rays = (long long)r[1]; }
+    if (stats && ctx->d_rays.p) { unsigned long long r[3] = {0, 0, 0}; CU(cudaMemcpyAsync(r, ctx->d_rays.p, sizeof r, cudaMemcpyDeviceToHost, s)); CU(cudaStreamSynchronize(s)); ctx->stats.rays = (long long)r[0]; ctx->stats.shadow_rays = (long long)r[1]; ctx->stats.rays_extend = (long long)r[2]; }
     CU(cudaStreamSynchronize(s));
     if (!ctx->pending.empty()) {
         float *acc[6] = {&ctx->stats.ms_generate, &ctx->stats.ms_extend, &ctx->stats.ms_shade, &ctx->stats.ms_accumulate, &ctx->stats.ms_shadow,

@@ -685,7 +685,7 @@ __global__ void __launch_bounds__(RT_EXT_BLOCK, RT_TAIL_CTAS) k_tail(DScene sc, 
 __global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restrict__ radiance, AccumPlan plan, int W, int H,
                                                          int n_samples, const int *__restrict__ qcount, int max_depth,
                                                          unsigned long long *total_rays, const int *__restrict__ shcount,
-                                                         const int *__restrict__ const_tiles, float3 bg) {
+                                                         const int *__restrict__ const_tiles, float3 bg, int ext_first, int ext_end) {
     const int np = W * H;
     if (blockIdx.x == 0 && threadIdx.x == 0) {     // rays traced this pass = sum of the per-bounce queue lengths
         unsigned long long r = 0, sh = 0;
@@ -693,6 +693,9 @@ __global__ void __launch_bounds__(RT_BLOCK) k_accumulate(const float4 *__restric
         r = (unsigned long long)np * (unsigned long long)n_samples;
         for (int b = 0; b < max_depth; ++b) { if (b > 0) r += (unsigned long long)qcount[b]; if (shcount) sh += (unsigned long long)shcount[b]; }
         total_rays[0] += r; total_rays[1] += sh;
+        unsigned long long re = 0;      // rays that went through an extend launch: bounces [ext_first, ext_end) (the rest: generate's lists, the tail stage)
+        for (int b = ext_first; b < ext_end && b < max_depth; ++b) re += (unsigned long long)qcount[b];
+        total_rays[2] += re;
     }
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < np; k += gridDim.x * blockDim.x) {
         const int p = plane_to_pixel(W, H, k);
@@ -1064,10 +1067,10 @@ void launch_light_slots(const LaunchCfg &c, int n, const int *prim_obj, const in
 }
 
 void launch_accumulate(const LaunchCfg &c, const Queues &q, const AccumPlan &plan, int W, int H, int n_samples, int max_depth,
-                       unsigned long long *total_rays, const int *const_tiles, float3 bg) {
+                       unsigned long long *total_rays, const int *const_tiles, float3 bg, int ext_first, int ext_end) {
     int blocks = (W * H + RT_BLOCK - 1) / RT_BLOCK;
     k_accumulate<<<blocks, RT_BLOCK, 0, c.stream>>>(q.radiance, plan, W, H, n_samples, q.qcount, max_depth, total_rays, q.shcount,
-                                                    const_tiles, bg);
+                                                    const_tiles, bg, ext_first, ext_end);
     bump(c);
 }
 

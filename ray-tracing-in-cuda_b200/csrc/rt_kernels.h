@@ -27,7 +27,7 @@ struct ChunkPtrs { const float *p[RT_ACC_CHUNKS]; };
 // one pass's sample planes by chunk: run j = planes [first[j], first[j + 1]) goes to buf[j] (cleared first when clear[j])
 struct AccumPlan { int n; int first[RT_ACC_CHUNKS + 1]; int clear[RT_ACC_CHUNKS]; float *buf[RT_ACC_CHUNKS]; };
 void launch_accumulate(const LaunchCfg &c, const Queues &q, const AccumPlan &plan, int W, int H, int n_samples, int max_depth,
-                       unsigned long long *total_rays, const int *const_tiles, float3 bg);
+                       unsigned long long *total_rays, const int *const_tiles, float3 bg, int ext_first, int ext_end);
 void launch_primary_only(const LaunchCfg &c, const DScene &sc, const AccumPlan &plan, unsigned seed, int spp_begin, int n_samples,
                          unsigned long long *total_rays);
 void launch_fold_chunks(const LaunchCfg &c, float *accum, const ChunkPtrs &cp, int n_chunks, bool keep, long long n);
