@@ -129,7 +129,7 @@ enum { RT_RENDER_KEEP_ACCUM = 1,     /* add to the accumulation buffer instead o
                                         short late-bounce launches of one overlap the other; same image either way) */
        RT_RENDER_NO_TILE_LISTS = 256, /* traverse the tree for bounce 0 too (default: the generate stage resolves bounce-0 hits from the
                                         per-tile candidate lists of the camera beams; same image either way) */
-       RT_RENDER_NO_TAIL = 1024,     /* keep the queue schedule to the last bounce (default: from bounce 8 on one launch finishes every
+       RT_RENDER_NO_TAIL = 1024,     /* keep the queue schedule to the last bounce (default: from bounce 8 on — 2 on all-sphere scenes — one launch finishes every
                                         surviving path — same image either way) */
        RT_RENDER_NEE_MIS = 2048,     /* RT_RENDER_NEE with multiple importance sampling: light samples and the emission a scattered ray finds on
                                         a sampled light are combined with the balance heuristic (implies RT_RENDER_NEE) */

@@ -1,6 +1,6 @@
 // rt_kernels.cu — the wavefront path-tracing kernels for sm_100a:
 //   tile_lists (once per scene) ; generate (+ bounce-0 hits) -> [ extend (LBVH traversal) -> shade (+ stream compaction)
-//   (-> shadow) ] x max_depth (from bounce 8: one tail launch finishes the surviving paths) -> accumulate (per sample chunk)
+//   (-> shadow) ] x max_depth (from bounce 8 — 2 on all-sphere scenes — one tail launch finishes the surviving paths) -> accumulate (per sample chunk)
 //   -> fold chunks ; tonemap
 // They replace the reference's megakernel (gpu-version/main.cu:72-105 `render` + 17-70 `ray_color`), which runs one
 // thread per pixel, serial over samples, with virtual dispatch through device-heap pointers.
